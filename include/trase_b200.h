@@ -1,0 +1,226 @@
+/*
+ * trase_b200 — C ABI of the B200-native differentiable Gaussian rasterizer.
+ *
+ * This is the drop-in boundary for TRASE's rasterizer hot path.  Every entry
+ * point takes plain pointers and sizes (no torch types); all device buffers
+ * are owned by the caller (in the Python host: torch tensors), the library
+ * never allocates device memory.  Kernels are launched on the CUDA stream the
+ * caller passes (`stream`, a cudaStream_t cast to void*).
+ *
+ * "ref:" comments cite the reference interface each declaration replaces;
+ * paths are relative to the reference repository root, DGR/ =
+ * submodules/diff-gaussian-rasterization/.
+ *
+ * Return convention: 0 = ok, non-zero = error; the message is available from
+ * trase_b200_last_error() (thread-local).  The Python host turns a non-zero
+ * status into RuntimeError, mirroring AT_ERROR / std::runtime_error in the
+ * reference (DGR/rasterize_points.cu:63-66, DGR/cuda_rasterizer/rasterizer_impl.cu:248-251).
+ *
+ * Layout conventions (identical to the reference): row-major contiguous fp32;
+ * images planar CHW; SH coefficients [P][M][3]; features [P][32]; a NULL
+ * pointer means "input not provided" (DGR/diff_gaussian_rasterization/__init__.py:206-219).
+ */
+#ifndef TRASE_B200_H_
+#define TRASE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define TRASE_API __attribute__((visibility("default")))
+#else
+#define TRASE_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TRASE_B200_NUM_CHANNELS 3   /* ref: DGR/cuda_rasterizer/config.h:13 */
+#define TRASE_B200_NUM_OBJECTS 32   /* ref: DGR/cuda_rasterizer/config.h:15 */
+#define TRASE_B200_TILE 16          /* ref: DGR/cuda_rasterizer/config.h:16-17 */
+
+/* Library version (major*10000 + minor*100 + patch). */
+TRASE_API int trase_b200_version(void);
+
+/* Message of the last failing call on this host thread ("" if none). */
+TRASE_API const char* trase_b200_last_error(void);
+
+/* ------------------------------------------------------------------------
+ * Workspace sizing.  ref: CudaRasterizer::required<GeometryState|ImageState|
+ * BinningState>() (DGR/cuda_rasterizer/rasterizer_impl.h:72-77) and the three
+ * fromChunk() carvers (DGR/cuda_rasterizer/rasterizer_impl.cu:158-197).
+ *
+ *  geom    : per-Gaussian state written by forward, read by backward.
+ *  img     : per-pixel final transmittance + contributor count, per-tile ranges.
+ *  binning : depth-sorted instance list (Gaussian index per tile instance) and
+ *            the sorted 64-bit tile|depth keys; `capacity` instances.
+ *  scratch : sort ping-pong buffers and histograms; only live during forward.
+ * ---------------------------------------------------------------------- */
+TRASE_API size_t trase_b200_geom_bytes(int P);
+TRASE_API size_t trase_b200_img_bytes(int W, int H);
+TRASE_API size_t trase_b200_binning_bytes(int64_t capacity);
+TRASE_API size_t trase_b200_scratch_bytes(int P, int64_t capacity);
+
+/* Byte offsets of the arrays inside the three persistent workspaces, so that a
+ * host (and the parity tests) can view them the way the reference's tests
+ * would view geomBuffer/binningBuffer/imgBuffer.  Each call fills `out[n]`. */
+enum {
+  TRASE_GEOM_DEPTHS = 0,        /* f32[P]   view-space z            */
+  TRASE_GEOM_MEANS2D,           /* f32[P][2] pixel centre            */
+  TRASE_GEOM_CONIC_OPACITY,     /* f32[P][4] conic a,b,c + opacity   */
+  TRASE_GEOM_RGBD,              /* f32[P][4] rgb (SH or precomp) + z */
+  TRASE_GEOM_COV3D,             /* f32[P][6]                         */
+  TRASE_GEOM_CLAMPED,           /* u8[P] bit c set: channel c clamped */
+  TRASE_GEOM_TILES_TOUCHED,     /* u32[P]                            */
+  TRASE_GEOM_POINT_OFFSETS,     /* u32[P] inclusive prefix sum       */
+  TRASE_GEOM_BLOCK_SUMS,        /* u32[ceil(P/256)+1]                */
+  TRASE_GEOM_COUNTERS,          /* u32[8]: [0]=num_rendered [1]=overflow */
+  TRASE_GEOM_NUM_ARRAYS
+};
+enum {
+  TRASE_IMG_FINAL_T = 0,        /* f32[H*W]                          */
+  TRASE_IMG_N_CONTRIB,          /* u32[H*W]                          */
+  TRASE_IMG_RANGES,             /* u32[T][2]                         */
+  TRASE_IMG_NUM_ARRAYS
+};
+enum {
+  TRASE_BIN_POINT_LIST = 0,     /* u32[capacity] sorted Gaussian ids */
+  TRASE_BIN_POINT_LIST_KEYS,    /* u64[capacity] sorted keys         */
+  TRASE_BIN_NUM_ARRAYS
+};
+TRASE_API void trase_b200_geom_offsets(int P, size_t* out /*[TRASE_GEOM_NUM_ARRAYS]*/);
+TRASE_API void trase_b200_img_offsets(int W, int H, size_t* out /*[TRASE_IMG_NUM_ARRAYS]*/);
+TRASE_API void trase_b200_binning_offsets(int64_t capacity, size_t* out /*[TRASE_BIN_NUM_ARRAYS]*/);
+
+/* ------------------------------------------------------------------------
+ * Forward.  ref: RasterizeGaussiansCUDA (DGR/rasterize_points.cu:40-127) →
+ * CudaRasterizer::Rasterizer::forward (DGR/cuda_rasterizer/rasterizer_impl.cu:201-349).
+ *
+ * Differences from the reference, none visible in the results:
+ *  - no host synchronisation inside the call: the instance count R is produced
+ *    on the device; the caller provides a binning workspace of `capacity`
+ *    instances and (optionally) a pinned host int that receives R with an
+ *    asynchronous copy on `stream`.  If R > capacity the tile ranges are left
+ *    empty, counters[1] is set and the caller must retry with a larger
+ *    workspace (the Python host does this).
+ *  - output images are written for every pixel (no pre-zeroing needed).
+ * ---------------------------------------------------------------------- */
+typedef struct trase_b200_fwd_args {
+  int P;                 /* number of Gaussians                                  */
+  int sh_degree;         /* active SH degree 0..3         (ref arg "degree")     */
+  int M;                 /* SH coefficients stored per Gaussian (0 if no SH)     */
+  int W, H;              /* image size                                            */
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int prefiltered;       /* ref: in_frustum trap, DGR/cuda_rasterizer/auxiliary.h:151-155 */
+  int debug;             /* !=0: synchronise and check after every launch
+                            (ref: CHECK_CUDA, DGR/cuda_rasterizer/auxiliary.h:161-171) */
+  const float* background;      /* [3]                                            */
+  const float* means3D;         /* [P][3]                                         */
+  const float* shs;             /* [P][M][3] or NULL                              */
+  const float* sh_objs;         /* [P][32]  (mandatory, as in the reference)      */
+  const float* colors_precomp;  /* [P][3] or NULL                                 */
+  const float* opacities;       /* [P]                                            */
+  const float* scales;          /* [P][3] or NULL                                 */
+  const float* rotations;       /* [P][4] or NULL                                 */
+  const float* cov3D_precomp;   /* [P][6] or NULL                                 */
+  const float* viewmatrix;      /* [16]                                           */
+  const float* projmatrix;      /* [16]                                           */
+  const float* campos;          /* [3]                                            */
+  float* out_color;             /* [3][H][W]                                      */
+  float* out_objects;           /* [32][H][W]                                     */
+  float* out_depth;             /* [1][H][W]                                      */
+  int* radii;                   /* [P]                                            */
+  void* geom;    size_t geom_bytes;
+  void* img;     size_t img_bytes;
+  void* binning; size_t binning_bytes;
+  void* scratch; size_t scratch_bytes;
+  int64_t capacity;             /* instances the binning/scratch buffers hold     */
+  int* num_rendered_host;       /* pinned host int or NULL (async D2H of R)       */
+  void* stream;                 /* cudaStream_t                                   */
+} trase_b200_fwd_args;
+
+TRASE_API int trase_b200_rasterize_forward(const trase_b200_fwd_args* args);
+
+/* Re-runs only key generation → sort → ranges → compositing on an existing
+ * geom workspace (used after a capacity overflow). */
+TRASE_API int trase_b200_rasterize_forward_rebin(const trase_b200_fwd_args* args);
+
+/* ------------------------------------------------------------------------
+ * Backward.  ref: RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:129-214)
+ * → CudaRasterizer::Rasterizer::backward (DGR/cuda_rasterizer/rasterizer_impl.cu:353-455).
+ * All dL_* outputs must be zero-filled by the caller (the reference does the
+ * same with torch::zeros, DGR/rasterize_points.cu:165-174); dL_dconic [P][4]
+ * is the internal float4 the reference keeps (DGR/cuda_rasterizer/backward.cu:566-568).
+ * ---------------------------------------------------------------------- */
+typedef struct trase_b200_bwd_args {
+  int P, sh_degree, M, W, H;
+  float tan_fovx, tan_fovy, scale_modifier;
+  int debug;
+  const float* background;
+  const float* means3D;
+  const float* shs;
+  const float* sh_objs;
+  const float* colors_precomp;
+  const float* scales;
+  const float* rotations;
+  const float* cov3D_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const int* radii;
+  const void* geom;
+  const void* img;
+  const void* binning;
+  int64_t capacity;
+  const float* dL_dout_color;    /* [3][H][W]  */
+  const float* dL_dout_objects;  /* [32][H][W] */
+  float* dL_dmeans2D;   /* [P][3] */
+  float* dL_dconic;     /* [P][4] */
+  float* dL_dopacity;   /* [P]    */
+  float* dL_dcolors;    /* [P][3] */
+  float* dL_dobjects;   /* [P][32]*/
+  float* dL_dmeans3D;   /* [P][3] */
+  float* dL_dcov3D;     /* [P][6] */
+  float* dL_dsh;        /* [P][M][3] or NULL */
+  float* dL_dscales;    /* [P][3] or NULL */
+  float* dL_drotations; /* [P][4] or NULL */
+  void* stream;
+} trase_b200_bwd_args;
+
+TRASE_API int trase_b200_rasterize_backward(const trase_b200_bwd_args* args);
+
+/* ref: markVisible (DGR/rasterize_points.cu:216-235) → checkFrustum
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:57-69).  present[i] = 1 if the
+ * view-space z of means3D[i] is > 0.2. */
+TRASE_API int trase_b200_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                            const float* projmatrix, uint8_t* present, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Stable key/value radix sort on the low `end_bit` bits of 64-bit keys.
+ * ref: cub::DeviceRadixSort::SortPairs call at DGR/cuda_rasterizer/rasterizer_impl.cu:310-316.
+ * `count_dev` points to the number of pairs (device u32, clamped to
+ * `capacity`).  The sorted result ends up in (keys_out, vals_out); keys_in /
+ * vals_in are clobbered.  Exposed so that the sort can be tested and profiled
+ * on its own.
+ * ---------------------------------------------------------------------- */
+TRASE_API size_t trase_b200_sort_scratch_bytes(int64_t capacity);
+TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
+                          uint32_t* vals_out, const uint32_t* count_dev, int64_t capacity,
+                          int end_bit, void* sort_scratch, size_t sort_scratch_bytes,
+                          void* stream);
+
+/* ref: getHigherMsb (DGR/cuda_rasterizer/rasterizer_impl.cu:38-53). */
+TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);
+
+/* Kernel-variant selection for benchmarking (no reference counterpart; the
+ * reference fixes its launch shapes at compile time, DGR/cuda_rasterizer/config.h).
+ * Keys: "fwd_ppt", "bwd_ppt" (pixels per thread: 1 or 2). Results do not depend
+ * on the variant beyond floating-point summation order. */
+TRASE_API void trase_b200_set_tuning(const char* key, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TRASE_B200_H_ */

@@ -1,0 +1,146 @@
+"""ctypes binding of the C ABI declared in include/trase_b200.h.
+
+This is the whole Python<->native boundary: raw device pointers, sizes and a
+CUDA stream handle.  torch only supplies memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtrase_b200.so")
+
+c_float_p = C.c_void_p  # device pointers are passed as integers
+
+
+class FwdArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("sh_degree", C.c_int), ("M", C.c_int), ("W", C.c_int), ("H", C.c_int),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
+        ("prefiltered", C.c_int), ("debug", C.c_int),
+        ("background", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p), ("sh_objs", C.c_void_p),
+        ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
+        ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p),
+        ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
+        ("out_color", C.c_void_p), ("out_objects", C.c_void_p), ("out_depth", C.c_void_p), ("radii", C.c_void_p),
+        ("geom", C.c_void_p), ("geom_bytes", C.c_size_t),
+        ("img", C.c_void_p), ("img_bytes", C.c_size_t),
+        ("binning", C.c_void_p), ("binning_bytes", C.c_size_t),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+        ("capacity", C.c_int64),
+        ("num_rendered_host", C.c_void_p),
+        ("stream", C.c_void_p),
+    ]
+
+
+class BwdArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("sh_degree", C.c_int), ("M", C.c_int), ("W", C.c_int), ("H", C.c_int),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
+        ("debug", C.c_int),
+        ("background", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p), ("sh_objs", C.c_void_p),
+        ("colors_precomp", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+        ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+        ("campos", C.c_void_p), ("radii", C.c_void_p),
+        ("geom", C.c_void_p), ("img", C.c_void_p), ("binning", C.c_void_p), ("capacity", C.c_int64),
+        ("dL_dout_color", C.c_void_p), ("dL_dout_objects", C.c_void_p),
+        ("dL_dmeans2D", C.c_void_p), ("dL_dconic", C.c_void_p), ("dL_dopacity", C.c_void_p),
+        ("dL_dcolors", C.c_void_p), ("dL_dobjects", C.c_void_p), ("dL_dmeans3D", C.c_void_p),
+        ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p), ("dL_dscales", C.c_void_p),
+        ("dL_drotations", C.c_void_p),
+        ("stream", C.c_void_p),
+    ]
+
+
+GEOM_ARRAYS = ["depths", "means2D", "conic_opacity", "rgbd", "cov3D", "clamped", "tiles_touched",
+               "point_offsets", "block_sums", "counters"]
+IMG_ARRAYS = ["final_T", "n_contrib", "ranges"]
+BIN_ARRAYS = ["point_list", "point_list_keys"]
+
+# every symbol include/trase_b200.h declares (checked by tests/test_abi.py)
+EXPORTS = [
+    "trase_b200_version", "trase_b200_last_error", "trase_b200_geom_bytes", "trase_b200_img_bytes",
+    "trase_b200_binning_bytes", "trase_b200_scratch_bytes", "trase_b200_geom_offsets",
+    "trase_b200_img_offsets", "trase_b200_binning_offsets", "trase_b200_rasterize_forward",
+    "trase_b200_rasterize_forward_rebin", "trase_b200_rasterize_backward", "trase_b200_mark_visible",
+    "trase_b200_sort_scratch_bytes", "trase_b200_sort_pairs", "trase_b200_higher_msb",
+    "trase_b200_set_tuning",
+]
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Loads libtrase_b200.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "trase_b200: native library %s is missing. Build it with `python -m trase_b200.build` "
+            "(there is no CPU or PyTorch fallback for the rasterizer)." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    lib.trase_b200_version.restype = C.c_int
+    lib.trase_b200_last_error.restype = C.c_char_p
+    for name in ("geom_bytes",):
+        getattr(lib, "trase_b200_" + name).restype = C.c_size_t
+        getattr(lib, "trase_b200_" + name).argtypes = [C.c_int]
+    lib.trase_b200_img_bytes.restype = C.c_size_t
+    lib.trase_b200_img_bytes.argtypes = [C.c_int, C.c_int]
+    lib.trase_b200_binning_bytes.restype = C.c_size_t
+    lib.trase_b200_binning_bytes.argtypes = [C.c_int64]
+    lib.trase_b200_scratch_bytes.restype = C.c_size_t
+    lib.trase_b200_scratch_bytes.argtypes = [C.c_int, C.c_int64]
+    lib.trase_b200_geom_offsets.restype = None
+    lib.trase_b200_geom_offsets.argtypes = [C.c_int, C.POINTER(C.c_size_t)]
+    lib.trase_b200_img_offsets.restype = None
+    lib.trase_b200_img_offsets.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_size_t)]
+    lib.trase_b200_binning_offsets.restype = None
+    lib.trase_b200_binning_offsets.argtypes = [C.c_int64, C.POINTER(C.c_size_t)]
+    lib.trase_b200_rasterize_forward.restype = C.c_int
+    lib.trase_b200_rasterize_forward.argtypes = [C.POINTER(FwdArgs)]
+    lib.trase_b200_rasterize_forward_rebin.restype = C.c_int
+    lib.trase_b200_rasterize_forward_rebin.argtypes = [C.POINTER(FwdArgs)]
+    lib.trase_b200_rasterize_backward.restype = C.c_int
+    lib.trase_b200_rasterize_backward.argtypes = [C.POINTER(BwdArgs)]
+    lib.trase_b200_mark_visible.restype = C.c_int
+    lib.trase_b200_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.trase_b200_sort_scratch_bytes.restype = C.c_size_t
+    lib.trase_b200_sort_scratch_bytes.argtypes = [C.c_int64]
+    lib.trase_b200_sort_pairs.restype = C.c_int
+    lib.trase_b200_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                          C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.trase_b200_higher_msb.restype = C.c_uint32
+    lib.trase_b200_higher_msb.argtypes = [C.c_uint32]
+    lib.trase_b200_set_tuning.restype = None
+    lib.trase_b200_set_tuning.argtypes = [C.c_char_p, C.c_int]
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise RuntimeError(load().trase_b200_last_error().decode() or "trase_b200: native call failed (%d)" % rc)
+
+
+def geom_offsets(P: int) -> dict:
+    arr = (C.c_size_t * len(GEOM_ARRAYS))()
+    load().trase_b200_geom_offsets(P, arr)
+    return dict(zip(GEOM_ARRAYS, list(arr)))
+
+
+def img_offsets(W: int, H: int) -> dict:
+    arr = (C.c_size_t * len(IMG_ARRAYS))()
+    load().trase_b200_img_offsets(W, H, arr)
+    return dict(zip(IMG_ARRAYS, list(arr)))
+
+
+def binning_offsets(capacity: int) -> dict:
+    arr = (C.c_size_t * len(BIN_ARRAYS))()
+    load().trase_b200_binning_offsets(capacity, arr)
+    return dict(zip(BIN_ARRAYS, list(arr)))
+
+
+def set_tuning(key: str, value: int) -> None:
+    load().trase_b200_set_tuning(key.encode(), int(value))

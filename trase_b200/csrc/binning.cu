@@ -1,0 +1,412 @@
+// Binning: block-offset scan, tile|depth key duplication, stable LSD radix sort
+// (hand-written, no CUB), tile-range identification.
+//
+// Reference counterparts:
+//   cub::DeviceScan::InclusiveSum      DGR/cuda_rasterizer/rasterizer_impl.cu:284
+//   duplicateWithKeys                  DGR/cuda_rasterizer/rasterizer_impl.cu:73-114
+//   cub::DeviceRadixSort::SortPairs    DGR/cuda_rasterizer/rasterizer_impl.cu:310-316
+//   identifyTileRanges                 DGR/cuda_rasterizer/rasterizer_impl.cu:119-141
+//
+// Design differences: the instance count R never goes to the host between
+// kernels (the reference blocks on a 4-byte D2H at rasterizer_impl.cu:288);
+// every kernel reads R from device memory and grids are sized for the
+// caller's capacity.  The prefix sum is folded into the producer (per-block
+// sums come out of the preprocess kernel) and the consumer (the duplicate
+// kernel scans its own 256 counts), so only the tiny block-sum scan is a
+// kernel of its own.
+#include "common.cuh"
+
+namespace tb {
+
+__device__ __forceinline__ void tile_rect_dev(const float2 p, int max_radius, int grid_x, int grid_y, uint2& rmin,
+                                              uint2& rmax) {
+  rmin = {(unsigned)min(grid_x, max((int)0, (int)((p.x - max_radius) / TILE))),
+          (unsigned)min(grid_y, max((int)0, (int)((p.y - max_radius) / TILE)))};
+  rmax = {(unsigned)min(grid_x, max((int)0, (int)((p.x + max_radius + TILE - 1) / TILE))),
+          (unsigned)min(grid_y, max((int)0, (int)((p.y + max_radius + TILE - 1) / TILE)))};
+}
+
+// ---------------------------------------------------------------------------
+// Exclusive scan of the per-block tile counts (one block; nblk <= a few
+// thousand).  Also publishes R = total and the overflow flag.
+constexpr int SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums_kernel(const uint32_t* __restrict__ block_sums,
+                                                                       uint32_t* __restrict__ block_offsets, int nblk,
+                                                                       uint32_t* __restrict__ counters,
+                                                                       unsigned long long capacity) {
+  __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+  __shared__ uint32_t s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < nblk; base += SCAN_THREADS) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = (i < nblk) ? block_sums[i] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0;
+    for (int w = 0; w < warp; w++) warp_off += s_warp[w];
+    const uint32_t excl = s_carry + warp_off + incl - v;
+    if (i < nblk) block_offsets[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == SCAN_THREADS - 1) s_carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const uint32_t total = s_carry;
+    block_offsets[nblk] = total;
+    counters[0] = total;
+    counters[1] = ((unsigned long long)total > capacity) ? 1u : 0u;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Key duplication.  One thread per Gaussian computes its offset (block scan +
+// scanned block offset); Gaussians touching more than DUP_COOP tiles are
+// emitted by the whole warp so that one large splat does not serialise a lane.
+constexpr int DUP_COOP = 16;
+__global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
+    int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+    const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_offsets,
+    uint32_t* __restrict__ point_offsets, const uint32_t* __restrict__ counters, uint64_t* __restrict__ keys,
+    uint32_t* __restrict__ vals, const int* __restrict__ radii, int grid_x, int grid_y) {
+  __shared__ uint32_t s_warp[PRE_BLOCK / 32];
+  const int idx = blockIdx.x * PRE_BLOCK + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t cnt = (idx < P) ? tiles_touched[idx] : 0u;
+  uint32_t incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t warp_off = 0;
+#pragma unroll
+  for (int w = 0; w < PRE_BLOCK / 32; w++)
+    if (w < warp) warp_off += s_warp[w];
+  const uint32_t off_incl = block_offsets[blockIdx.x] + warp_off + incl;
+  if (idx < P) point_offsets[idx] = off_incl;
+  if (counters[1]) return;  // capacity overflow: emit nothing (host retries)
+
+  uint32_t off = off_incl - cnt;
+  uint2 rmin = {0, 0}, rmax = {0, 0};
+  uint32_t depth_bits = 0;
+  if (cnt > 0) {
+    tile_rect_dev(means2D[idx], radii[idx], grid_x, grid_y, rmin, rmax);
+    depth_bits = __float_as_uint(depths[idx]);
+  }
+  const uint32_t w = rmax.x - rmin.x;
+
+  // small splats: the owning lane writes its own instances, row-major (y outer, x inner)
+  if (cnt > 0 && cnt <= DUP_COOP) {
+    for (uint32_t y = rmin.y; y < rmax.y; y++)
+      for (uint32_t x = rmin.x; x < rmax.x; x++) {
+        uint64_t key = (uint64_t)(y * (uint32_t)grid_x + x);
+        key <<= 32;
+        key |= depth_bits;
+        keys[off] = key;
+        vals[off] = (uint32_t)idx;
+        off++;
+      }
+  }
+  // large splats: warp-cooperative
+  unsigned big = __ballot_sync(0xffffffffu, cnt > DUP_COOP);
+  while (big) {
+    const int src = __ffs(big) - 1;
+    big &= big - 1;
+    const uint32_t b_cnt = __shfl_sync(0xffffffffu, cnt, src);
+    const uint32_t b_off = __shfl_sync(0xffffffffu, off, src);
+    const uint32_t b_w = __shfl_sync(0xffffffffu, w, src);
+    const uint32_t b_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
+    const uint32_t b_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
+    const uint32_t b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
+    const uint32_t b_idx = (uint32_t)(blockIdx.x * PRE_BLOCK + (warp << 5) + src);
+    for (uint32_t k = lane; k < b_cnt; k += 32) {
+      const uint32_t y = b_y0 + k / b_w, x = b_x0 + k % b_w;
+      uint64_t key = (uint64_t)(y * (uint32_t)grid_x + x);
+      key <<= 32;
+      key |= b_depth;
+      keys[b_off + k] = key;
+      vals[b_off + k] = b_idx;
+    }
+  }
+}
+
+cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s) {
+  const int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
+  scan_block_sums_kernel<<<1, SCAN_THREADS, 0, s>>>(p.block_sums, p.block_offsets, nblk, p.counters,
+                                                   (unsigned long long)a.capacity);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const int grid_x = (a.W + TILE - 1) / TILE, grid_y = (a.H + TILE - 1) / TILE;
+  duplicate_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, p.means2D, p.depths, p.tiles_touched, p.block_offsets,
+                                                   p.point_offsets, p.counters, p.keys_unsorted, p.vals_unsorted,
+                                                   a.radii, grid_x, grid_y);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// LSD radix sort, 8-bit digits, three kernels per pass:
+//   upsweep  : per-block digit histogram  → hist[digit][block], digit totals
+//   scan     : one block per digit: exclusive scan along blocks + digit base
+//   downsweep: stable in-block ranking (warp match-any) and scatter
+// Keys are laid out warp-striped inside a block tile (warp w owns 512
+// consecutive keys, item j / lane l ↔ key w*512 + j*32 + l) so loads are
+// coalesced and "earlier in memory" == (warp, item, lane) lexicographic order,
+// which is what the ranking uses to stay stable.
+__device__ __forceinline__ uint32_t sort_count(const uint32_t* count_dev, unsigned long long capacity) {
+  unsigned long long r = *count_dev;
+  return (uint32_t)(r < capacity ? r : capacity);
+}
+
+__global__ void __launch_bounds__(SORT_THREADS) radix_upsweep_kernel(const uint64_t* __restrict__ keys,
+                                                                     const uint32_t* __restrict__ count_dev,
+                                                                     unsigned long long capacity, int shift,
+                                                                     uint32_t* __restrict__ hist, int nblk_stride,
+                                                                     uint32_t* __restrict__ digit_total) {
+  const uint32_t R = sort_count(count_dev, capacity);
+  const uint32_t block_start = blockIdx.x * SORT_TILE;
+  if (block_start >= R) return;
+  __shared__ uint32_t s_hist[SORT_RADIX];
+  s_hist[threadIdx.x] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t warp_base = block_start + warp * (32 * SORT_ITEMS);
+#pragma unroll
+  for (int j = 0; j < SORT_ITEMS; j++) {
+    uint32_t i = warp_base + j * 32 + lane;
+    if (i < R) {
+      uint32_t d = (uint32_t)(keys[i] >> shift) & (SORT_RADIX - 1);
+      atomicAdd(&s_hist[d], 1u);
+    }
+  }
+  __syncthreads();
+  uint32_t c = s_hist[threadIdx.x];
+  hist[(size_t)threadIdx.x * nblk_stride + blockIdx.x] = c;
+  if (c) atomicAdd(&digit_total[threadIdx.x], c);
+}
+
+__global__ void __launch_bounds__(SORT_THREADS) radix_scan_kernel(uint32_t* __restrict__ hist, int nblk_stride,
+                                                                  const uint32_t* __restrict__ digit_total,
+                                                                  const uint32_t* __restrict__ count_dev,
+                                                                  unsigned long long capacity) {
+  const uint32_t R = sort_count(count_dev, capacity);
+  const int nblk = (int)((R + SORT_TILE - 1) / SORT_TILE);
+  const int d = blockIdx.x;
+  __shared__ uint32_t s_warp[SORT_THREADS / 32];
+  __shared__ uint32_t s_carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // digit base = number of keys with a smaller digit
+  uint32_t v = (threadIdx.x < d) ? digit_total[threadIdx.x] : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) s_warp[warp] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_THREADS / 32; w++) t += s_warp[w];
+    s_carry = t;
+  }
+  __syncthreads();
+  uint32_t* row = hist + (size_t)d * nblk_stride;
+  for (int base = 0; base < nblk; base += SORT_THREADS) {
+    const int i = base + threadIdx.x;
+    const uint32_t x = (i < nblk) ? row[i] : 0u;
+    uint32_t incl = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_THREADS / 32; w++)
+      if (w < warp) warp_off += s_warp[w];
+    const uint32_t carry = s_carry;
+    const uint32_t excl = carry + warp_off + incl - x;
+    if (i < nblk) row[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == SORT_THREADS - 1) s_carry = excl + x;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
+    const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, uint64_t* __restrict__ keys_out,
+    uint32_t* __restrict__ vals_out, const uint32_t* __restrict__ count_dev, unsigned long long capacity, int shift,
+    const uint32_t* __restrict__ hist, int nblk_stride) {
+  const uint32_t R = sort_count(count_dev, capacity);
+  const uint32_t block_start = blockIdx.x * SORT_TILE;
+  if (block_start >= R) return;
+  constexpr int NW = SORT_THREADS / 32;
+  __shared__ uint32_t s_cnt[NW][SORT_RADIX];
+#pragma unroll
+  for (int w = 0; w < NW; w++) s_cnt[w][threadIdx.x] = 0;
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t lane_lt = (1u << lane) - 1u;
+  const uint32_t warp_base = block_start + warp * (32 * SORT_ITEMS);
+  uint64_t key[SORT_ITEMS];
+  uint32_t rank[SORT_ITEMS];
+#pragma unroll
+  for (int j = 0; j < SORT_ITEMS; j++) {
+    const uint32_t i = warp_base + j * 32 + lane;
+    key[j] = (i < R) ? keys_in[i] : ~0ull;
+  }
+#pragma unroll
+  for (int j = 0; j < SORT_ITEMS; j++) {
+    const uint32_t i = warp_base + j * 32 + lane;
+    const bool valid = i < R;
+    const uint32_t d = (uint32_t)(key[j] >> shift) & (SORT_RADIX - 1);
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : 0xffffffffu);
+    const int leader = __ffs(peers) - 1;
+    uint32_t c = 0;
+    if (valid && lane == leader) c = s_cnt[warp][d];
+    c = __shfl_sync(0xffffffffu, c, leader);
+    rank[j] = c + __popc(peers & lane_lt);
+    if (valid && lane == leader) s_cnt[warp][d] = c + __popc(peers);
+    __syncwarp();
+  }
+  __syncthreads();
+  {
+    // per-digit exclusive offsets across warps, plus this block's global base
+    const int d = threadIdx.x;
+    uint32_t run = hist[(size_t)d * nblk_stride + blockIdx.x];
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+      uint32_t t = s_cnt[w][d];
+      s_cnt[w][d] = run;
+      run += t;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < SORT_ITEMS; j++) {
+    const uint32_t i = warp_base + j * 32 + lane;
+    if (i < R) {
+      const uint32_t d = (uint32_t)(key[j] >> shift) & (SORT_RADIX - 1);
+      const uint32_t pos = s_cnt[warp][d] + rank[j];
+      keys_out[pos] = key[j];
+      vals_out[pos] = vals_in[i];
+    }
+  }
+}
+
+__global__ void copy_pairs_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                  const uint32_t* __restrict__ count_dev, unsigned long long capacity) {
+  const uint32_t R = sort_count(count_dev, capacity);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < R; i += gridDim.x * blockDim.x) {
+    keys_out[i] = keys_in[i];
+    vals_out[i] = vals_in[i];
+  }
+}
+
+// Ping-pong sort.  Data starts in (keys_a, vals_a); after `passes` passes it is
+// in A again when `passes` is even, in B when odd (see sort_result_in_b).
+int sort_num_passes(int end_bit) {
+  int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  if (passes < 1) passes = 1;
+  if (passes > SORT_MAX_PASSES) passes = SORT_MAX_PASSES;
+  return passes;
+}
+cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b,
+                                 const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
+                                 size_t scratch_bytes, cudaStream_t s) {
+  if (capacity <= 0) return cudaSuccess;
+  if (scratch_bytes < sort_scratch_bytes(capacity)) return cudaErrorInvalidValue;
+  const int nblk = (int)sort_num_blocks(capacity);
+  uint32_t* hist = reinterpret_cast<uint32_t*>(scratch);
+  uint32_t* digit_total =
+      reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(scratch) + align_up((size_t)nblk * SORT_RADIX * 4, WS_ALIGN));
+  const int passes = sort_num_passes(end_bit);
+  cudaError_t e = cudaMemsetAsync(digit_total, 0, (size_t)SORT_MAX_PASSES * SORT_RADIX * 4, s);
+  if (e != cudaSuccess) return e;
+  uint64_t* kin = keys_a; uint32_t* vin = vals_a;
+  uint64_t* kout = keys_b; uint32_t* vout = vals_b;
+  const unsigned long long cap = (unsigned long long)capacity;
+  for (int pass = 0; pass < passes; pass++) {
+    const int shift = pass * SORT_RADIX_BITS;
+    uint32_t* tot = digit_total + pass * SORT_RADIX;
+    radix_upsweep_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
+    radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap);
+    radix_downsweep_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift, hist, nblk);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    uint64_t* tk = kin; kin = kout; kout = tk;
+    uint32_t* tv = vin; vin = vout; vout = tv;
+  }
+  return cudaSuccess;
+}
+
+cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                              const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
+                              size_t scratch_bytes, cudaStream_t s) {
+  if (capacity <= 0) return cudaSuccess;
+  cudaError_t e = launch_sort_pingpong(keys_in, vals_in, keys_out, vals_out, count_dev, capacity, end_bit, scratch,
+                                       scratch_bytes, s);
+  if (e != cudaSuccess) return e;
+  if ((sort_num_passes(end_bit) & 1) == 0) {  // result sits in the input buffers
+    int g = (int)sort_num_blocks(capacity) * (SORT_ITEMS / 4);
+    if (g < 1) g = 1;
+    copy_pairs_kernel<<<g, SORT_THREADS, 0, s>>>(keys_in, vals_in, keys_out, vals_out, count_dev,
+                                                 (unsigned long long)capacity);
+    e = cudaGetLastError();
+  }
+  return e;
+}
+
+// ---------------------------------------------------------------------------
+// Tile ranges: ranges[t] = [first, last) positions of tile t in the sorted list.
+__global__ void identify_ranges_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ counters,
+                                       unsigned long long capacity, uint2* __restrict__ ranges) {
+  if (counters[1]) return;  // overflow: leave every range empty
+  const uint32_t L = sort_count(counters, capacity);
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < L; idx += gridDim.x * blockDim.x) {
+    const uint32_t currtile = (uint32_t)(keys[idx] >> 32);
+    if (idx == 0)
+      ranges[currtile].x = 0;
+    else {
+      const uint32_t prevtile = (uint32_t)(keys[idx - 1] >> 32);
+      if (currtile != prevtile) {
+        ranges[prevtile].y = idx;
+        ranges[currtile].x = idx;
+      }
+    }
+    if (idx == L - 1) ranges[currtile].y = L;
+  }
+}
+
+cudaError_t launch_identify_ranges(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s) {
+  const int grid_x = (a.W + TILE - 1) / TILE, grid_y = (a.H + TILE - 1) / TILE;
+  cudaError_t e = cudaMemsetAsync(p.ranges, 0, (size_t)grid_x * grid_y * sizeof(uint2), s);
+  if (e != cudaSuccess) return e;
+  if (a.capacity <= 0) return cudaSuccess;
+  long long g = (a.capacity + 255) / 256;
+  if (g > 148 * 16) g = 148 * 16;
+  identify_ranges_kernel<<<(int)g, 256, 0, s>>>(p.point_list_keys, p.counters, (unsigned long long)a.capacity,
+                                                p.ranges);
+  return cudaGetLastError();
+}
+
+// Number of tile-id bits the sort has to cover; equals what the reference's
+// getHigherMsb returns (rasterizer_impl.cu:38-53): the bit length of n, at least 1.
+uint32_t higher_msb(uint32_t n) {
+  uint32_t bits = 0;
+  while (bits < 32 && (n >> bits)) bits++;
+  return bits < 1 ? 1 : bits;
+}
+
+}  // namespace tb

@@ -1,0 +1,149 @@
+// Shared definitions for the trase_b200 kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/trase_b200.h"
+
+namespace tb {
+
+constexpr int TILE = TRASE_B200_TILE;           // 16x16 pixel tiles
+constexpr int NUM_OBJECTS = TRASE_B200_NUM_OBJECTS;
+constexpr int PRE_BLOCK = 256;                  // threads per preprocess block
+
+constexpr size_t WS_ALIGN = 256;
+
+__host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---- workspace layouts (see include/trase_b200.h) --------------------------
+struct GeomLayout {
+  size_t off[TRASE_GEOM_NUM_ARRAYS];
+  size_t total;
+};
+inline GeomLayout geom_layout(int P) {
+  GeomLayout L;
+  size_t p = (size_t)(P > 0 ? P : 0);
+  size_t nblk = (p + PRE_BLOCK - 1) / PRE_BLOCK;
+  size_t cur = 0;
+  auto take = [&](int which, size_t bytes) {
+    L.off[which] = cur;
+    cur = align_up(cur + bytes, WS_ALIGN);
+  };
+  take(TRASE_GEOM_DEPTHS, p * 4);
+  take(TRASE_GEOM_MEANS2D, p * 8);
+  take(TRASE_GEOM_CONIC_OPACITY, p * 16);
+  take(TRASE_GEOM_RGBD, p * 16);
+  take(TRASE_GEOM_COV3D, p * 24);
+  take(TRASE_GEOM_CLAMPED, p);
+  take(TRASE_GEOM_TILES_TOUCHED, p * 4);
+  take(TRASE_GEOM_POINT_OFFSETS, p * 4);
+  take(TRASE_GEOM_BLOCK_SUMS, 2 * (nblk + 1) * 4);  // raw sums, then scanned offsets
+  take(TRASE_GEOM_COUNTERS, 8 * 4);
+  L.total = cur;
+  return L;
+}
+struct ImgLayout {
+  size_t off[TRASE_IMG_NUM_ARRAYS];
+  size_t total;
+};
+inline ImgLayout img_layout(int W, int H) {
+  ImgLayout L;
+  size_t n = (size_t)W * (size_t)H;
+  size_t tiles = (size_t)((W + TILE - 1) / TILE) * (size_t)((H + TILE - 1) / TILE);
+  size_t cur = 0;
+  auto take = [&](int which, size_t bytes) {
+    L.off[which] = cur;
+    cur = align_up(cur + bytes, WS_ALIGN);
+  };
+  take(TRASE_IMG_FINAL_T, n * 4);
+  take(TRASE_IMG_N_CONTRIB, n * 4);
+  take(TRASE_IMG_RANGES, tiles * 8);
+  L.total = cur;
+  return L;
+}
+struct BinLayout {
+  size_t off[TRASE_BIN_NUM_ARRAYS];
+  size_t total;
+};
+inline BinLayout bin_layout(int64_t capacity) {
+  BinLayout L;
+  size_t c = (size_t)(capacity > 0 ? capacity : 0);
+  size_t cur = 0;
+  auto take = [&](int which, size_t bytes) {
+    L.off[which] = cur;
+    cur = align_up(cur + bytes, WS_ALIGN);
+  };
+  take(TRASE_BIN_POINT_LIST, c * 4);
+  take(TRASE_BIN_POINT_LIST_KEYS, c * 8);
+  L.total = cur;
+  return L;
+}
+
+// ---- radix sort geometry ---------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;                       // keys per thread
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // keys per block
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_MAX_PASSES = 8;
+
+inline size_t sort_num_blocks(int64_t capacity) {
+  return (size_t)((capacity + SORT_TILE - 1) / SORT_TILE);
+}
+// scratch: [block_hist: RADIX * nblocks u32][digit_totals: MAX_PASSES * RADIX u32]
+inline size_t sort_scratch_bytes(int64_t capacity) {
+  size_t nb = sort_num_blocks(capacity);
+  if (nb == 0) nb = 1;
+  return align_up(nb * SORT_RADIX * 4, WS_ALIGN) + align_up(SORT_MAX_PASSES * SORT_RADIX * 4, WS_ALIGN);
+}
+// forward scratch: unsorted keys (u64), unsorted values (u32), sort scratch
+struct ScratchLayout {
+  size_t keys_unsorted, vals_unsorted, sort, total;
+};
+inline ScratchLayout scratch_layout(int64_t capacity) {
+  ScratchLayout L;
+  size_t c = (size_t)(capacity > 0 ? capacity : 0);
+  size_t cur = 0;
+  L.keys_unsorted = cur; cur = align_up(cur + c * 8, WS_ALIGN);
+  L.vals_unsorted = cur; cur = align_up(cur + c * 4, WS_ALIGN);
+  L.sort = cur; cur = align_up(cur + sort_scratch_bytes(capacity), WS_ALIGN);
+  L.total = cur;
+  return L;
+}
+
+// host-side error recording (api.cu)
+void set_error(const char* fmt, ...);
+
+// launchers (one per .cu)
+struct FwdPointers {
+  // geom
+  float* depths; float2* means2D; float4* conic_opacity; float4* rgbd; float* cov3D;
+  uint8_t* clamped; uint32_t* tiles_touched; uint32_t* point_offsets; uint32_t* block_sums; uint32_t* block_offsets;
+  uint32_t* counters;
+  // img
+  float* final_T; uint32_t* n_contrib; uint2* ranges;
+  // binning
+  uint32_t* point_list; uint64_t* point_list_keys;
+  // scratch
+  uint64_t* keys_unsorted; uint32_t* vals_unsorted; void* sort_scratch; size_t sort_scratch_bytes;
+};
+
+cudaError_t launch_preprocess_forward(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
+cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
+cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                              const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
+                              size_t scratch_bytes, cudaStream_t s);
+int sort_num_passes(int end_bit);
+cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b,
+                                 const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
+                                 size_t scratch_bytes, cudaStream_t s);
+cudaError_t launch_identify_ranges(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
+cudaError_t launch_render_forward(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
+cudaError_t launch_render_backward(const trase_b200_bwd_args& a, const FwdPointers& p, cudaStream_t s);
+cudaError_t launch_preprocess_backward(const trase_b200_bwd_args& a, const FwdPointers& p, cudaStream_t s);
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
+
+uint32_t higher_msb(uint32_t n);
+void set_tuning(const char* key, int value);
+
+}  // namespace tb

@@ -1,0 +1,632 @@
+// Per-Gaussian kernels: forward preprocess, backward preprocess (conic → cov3D
+// → scale/rotation, projection, SH), frustum test.
+//
+// Parity notes.  The reference computes these with glm (column-major) in fp32
+// with nvcc's default FMA contraction; integer outputs (radii, tile rects)
+// are decided by those floats, so the expression *shapes* below follow the
+// math of the reference exactly (operand order of every 3x3 product, the
+// double-precision ndc→pixel step, 1/(w+1e-7), un-normalised quaternion, ...):
+//   forward : DGR/cuda_rasterizer/forward.cu:23-259, auxiliary.h:39-52,134-159
+//   backward: DGR/cuda_rasterizer/backward.cu:18-389
+// What is new: one fused backward kernel instead of two, block-staged 16-byte
+// loads of the AoS inputs, a fused per-block tile count (feeds the scan), and
+// SH gradients written once (no read-modify-write of dL_dmeans).
+#include "common.cuh"
+#include <cstdio>
+
+namespace tb {
+
+// ---- SH constants (values of the real SH basis; same literals as any 3DGS code)
+__device__ __constant__ float kSH_C0 = 0.28209479177387814f;
+__device__ __constant__ float kSH_C1 = 0.4886025119029199f;
+__device__ __constant__ float kSH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                           -1.0925484305920792f, 0.5462742152960396f};
+__device__ __constant__ float kSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                           0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
+                                           -0.5900435899266435f};
+
+// ---- tiny column-major 3x3 (m[c][r]), products written term by term in the
+// order k = 0,1,2 so that rounding matches a column-major library product.
+struct Mat3 {
+  float m[3][3];
+};
+__device__ __forceinline__ Mat3 mat3_cols(float a0, float a1, float a2, float b0, float b1, float b2, float c0,
+                                          float c1, float c2) {
+  Mat3 r;
+  r.m[0][0] = a0; r.m[0][1] = a1; r.m[0][2] = a2;
+  r.m[1][0] = b0; r.m[1][1] = b1; r.m[1][2] = b2;
+  r.m[2][0] = c0; r.m[2][1] = c1; r.m[2][2] = c2;
+  return r;
+}
+__device__ __forceinline__ Mat3 mul(const Mat3& A, const Mat3& B) {
+  Mat3 R;
+#pragma unroll
+  for (int c = 0; c < 3; c++)
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+      R.m[c][r] = A.m[0][r] * B.m[c][0] + A.m[1][r] * B.m[c][1] + A.m[2][r] * B.m[c][2];
+  return R;
+}
+__device__ __forceinline__ Mat3 transpose(const Mat3& A) {
+  Mat3 R;
+#pragma unroll
+  for (int c = 0; c < 3; c++)
+#pragma unroll
+    for (int r = 0; r < 3; r++) R.m[c][r] = A.m[r][c];
+  return R;
+}
+
+__device__ __forceinline__ float3 xform4x3(const float3& p, const float* __restrict__ m) {
+  float3 t = {
+      m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12],
+      m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
+      m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14],
+  };
+  return t;
+}
+__device__ __forceinline__ float4 xform4x4(const float3& p, const float* __restrict__ m) {
+  float4 t = {m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12], m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
+              m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14], m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15]};
+  return t;
+}
+__device__ __forceinline__ float3 xform_vec4x3_T(const float3& p, const float* __restrict__ m) {
+  float3 t = {
+      m[0] * p.x + m[1] * p.y + m[2] * p.z,
+      m[4] * p.x + m[5] * p.y + m[6] * p.z,
+      m[8] * p.x + m[9] * p.y + m[10] * p.z,
+  };
+  return t;
+}
+
+// NDC → pixel centre; evaluated in double and narrowed (auxiliary.h:39-42).
+__device__ __forceinline__ float ndc2pix(float v, int S) { return ((v + 1.0) * S - 1.0) * 0.5; }
+
+// Tile rectangle of a splat (auxiliary.h:44-52): float division, truncation, clamp.
+__device__ __forceinline__ void tile_rect(const float2 p, int max_radius, int grid_x, int grid_y, uint2& rmin,
+                                          uint2& rmax) {
+  rmin = {(unsigned)min(grid_x, max((int)0, (int)((p.x - max_radius) / TILE))),
+          (unsigned)min(grid_y, max((int)0, (int)((p.y - max_radius) / TILE)))};
+  rmax = {(unsigned)min(grid_x, max((int)0, (int)((p.x + max_radius + TILE - 1) / TILE))),
+          (unsigned)min(grid_y, max((int)0, (int)((p.y + max_radius + TILE - 1) / TILE)))};
+}
+
+// Stage `n_items` rows of `FL` floats (AoS, row-major) for a block into shared
+// memory with 16-byte loads when the slab is aligned, scalar loads otherwise.
+template <int FL>
+__device__ __forceinline__ void stage_rows(const float* __restrict__ src, int first_row, int n_rows, float* s_dst) {
+  const float* base = src + (size_t)first_row * FL;
+  const int n = n_rows * FL;
+  if ((((uintptr_t)base) & 15) == 0) {
+    const int n4 = n >> 2;
+    const float4* b4 = reinterpret_cast<const float4*>(base);
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) reinterpret_cast<float4*>(s_dst)[i] = __ldg(b4 + i);
+    for (int i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) s_dst[i] = __ldg(base + i);
+  } else {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s_dst[i] = __ldg(base + i);
+  }
+}
+
+struct PreFwdParams {
+  int P, D, M, W, H, grid_x, grid_y;
+  float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+  int prefiltered;
+  const float* means3D; const float* scales; const float* rotations; const float* opacities;
+  const float* shs; const float* cov3D_precomp; const float* colors_precomp;
+  const float* view; const float* proj; const float* campos;
+  int* radii; float2* means2D; float* depths; float* cov3Ds; float4* rgbd; float4* conic_opacity;
+  uint8_t* clamped; uint32_t* tiles_touched; uint32_t* block_sums;
+};
+
+// SH → RGB (forward.cu:23-74).  `sh` points at this Gaussian's [M][3] block.
+__device__ __forceinline__ float3 sh_to_rgb(int deg, const float3 pos, const float3 campos,
+                                            const float* __restrict__ shp, uint8_t& clamp_bits) {
+  float3 dir = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
+  // glm::length = sqrt(dot(v,v)); dot is x*x + y*y + z*z evaluated left to right
+  float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+  dir.x = dir.x / len; dir.y = dir.y / len; dir.z = dir.z / len;
+
+  // 16-byte loads of the (up to) 48 floats of this Gaussian's SH block when it
+  // is 16-byte aligned (M = 4 or 16 on an aligned tensor), scalar loads otherwise.
+  float shv[48];
+  const int nfl = (deg + 1) * (deg + 1) * 3;
+  if ((((uintptr_t)shp) & 15) == 0) {
+    const float4* s4 = reinterpret_cast<const float4*>(shp);
+    const int nvec = (nfl + 3) >> 2;
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+      if (i < nvec) {
+        float4 v = __ldg(s4 + i);
+        shv[4 * i] = v.x; shv[4 * i + 1] = v.y; shv[4 * i + 2] = v.z; shv[4 * i + 3] = v.w;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 48; i++)
+      if (i < nfl) shv[i] = __ldg(shp + i);
+  }
+  auto SH = [&](int i) -> float3 { return float3{shv[3 * i], shv[3 * i + 1], shv[3 * i + 2]}; };
+  float3 c0 = SH(0);
+  float3 result = {kSH_C0 * c0.x, kSH_C0 * c0.y, kSH_C0 * c0.z};
+  if (deg > 0) {
+    float x = dir.x, y = dir.y, z = dir.z;
+    float3 s1 = SH(1), s2 = SH(2), s3 = SH(3);
+    result.x = result.x - kSH_C1 * y * s1.x + kSH_C1 * z * s2.x - kSH_C1 * x * s3.x;
+    result.y = result.y - kSH_C1 * y * s1.y + kSH_C1 * z * s2.y - kSH_C1 * x * s3.y;
+    result.z = result.z - kSH_C1 * y * s1.z + kSH_C1 * z * s2.z - kSH_C1 * x * s3.z;
+    if (deg > 1) {
+      float xx = x * x, yy = y * y, zz = z * z;
+      float xy = x * y, yz = y * z, xz = x * z;
+      float3 s4 = SH(4), s5 = SH(5), s6 = SH(6), s7 = SH(7), s8 = SH(8);
+      result.x = result.x + kSH_C2[0] * xy * s4.x + kSH_C2[1] * yz * s5.x + kSH_C2[2] * (2.0f * zz - xx - yy) * s6.x +
+                 kSH_C2[3] * xz * s7.x + kSH_C2[4] * (xx - yy) * s8.x;
+      result.y = result.y + kSH_C2[0] * xy * s4.y + kSH_C2[1] * yz * s5.y + kSH_C2[2] * (2.0f * zz - xx - yy) * s6.y +
+                 kSH_C2[3] * xz * s7.y + kSH_C2[4] * (xx - yy) * s8.y;
+      result.z = result.z + kSH_C2[0] * xy * s4.z + kSH_C2[1] * yz * s5.z + kSH_C2[2] * (2.0f * zz - xx - yy) * s6.z +
+                 kSH_C2[3] * xz * s7.z + kSH_C2[4] * (xx - yy) * s8.z;
+      if (deg > 2) {
+        float3 s9 = SH(9), s10 = SH(10), s11 = SH(11), s12 = SH(12), s13 = SH(13), s14 = SH(14), s15 = SH(15);
+        result.x = result.x + kSH_C3[0] * y * (3.0f * xx - yy) * s9.x + kSH_C3[1] * xy * z * s10.x +
+                   kSH_C3[2] * y * (4.0f * zz - xx - yy) * s11.x +
+                   kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * s12.x +
+                   kSH_C3[4] * x * (4.0f * zz - xx - yy) * s13.x + kSH_C3[5] * z * (xx - yy) * s14.x +
+                   kSH_C3[6] * x * (xx - 3.0f * yy) * s15.x;
+        result.y = result.y + kSH_C3[0] * y * (3.0f * xx - yy) * s9.y + kSH_C3[1] * xy * z * s10.y +
+                   kSH_C3[2] * y * (4.0f * zz - xx - yy) * s11.y +
+                   kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * s12.y +
+                   kSH_C3[4] * x * (4.0f * zz - xx - yy) * s13.y + kSH_C3[5] * z * (xx - yy) * s14.y +
+                   kSH_C3[6] * x * (xx - 3.0f * yy) * s15.y;
+        result.z = result.z + kSH_C3[0] * y * (3.0f * xx - yy) * s9.z + kSH_C3[1] * xy * z * s10.z +
+                   kSH_C3[2] * y * (4.0f * zz - xx - yy) * s11.z +
+                   kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * s12.z +
+                   kSH_C3[4] * x * (4.0f * zz - xx - yy) * s13.z + kSH_C3[5] * z * (xx - yy) * s14.z +
+                   kSH_C3[6] * x * (xx - 3.0f * yy) * s15.z;
+      }
+    }
+  }
+  result.x += 0.5f; result.y += 0.5f; result.z += 0.5f;
+  clamp_bits = (uint8_t)((result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0));
+  return float3{(result.x < 0.0f) ? 0.0f : result.x, (result.y < 0.0f) ? 0.0f : result.y,
+                (result.z < 0.0f) ? 0.0f : result.z};
+}
+
+// Σ = (S R)^T (S R) (forward.cu:121-154); quaternion (r,x,y,z), not normalised.
+__device__ __forceinline__ void cov3d_from_scale_rot(const float3 scale, float mod, const float4 rot, float* cov3D) {
+  float sx = mod * scale.x, sy = mod * scale.y, sz = mod * scale.z;
+  float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+  Mat3 R = mat3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                     2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                     2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+  Mat3 S = mat3_cols(sx, 0.0f, 0.0f, 0.0f, sy, 0.0f, 0.0f, 0.0f, sz);
+  Mat3 M = mul(S, R);
+  Mat3 Sigma = mul(transpose(M), M);
+  cov3D[0] = Sigma.m[0][0]; cov3D[1] = Sigma.m[0][1]; cov3D[2] = Sigma.m[0][2];
+  cov3D[3] = Sigma.m[1][1]; cov3D[4] = Sigma.m[1][2]; cov3D[5] = Sigma.m[2][2];
+}
+
+// EWA projection of Σ to the image plane (forward.cu:77-116).
+__device__ __forceinline__ float3 cov2d_from_cov3d(const float3& mean, float focal_x, float focal_y, float tan_fovx,
+                                                   float tan_fovy, const float* cov3D,
+                                                   const float* __restrict__ view) {
+  float3 t = xform4x3(mean, view);
+  const float limx = 1.3f * tan_fovx;
+  const float limy = 1.3f * tan_fovy;
+  const float txtz = t.x / t.z;
+  const float tytz = t.y / t.z;
+  t.x = min(limx, max(-limx, txtz)) * t.z;
+  t.y = min(limy, max(-limy, tytz)) * t.z;
+
+  Mat3 J = mat3_cols(focal_x / t.z, 0.0f, -(focal_x * t.x) / (t.z * t.z), 0.0f, focal_y / t.z,
+                     -(focal_y * t.y) / (t.z * t.z), 0, 0, 0);
+  Mat3 Wm = mat3_cols(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
+  Mat3 T = mul(Wm, J);
+  Mat3 Vrk = mat3_cols(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
+  Mat3 cov = mul(mul(transpose(T), transpose(Vrk)), T);
+  cov.m[0][0] += 0.3f;
+  cov.m[1][1] += 0.3f;
+  return {float(cov.m[0][0]), float(cov.m[0][1]), float(cov.m[1][1])};
+}
+
+__global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreFwdParams q) {
+  __shared__ float s_mean[PRE_BLOCK * 3];
+  __shared__ float s_scale[PRE_BLOCK * 3];
+  __shared__ uint32_t s_warp_sum[PRE_BLOCK / 32];
+
+  const int first = blockIdx.x * PRE_BLOCK;
+  const int n_rows = min(PRE_BLOCK, q.P - first);
+  stage_rows<3>(q.means3D, first, n_rows, s_mean);
+  if (q.cov3D_precomp == nullptr) stage_rows<3>(q.scales, first, n_rows, s_scale);
+  __syncthreads();
+
+  const int idx = first + threadIdx.x;
+  uint32_t my_tiles = 0;
+  if (idx < q.P) {
+    int out_radius = 0;
+    do {
+      const float3 p_orig = {s_mean[3 * threadIdx.x], s_mean[3 * threadIdx.x + 1], s_mean[3 * threadIdx.x + 2]};
+      // near cull (auxiliary.h:134-159): view-space z <= 0.2 is invisible; no x/y cull
+      const float3 p_view = xform4x3(p_orig, q.view);
+      if (p_view.z <= 0.2f) {
+        if (q.prefiltered) {
+          printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+          __trap();
+        }
+        break;
+      }
+      float4 p_hom = xform4x4(p_orig, q.proj);
+      float p_w = 1.0f / (p_hom.w + 0.0000001f);
+      float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+
+      float cov3D_local[6];
+      const float* cov3D;
+      if (q.cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int i = 0; i < 6; i++) cov3D_local[i] = __ldg(q.cov3D_precomp + (size_t)idx * 6 + i);
+        cov3D = cov3D_local;
+      } else {
+        const float3 sc = {s_scale[3 * threadIdx.x], s_scale[3 * threadIdx.x + 1], s_scale[3 * threadIdx.x + 2]};
+        const float4 rot = __ldg(reinterpret_cast<const float4*>(q.rotations) + idx);
+        cov3d_from_scale_rot(sc, q.scale_modifier, rot, cov3D_local);
+#pragma unroll
+        for (int i = 0; i < 6; i++) q.cov3Ds[(size_t)idx * 6 + i] = cov3D_local[i];
+        cov3D = cov3D_local;
+      }
+
+      float3 cov = cov2d_from_cov3d(p_orig, q.focal_x, q.focal_y, q.tan_fovx, q.tan_fovy, cov3D, q.view);
+
+      float det = (cov.x * cov.z - cov.y * cov.y);
+      if (det == 0.0f) break;
+      float det_inv = 1.f / det;
+      float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+
+      float mid = 0.5f * (cov.x + cov.z);
+      float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
+      float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
+      float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+      float2 point_image = {ndc2pix(p_proj.x, q.W), ndc2pix(p_proj.y, q.H)};
+      uint2 rmin, rmax;
+      tile_rect(point_image, (int)my_radius, q.grid_x, q.grid_y, rmin, rmax);
+      if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) break;
+
+      float3 rgb;
+      if (q.colors_precomp == nullptr) {
+        uint8_t cb;
+        const float3 cam = {q.campos[0], q.campos[1], q.campos[2]};
+        rgb = sh_to_rgb(q.D, p_orig, cam, q.shs + (size_t)idx * q.M * 3, cb);
+        q.clamped[idx] = cb;
+      } else {
+        rgb = {__ldg(q.colors_precomp + (size_t)idx * 3), __ldg(q.colors_precomp + (size_t)idx * 3 + 1),
+               __ldg(q.colors_precomp + (size_t)idx * 3 + 2)};
+      }
+
+      q.depths[idx] = p_view.z;
+      out_radius = (int)my_radius;
+      q.means2D[idx] = point_image;
+      q.conic_opacity[idx] = {conic.x, conic.y, conic.z, __ldg(q.opacities + idx)};
+      q.rgbd[idx] = {rgb.x, rgb.y, rgb.z, p_view.z};
+      my_tiles = (rmax.y - rmin.y) * (rmax.x - rmin.x);
+    } while (false);
+    q.radii[idx] = out_radius;
+    q.tiles_touched[idx] = my_tiles;
+  }
+
+  // per-block tile count → feeds the block-offset scan (no separate reduce pass)
+  uint32_t v = my_tiles;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) s_warp_sum[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < PRE_BLOCK / 32; w++) t += s_warp_sum[w];
+    q.block_sums[blockIdx.x] = t;
+  }
+}
+
+cudaError_t launch_preprocess_forward(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s) {
+  PreFwdParams q;
+  q.P = a.P; q.D = a.sh_degree; q.M = a.M; q.W = a.W; q.H = a.H;
+  q.grid_x = (a.W + TILE - 1) / TILE; q.grid_y = (a.H + TILE - 1) / TILE;
+  q.tan_fovx = a.tan_fovx; q.tan_fovy = a.tan_fovy;
+  q.focal_y = a.H / (2.0f * a.tan_fovy);
+  q.focal_x = a.W / (2.0f * a.tan_fovx);
+  q.scale_modifier = a.scale_modifier; q.prefiltered = a.prefiltered;
+  q.means3D = a.means3D; q.scales = a.scales; q.rotations = a.rotations; q.opacities = a.opacities;
+  q.shs = a.shs; q.cov3D_precomp = a.cov3D_precomp; q.colors_precomp = a.colors_precomp;
+  q.view = a.viewmatrix; q.proj = a.projmatrix; q.campos = a.campos;
+  q.radii = a.radii; q.means2D = p.means2D; q.depths = p.depths; q.cov3Ds = p.cov3D; q.rgbd = p.rgbd;
+  q.conic_opacity = p.conic_opacity; q.clamped = p.clamped; q.tiles_touched = p.tiles_touched;
+  q.block_sums = p.block_sums;
+  int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
+  preprocess_fwd_kernel<<<nblk, PRE_BLOCK, 0, s>>>(q);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Frustum test (rasterizer_impl.cu:57-69)
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
+                                    uint8_t* __restrict__ present) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+  float3 pv = xform4x3(p, view);
+  present[idx] = (pv.z <= 0.2f) ? 0 : 1;
+}
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Backward preprocess: one kernel for what the reference does in two
+// (computeCov2DCUDA, backward.cu:139-269; preprocessCUDA, backward.cu:339-389).
+struct PreBwdParams {
+  int P, D, M;
+  float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+  const float* means3D; const int* radii; const float* shs; const uint8_t* clamped;
+  const float* scales; const float* rotations; const float* cov3Ds;  // cov3Ds: precomp or geom
+  const float* view; const float* proj; const float* campos;
+  const float* dL_dmean2D;  // [P][3]
+  const float* dL_dconic;   // [P][4]
+  const float* dL_dcolor;   // [P][3]
+  float* dL_dmeans3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;
+};
+
+__device__ __forceinline__ float3 dnormvdv3(float3 v, float3 dv) {
+  float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  float invsum32 = 1.0f / sqrt(sum2 * sum2 * sum2);
+  float3 o;
+  o.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  o.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  o.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+  return o;
+}
+
+__global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdParams q) {
+  const int idx = blockIdx.x * PRE_BLOCK + threadIdx.x;
+  if (idx >= q.P || !(q.radii[idx] > 0)) return;
+
+  const float3 mean = {q.means3D[3 * idx], q.means3D[3 * idx + 1], q.means3D[3 * idx + 2]};
+  const float* view = q.view;
+
+  // ---- conic → cov2D → cov3D and the Jacobian part of dL/dmean (backward.cu:139-269)
+  float cov3D[6];
+#pragma unroll
+  for (int i = 0; i < 6; i++) cov3D[i] = q.cov3Ds[(size_t)idx * 6 + i];
+  const float4 dLc4 = reinterpret_cast<const float4*>(q.dL_dconic)[idx];
+  const float3 dL_dconic = {dLc4.x, dLc4.y, dLc4.w};
+  float3 t = xform4x3(mean, view);
+  const float h_x = q.focal_x, h_y = q.focal_y;
+  const float limx = 1.3f * q.tan_fovx;
+  const float limy = 1.3f * q.tan_fovy;
+  const float txtz = t.x / t.z;
+  const float tytz = t.y / t.z;
+  t.x = min(limx, max(-limx, txtz)) * t.z;
+  t.y = min(limy, max(-limy, tytz)) * t.z;
+  const float x_grad_mul = txtz < -limx || txtz > limx ? 0 : 1;
+  const float y_grad_mul = tytz < -limy || tytz > limy ? 0 : 1;
+
+  Mat3 J = mat3_cols(h_x / t.z, 0.0f, -(h_x * t.x) / (t.z * t.z), 0.0f, h_y / t.z, -(h_y * t.y) / (t.z * t.z), 0, 0, 0);
+  Mat3 Wm = mat3_cols(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
+  Mat3 Vrk = mat3_cols(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
+  Mat3 T = mul(Wm, J);
+  Mat3 cov2D = mul(mul(transpose(T), transpose(Vrk)), T);
+
+  float a = cov2D.m[0][0] += 0.3f;
+  float b = cov2D.m[0][1];
+  float c = cov2D.m[1][1] += 0.3f;
+
+  float denom = a * c - b * b;
+  float dL_da = 0, dL_db = 0, dL_dc = 0;
+  float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+  float dcov[6];
+  if (denom2inv != 0) {
+    dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
+    dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
+    dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
+
+    dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+    dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+    dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+    dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
+              2 * T.m[1][0] * T.m[1][1] * dL_dc;
+    dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
+              2 * T.m[1][0] * T.m[1][2] * dL_dc;
+    dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
+              2 * T.m[1][1] * T.m[1][2] * dL_dc;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 6; i++) dcov[i] = 0;
+  }
+#pragma unroll
+  for (int i = 0; i < 6; i++) q.dL_dcov3D[(size_t)idx * 6 + i] = dcov[i];
+
+  float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
+                  (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
+  float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
+                  (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
+  float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
+                  (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
+  float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
+                  (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
+  float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
+                  (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
+  float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
+                  (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
+
+  float dL_dJ00 = Wm.m[0][0] * dL_dT00 + Wm.m[0][1] * dL_dT01 + Wm.m[0][2] * dL_dT02;
+  float dL_dJ02 = Wm.m[2][0] * dL_dT00 + Wm.m[2][1] * dL_dT01 + Wm.m[2][2] * dL_dT02;
+  float dL_dJ11 = Wm.m[1][0] * dL_dT10 + Wm.m[1][1] * dL_dT11 + Wm.m[1][2] * dL_dT12;
+  float dL_dJ12 = Wm.m[2][0] * dL_dT10 + Wm.m[2][1] * dL_dT11 + Wm.m[2][2] * dL_dT12;
+
+  float tz = 1.f / t.z;
+  float tz2 = tz * tz;
+  float tz3 = tz2 * tz;
+
+  float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+  float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+  float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                 (2 * h_y * t.y) * tz3 * dL_dJ12;
+
+  float3 dL_dmean_acc = xform_vec4x3_T({dL_dtx, dL_dty, dL_dtz}, view);
+
+  // ---- projection part (backward.cu:361-377)
+  const float* proj = q.proj;
+  float4 m_hom = xform4x4(mean, proj);
+  float m_w = 1.0f / (m_hom.w + 0.0000001f);
+  const float3 g2 = {q.dL_dmean2D[3 * idx], q.dL_dmean2D[3 * idx + 1], 0.f};
+  float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+  float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+  float3 dL_dmean;
+  dL_dmean.x = (proj[0] * m_w - proj[3] * mul1) * g2.x + (proj[1] * m_w - proj[3] * mul2) * g2.y;
+  dL_dmean.y = (proj[4] * m_w - proj[7] * mul1) * g2.x + (proj[5] * m_w - proj[7] * mul2) * g2.y;
+  dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * g2.x + (proj[9] * m_w - proj[11] * mul2) * g2.y;
+  dL_dmean_acc.x += dL_dmean.x; dL_dmean_acc.y += dL_dmean.y; dL_dmean_acc.z += dL_dmean.z;
+
+  // ---- SH backward (backward.cu:18-134)
+  if (q.shs) {
+    const float3 campos = {q.campos[0], q.campos[1], q.campos[2]};
+    const float3 dir_orig = {mean.x - campos.x, mean.y - campos.y, mean.z - campos.z};
+    float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+    const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+    const float* shp = q.shs + (size_t)idx * q.M * 3;
+    auto SH = [&](int i) -> float3 {
+      return float3{__ldg(shp + 3 * i), __ldg(shp + 3 * i + 1), __ldg(shp + 3 * i + 2)};
+    };
+    const uint8_t cb = q.clamped[idx];
+    float3 dL_dRGB = {q.dL_dcolor[3 * idx], q.dL_dcolor[3 * idx + 1], q.dL_dcolor[3 * idx + 2]};
+    dL_dRGB.x *= (cb & 1) ? 0 : 1;
+    dL_dRGB.y *= (cb & 2) ? 0 : 1;
+    dL_dRGB.z *= (cb & 4) ? 0 : 1;
+
+    float3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
+    float* dsh = q.dL_dsh + (size_t)idx * q.M * 3;
+    auto put = [&](int i, float w) {
+      dsh[3 * i] = w * dL_dRGB.x; dsh[3 * i + 1] = w * dL_dRGB.y; dsh[3 * i + 2] = w * dL_dRGB.z;
+    };
+    auto axpy = [](float3& acc, float w, const float3& v) {
+      acc.x += w * v.x; acc.y += w * v.y; acc.z += w * v.z;
+    };
+    put(0, kSH_C0);
+    if (q.D > 0) {
+      float3 s1 = SH(1), s2 = SH(2), s3 = SH(3);
+      put(1, -kSH_C1 * y);
+      put(2, kSH_C1 * z);
+      put(3, -kSH_C1 * x);
+      dRGBdx = {-kSH_C1 * s3.x, -kSH_C1 * s3.y, -kSH_C1 * s3.z};
+      dRGBdy = {-kSH_C1 * s1.x, -kSH_C1 * s1.y, -kSH_C1 * s1.z};
+      dRGBdz = {kSH_C1 * s2.x, kSH_C1 * s2.y, kSH_C1 * s2.z};
+      if (q.D > 1) {
+        float xx = x * x, yy = y * y, zz = z * z;
+        float xy = x * y, yz = y * z, xz = x * z;
+        float3 s4 = SH(4), s5 = SH(5), s6 = SH(6), s7 = SH(7), s8 = SH(8);
+        put(4, kSH_C2[0] * xy);
+        put(5, kSH_C2[1] * yz);
+        put(6, kSH_C2[2] * (2.f * zz - xx - yy));
+        put(7, kSH_C2[3] * xz);
+        put(8, kSH_C2[4] * (xx - yy));
+        axpy(dRGBdx, kSH_C2[0] * y, s4); axpy(dRGBdx, kSH_C2[2] * 2.f * -x, s6);
+        axpy(dRGBdx, kSH_C2[3] * z, s7); axpy(dRGBdx, kSH_C2[4] * 2.f * x, s8);
+        axpy(dRGBdy, kSH_C2[0] * x, s4); axpy(dRGBdy, kSH_C2[1] * z, s5);
+        axpy(dRGBdy, kSH_C2[2] * 2.f * -y, s6); axpy(dRGBdy, kSH_C2[4] * 2.f * -y, s8);
+        axpy(dRGBdz, kSH_C2[1] * y, s5); axpy(dRGBdz, kSH_C2[2] * 2.f * 2.f * z, s6);
+        axpy(dRGBdz, kSH_C2[3] * x, s7);
+        if (q.D > 2) {
+          float3 s9 = SH(9), s10 = SH(10), s11 = SH(11), s12 = SH(12), s13 = SH(13), s14 = SH(14), s15 = SH(15);
+          put(9, kSH_C3[0] * y * (3.f * xx - yy));
+          put(10, kSH_C3[1] * xy * z);
+          put(11, kSH_C3[2] * y * (4.f * zz - xx - yy));
+          put(12, kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+          put(13, kSH_C3[4] * x * (4.f * zz - xx - yy));
+          put(14, kSH_C3[5] * z * (xx - yy));
+          put(15, kSH_C3[6] * x * (xx - 3.f * yy));
+          axpy(dRGBdx, kSH_C3[0] * 3.f * 2.f * xy, s9); axpy(dRGBdx, kSH_C3[1] * yz, s10);
+          axpy(dRGBdx, kSH_C3[2] * -2.f * xy, s11); axpy(dRGBdx, kSH_C3[3] * -3.f * 2.f * xz, s12);
+          axpy(dRGBdx, kSH_C3[4] * (-3.f * xx + 4.f * zz - yy), s13); axpy(dRGBdx, kSH_C3[5] * 2.f * xz, s14);
+          axpy(dRGBdx, kSH_C3[6] * 3.f * (xx - yy), s15);
+          axpy(dRGBdy, kSH_C3[0] * 3.f * (xx - yy), s9); axpy(dRGBdy, kSH_C3[1] * xz, s10);
+          axpy(dRGBdy, kSH_C3[2] * (-3.f * yy + 4.f * zz - xx), s11); axpy(dRGBdy, kSH_C3[3] * -3.f * 2.f * yz, s12);
+          axpy(dRGBdy, kSH_C3[4] * -2.f * xy, s13); axpy(dRGBdy, kSH_C3[5] * -2.f * yz, s14);
+          axpy(dRGBdy, kSH_C3[6] * -3.f * 2.f * xy, s15);
+          axpy(dRGBdz, kSH_C3[1] * xy, s10); axpy(dRGBdz, kSH_C3[2] * 4.f * 2.f * yz, s11);
+          axpy(dRGBdz, kSH_C3[3] * 3.f * (2.f * zz - xx - yy), s12); axpy(dRGBdz, kSH_C3[4] * 4.f * 2.f * xz, s13);
+          axpy(dRGBdz, kSH_C3[5] * (xx - yy), s14);
+        }
+      }
+    }
+    float3 dL_ddir = {dRGBdx.x * dL_dRGB.x + dRGBdx.y * dL_dRGB.y + dRGBdx.z * dL_dRGB.z,
+                      dRGBdy.x * dL_dRGB.x + dRGBdy.y * dL_dRGB.y + dRGBdy.z * dL_dRGB.z,
+                      dRGBdz.x * dL_dRGB.x + dRGBdz.y * dL_dRGB.y + dRGBdz.z * dL_dRGB.z};
+    float3 dm = dnormvdv3(dir_orig, dL_ddir);
+    dL_dmean_acc.x += dm.x; dL_dmean_acc.y += dm.y; dL_dmean_acc.z += dm.z;
+  }
+  q.dL_dmeans3D[3 * idx] = dL_dmean_acc.x;
+  q.dL_dmeans3D[3 * idx + 1] = dL_dmean_acc.y;
+  q.dL_dmeans3D[3 * idx + 2] = dL_dmean_acc.z;
+
+  // ---- cov3D → scale / rotation (backward.cu:273-334)
+  if (q.scales) {
+    const float3 scale = {q.scales[3 * idx], q.scales[3 * idx + 1], q.scales[3 * idx + 2]};
+    const float4 rot = reinterpret_cast<const float4*>(q.rotations)[idx];
+    float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+    Mat3 R = mat3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                       2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                       2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    const float3 s = {q.scale_modifier * scale.x, q.scale_modifier * scale.y, q.scale_modifier * scale.z};
+    Mat3 S = mat3_cols(s.x, 0.0f, 0.0f, 0.0f, s.y, 0.0f, 0.0f, 0.0f, s.z);
+    Mat3 M = mul(S, R);
+    Mat3 dL_dSigma = mat3_cols(dcov[0], 0.5f * dcov[1], 0.5f * dcov[2], 0.5f * dcov[1], dcov[3], 0.5f * dcov[4],
+                               0.5f * dcov[2], 0.5f * dcov[4], dcov[5]);
+    // dL_dM = 2 * M * dL_dSigma  (scalar * matrix scales every column first)
+    Mat3 M2;
+#pragma unroll
+    for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+      for (int rr = 0; rr < 3; rr++) M2.m[cc][rr] = M.m[cc][rr] * 2.0f;
+    Mat3 dL_dM = mul(M2, dL_dSigma);
+    Mat3 Rt = transpose(R);
+    Mat3 dL_dMt = transpose(dL_dM);
+
+    float3 dscale;
+    dscale.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
+    dscale.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
+    dscale.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+    q.dL_dscale[3 * idx] = dscale.x; q.dL_dscale[3 * idx + 1] = dscale.y; q.dL_dscale[3 * idx + 2] = dscale.z;
+
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      dL_dMt.m[0][k] *= s.x; dL_dMt.m[1][k] *= s.y; dL_dMt.m[2][k] *= s.z;
+    }
+    float4 dq;
+    dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+           2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
+    dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+           2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
+    dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+           2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
+    dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+           2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
+    reinterpret_cast<float4*>(q.dL_drot)[idx] = dq;
+  }
+}
+
+cudaError_t launch_preprocess_backward(const trase_b200_bwd_args& a, const FwdPointers& p, cudaStream_t s) {
+  PreBwdParams q;
+  q.P = a.P; q.D = a.sh_degree; q.M = a.M;
+  q.tan_fovx = a.tan_fovx; q.tan_fovy = a.tan_fovy;
+  q.focal_y = a.H / (2.0f * a.tan_fovy);
+  q.focal_x = a.W / (2.0f * a.tan_fovx);
+  q.scale_modifier = a.scale_modifier;
+  q.means3D = a.means3D; q.radii = a.radii; q.shs = a.shs; q.clamped = p.clamped;
+  q.scales = a.scales; q.rotations = a.rotations;
+  q.cov3Ds = (a.cov3D_precomp != nullptr) ? a.cov3D_precomp : p.cov3D;
+  q.view = a.viewmatrix; q.proj = a.projmatrix; q.campos = a.campos;
+  q.dL_dmean2D = a.dL_dmeans2D; q.dL_dconic = a.dL_dconic; q.dL_dcolor = a.dL_dcolors;
+  q.dL_dmeans3D = a.dL_dmeans3D; q.dL_dcov3D = a.dL_dcov3D; q.dL_dsh = a.dL_dsh;
+  q.dL_dscale = a.dL_dscales; q.dL_drot = a.dL_drotations;
+  int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
+  preprocess_bwd_kernel<<<nblk, PRE_BLOCK, 0, s>>>(q);
+  return cudaGetLastError();
+}
+
+}  // namespace tb

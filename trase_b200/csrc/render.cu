@@ -1,0 +1,480 @@
+// Tile compositing: forward (front-to-back alpha blending of RGB + 32 feature
+// channels + depth) and backward (back-to-front, warp-reduced gradients).
+//
+// Reference counterparts:
+//   forward  renderCUDA  DGR/cuda_rasterizer/forward.cu:264-396
+//   backward renderCUDA  DGR/cuda_rasterizer/backward.cu:392-574
+//
+// Bit-exactness.  n_contrib (and the set of blended pairs) depends on the exact
+// fp32 value of alpha and of the running transmittance.  The alpha chain below
+// is pinned with explicit round-to-nearest intrinsics to the operation order
+// the reference's compiled kernel uses (checked against its SASS):
+//   S     = fma(dx, dx*a, (dy*c)*dy)
+//   power = fma(S, -0.5, -((dx*b)*dy))
+//   alpha = min(0.99, o * expf(power));   T' = T * (1 - alpha)
+// Colour/feature accumulation order is free (tolerance 1e-4 abs).
+//
+// What differs from the reference:
+//  - forward stages the 32-channel feature row, colour and depth of every
+//    Gaussian of a batch in shared memory once per tile (the reference re-reads
+//    36 floats from global memory per pixel per Gaussian);
+//  - each thread can own PPT vertically adjacent pixels, so every shared-memory
+//    broadcast read and every cross-lane reduction is amortised over PPT pixels;
+//  - backward replaces the per-channel accum_rec/last_color recursions by one
+//    scalar recursion on dot(colour, dL/dpixel) (linear in the channels, so the
+//    result is the same up to rounding) — this removes 70 live registers;
+//  - backward reduces the 41 per-Gaussian partial gradients across the warp
+//    (transposed butterfly: 31 shuffles for the 32 feature channels) and issues
+//    one coalesced reduction per warp instead of 41 atomics per pixel;
+//  - backward starts at the tile's largest contributor count instead of the end
+//    of the tile's list.
+#include "common.cuh"
+
+namespace tb {
+
+struct Tuning {
+  int fwd_ppt = 2;
+  int bwd_ppt = 2;
+};
+static Tuning g_tuning;
+void set_tuning(const char* key, int value);
+
+constexpr int FWD_BATCH = 128;
+constexpr int BWD_BATCH = 64;
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ float splat_power(const float2 xy, const float4 co, float pxf, float pyf, float& dx,
+                                             float& dy) {
+  dx = xy.x - pxf;
+  dy = xy.y - pyf;
+  const float S = __fmaf_rn(dx, __fmul_rn(dx, co.x), __fmul_rn(__fmul_rn(dy, co.z), dy));
+  return __fmaf_rn(S, -0.5f, -__fmul_rn(__fmul_rn(dx, co.y), dy));
+}
+
+struct RenderFwdParams {
+  const uint2* ranges; const uint32_t* point_list;
+  int W, H;
+  const float2* means2D; const float4* rgbd; const float4* feat4;  // feat4: sh_objs as float4[P][8]
+  const float4* conic_opacity;
+  float* final_T; uint32_t* n_contrib; const float* bg;
+  float* out_color; float* out_objects; float* out_depth;
+};
+
+template <int PPT>
+__global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdParams q) {
+  constexpr int NT = 256 / PPT;
+  __shared__ float2 s_xy[FWD_BATCH];
+  __shared__ float4 s_co[FWD_BATCH];
+  __shared__ float4 s_rgbd[FWD_BATCH];
+  __shared__ float4 s_feat[FWD_BATCH * 8];
+
+  const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+  const uint2 range = q.ranges[tile];
+  const int px = blockIdx.x * TILE + (threadIdx.x & 15);
+  const int py0 = blockIdx.y * TILE + (threadIdx.x >> 4) * PPT;
+  const float pxf = (float)px;
+
+  float pyf[PPT], T[PPT], C[PPT][3], D[PPT], O[PPT][NUM_OBJECTS];
+  bool done[PPT], inside[PPT];
+  uint32_t last[PPT];
+#pragma unroll
+  for (int p = 0; p < PPT; p++) {
+    pyf[p] = (float)(py0 + p);
+    inside[p] = (px < q.W) && (py0 + p < q.H);
+    done[p] = !inside[p];
+    T[p] = 1.0f; D[p] = 0.f; last[p] = 0;
+    C[p][0] = C[p][1] = C[p][2] = 0.f;
+#pragma unroll
+    for (int ch = 0; ch < NUM_OBJECTS; ch++) O[p][ch] = 0.f;
+  }
+
+  for (uint32_t base = range.x; base < range.y; base += FWD_BATCH) {
+    bool all_done = true;
+#pragma unroll
+    for (int p = 0; p < PPT; p++) all_done = all_done && done[p];
+    if (__syncthreads_and(all_done)) break;
+
+    const int n = min((uint32_t)FWD_BATCH, range.y - base);
+    for (int k = threadIdx.x; k < n; k += NT) {
+      const uint32_t id = q.point_list[base + k];
+      s_xy[k] = q.means2D[id];
+      s_co[k] = q.conic_opacity[id];
+      s_rgbd[k] = q.rgbd[id];
+    }
+    for (int e = threadIdx.x; e < n * 8; e += NT) {
+      const uint32_t id = q.point_list[base + (e >> 3)];
+      s_feat[e] = __ldg(q.feat4 + (size_t)id * 8 + (e & 7));
+    }
+    __syncthreads();
+
+    if (!all_done) {
+      for (int j = 0; j < n; j++) {
+        const float2 xy = s_xy[j];
+        const float4 co = s_co[j];
+        float w[PPT];
+        bool any = false;
+        bool still = false;
+#pragma unroll
+        for (int p = 0; p < PPT; p++) {
+          w[p] = 0.f;
+          if (!done[p]) {
+            float dx, dy;
+            const float power = splat_power(xy, co, pxf, pyf[p], dx, dy);
+            if (!(power > 0.0f)) {
+              const float alpha = fminf(0.99f, co.w * expf(power));
+              if (!(alpha < 1.0f / 255.0f)) {
+                const float test_T = T[p] * (1 - alpha);
+                if (test_T < 0.0001f) {
+                  done[p] = true;
+                } else {
+                  w[p] = alpha * T[p];
+                  T[p] = test_T;
+                  last[p] = (base - range.x) + j + 1;
+                  any = true;
+                }
+              }
+            }
+          }
+          still = still || !done[p];
+        }
+        if (any) {
+          const float4 cd = s_rgbd[j];
+#pragma unroll
+          for (int p = 0; p < PPT; p++) {
+            C[p][0] = fmaf(cd.x, w[p], C[p][0]);
+            C[p][1] = fmaf(cd.y, w[p], C[p][1]);
+            C[p][2] = fmaf(cd.z, w[p], C[p][2]);
+            D[p] = fmaf(cd.w, w[p], D[p]);
+          }
+#pragma unroll
+          for (int c4 = 0; c4 < 8; c4++) {
+            const float4 f = s_feat[j * 8 + c4];
+#pragma unroll
+            for (int p = 0; p < PPT; p++) {
+              O[p][4 * c4 + 0] = fmaf(f.x, w[p], O[p][4 * c4 + 0]);
+              O[p][4 * c4 + 1] = fmaf(f.y, w[p], O[p][4 * c4 + 1]);
+              O[p][4 * c4 + 2] = fmaf(f.z, w[p], O[p][4 * c4 + 2]);
+              O[p][4 * c4 + 3] = fmaf(f.w, w[p], O[p][4 * c4 + 3]);
+            }
+          }
+        }
+        if (!still) break;
+      }
+    }
+  }
+
+  const size_t HW = (size_t)q.H * q.W;
+  const float bg0 = q.bg[0], bg1 = q.bg[1], bg2 = q.bg[2];
+#pragma unroll
+  for (int p = 0; p < PPT; p++) {
+    if (inside[p]) {
+      const size_t pix = (size_t)q.W * (py0 + p) + px;
+      q.final_T[pix] = T[p];
+      q.n_contrib[pix] = last[p];
+      q.out_color[pix] = C[p][0] + T[p] * bg0;
+      q.out_color[HW + pix] = C[p][1] + T[p] * bg1;
+      q.out_color[2 * HW + pix] = C[p][2] + T[p] * bg2;
+#pragma unroll
+      for (int ch = 0; ch < NUM_OBJECTS; ch++) q.out_objects[ch * HW + pix] = O[p][ch];
+      q.out_depth[pix] = D[p];
+    }
+  }
+}
+
+cudaError_t launch_render_forward(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s) {
+  RenderFwdParams q;
+  q.ranges = p.ranges; q.point_list = p.point_list; q.W = a.W; q.H = a.H;
+  q.means2D = p.means2D; q.rgbd = p.rgbd; q.feat4 = reinterpret_cast<const float4*>(a.sh_objs);
+  q.conic_opacity = p.conic_opacity; q.final_T = p.final_T; q.n_contrib = p.n_contrib; q.bg = a.background;
+  q.out_color = a.out_color; q.out_objects = a.out_objects; q.out_depth = a.out_depth;
+  dim3 grid((a.W + TILE - 1) / TILE, (a.H + TILE - 1) / TILE, 1);
+  if (g_tuning.fwd_ppt == 1)
+    render_fwd_kernel<1><<<grid, 256, 0, s>>>(q);
+  else
+    render_fwd_kernel<2><<<grid, 128, 0, s>>>(q);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Backward
+struct RenderBwdParams {
+  const uint2* ranges; const uint32_t* point_list;
+  int W, H;
+  const float* bg;
+  const float2* means2D; const float4* conic_opacity; const float4* rgbd; const float4* feat4;
+  const float* final_T; const uint32_t* n_contrib;
+  const float* dL_dpix; const float* dL_dpix_obj;
+  float* dL_dmean2D;  // [P][3]
+  float* dL_dconic;   // [P][4]
+  float* dL_dopacity; float* dL_dcolors; float* dL_dobjects;
+};
+
+// Sum v[i] over the 32 lanes for i = 0..31; on return lane l holds the total of
+// channel l in v[0].  31 shuffles instead of 32*5.
+__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    const bool hi = lane & 16;
+    const float send = hi ? v[i] : v[i + 16];
+    const float keep = hi ? v[i + 16] : v[i];
+    v[i] = keep + __shfl_xor_sync(FULL, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const bool hi = lane & 8;
+    const float send = hi ? v[i] : v[i + 8];
+    const float keep = hi ? v[i + 8] : v[i];
+    v[i] = keep + __shfl_xor_sync(FULL, send, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const bool hi = lane & 4;
+    const float send = hi ? v[i] : v[i + 4];
+    const float keep = hi ? v[i + 4] : v[i];
+    v[i] = keep + __shfl_xor_sync(FULL, send, 4);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const bool hi = lane & 2;
+    const float send = hi ? v[i] : v[i + 2];
+    const float keep = hi ? v[i + 2] : v[i];
+    v[i] = keep + __shfl_xor_sync(FULL, send, 2);
+  }
+  {
+    const bool hi = lane & 1;
+    const float send = hi ? v[0] : v[1];
+    const float keep = hi ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(FULL, send, 1);
+  }
+  return v[0];
+}
+// Same for 16 values: lane l ends with the total of value (l & 15) … both
+// halves of the warp hold a copy after the final full exchange.
+__device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lane) {
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const bool hi = lane & 8;
+    const float send = hi ? v[i] : v[i + 8];
+    const float keep = hi ? v[i + 8] : v[i];
+    v[i] = keep + __shfl_xor_sync(FULL, send, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const bool hi = lane & 4;
+    const float send = hi ? v[i] : v[i + 4];
+    const float keep = hi ? v[i + 4] : v[i];
+    v[i] = keep + __shfl_xor_sync(FULL, send, 4);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const bool hi = lane & 2;
+    const float send = hi ? v[i] : v[i + 2];
+    const float keep = hi ? v[i + 2] : v[i];
+    v[i] = keep + __shfl_xor_sync(FULL, send, 2);
+  }
+  {
+    const bool hi = lane & 1;
+    const float send = hi ? v[0] : v[1];
+    const float keep = hi ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(FULL, send, 1);
+  }
+  v[0] += __shfl_xor_sync(FULL, v[0], 16);
+  return v[0];
+}
+
+template <int PPT>
+__global__ void __launch_bounds__(256 / PPT) render_bwd_kernel(const RenderBwdParams q) {
+  constexpr int NT = 256 / PPT;
+  __shared__ uint32_t s_id[BWD_BATCH];
+  __shared__ float2 s_xy[BWD_BATCH];
+  __shared__ float4 s_co[BWD_BATCH];
+  __shared__ float4 s_rgbd[BWD_BATCH];
+  __shared__ float4 s_feat[BWD_BATCH * 8];
+  __shared__ uint32_t s_max[NT / 32];
+
+  const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+  const uint2 range = q.ranges[tile];
+  const int lane = threadIdx.x & 31;
+  const int px = blockIdx.x * TILE + (threadIdx.x & 15);
+  const int py0 = blockIdx.y * TILE + (threadIdx.x >> 4) * PPT;
+  const float pxf = (float)px;
+  const size_t HW = (size_t)q.H * q.W;
+
+  float pyf[PPT], T[PPT], T_final[PPT], S[PPT], last_alpha[PPT], last_dot[PPT], bg_dot[PPT];
+  float dLc[PPT][3], dLo[PPT][NUM_OBJECTS];
+  uint32_t last[PPT];
+  uint32_t my_max = 0;
+#pragma unroll
+  for (int p = 0; p < PPT; p++) {
+    pyf[p] = (float)(py0 + p);
+    const bool inside = (px < q.W) && (py0 + p < q.H);
+    const size_t pix = (size_t)q.W * (py0 + p) + px;
+    T_final[p] = inside ? q.final_T[pix] : 0.f;
+    T[p] = T_final[p];
+    last[p] = inside ? q.n_contrib[pix] : 0u;
+    my_max = max(my_max, last[p]);
+    S[p] = 0.f; last_alpha[p] = 0.f; last_dot[p] = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; c++) dLc[p][c] = inside ? q.dL_dpix[c * HW + pix] : 0.f;
+#pragma unroll
+    for (int ch = 0; ch < NUM_OBJECTS; ch++) dLo[p][ch] = inside ? q.dL_dpix_obj[ch * HW + pix] : 0.f;
+    bg_dot[p] = q.bg[0] * dLc[p][0] + q.bg[1] * dLc[p][1] + q.bg[2] * dLc[p][2];
+  }
+  // largest contributor count of the tile: nothing behind it received any weight
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) my_max = max(my_max, __shfl_xor_sync(FULL, my_max, o));
+  if (lane == 0) s_max[threadIdx.x >> 5] = my_max;
+  __syncthreads();
+  uint32_t tile_max = 0;
+#pragma unroll
+  for (int w = 0; w < NT / 32; w++) tile_max = max(tile_max, s_max[w]);
+  const uint32_t n_total = min(tile_max, range.y - range.x);
+
+  const float ddelx_dx = 0.5 * q.W;
+  const float ddely_dy = 0.5 * q.H;
+
+  // walk the list back to front in batches; element e (0-based in the tile's
+  // list) is visited by pixel p iff e < last[p]
+  for (int hi = (int)n_total; hi > 0; hi -= BWD_BATCH) {
+    const int n = min(BWD_BATCH, hi);
+    __syncthreads();
+    // s_*[k] holds element e = hi - 1 - k
+    for (int k = threadIdx.x; k < n; k += NT) {
+      const uint32_t id = q.point_list[range.x + hi - 1 - k];
+      s_id[k] = id;
+      s_xy[k] = q.means2D[id];
+      s_co[k] = q.conic_opacity[id];
+      s_rgbd[k] = q.rgbd[id];
+    }
+    for (int e = threadIdx.x; e < n * 8; e += NT) {
+      const uint32_t id = q.point_list[range.x + hi - 1 - (e >> 3)];
+      s_feat[e] = __ldg(q.feat4 + (size_t)id * 8 + (e & 7));
+    }
+    __syncthreads();
+
+    for (int k = 0; k < n; k++) {
+      const uint32_t e = (uint32_t)(hi - 1 - k);
+      const float2 xy = s_xy[k];
+      const float4 co = s_co[k];
+      float w[PPT], G[PPT], dx[PPT], dy[PPT], alpha[PPT];
+      bool act[PPT];
+      bool any = false;
+#pragma unroll
+      for (int p = 0; p < PPT; p++) {
+        act[p] = false;
+        if (e < last[p]) {
+          const float power = splat_power(xy, co, pxf, pyf[p], dx[p], dy[p]);
+          if (!(power > 0.0f)) {
+            G[p] = expf(power);
+            alpha[p] = fminf(0.99f, co.w * G[p]);
+            if (!(alpha[p] < 1.0f / 255.0f)) {
+              T[p] = T[p] / (1.f - alpha[p]);
+              w[p] = alpha[p] * T[p];
+              act[p] = true;
+              any = true;
+            }
+          }
+        }
+      }
+      if (!__any_sync(FULL, any)) continue;
+
+      float vobj[32];
+      float vs[16];
+#pragma unroll
+      for (int i = 0; i < 32; i++) vobj[i] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; i++) vs[i] = 0.f;
+
+      if (any) {
+        const float4 cd = s_rgbd[k];
+        float dot[PPT];
+#pragma unroll
+        for (int p = 0; p < PPT; p++) {
+          dot[p] = cd.x * dLc[p][0];
+          dot[p] = fmaf(cd.y, dLc[p][1], dot[p]);
+          dot[p] = fmaf(cd.z, dLc[p][2], dot[p]);
+        }
+#pragma unroll
+        for (int c4 = 0; c4 < 8; c4++) {
+          const float4 f = s_feat[k * 8 + c4];
+#pragma unroll
+          for (int p = 0; p < PPT; p++) {
+            dot[p] = fmaf(f.x, dLo[p][4 * c4 + 0], dot[p]);
+            dot[p] = fmaf(f.y, dLo[p][4 * c4 + 1], dot[p]);
+            dot[p] = fmaf(f.z, dLo[p][4 * c4 + 2], dot[p]);
+            dot[p] = fmaf(f.w, dLo[p][4 * c4 + 3], dot[p]);
+          }
+        }
+#pragma unroll
+        for (int p = 0; p < PPT; p++) {
+          if (act[p]) {
+            // scalar form of accum_rec: S = last_alpha*last_dot + (1-last_alpha)*S
+            S[p] = last_alpha[p] * last_dot[p] + (1.f - last_alpha[p]) * S[p];
+            last_dot[p] = dot[p];
+            float dL_dalpha = (dot[p] - S[p]) * T[p];
+            last_alpha[p] = alpha[p];
+            dL_dalpha += (-T_final[p] / (1.f - alpha[p])) * bg_dot[p];
+
+            const float dL_dG = co.w * dL_dalpha;
+            const float gdx = G[p] * dx[p];
+            const float gdy = G[p] * dy[p];
+            const float dG_ddelx = -gdx * co.x - gdy * co.y;
+            const float dG_ddely = -gdy * co.z - gdx * co.y;
+            vs[0] += w[p] * dLc[p][0];
+            vs[1] += w[p] * dLc[p][1];
+            vs[2] += w[p] * dLc[p][2];
+            vs[3] += dL_dG * dG_ddelx * ddelx_dx;
+            vs[4] += dL_dG * dG_ddely * ddely_dy;
+            vs[5] += -0.5f * gdx * dx[p] * dL_dG;
+            vs[6] += -0.5f * gdx * dy[p] * dL_dG;
+            vs[7] += -0.5f * gdy * dy[p] * dL_dG;
+            vs[8] += G[p] * dL_dalpha;
+#pragma unroll
+            for (int ch = 0; ch < NUM_OBJECTS; ch++) vobj[ch] = fmaf(w[p], dLo[p][ch], vobj[ch]);
+          }
+        }
+      }
+      const float tot_obj = warp_transpose_reduce32(vobj, lane);
+      const float tot_s = warp_transpose_reduce16(vs, lane);
+      const uint32_t id = s_id[k];
+      atomicAdd(q.dL_dobjects + (size_t)id * NUM_OBJECTS + lane, tot_obj);
+      if (lane < 9) {
+        float* dst;
+        if (lane < 3) dst = q.dL_dcolors + (size_t)id * 3 + lane;
+        else if (lane < 5) dst = q.dL_dmean2D + (size_t)id * 3 + (lane - 3);
+        else if (lane < 7) dst = q.dL_dconic + (size_t)id * 4 + (lane - 5);
+        else if (lane == 7) dst = q.dL_dconic + (size_t)id * 4 + 3;
+        else dst = q.dL_dopacity + id;
+        atomicAdd(dst, tot_s);
+      }
+    }
+  }
+}
+
+cudaError_t launch_render_backward(const trase_b200_bwd_args& a, const FwdPointers& p, cudaStream_t s) {
+  RenderBwdParams q;
+  q.ranges = p.ranges; q.point_list = p.point_list; q.W = a.W; q.H = a.H; q.bg = a.background;
+  q.means2D = p.means2D; q.conic_opacity = p.conic_opacity; q.rgbd = p.rgbd;
+  q.feat4 = reinterpret_cast<const float4*>(a.sh_objs);
+  q.final_T = p.final_T; q.n_contrib = p.n_contrib;
+  q.dL_dpix = a.dL_dout_color; q.dL_dpix_obj = a.dL_dout_objects;
+  q.dL_dmean2D = a.dL_dmeans2D; q.dL_dconic = a.dL_dconic; q.dL_dopacity = a.dL_dopacity;
+  q.dL_dcolors = a.dL_dcolors; q.dL_dobjects = a.dL_dobjects;
+  dim3 grid((a.W + TILE - 1) / TILE, (a.H + TILE - 1) / TILE, 1);
+  if (g_tuning.bwd_ppt == 1)
+    render_bwd_kernel<1><<<grid, 256, 0, s>>>(q);
+  else
+    render_bwd_kernel<2><<<grid, 128, 0, s>>>(q);
+  return cudaGetLastError();
+}
+
+void set_tuning(const char* key, int value) {
+  auto eq = [](const char* a, const char* b) {
+    while (*a && *b && *a == *b) { a++; b++; }
+    return *a == 0 && *b == 0;
+  };
+  if (eq(key, "fwd_ppt")) g_tuning.fwd_ppt = value;
+  if (eq(key, "bwd_ppt")) g_tuning.bwd_ppt = value;
+}
+
+}  // namespace tb
