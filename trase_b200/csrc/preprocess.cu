@@ -56,6 +56,29 @@ __device__ __forceinline__ Mat3 transpose(const Mat3& A) {
   return R;
 }
 
+// ---- pinned fp32 sequences -------------------------------------------------
+// ptxas is free to re-fuse un-annotated mul/add pairs, and does so differently
+// in differently shaped kernels.  Everything that decides an integer output of
+// the forward pass (radius, tile rectangle, depth key) is therefore written
+// with explicit round-to-nearest intrinsics, in the operation order read off
+// the reference's compiled sm_100 kernel (cuobjdump -sass of oracle/_ref):
+//   a1*b1 + a2*b2 + a3*b3        -> fma(a3,b3, fma(a1,b1, a2*b2))
+//   ... + m                      -> fadd(that, m)
+__device__ __forceinline__ float dot3p(float a1, float b1, float a2, float b2, float a3, float b3) {
+  return __fmaf_rn(a3, b3, __fmaf_rn(a1, b1, __fmul_rn(a2, b2)));
+}
+__device__ __forceinline__ float3 xform4x3p(const float3& p, const float* __restrict__ m) {
+  return float3{__fadd_rn(dot3p(m[0], p.x, m[4], p.y, m[8], p.z), m[12]),
+                __fadd_rn(dot3p(m[1], p.x, m[5], p.y, m[9], p.z), m[13]),
+                __fadd_rn(dot3p(m[2], p.x, m[6], p.y, m[10], p.z), m[14])};
+}
+__device__ __forceinline__ float4 xform4x4p(const float3& p, const float* __restrict__ m) {
+  return float4{__fadd_rn(dot3p(m[0], p.x, m[4], p.y, m[8], p.z), m[12]),
+                __fadd_rn(dot3p(m[1], p.x, m[5], p.y, m[9], p.z), m[13]),
+                __fadd_rn(dot3p(m[2], p.x, m[6], p.y, m[10], p.z), m[14]),
+                __fadd_rn(dot3p(m[3], p.x, m[7], p.y, m[11], p.z), m[15])};
+}
+
 __device__ __forceinline__ float3 xform4x3(const float3& p, const float* __restrict__ m) {
   float3 t = {
       m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12],
@@ -79,7 +102,9 @@ __device__ __forceinline__ float3 xform_vec4x3_T(const float3& p, const float* _
 }
 
 // NDC → pixel centre; evaluated in double and narrowed (auxiliary.h:39-42).
-__device__ __forceinline__ float ndc2pix(float v, int S) { return ((v + 1.0) * S - 1.0) * 0.5; }
+__device__ __forceinline__ float ndc2pix(float v, int S) {
+  return (float)__dmul_rn(__fma_rn(__dadd_rn((double)v, 1.0), (double)S, -1.0), 0.5);
+}
 
 // Tile rectangle of a splat (auxiliary.h:44-52): float division, truncation, clamp.
 __device__ __forceinline__ void tile_rect(const float2 p, int max_radius, int grid_x, int grid_y, uint2& rmin,
@@ -190,40 +215,72 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3 pos, const flo
 }
 
 // Σ = (S R)^T (S R) (forward.cu:121-154); quaternion (r,x,y,z), not normalised.
+// S is diagonal, so M[c][r] = s_r * R[c][r] (the zero terms of the full product
+// add ±0 and do not change the rounding).
 __device__ __forceinline__ void cov3d_from_scale_rot(const float3 scale, float mod, const float4 rot, float* cov3D) {
-  float sx = mod * scale.x, sy = mod * scale.y, sz = mod * scale.z;
-  float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
-  Mat3 R = mat3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                     2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                     2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-  Mat3 S = mat3_cols(sx, 0.0f, 0.0f, 0.0f, sy, 0.0f, 0.0f, 0.0f, sz);
-  Mat3 M = mul(S, R);
-  Mat3 Sigma = mul(transpose(M), M);
-  cov3D[0] = Sigma.m[0][0]; cov3D[1] = Sigma.m[0][1]; cov3D[2] = Sigma.m[0][2];
-  cov3D[3] = Sigma.m[1][1]; cov3D[4] = Sigma.m[1][2]; cov3D[5] = Sigma.m[2][2];
+  const float sx = __fmul_rn(mod, scale.x), sy = __fmul_rn(mod, scale.y), sz = __fmul_rn(mod, scale.z);
+  const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+  const float xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
+  const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+  // R[c][r], column-major
+  const float R00 = __fsub_rn(1.f, __fmul_rn(2.f, __fadd_rn(yy, zz)));
+  const float R01 = __fmul_rn(2.f, __fmaf_rn(x, y, -rz));
+  const float R02 = __fmul_rn(2.f, __fmaf_rn(r, y, xz));
+  const float R10 = __fmul_rn(2.f, __fmaf_rn(x, y, rz));
+  const float R11 = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(x, x, zz)));
+  const float R12 = __fmul_rn(2.f, __fmaf_rn(y, z, -rx));
+  const float R20 = __fmul_rn(2.f, __fmaf_rn(-r, y, xz));
+  const float R21 = __fmul_rn(2.f, __fmaf_rn(y, z, rx));
+  const float R22 = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(x, x, yy)));
+  const float M00 = __fmul_rn(sx, R00), M01 = __fmul_rn(sy, R01), M02 = __fmul_rn(sz, R02);
+  const float M10 = __fmul_rn(sx, R10), M11 = __fmul_rn(sy, R11), M12 = __fmul_rn(sz, R12);
+  const float M20 = __fmul_rn(sx, R20), M21 = __fmul_rn(sy, R21), M22 = __fmul_rn(sz, R22);
+  // Sigma[c][r] = dot(column r of M, column c of M)
+  cov3D[0] = dot3p(M00, M00, M01, M01, M02, M02);
+  cov3D[1] = dot3p(M10, M00, M11, M01, M12, M02);
+  cov3D[2] = dot3p(M20, M00, M21, M01, M22, M02);
+  cov3D[3] = dot3p(M10, M10, M11, M11, M12, M12);
+  cov3D[4] = dot3p(M20, M10, M21, M11, M22, M12);
+  cov3D[5] = dot3p(M20, M20, M21, M21, M22, M22);
 }
 
-// EWA projection of Σ to the image plane (forward.cu:77-116).
+// EWA projection of Σ to the image plane (forward.cu:77-116):
+// cov = T^T Vrk^T T with T = W J, +0.3 on the diagonal.
 __device__ __forceinline__ float3 cov2d_from_cov3d(const float3& mean, float focal_x, float focal_y, float tan_fovx,
-                                                   float tan_fovy, const float* cov3D,
-                                                   const float* __restrict__ view) {
-  float3 t = xform4x3(mean, view);
-  const float limx = 1.3f * tan_fovx;
-  const float limy = 1.3f * tan_fovy;
-  const float txtz = t.x / t.z;
-  const float tytz = t.y / t.z;
-  t.x = min(limx, max(-limx, txtz)) * t.z;
-  t.y = min(limy, max(-limy, tytz)) * t.z;
+                                                   float tan_fovy, const float* c, const float* __restrict__ v) {
+  float3 t = xform4x3p(mean, v);
+  const float limx = __fmul_rn(1.3f, tan_fovx);
+  const float limy = __fmul_rn(1.3f, tan_fovy);
+  const float txtz = __fdiv_rn(t.x, t.z);
+  const float tytz = __fdiv_rn(t.y, t.z);
+  t.x = __fmul_rn(fminf(limx, fmaxf(-limx, txtz)), t.z);
+  t.y = __fmul_rn(fminf(limy, fmaxf(-limy, tytz)), t.z);
 
-  Mat3 J = mat3_cols(focal_x / t.z, 0.0f, -(focal_x * t.x) / (t.z * t.z), 0.0f, focal_y / t.z,
-                     -(focal_y * t.y) / (t.z * t.z), 0, 0, 0);
-  Mat3 Wm = mat3_cols(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
-  Mat3 T = mul(Wm, J);
-  Mat3 Vrk = mat3_cols(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
-  Mat3 cov = mul(mul(transpose(T), transpose(Vrk)), T);
-  cov.m[0][0] += 0.3f;
-  cov.m[1][1] += 0.3f;
-  return {float(cov.m[0][0]), float(cov.m[0][1]), float(cov.m[1][1])};
+  const float tz2 = __fmul_rn(t.z, t.z);
+  const float J00 = __fdiv_rn(focal_x, t.z);
+  const float J02 = __fdiv_rn(-__fmul_rn(focal_x, t.x), tz2);
+  const float J11 = __fdiv_rn(focal_y, t.z);
+  const float J12 = __fdiv_rn(-__fmul_rn(focal_y, t.y), tz2);
+  // T = W J with W = [v0 v4 v8 | v1 v5 v9 | v2 v6 v10] (columns) and
+  // J = [J00 0 J02 | 0 J11 J12 | 0 0 0]: T[c][r] = W[0][r] J[c][0] + W[1][r] J[c][1] + W[2][r] J[c][2]
+  const float T00 = __fmaf_rn(v[2], J02, __fmul_rn(v[0], J00));
+  const float T01 = __fmaf_rn(v[6], J02, __fmul_rn(v[4], J00));
+  const float T02 = __fmaf_rn(v[10], J02, __fmul_rn(v[8], J00));
+  const float T10 = __fmaf_rn(v[2], J12, __fmul_rn(v[1], J11));
+  const float T11 = __fmaf_rn(v[6], J12, __fmul_rn(v[5], J11));
+  const float T12 = __fmaf_rn(v[10], J12, __fmul_rn(v[9], J11));
+  // X = T^T Vrk^T : X[c][r] = T[r][0] V[0][c] + T[r][1] V[1][c] + T[r][2] V[2][c]   (rows r = 0,1 needed)
+  const float X00 = dot3p(T00, c[0], T01, c[1], T02, c[2]);
+  const float X10 = dot3p(T00, c[1], T01, c[3], T02, c[4]);
+  const float X20 = dot3p(T00, c[2], T01, c[4], T02, c[5]);
+  const float X01 = dot3p(T10, c[0], T11, c[1], T12, c[2]);
+  const float X11 = dot3p(T10, c[1], T11, c[3], T12, c[4]);
+  const float X21 = dot3p(T10, c[2], T11, c[4], T12, c[5]);
+  // cov = X T : cov[c][r] = X[0][r] T[c][0] + X[1][r] T[c][1] + X[2][r] T[c][2]
+  const float cov00 = dot3p(T00, X00, T01, X10, T02, X20);
+  const float cov01 = dot3p(T00, X01, T01, X11, T02, X21);
+  const float cov11 = dot3p(T10, X01, T11, X11, T12, X21);
+  return {__fadd_rn(cov00, 0.3f), cov01, __fadd_rn(cov11, 0.3f)};
 }
 
 __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreFwdParams q) {
@@ -244,7 +301,7 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreFwdP
     do {
       const float3 p_orig = {s_mean[3 * threadIdx.x], s_mean[3 * threadIdx.x + 1], s_mean[3 * threadIdx.x + 2]};
       // near cull (auxiliary.h:134-159): view-space z <= 0.2 is invisible; no x/y cull
-      const float3 p_view = xform4x3(p_orig, q.view);
+      const float3 p_view = xform4x3p(p_orig, q.view);
       if (p_view.z <= 0.2f) {
         if (q.prefiltered) {
           printf("Point is filtered although prefiltered is set. This shouldn't happen!");
@@ -252,9 +309,9 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreFwdP
         }
         break;
       }
-      float4 p_hom = xform4x4(p_orig, q.proj);
-      float p_w = 1.0f / (p_hom.w + 0.0000001f);
-      float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+      float4 p_hom = xform4x4p(p_orig, q.proj);
+      float p_w = __frcp_rn(__fadd_rn(p_hom.w, 0.0000001f));
+      float3 p_proj = {__fmul_rn(p_hom.x, p_w), __fmul_rn(p_hom.y, p_w), __fmul_rn(p_hom.z, p_w)};
 
       float cov3D_local[6];
       const float* cov3D;
@@ -273,15 +330,16 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreFwdP
 
       float3 cov = cov2d_from_cov3d(p_orig, q.focal_x, q.focal_y, q.tan_fovx, q.tan_fovy, cov3D, q.view);
 
-      float det = (cov.x * cov.z - cov.y * cov.y);
+      float det = __fmaf_rn(cov.x, cov.z, -__fmul_rn(cov.y, cov.y));
       if (det == 0.0f) break;
-      float det_inv = 1.f / det;
-      float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+      float det_inv = __frcp_rn(det);
+      float3 conic = {__fmul_rn(cov.z, det_inv), -__fmul_rn(cov.y, det_inv), __fmul_rn(cov.x, det_inv)};
 
-      float mid = 0.5f * (cov.x + cov.z);
-      float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
-      float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
-      float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+      float mid = __fmul_rn(0.5f, __fadd_rn(cov.x, cov.z));
+      float sq = __fsqrt_rn(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
+      float lambda1 = __fadd_rn(mid, sq);
+      float lambda2 = __fsub_rn(mid, sq);
+      float my_radius = ceilf(__fmul_rn(3.f, __fsqrt_rn(fmaxf(lambda1, lambda2))));
       float2 point_image = {ndc2pix(p_proj.x, q.W), ndc2pix(p_proj.y, q.H)};
       uint2 rmin, rmax;
       tile_rect(point_image, (int)my_radius, q.grid_x, q.grid_y, rmin, rmax);
