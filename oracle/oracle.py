@@ -53,7 +53,7 @@ def forward(means3D, opacities, sh_objs, viewmatrix, projmatrix, campos, W, H, t
     sh_objs = _f32(sh_objs).reshape(P, NOBJ)
     view, proj, cam, bg = _f32(viewmatrix).reshape(16), _f32(projmatrix).reshape(16), _f32(campos), _f32(bg)
     shs = _f32(shs)
-    M = 0 if shs is None else shs.reshape(P, -1, 3).shape[1]
+    M = 0 if shs is None else (shs.shape[1] if shs.ndim == 3 else shs.size // max(3 * P, 1))
     colors_precomp, scales, rotations, cov3D_precomp = map(_f32, (colors_precomp, scales, rotations, cov3D_precomp))
     o = dict(P=P, W=W, H=H)
     o["radii"] = np.zeros(P, np.int32)

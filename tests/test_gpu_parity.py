@@ -1,0 +1,277 @@
+"""GPU: the CUDA path (through the C ABI) against (1) golden vectors from the
+reference, (2) the CPU oracle on seeded scenes, (3) the compiled reference
+itself (oracle/_ref) at sizes up to BASELINE.json's config 2, plus edge cases.
+
+Tolerances (BASELINE.json north_star): tile ranges, sorted keys, radii and
+per-pixel contributor counts bit-exact; colour/feature/depth <= 1e-4 abs;
+gradients <= 1e-3 relative."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN_CASES, load_golden
+from helpers import (GRAD_NAMES, cuda_backward, cuda_forward, golden_inputs_cuda, rel_err, scene_args, views)
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda:0")
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+# ---------------------------------------------------------------- golden ----
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_golden_forward_bit_exact(native_lib, name):
+    g = load_golden(name)
+    a = golden_inputs_cuda(g, DEV)
+    res = cuda_forward(a)
+    v = views(res, a)
+    vis = g["ref_radii"] > 0
+    assert res.num_rendered == int(g["num_rendered"])
+    assert np.array_equal(_np(res.radii), g["ref_radii"])
+    assert np.array_equal(_np(v["tiles_touched"]), g["ref_tiles_touched"])
+    assert np.array_equal(_np(v["point_list_keys"]), g["ref_point_list_keys"])
+    assert np.array_equal(_np(v["point_list"]), g["ref_point_list"])
+    assert np.array_equal(_np(v["ranges"]), g["ref_ranges"])
+    assert np.array_equal(_np(v["n_contrib"]), g["ref_n_contrib"])
+    assert np.array_equal(_np(v["depths"])[vis], g["ref_depths"][vis])
+    assert np.array_equal(_np(v["means2D"])[vis], g["ref_means2D"][vis])
+    assert np.array_equal(_np(v["conic_opacity"])[vis], g["ref_conic_opacity"][vis])
+    assert np.abs(_np(res.color) - g["ref_color"]).max() <= 1e-4
+    assert np.abs(_np(res.objects) - g["ref_objects"]).max() <= 1e-4
+    assert np.abs(_np(res.depth) - g["ref_depth"]).max() <= 1e-4
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+@pytest.mark.parametrize("ppt", [1, 2])
+def test_golden_backward(native_lib, name, ppt):
+    from trase_b200 import _lib
+    g = load_golden(name)
+    a = golden_inputs_cuda(g, DEV)
+    _lib.set_tuning("fwd_ppt", ppt)
+    _lib.set_tuning("bwd_ppt", ppt)
+    try:
+        res = cuda_forward(a)
+        b = cuda_backward(a, res, torch.from_numpy(g["in_dL_dcolor"]).to(DEV),
+                          torch.from_numpy(g["in_dL_dobjects"]).to(DEV))
+        assert np.array_equal(_np(views(res, a)["n_contrib"]), g["ref_n_contrib"])
+    finally:
+        _lib.set_tuning("fwd_ppt", 2)
+        _lib.set_tuning("bwd_ppt", 2)
+    for k in GRAD_NAMES:
+        assert rel_err(g["ref_grad_" + k], _np(b[k])) <= 1e-3, k
+
+
+# ---------------------------------------------------------------- oracle ----
+@pytest.mark.parametrize("P,W,H,seed,bg,deg", [(20000, 128, 128, 1, 0.0, 3), (5000, 100, 75, 5, 1.0, 2),
+                                               (3000, 37, 91, 6, 0.3, 0)])
+def test_against_cpu_oracle(native_lib, P, W, H, seed, bg, deg):
+    from oracle import oracle
+    from trase_b200 import synth
+    sc = synth.make_scene(P, W, H, seed, sh_degree=deg)
+    up = synth.make_upstream_grads(W, H, seed)
+    f = oracle.forward_scene(sc, [bg] * 3)
+    a = scene_args(sc, bg, DEV)
+    res = cuda_forward(a)
+    v = views(res, a)
+    assert res.num_rendered == f["num_rendered"]
+    assert np.array_equal(_np(res.radii), f["radii"])
+    assert np.array_equal(_np(v["point_list_keys"]).view(np.uint64), f["point_list_keys"])
+    assert np.array_equal(_np(v["point_list"]).view(np.uint32), f["point_list"])
+    assert np.array_equal(_np(v["ranges"]).view(np.uint32), f["ranges"])
+    assert (_np(v["n_contrib"]).view(np.uint32) != f["n_contrib"]).mean() <= 1e-3   # expf: see oracle header
+    assert np.abs(_np(res.color) - f["color"]).max() <= 1e-4
+    assert np.abs(_np(res.objects) - f["objects"]).max() <= 1e-4
+    assert np.abs(_np(res.depth) - f["depth"]).max() <= 1e-4
+    b = cuda_backward(a, res, up["dL_dcolor"].to(DEV), up["dL_dobjects"].to(DEV))
+    ob = oracle.backward(f, up["dL_dcolor"].numpy(), up["dL_dobjects"].numpy())
+    for k in GRAD_NAMES:
+        assert rel_err(ob[k], _np(b[k])) <= 1e-3, k
+
+
+# ------------------------------------------------ compiled reference --------
+def _ref_or_skip():
+    from oracle import ref_loader
+    if not ref_loader.available():
+        pytest.skip("oracle/_ref not built")
+    return ref_loader
+
+
+@pytest.mark.parametrize("P,W,H,seed,bg", [(20000, 128, 128, 1, 0.0), (200000, 536, 960, 3, 1.0),
+                                           (300000, 1352, 1014, 2, 0.0)])
+def test_against_compiled_reference(native_lib, P, W, H, seed, bg):
+    ref_loader = _ref_or_skip()
+    from trase_b200 import synth
+    sc = synth.scene_to(synth.make_scene(P, W, H, seed), DEV)
+    up = {k: v.to(DEV) for k, v in synth.make_upstream_grads(W, H, seed).items()}
+    bgt = torch.full((3,), bg, device=DEV)
+    ref = ref_loader.run_forward(sc, bgt)
+    a = scene_args(sc, bg, DEV)
+    res = cuda_forward(a)
+    v = views(res, a)
+    vis = ref["radii"] > 0
+    assert res.num_rendered == int(ref["num_rendered"])
+    assert torch.equal(res.radii, ref["radii"])
+    assert torch.equal(v["tiles_touched"], ref["tiles_touched"])
+    assert torch.equal(v["point_list_keys"], ref["point_list_keys"])
+    assert torch.equal(v["point_list"], ref["point_list"])
+    assert torch.equal(v["ranges"], ref["ranges"])
+    assert torch.equal(v["n_contrib"], ref["n_contrib"])
+    assert torch.equal(v["depths"][vis], ref["depths"][vis])
+    assert torch.equal(v["means2D"][vis], ref["means2D"][vis])
+    assert torch.equal(v["conic_opacity"][vis], ref["conic_opacity"][vis])
+    assert torch.equal(v["cov3D"][vis], ref["cov3D"][vis])
+    assert (res.color - ref["color"]).abs().max() <= 1e-4
+    assert (res.objects - ref["objects"]).abs().max() <= 1e-4
+    assert (res.depth - ref["depth"]).abs().max() <= 1e-4
+    rb = [ref_loader.run_backward(sc, bgt, ref, up["dL_dcolor"], up["dL_dobjects"]) for _ in range(3)]
+    b = cuda_backward(a, res, up["dL_dcolor"], up["dL_dobjects"])
+    for k in GRAD_NAMES:
+        r = sum(x[k].double() for x in rb) / 3
+        assert rel_err(_np(r), _np(b[k])) <= 1e-3, k
+
+
+# ------------------------------------------------------------ edge cases ----
+def test_empty_scene_returns_zero_images(native_lib):
+    from trase_b200 import synth
+    sc = synth.make_scene(0, 40, 24, 1)
+    a = scene_args(sc, 1.0, DEV)
+    res = cuda_forward(a)
+    assert res.num_rendered == 0 and res.radii.numel() == 0
+    assert not res.color.any() and not res.objects.any() and not res.depth.any()
+    b = cuda_backward(a, res, torch.zeros(3, 24, 40, device=DEV), torch.zeros(32, 24, 40, device=DEV))
+    assert b["sh"].shape == (0, 0, 3)   # M is taken as 0 when sh.size(0) == 0 (rasterize_points.cu:92-96)
+
+
+def test_all_culled_scene_renders_background(native_lib):
+    from trase_b200 import synth
+    sc = synth.make_scene(500, 40, 24, 1)
+    sc["means3D"][:, 2] = -sc["means3D"][:, 2].abs() - 1.0
+    a = scene_args(sc, 0.25, DEV)
+    res = cuda_forward(a)
+    assert res.num_rendered == 0 and not res.radii.any()
+    assert torch.all(res.color == 0.25) and not res.objects.any()
+    b = cuda_backward(a, res, torch.ones(3, 24, 40, device=DEV), torch.ones(32, 24, 40, device=DEV))
+    assert all(not x.any() for x in b.values())
+
+
+def test_capacity_overflow_triggers_rebin(native_lib):
+    from trase_b200 import synth, _raster
+    sc = synth.make_scene(4000, 64, 64, 4)
+    a = scene_args(sc, 0.0, DEV)
+    full = cuda_forward(a)
+    key = (0, 4000, 64, 64)
+    _raster._capacity_hint[key] = 10          # force a far too small first guess
+    small = cuda_forward(a)
+    assert small.num_rendered == full.num_rendered
+    assert torch.equal(small.color, full.color) and torch.equal(small.objects, full.objects)
+    assert torch.equal(views(small, a)["point_list"], views(full, a)["point_list"])
+
+
+def test_debug_mode_synchronises_and_matches(native_lib):
+    from trase_b200 import synth
+    sc = synth.make_scene(3000, 48, 48, 9)
+    a = scene_args(sc, 0.0, DEV)
+    r0, r1 = cuda_forward(a), cuda_forward(a, debug=True)
+    assert torch.equal(r0.color, r1.color) and torch.equal(r0.radii, r1.radii)
+
+
+def test_forward_is_deterministic(native_lib):
+    from trase_b200 import synth
+    sc = synth.make_scene(20000, 160, 96, 8)
+    a = scene_args(sc, 0.0, DEV)
+    r0, r1 = cuda_forward(a), cuda_forward(a)
+    for k in ("color", "objects", "depth", "radii"):
+        assert torch.equal(getattr(r0, k), getattr(r1, k))
+
+
+def test_scale_modifier_and_degrees(native_lib):
+    from oracle import oracle
+    from trase_b200 import synth
+    for deg, mod in [(0, 0.5), (1, 1.7), (2, 1.0)]:
+        sc = synth.make_scene(4000, 64, 48, 20 + deg, sh_degree=deg)
+        f = oracle.forward_scene(sc, [0, 0, 0], scale_modifier=mod)
+        a = scene_args(sc, 0.0, DEV)
+        res = cuda_forward(a, scale_modifier=mod)
+        assert np.array_equal(_np(res.radii), f["radii"])
+        assert np.abs(_np(res.color) - f["color"]).max() <= 1e-4
+
+
+def test_mark_visible(native_lib):
+    from trase_b200 import synth, _raster
+    from oracle import oracle
+    sc = synth.make_scene(10000, 64, 64, 2)
+    got = _raster.mark_visible(sc["means3D"].to(DEV), sc["cam"]["viewmatrix"].to(DEV), sc["cam"]["projmatrix"].to(DEV))
+    assert got.dtype == torch.bool
+    assert np.array_equal(_np(got), oracle.mark_visible(sc["means3D"].numpy(), sc["cam"]["viewmatrix"].numpy()))
+
+
+# ------------------------------------------------------------ radix sort ----
+@pytest.mark.parametrize("n,end_bit", [(0, 40), (1, 33), (4095, 39), (4097, 45), (1_000_003, 45), (3_000_000, 64)])
+def test_sort_pairs_matches_stable_sort(native_lib, n, end_bit):
+    rng = np.random.default_rng(n + end_bit)
+    cap = max(n + 17, 1)
+    mask = (1 << end_bit) - 1 if end_bit < 64 else (1 << 64) - 1
+    # few distinct depth values -> many duplicate keys, which exercises stability
+    keys = (rng.integers(0, 5440, cap, dtype=np.uint64) << np.uint64(32)) | rng.integers(0, 300, cap, dtype=np.uint64)
+    keys = keys & np.uint64(mask)
+    vals = np.arange(cap, dtype=np.uint32)
+    order = np.argsort(keys[:n], kind="stable")
+    k_in = torch.from_numpy(keys.view(np.int64)).to(DEV)
+    v_in = torch.from_numpy(vals.view(np.int32)).to(DEV)
+    k_out, v_out = torch.zeros_like(k_in), torch.zeros_like(v_in)
+    cnt = torch.tensor([n], dtype=torch.int32, device=DEV)
+    sb = native_lib.trase_b200_sort_scratch_bytes(cap)
+    scratch = torch.empty(sb, dtype=torch.uint8, device=DEV)
+    rc = native_lib.trase_b200_sort_pairs(k_in.data_ptr(), v_in.data_ptr(), k_out.data_ptr(), v_out.data_ptr(),
+                                          cnt.data_ptr(), cap, end_bit, scratch.data_ptr(), sb,
+                                          torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(_np(k_out)[:n].view(np.uint64), keys[:n][order])
+    assert np.array_equal(_np(v_out)[:n].view(np.uint32), vals[:n][order])
+
+
+# -------------------------------------------------- public autograd API -----
+def test_autograd_api_end_to_end(native_lib):
+    from trase_b200 import synth
+    from trase_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from oracle import oracle
+    sc_cpu = synth.make_scene(6000, 80, 64, 31)
+    sc = synth.scene_to(sc_cpu, DEV)
+    up = {k: v.to(DEV) for k, v in synth.make_upstream_grads(80, 64, 31).items()}
+    st = synth.settings_from(sc, torch.zeros(3, device=DEV), GaussianRasterizationSettings)
+    leaves = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "shs", "sh_objs", "opacities", "scales",
+                                                              "rotations")}
+    means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+    color, radii, objects, depth = GaussianRasterizer(st)(
+        means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"], shs=leaves["shs"],
+        sh_objs=leaves["sh_objs"], scales=leaves["scales"], rotations=leaves["rotations"])
+    assert color.shape == (3, 64, 80) and objects.shape == (32, 64, 80) and depth.shape == (1, 64, 80)
+    assert radii.dtype == torch.int32 and radii.shape == (6000,)
+    loss = (color * up["dL_dcolor"]).sum() + (objects * up["dL_dobjects"]).sum() + (depth * up["dL_ddepth"]).sum()
+    loss.backward()
+    f = oracle.forward_scene(sc_cpu, [0, 0, 0])
+    ob = oracle.backward(f, up["dL_dcolor"].cpu().numpy(), up["dL_dobjects"].cpu().numpy())
+    assert leaves["sh_objs"].grad.shape == (6000, 1, 32)          # grad_objects.unsqueeze(1)
+    assert rel_err(ob["means3D"], _np(leaves["means3D"].grad)) <= 1e-3
+    assert rel_err(ob["means2D"], _np(means2D.grad)) <= 1e-3
+    assert rel_err(ob["sh"], _np(leaves["shs"].grad)) <= 1e-3
+    assert rel_err(ob["objects"], _np(leaves["sh_objs"].grad)) <= 1e-3
+    assert rel_err(ob["opacities"], _np(leaves["opacities"].grad)) <= 1e-3
+    assert rel_err(ob["scales"], _np(leaves["scales"].grad)) <= 1e-3
+    assert rel_err(ob["rotations"], _np(leaves["rotations"].grad)) <= 1e-3
+
+
+def test_runs_on_a_side_stream(native_lib):
+    from trase_b200 import synth
+    sc = synth.make_scene(5000, 64, 64, 3)
+    a = scene_args(sc, 0.0, DEV)
+    base = cuda_forward(a)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        side = cuda_forward(a)
+    s.synchronize()
+    assert torch.equal(base.color, side.color)
