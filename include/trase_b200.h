@@ -191,6 +191,22 @@ typedef struct trase_b200_bwd_args {
 
 TRASE_API int trase_b200_rasterize_backward(const trase_b200_bwd_args* args);
 
+/* Same, restricted to a subset of its two kernels: bit 0 = compositing backward
+ * (ref: BACKWARD::render, DGR/cuda_rasterizer/backward.cu:639-679), bit 1 =
+ * preprocess backward (ref: BACKWARD::preprocess, backward.cu:576-637).  For
+ * tests and profiling of one stage at a time. */
+TRASE_API int trase_b200_rasterize_backward_stages(const trase_b200_bwd_args* args, int stages);
+
+/* Per-stage device timing with CUDA events on the launching stream (the
+ * reference has none; its CHECK_CUDA debug mode only synchronises,
+ * DGR/cuda_rasterizer/auxiliary.h:161-171).  After enable(1), every forward /
+ * backward call records an event pair around each stage; read() waits for the
+ * recorded events, returns the number of stages and fills total_ms[i] /
+ * count[i] (i: 0 preprocess_fwd, 1 scan+duplicate, 2 sort, 3 ranges,
+ * 4 render_fwd, 5 render_bwd, 6 preprocess_bwd, 7 unused), then clears. */
+TRASE_API void trase_b200_profile_enable(int on);
+TRASE_API int trase_b200_profile_read(double* total_ms, int* count);
+
 /* ref: markVisible (DGR/rasterize_points.cu:216-235) → checkFrustum
  * (DGR/cuda_rasterizer/rasterizer_impl.cu:57-69).  present[i] = 1 if the
  * view-space z of means3D[i] is > 0.2. */

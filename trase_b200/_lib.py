@@ -65,7 +65,8 @@ EXPORTS = [
     "trase_b200_img_offsets", "trase_b200_binning_offsets", "trase_b200_rasterize_forward",
     "trase_b200_rasterize_forward_rebin", "trase_b200_rasterize_backward", "trase_b200_mark_visible",
     "trase_b200_sort_scratch_bytes", "trase_b200_sort_pairs", "trase_b200_higher_msb",
-    "trase_b200_set_tuning",
+    "trase_b200_set_tuning", "trase_b200_rasterize_backward_stages", "trase_b200_profile_enable",
+    "trase_b200_profile_read",
 ]
 
 _lib = None
@@ -113,6 +114,12 @@ def load() -> C.CDLL:
                                           C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.trase_b200_higher_msb.restype = C.c_uint32
     lib.trase_b200_higher_msb.argtypes = [C.c_uint32]
+    lib.trase_b200_rasterize_backward_stages.restype = C.c_int
+    lib.trase_b200_rasterize_backward_stages.argtypes = [C.POINTER(BwdArgs), C.c_int]
+    lib.trase_b200_profile_enable.restype = None
+    lib.trase_b200_profile_enable.argtypes = [C.c_int]
+    lib.trase_b200_profile_read.restype = C.c_int
+    lib.trase_b200_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_int)]
     lib.trase_b200_set_tuning.restype = None
     lib.trase_b200_set_tuning.argtypes = [C.c_char_p, C.c_int]
     _lib = lib
@@ -140,6 +147,20 @@ def binning_offsets(capacity: int) -> dict:
     arr = (C.c_size_t * len(BIN_ARRAYS))()
     load().trase_b200_binning_offsets(capacity, arr)
     return dict(zip(BIN_ARRAYS, list(arr)))
+
+
+STAGES = ["preprocess_fwd", "scan_duplicate", "sort", "ranges", "render_fwd", "render_bwd", "preprocess_bwd", "other"]
+
+
+def profile_enable(on: bool) -> None:
+    load().trase_b200_profile_enable(int(on))
+
+
+def profile_read() -> dict:
+    ms = (C.c_double * 8)()
+    cnt = (C.c_int * 8)()
+    load().trase_b200_profile_read(ms, cnt)
+    return {STAGES[i]: (ms[i], cnt[i]) for i in range(8)}
 
 
 def set_tuning(key: str, value: int) -> None:

@@ -5,6 +5,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <utility>
+#include <vector>
 
 namespace tb {
 
@@ -22,16 +25,46 @@ static int fail_cuda(const char* where, cudaError_t e) {
   return 2;
 }
 
+// ---- optional per-stage timing (bench.py's roofline leg) --------------------
+// CUDA events recorded on the launching stream around each stage; off by default.
+enum { ST_PREPROCESS_FWD = 0, ST_SCAN_DUP, ST_SORT, ST_RANGES, ST_RENDER_FWD, ST_RENDER_BWD, ST_PREPROCESS_BWD,
+       ST_OTHER, ST_COUNT };
+struct ProfRec { int stage; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof_live;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_prof_free;
+static std::mutex g_prof_mu;
+
+static void prof_begin(int stage, cudaStream_t s, ProfRec& r) {
+  r.stage = -1;
+  if (!g_prof_on || stage < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (!g_prof_free.empty()) { r.a = g_prof_free.back().first; r.b = g_prof_free.back().second; g_prof_free.pop_back(); }
+  else { if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return; }
+  r.stage = stage;
+  cudaEventRecord(r.a, s);
+}
+static void prof_end(cudaStream_t s, ProfRec& r) {
+  if (r.stage < 0) return;
+  cudaEventRecord(r.b, s);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_live.push_back(r);
+}
+
 // debug mode: synchronise and check after each launch (auxiliary.h:161-171)
-#define TB_STEP(name, expr)                                        \
+#define TB_STEP_ST(stage, name, expr)                              \
   do {                                                             \
+    ProfRec pr__;                                                  \
+    prof_begin(stage, stream, pr__);                               \
     cudaError_t e__ = (expr);                                      \
+    prof_end(stream, pr__);                                        \
     if (e__ != cudaSuccess) return fail_cuda(name, e__);           \
     if (debug) {                                                   \
       e__ = cudaStreamSynchronize(stream);                         \
       if (e__ != cudaSuccess) return fail_cuda(name, e__);         \
     }                                                              \
   } while (0)
+#define TB_STEP(name, expr) TB_STEP_ST(-1, name, expr)
 
 static FwdPointers carve(void* geom, int P, void* img, int W, int H, void* binning, int64_t capacity, void* scratch) {
   FwdPointers p;
@@ -150,16 +183,16 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
   pd.keys_unsorted = keys_a;
   pd.vals_unsorted = vals_a;
 
-  if (with_preprocess) TB_STEP("preprocess_forward", launch_preprocess_forward(*a, p, stream));
-  TB_STEP("scan_and_duplicate", launch_scan_and_duplicate(*a, pd, stream));
+  if (with_preprocess) TB_STEP_ST(ST_PREPROCESS_FWD, "preprocess_forward", launch_preprocess_forward(*a, p, stream));
+  TB_STEP_ST(ST_SCAN_DUP, "scan_and_duplicate", launch_scan_and_duplicate(*a, pd, stream));
   if (a->num_rendered_host)
     TB_STEP("copy num_rendered",
             cudaMemcpyAsync(a->num_rendered_host, p.counters, sizeof(int), cudaMemcpyDeviceToHost, stream));
   if (a->capacity > 0)
-    TB_STEP("sort_pairs", launch_sort_pingpong(keys_a, vals_a, keys_b, vals_b, p.counters, a->capacity, end_bit,
+    TB_STEP_ST(ST_SORT, "sort_pairs", launch_sort_pingpong(keys_a, vals_a, keys_b, vals_b, p.counters, a->capacity, end_bit,
                                                p.sort_scratch, p.sort_scratch_bytes, stream));
-  TB_STEP("identify_ranges", launch_identify_ranges(*a, p, stream));
-  TB_STEP("render_forward", launch_render_forward(*a, p, stream));
+  TB_STEP_ST(ST_RANGES, "identify_ranges", launch_identify_ranges(*a, p, stream));
+  TB_STEP_ST(ST_RENDER_FWD, "render_forward", launch_render_forward(*a, p, stream));
   return 0;
 }
 
@@ -193,7 +226,7 @@ void trase_b200_binning_offsets(int64_t capacity, size_t* out) {
 int trase_b200_rasterize_forward(const trase_b200_fwd_args* a) { return forward_impl(a, true); }
 int trase_b200_rasterize_forward_rebin(const trase_b200_fwd_args* a) { return forward_impl(a, false); }
 
-int trase_b200_rasterize_backward(const trase_b200_bwd_args* a) {
+static int backward_impl(const trase_b200_bwd_args* a, int stages) {
   g_err[0] = 0;
   if (!a) { set_error("trase_b200: null argument struct"); return 1; }
   if (a->P < 0 || a->W <= 0 || a->H <= 0) { set_error("trase_b200: bad sizes"); return 1; }
@@ -218,9 +251,31 @@ int trase_b200_rasterize_backward(const trase_b200_bwd_args* a) {
   const int debug = a->debug;
   FwdPointers p = carve(const_cast<void*>(a->geom), a->P, const_cast<void*>(a->img), a->W, a->H,
                         const_cast<void*>(a->binning), a->capacity, nullptr);
-  TB_STEP("render_backward", launch_render_backward(*a, p, stream));
-  TB_STEP("preprocess_backward", launch_preprocess_backward(*a, p, stream));
+  if (stages & 1) TB_STEP_ST(ST_RENDER_BWD, "render_backward", launch_render_backward(*a, p, stream));
+  if (stages & 2) TB_STEP_ST(ST_PREPROCESS_BWD, "preprocess_backward", launch_preprocess_backward(*a, p, stream));
   return 0;
+}
+
+int trase_b200_rasterize_backward(const trase_b200_bwd_args* a) { return backward_impl(a, 3); }
+int trase_b200_rasterize_backward_stages(const trase_b200_bwd_args* a, int stages) { return backward_impl(a, stages); }
+
+void trase_b200_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = on != 0;
+}
+int trase_b200_profile_read(double* total_ms /*[8]*/, int* count /*[8]*/) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (int i = 0; i < ST_COUNT; i++) { total_ms[i] = 0; count[i] = 0; }
+  for (auto& r : g_prof_live) {
+    float ms = 0.f;
+    if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+      total_ms[r.stage] += ms;
+      count[r.stage]++;
+    }
+    g_prof_free.push_back({r.a, r.b});
+  }
+  g_prof_live.clear();
+  return ST_COUNT;
 }
 
 int trase_b200_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

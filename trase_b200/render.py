@@ -1,0 +1,121 @@
+"""Render glue: mirror of the reference's `render()`
+(gaussian_renderer/__init__.py:37-155) on top of the B200 rasterizer, plus the
+minimal parameter container it reads (the `get_*` properties of
+scene/gaussian_model.py:181-205).  Same arguments, same output dict keys.
+"""
+from __future__ import annotations
+
+import math
+from types import SimpleNamespace
+
+import torch
+
+from .diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+
+
+class GaussianParams(torch.nn.Module):
+    """Raw (pre-activation) per-Gaussian parameters with the reference's
+    activations: exp for scaling, sigmoid for opacity, normalize for rotation
+    (scene/gaussian_model.py:45-60, 181-205)."""
+
+    def __init__(self, xyz, features_dc, features_rest, scaling, rotation, opacity, gaussian_features,
+                 active_sh_degree=3, max_sh_degree=3):
+        super().__init__()
+        P = torch.nn.Parameter
+        self._xyz = P(xyz)
+        self._features_dc = P(features_dc)          # [P,1,3]
+        self._features_rest = P(features_rest)      # [P,15,3]
+        self._scaling = P(scaling)                  # log-scale
+        self._rotation = P(rotation)
+        self._opacity = P(opacity)                  # logit
+        self._gaussian_features = P(gaussian_features)  # [P,1,32]
+        self.active_sh_degree = active_sh_degree
+        self.max_sh_degree = max_sh_degree
+
+    @classmethod
+    def from_activated(cls, scene: dict, device) -> "GaussianParams":
+        """From a synthetic scene holding activated values (trase_b200.synth)."""
+        d = lambda t: t.to(device)
+        op = scene["opacities"].clamp(1e-6, 1 - 1e-6)
+        return cls(d(scene["means3D"]), d(scene["shs"][:, :1].contiguous()), d(scene["shs"][:, 1:].contiguous()),
+                   d(torch.log(scene["scales"])), d(scene["rotations"]), d(torch.log(op / (1 - op))),
+                   d(scene["sh_objs"]), active_sh_degree=scene["sh_degree"])
+
+    @property
+    def get_xyz(self):
+        return self._xyz
+
+    @property
+    def get_scaling(self):
+        return torch.exp(self._scaling)
+
+    @property
+    def get_rotation(self):
+        return torch.nn.functional.normalize(self._rotation)
+
+    @property
+    def get_opacity(self):
+        return torch.sigmoid(self._opacity)
+
+    @property
+    def get_features(self):
+        return torch.cat((self._features_dc, self._features_rest), dim=1)
+
+    @property
+    def get_gaussian_features(self):
+        return self._gaussian_features
+
+
+def make_view(cam: dict, device) -> SimpleNamespace:
+    """Camera object with the attributes `render()` reads (scene/cameras.py:27-79)."""
+    return SimpleNamespace(FoVx=2 * math.atan(cam["tanfovx"]), FoVy=2 * math.atan(cam["tanfovy"]),
+                           image_height=cam["H"], image_width=cam["W"],
+                           world_view_transform=cam["viewmatrix"].to(device),
+                           full_proj_transform=cam["projmatrix"].to(device), camera_center=cam["campos"].to(device))
+
+
+PIPE_DEFAULT = SimpleNamespace(convert_SHs_python=False, compute_cov3D_python=False, debug=False)
+
+
+def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, is_6dof=False, scaling_modifier=1.0,
+           override_color=None, mask=None, norm_gaussian_features=True, is_smooth_gaussian_features=False,
+           smooth_K=16):
+    """gaussian_renderer/__init__.py:37-155.  Background tensor must be on the GPU."""
+    if is_6dof or is_smooth_gaussian_features or getattr(pipe, "convert_SHs_python", False) or \
+            getattr(pipe, "compute_cov3D_python", False):
+        raise NotImplementedError("6-DoF deformation, kNN-smoothed features and the *_python pipeline switches "
+                                  "are outside the accelerated path")
+    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True) + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    raster_settings = GaussianRasterizationSettings(
+        image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width),
+        tanfovx=math.tan(viewpoint_camera.FoVx * 0.5), tanfovy=math.tan(viewpoint_camera.FoVy * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=viewpoint_camera.world_view_transform,
+        projmatrix=viewpoint_camera.full_proj_transform, sh_degree=pc.active_sh_degree,
+        campos=viewpoint_camera.camera_center, prefiltered=False, debug=pipe.debug)
+    rasterizer = GaussianRasterizer(raster_settings=raster_settings)
+
+    means3D = pc.get_xyz + d_xyz
+    means2D = screenspace_points
+    opacity = pc.get_opacity
+    scales = pc.get_scaling + d_scaling
+    rotations = pc.get_rotation + d_rotation
+    shs, colors_precomp = (pc.get_features, None) if override_color is None else (None, override_color)
+    sh_objs = pc.get_gaussian_features
+    if norm_gaussian_features:
+        sh_objs = sh_objs / (sh_objs.norm(dim=2, keepdim=True) + 1e-9)
+    if mask is not None:
+        means3D, means2D, opacity, sh_objs = means3D[mask], means2D[mask], opacity[mask], sh_objs[mask]
+        scales, rotations = scales[mask], rotations[mask]
+        if colors_precomp is not None:
+            colors_precomp = colors_precomp[mask]
+        else:
+            shs = shs[mask]
+    rendered_image, radii, rendered_feats, depth = rasterizer(
+        means3D=means3D, means2D=means2D, shs=shs, sh_objs=sh_objs, colors_precomp=colors_precomp,
+        opacities=opacity, scales=scales, rotations=rotations, cov3D_precomp=None)
+    return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
+            "radii": radii, "render_gaussian_features": rendered_feats, "depth": depth}
