@@ -227,6 +227,33 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
                           int end_bit, void* sort_scratch, size_t sort_scratch_bytes,
                           void* stream);
 
+/* The same sort for callers that cannot allocate device memory.  It has no
+ * counterpart in the reference (which sizes a CUB temp buffer and has torch
+ * allocate it on every call, DGR/rasterize_points.cu:30-38).
+ *
+ * Meant for hosts where cudaMalloc is off the table at sort time: an engine
+ * that claimed the whole GPU for its own arena, a process under a hard memory
+ * cap, a frame loop that may not take the driver's allocator lock (cudaMalloc
+ * and cudaFree can stall every stream), or a plug-in running inside another
+ * runtime's no-allocation callback.  The histogram workspace lives inside the
+ * library in a fixed ~1 MiB device array that every GPU loading the library
+ * holds until the process exits; the caller passes only its own key/value
+ * buffers and the device count.
+ *
+ *  - capacity may not exceed TRASE_B200_STATIC_SORT_MAX; beyond that the call
+ *    returns an error and launches nothing.
+ *  - All calls on a GPU share the one workspace and see the previous call's
+ *    contents; what must start at zero is cleared on `stream` at the start of
+ *    every call.  Calls whose GPU work overlaps race on it: issue them one at
+ *    a time (same stream, or ordered with events).
+ *  - The first call on each GPU resolves the workspace's device address with
+ *    that GPU current; make that first call before any stream capture begins.
+ *  - Calls no cudaMalloc/cudaFree or other allocating routine. */
+#define TRASE_B200_STATIC_SORT_MAX (1 << 22)
+TRASE_API int trase_b200_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
+                                           uint32_t* vals_out, const uint32_t* count_dev, int64_t capacity,
+                                           int end_bit, void* stream);
+
 /* ref: getHigherMsb (DGR/cuda_rasterizer/rasterizer_impl.cu:38-53). */
 TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);
 
