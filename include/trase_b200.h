@@ -227,6 +227,23 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
                           int end_bit, void* sort_scratch, size_t sort_scratch_bytes,
                           void* stream);
 
+/* ------------------------------------------------------------------------
+ * DeformNetwork MLP building block.  ref: the eleven nn.Linear layers of
+ * DeformNetwork.forward (utils/time_utils.py:106-131), which the reference runs
+ * as cuBLAS SGEMM + separate bias/ReLU kernels, and their autograd backward.
+ *
+ *   D[M,N] = epilogue( A[M,K] · B[N,K]^T ),  epilogue = (+bias[n]) → (ReLU) → (·[Z[m,n] > 0])
+ *
+ * A, B, D, Z row-major fp32 with row pitches lda/ldb/ldd/ldz in floats
+ * (multiples of 4; base pointers 16-byte aligned), N <= 256.  TF32 tensor-core
+ * products (tcgen05, fp32 accumulation in TMEM).  Forward layer: B = weight
+ * [out,in], bias, relu=1.  Backward data gradient: A = dZ, B = weight^T, Z =
+ * the layer's (post-ReLU) input, which applies the ReLU derivative in the
+ * epilogue.  bias / Z may be NULL.
+ * ---------------------------------------------------------------------- */
+TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const float* B, int ldb, float* D, int ldd, int M, int N,
+                                   int K, const float* bias, int relu, const float* Z, int ldz, void* stream);
+
 /* The same sort for callers that cannot allocate device memory.  It has no
  * counterpart in the reference (which sizes a CUB temp buffer and has torch
  * allocate it on every call, DGR/rasterize_points.cu:30-38).
