@@ -279,7 +279,9 @@ def run_ours(args, rank, world, device):
     if not os.path.exists(_lib.LIB_PATH):
         tb_build.build()
     _lib.load()  # fails loudly when the CUDA library is missing: there is no fallback
-    wl = Workload(args.workload, device, rank, mlp_backend=args.mlp)
+    if args.mlp == "torch-tf32":
+        torch.backends.cuda.matmul.allow_tf32 = True
+    wl = Workload(args.workload, device, rank, mlp_backend="native" if args.mlp == "native" else "torch")
     cfg = wl.cfg
     step = lambda: wl.step_resident(world)
     sampler = ClockSampler(device.index) if rank == 0 else None
@@ -386,7 +388,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="neu3d", choices=list(WORKLOADS))
-    ap.add_argument("--mlp", default=os.environ.get("TRASE_B200_MLP", "torch"), choices=["torch", "native"])
+    ap.add_argument("--mlp", default=os.environ.get("TRASE_B200_MLP", "torch"), choices=["torch", "torch-tf32", "native"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -239,10 +239,31 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
  * products (tcgen05, fp32 accumulation in TMEM).  Forward layer: B = weight
  * [out,in], bias, relu=1.  Backward data gradient: A = dZ, B = weight^T, Z =
  * the layer's (post-ReLU) input, which applies the ReLU derivative in the
- * epilogue.  bias / Z may be NULL.
+ * epilogue; colsum[n] += sum_m D[m,n] then yields the bias gradient of the
+ * previous layer for free.  bias / Z / colsum may be NULL.  round_tf32 != 0
+ * rounds D to TF32 (nearest) on the way out: the tensor core truncates fp32
+ * operands to TF32, so a chain of layers stays at round-to-nearest accuracy
+ * when every producer rounds (the embedding kernel below does the same).
  * ---------------------------------------------------------------------- */
 TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const float* B, int ldb, float* D, int ldd, int M, int N,
-                                   int K, const float* bias, int relu, const float* Z, int ldz, void* stream);
+                                   int K, const float* bias, int relu, const float* Z, int ldz, float* colsum,
+                                   int round_tf32, void* stream);
+
+/* Positional encoding of (xyz, t) — ref: Embedder.embed (utils/time_utils.py:27-57)
+ * and the torch.cat at utils/time_utils.py:110 — written into columns
+ * [0, 3+6*Lx+1+2*Lt) of the row-major buffer out[M][ld].  t_stride = 0 broadcasts
+ * one time stamp to every row, t_stride = 1 reads t[m]. */
+TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt,
+                                      float* out, int ld, void* stream);
+
+/* Weight gradient of one nn.Linear: D[i][j] += sum_m P[m][i] * Q[m][j]
+ * (dW = dZ^T X; ref: autograd backward of utils/time_utils.py:113, cuBLAS SGEMM
+ * in the reference).  P [M][I], Q [M][J], D [I][J] row-major fp32; I, J <= 256,
+ * J a multiple of 4.  D is ACCUMULATED into (zero it first).  TF32 tcgen05
+ * products read both operands straight from the row-major activations
+ * (MN-major descriptors), the row range is split over the SMs. */
+TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, const float* Q, int ldq, int J, int M, float* D,
+                                    int ldd, void* stream);
 
 /* The same sort for callers that cannot allocate device memory.  It has no
  * counterpart in the reference (which sizes a CUB temp buffer and has torch

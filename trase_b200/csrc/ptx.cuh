@@ -134,13 +134,16 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 // ---- descriptors -----------------------------------------------------------------
 // Shared-memory matrix descriptor (sm_100): start address, leading / stride byte
 // offsets (all >> 4), version 1, layout type 2 = 128-byte swizzle.
-__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout_type: 2 = SWIZZLE_128B, 1 = SWIZZLE_128B with 32-byte atoms (the only
+// layout the tensor core accepts for MN-major TF32 operands).
+__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                         uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;
   return d;
 }
 // Instruction descriptor for kind::tf32 with fp32 accumulation.
