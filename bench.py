@@ -388,7 +388,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="neu3d", choices=list(WORKLOADS))
-    ap.add_argument("--mlp", default=os.environ.get("TRASE_B200_MLP", "torch"), choices=["torch", "torch-tf32", "native"])
+    ap.add_argument("--mlp", default=os.environ.get("TRASE_B200_MLP", "native"), choices=["torch", "torch-tf32", "native"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -232,22 +232,26 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
  * DeformNetwork.forward (utils/time_utils.py:106-131), which the reference runs
  * as cuBLAS SGEMM + separate bias/ReLU kernels, and their autograd backward.
  *
- *   D[M,N] = epilogue( A[M,K] · B[N,K]^T ),  epilogue = (+bias[n]) → (ReLU) → (·[Z[m,n] > 0])
+ *   D[M,N] = epilogue( A[M,K] · B[N,K]^T ),  epilogue = (+bias[n]) → (ReLU) → (· mask_in bit)
  *
- * A, B, D, Z row-major fp32 with row pitches lda/ldb/ldd/ldz in floats
- * (multiples of 4; base pointers 16-byte aligned), N <= 256.  TF32 tensor-core
- * products (tcgen05, fp32 accumulation in TMEM).  Forward layer: B = weight
- * [out,in], bias, relu=1.  Backward data gradient: A = dZ, B = weight^T, Z =
- * the layer's (post-ReLU) input, which applies the ReLU derivative in the
- * epilogue; colsum[n] += sum_m D[m,n] then yields the bias gradient of the
- * previous layer for free.  bias / Z / colsum may be NULL.  round_tf32 != 0
- * rounds D to TF32 (nearest) on the way out: the tensor core truncates fp32
- * operands to TF32, so a chain of layers stays at round-to-nearest accuracy
- * when every producer rounds (the embedding kernel below does the same).
+ * A, B, D row-major fp32 with row pitches lda/ldb/ldd in floats (multiples of
+ * 4; base pointers 16-byte aligned), N <= 256.  TF32 tensor-core products
+ * (tcgen05, fp32 accumulation in TMEM).
+ *   Forward layer: B = weight [out,in], bias, relu=1; mask_out (optional,
+ *   [M][ceil(N/32)] uint32) receives one bit per element, set where the output
+ *   is > 0, so the backward pass never re-reads activations for the ReLU
+ *   derivative.
+ *   Backward data gradient: A = dZ, B = weight^T, mask_in = the bit mask of the
+ *   layer's input; colsum[n] += sum_m D[m,n] yields the bias gradient of the
+ *   previous layer in the same pass.
+ * round_tf32 != 0 rounds D to TF32 (nearest) on the way out: the tensor core
+ * truncates fp32 operands to TF32, so a chain of layers stays at
+ * round-to-nearest accuracy when every producer rounds.  bias, mask_in,
+ * mask_out and colsum may be NULL.
  * ---------------------------------------------------------------------- */
 TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const float* B, int ldb, float* D, int ldd, int M, int N,
-                                   int K, const float* bias, int relu, const float* Z, int ldz, float* colsum,
-                                   int round_tf32, void* stream);
+                                   int K, const float* bias, int relu, const uint32_t* mask_in, uint32_t* mask_out,
+                                   float* colsum, int round_tf32, void* stream);
 
 /* Positional encoding of (xyz, t) — ref: Embedder.embed (utils/time_utils.py:27-57)
  * and the torch.cat at utils/time_utils.py:110 — written into columns

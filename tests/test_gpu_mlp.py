@@ -12,15 +12,15 @@ def tf32_trunc(x):
     return (x.view(torch.int32) & ~0x1FFF).view(torch.float32)
 
 
-def run_gemm(native_lib, A, B, bias=None, relu=False, Z=None, D=None, colsum=None):
+def run_gemm(native_lib, A, B, bias=None, relu=False, mask_in=None, mask_out=None, D=None, colsum=None):
     M, K = A.shape
     N = B.shape[0]
     if D is None:
         D = torch.full((M, ((N + 3) // 4) * 4), float("nan"), device=A.device)[:, :N]
     rc = native_lib.trase_b200_gemm_tf32(A.data_ptr(), A.stride(0), B.data_ptr(), B.stride(0), D.data_ptr(),
                                          D.stride(0), M, N, K, bias.data_ptr() if bias is not None else None,
-                                         int(relu), Z.data_ptr() if Z is not None else None,
-                                         Z.stride(0) if Z is not None else 0,
+                                         int(relu), mask_in.data_ptr() if mask_in is not None else None,
+                                         mask_out.data_ptr() if mask_out is not None else None,
                                          colsum.data_ptr() if colsum is not None else None, 0,
                                          torch.cuda.current_stream().cuda_stream)
     assert rc == 0, native_lib.trase_b200_last_error()
@@ -54,17 +54,20 @@ def test_gemm_bias_relu_mask_and_strided_output(native_lib):
     A = torch.randn(M, K, device=DEV, generator=g)
     B = torch.randn(N, K, device=DEV, generator=g) * 0.1
     bias = torch.randn(N, device=DEV, generator=g)
-    Z = torch.randn(M, N, device=DEV, generator=g)
     ref = A @ B.T + bias
-    D = run_gemm(native_lib, A, B, bias=bias, relu=True)
+    mk = torch.zeros(M, N // 32, dtype=torch.int32, device=DEV)
+    D = run_gemm(native_lib, A, B, bias=bias, relu=True, mask_out=mk)
     assert (D - torch.relu(ref)).abs().max() <= 2e-2
     assert (D >= 0).all()
+    # the bit mask says exactly where the written output is positive
+    bits = ((mk.unsqueeze(-1) >> torch.arange(32, device=DEV, dtype=torch.int32)) & 1).reshape(M, N).bool()
+    assert torch.equal(bits, D > 0)
     cs = torch.zeros(N, device=DEV)
-    D = run_gemm(native_lib, A, B, Z=Z, colsum=cs)
-    want = (A @ B.T) * (Z > 0)
-    assert (D - want).abs().max() <= 2e-2
-    assert (cs - D.sum(0)).abs().max() <= 1e-3 * D.abs().sum(0).max()
-    assert (D[Z <= 0] == 0).all()
+    D2 = run_gemm(native_lib, A, B, mask_in=mk, colsum=cs)
+    want = (A @ B.T) * bits
+    assert (D2 - want).abs().max() <= 2e-2
+    assert (D2[~bits] == 0).all()
+    assert (cs - D2.sum(0)).abs().max() <= 1e-3 * D2.abs().sum(0).max()
     # output written into columns [84:340] of a wider buffer (the skip-connection layout)
     wide = torch.zeros(M, 340, device=DEV)
     run_gemm(native_lib, A, B, bias=bias, relu=True, D=wide[:, 84:340])

@@ -22,13 +22,14 @@ def tf32_round(w: torch.Tensor) -> torch.Tensor:
     return ((w.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
 
 
-def _gemm(lib, A, B, D, bias=None, relu=False, Z=None, colsum=None, round_tf32=True):
+def _gemm(lib, A, B, D, bias=None, relu=False, mask_in=None, mask_out=None, colsum=None, round_tf32=True):
     M, K = A.shape
     N = B.shape[0]
     _lib.check(lib.trase_b200_gemm_tf32(
         A.data_ptr(), A.stride(0), B.data_ptr(), B.stride(0), D.data_ptr(), D.stride(0), M, N, K,
-        bias.data_ptr() if bias is not None else None, int(relu), Z.data_ptr() if Z is not None else None,
-        Z.stride(0) if Z is not None else 0, colsum.data_ptr() if colsum is not None else None, int(round_tf32),
+        bias.data_ptr() if bias is not None else None, int(relu),
+        mask_in.data_ptr() if mask_in is not None else None, mask_out.data_ptr() if mask_out is not None else None,
+        colsum.data_ptr() if colsum is not None else None, int(round_tf32),
         torch.cuda.current_stream(A.device).cuda_stream))
 
 
@@ -65,12 +66,14 @@ class _DeformMLP(torch.autograd.Function):
                                                    skipbuf.stride(0), torch.cuda.current_stream(dev).cuda_stream))
             emb = skipbuf[:, :E]
             Wr = [tf32_round(w.detach()) for w in Ws]
-            acts = []
+            acts, masks = [], []
             inp = emb
             for i in range(nl):
                 out = skipbuf[:, E:] if i == skip else torch.empty((M, W), **f32)
-                _gemm(lib, inp, Wr[i], out, bias=bs[i].detach(), relu=True)
+                mk = torch.empty((M, W // 32), dtype=torch.int32, device=dev)
+                _gemm(lib, inp, Wr[i], out, bias=bs[i].detach(), relu=True, mask_out=mk)
                 acts.append(out)
+                masks.append(mk)
                 inp = skipbuf if i == skip else out
             # the three heads as one [16, W] GEMM (10 real rows)
             wh = torch.zeros((16, W), **f32)
@@ -80,7 +83,7 @@ class _DeformMLP(torch.autograd.Function):
             out16 = torch.empty((M, 16), **f32)
             wh = tf32_round(wh)
             _gemm(lib, acts[-1], wh, out16, bias=bh, round_tf32=False)
-        ctx.save_for_backward(skipbuf, wh, *acts, *Wr)
+        ctx.save_for_backward(skipbuf, wh, *acts, *Wr, *masks)
         ctx.meta = (nl, skip, E, M)
         return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
 
@@ -92,6 +95,7 @@ class _DeformMLP(torch.autograd.Function):
         skipbuf, wh = saved[0], saved[1]
         acts = saved[2:2 + nl]
         Ws = saved[2 + nl:2 + 2 * nl]
+        masks = saved[2 + 2 * nl:2 + 3 * nl]
         dev = skipbuf.device
         f32 = dict(dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
@@ -112,7 +116,7 @@ class _DeformMLP(torch.autograd.Function):
             # dZ_{nl-1} = (dout Wh) * relu'(h_last)
             dz = torch.empty((M, W), **f32)
             db = torch.zeros((W,), **f32)
-            _gemm(lib, dout, wh.t().contiguous(), dz, Z=acts[-1], colsum=db)
+            _gemm(lib, dout, wh.t().contiguous(), dz, mask_in=masks[-1], colsum=db)
             for i in range(nl - 1, -1, -1):
                 grads_b[i] = db
                 inp = skipbuf[:, :E] if i == 0 else (skipbuf if i - 1 == skip else acts[i - 1])
@@ -123,7 +127,7 @@ class _DeformMLP(torch.autograd.Function):
                     wt = Ws[i][:, E:] if i - 1 == skip else Ws[i]      # only the hidden part carries gradient
                     dz_prev = torch.empty((M, W), **f32)
                     db = torch.zeros((W,), **f32)
-                    _gemm(lib, dz, wt.t().contiguous(), dz_prev, Z=acts[i - 1], colsum=db)
+                    _gemm(lib, dz, wt.t().contiguous(), dz_prev, mask_in=masks[i - 1], colsum=db)
                     dz = dz_prev
             dwh = dwhT.t()
             out = [None, None, None, None, None]

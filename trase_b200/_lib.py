@@ -117,7 +117,7 @@ def load() -> C.CDLL:
                                                  C.c_int64, C.c_int, C.c_void_p]
     lib.trase_b200_gemm_tf32.restype = C.c_int
     lib.trase_b200_gemm_tf32.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
-                                         C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+                                         C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     lib.trase_b200_wgrad_tf32.restype = C.c_int
     lib.trase_b200_wgrad_tf32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                           C.c_void_p, C.c_int, C.c_void_p]

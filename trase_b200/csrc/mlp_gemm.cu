@@ -2,15 +2,17 @@
 // eleven nn.Linear layers evaluated by cuBLAS SGEMM on CUDA cores).
 //
 //   gemm_tn :  D[M,N] = epilogue( A[M,K] · B[N,K]^T )      A, B row-major (K contiguous)
-//              epilogue: (+ bias[n]) -> (ReLU) -> (· [Z[m,n] > 0])
-//     forward  layer : A = activations, B = weight [out,in], bias, ReLU
-//     backward dgrad : A = dZ [M,out], B = weight^T [in,out], mask Z = the layer input (post-ReLU)
+//              epilogue: (+ bias[n]) -> (ReLU) -> (· mask bit) ; side outputs: ReLU bit mask, column sums
+//     forward  layer : A = activations, B = weight [out,in], bias, ReLU, writes 1 bit/element (output > 0)
+//     backward dgrad : A = dZ [M,out], B = weight^T [in,out], mask = that bit mask of the layer input,
+//                      column sums = bias gradient of the previous layer
 //
 // Blackwell structure: persistent CTAs (one per SM), TMA 128-byte-swizzled tiles
-// into a 4-stage shared-memory ring, a single elected thread issues
+// into a 3-stage shared-memory ring, a single elected thread issues
 // tcgen05.mma.kind::tf32 (128 x BN x 8) with the fp32 accumulator in TMEM
 // (double-buffered: 2 x BN columns), four epilogue warps drain TMEM with
-// tcgen05.ld, apply the epilogue and write 128x32 slabs back with TMA stores,
+// tcgen05.ld, apply the epilogue, transpose 32x32 sub-slabs through swizzled shared memory and
+// write full 128-byte lines,
 // overlapping the next tile's MMAs.  K and M tails are handled by TMA
 // zero-fill / clipping, so no operand is ever padded in memory.
 #include "common.cuh"
@@ -24,70 +26,89 @@ using namespace ptx;
 constexpr int BM = 128;          // rows per tile (= TMEM lanes)
 constexpr int BK = 32;           // tf32 elements per k-block = one 128-byte swizzle row
 constexpr int UMMA_K = 8;        // tf32 elements per tcgen05.mma
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;
 constexpr int SLAB = 32;         // output columns per epilogue slab
-constexpr int GEMM_THREADS = 256;
+constexpr int EPI_WARPS = 8;      // two warps per TMEM lane quarter, alternating slabs: hides TMEM/LDS/TMA-store latency
+constexpr int GEMM_THREADS = 128 + 32 * EPI_WARPS;
 
 struct GemmEpilogue {
   const float* bias;  // [N] or null
   int relu;
-  int use_mask;       // multiply by (Z > 0), Z read through tmZ
+  const uint32_t* mask_in;   // [M][N/32] bit j of word s: keep column 32s+j (ReLU derivative), or null
+  uint32_t* mask_out;        // [M][N/32] written as (output > 0), or null
   float* colsum;      // [N] or null: += column sums of the written values (bias gradient)
+  float* D; int ldd;  // output, row pitch in floats
+  int prefetch_tiles; // L2 prefetch distance of the activation stream, in tiles per CTA
   int round_tf32;     // round outputs to TF32 (nearest) so the next GEMM's operand truncation is exact
   int M, N, K;
 };
 
-template <int BN>
+constexpr int RES_MAX_KB = 8;     // resident-B variant: whole K (<= 256) of the weight half stays in smem
+
+// RES = true: the CTA owns one 128-column half of the output, keeps that half of the weight matrix
+// resident in shared memory for its whole lifetime and streams only activation tiles — the weight
+// re-fetch from L2 (twice the activation traffic in the streaming variant) disappears.
+template <int BN, bool RES>
 struct GemmSmem {
   static constexpr int A_BYTES = BM * BK * 4;       // 16 KB
-  static constexpr int B_BYTES = BN * BK * 4;       // 32 KB (BN = 256)
+  static constexpr int B_BYTES = BN * BK * 4;       // one k-block of B: 32 KB (BN = 256), 16 KB (BN = 128)
   static constexpr int OUT_BYTES = BM * SLAB * 4;   // 16 KB
   static constexpr int OFF_A = 0;
   static constexpr int OFF_B = OFF_A + STAGES * A_BYTES;
-  static constexpr int OFF_OUT = OFF_B + STAGES * B_BYTES;
-  static constexpr int OFF_BIAS = OFF_OUT + 2 * OUT_BYTES;
-  static constexpr int OFF_BAR = OFF_BIAS + (BN < 32 ? 32 : BN) * 4;
+  static constexpr int OFF_OUT = OFF_B + (RES ? RES_MAX_KB : STAGES) * B_BYTES;
+  static constexpr int OFF_BIAS = OFF_OUT + EPI_WARPS * 4096;   // per epilogue warp: 32 rows x 128 B staging
+  static constexpr int OFF_COL = OFF_BIAS + (BN < 32 ? 32 : BN) * 4;   // [4 warps][BN] bias-gradient partial sums
+  static constexpr int OFF_BAR = OFF_COL + 4 * (BN < 32 ? 32 : BN) * 4;
   static constexpr int TOTAL = OFF_BAR + 256 + 1024;  // barriers + slack for 1024-byte alignment
 };
 
-template <int BN>
+template <int BN, bool RES>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmZ,
                     const GemmEpilogue ep) {
-  using L = GemmSmem<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  using L = GemmSmem<BN, RES>;
+  // 1024-byte alignment (128-byte swizzle atoms) comes from the declaration: aligning the pointer
+  // by integer arithmetic would hide the shared address space from the compiler and turn every
+  // LDS/STS of the epilogue into a generic LD/ST.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
   uint8_t* sA = smem + L::OFF_A;
   uint8_t* sB = smem + L::OFF_B;
   uint8_t* sOut = smem + L::OFF_OUT;
   float* sBias = reinterpret_cast<float*>(smem + L::OFF_BIAS);
+  float* sCol = reinterpret_cast<float*>(smem + L::OFF_COL);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::OFF_BAR);
   uint64_t* full = bars;                   // [STAGES]  TMA -> MMA
   uint64_t* empty = bars + STAGES;         // [STAGES]  MMA -> TMA
   uint64_t* tmem_full = bars + 2 * STAGES; // [2]       MMA -> epilogue
   uint64_t* tmem_empty = tmem_full + 2;    // [2]       epilogue -> MMA
-  uint64_t* zbar = tmem_empty + 2;         // [2]       mask tile landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(zbar + 2);
+  uint64_t* bfull = tmem_empty + 2;        // [1]       resident B landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = (ep.M + BM - 1) / BM;
   const int num_kb = (ep.K + BK - 1) / BK;
+  // RES: even CTAs own output columns [0,128), odd CTAs [128,256); both walk the same row tiles
+  const int n_off = RES ? (int)(blockIdx.x & 1) * BN : 0;
+  const int tile0 = RES ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_step = RES ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   constexpr uint32_t TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // power of two >= 32 (BN = 16 -> 32, 256 -> 512)
 
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmA); prefetch_tmap(&tmB); prefetch_tmap(&tmD);
-    if (ep.use_mask) prefetch_tmap(&tmZ);
+    prefetch_tmap(&tmA); prefetch_tmap(&tmB);
     for (int i = 0; i < STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); mbar_init(&zbar[i], 1); }
+    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], EPI_WARPS); }
+    mbar_init(bfull, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
-  for (int i = threadIdx.x; i < (BN < 32 ? 32 : BN); i += GEMM_THREADS) sBias[i] = (ep.bias && i < ep.N) ? ep.bias[i] : 0.f;
+  for (int i = threadIdx.x; i < (BN < 32 ? 32 : BN); i += GEMM_THREADS) sBias[i] = (ep.bias && n_off + i < ep.N) ? ep.bias[n_off + i] : 0.f;
+  for (int i = threadIdx.x; i < 4 * (BN < 32 ? 32 : BN); i += GEMM_THREADS) sCol[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -97,12 +118,26 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ===== TMA producer =====
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      if (RES) {
+        mbar_expect_tx(bfull, num_kb * L::B_BYTES);
+        for (int kb = 0; kb < num_kb; kb++) tma_load_2d(sB + kb * L::B_BYTES, &tmB, bfull, kb * BK, n_off);
+      }
+      // The smem ring only holds ~1 us of activations; HBM latency under load is longer than that, so
+      // the tiles this CTA will need `pf` iterations from now are pulled into L2 first (TMA prefetch).
+      const int pf = ep.prefetch_tiles;
+      for (int i = 0; i < pf; i++) {
+        const int t = tile0 + i * tile_step;
+        if (t < num_tiles)
+          for (int kb = 0; kb < num_kb; kb++) tma_prefetch_l2_2d(&tmA, kb * BK, t * BM);
+      }
+      for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+        const int tpf = tile + pf * tile_step;
         for (int kb = 0; kb < num_kb; kb++) {
+          if (pf && tpf < num_tiles) tma_prefetch_l2_2d(&tmA, kb * BK, tpf * BM);
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], L::A_BYTES + L::B_BYTES);
+          mbar_expect_tx(&full[stage], RES ? L::A_BYTES : L::A_BYTES + L::B_BYTES);
           tma_load_2d(sA + stage * L::A_BYTES, &tmA, &full[stage], kb * BK, tile * BM);
-          tma_load_2d(sB + stage * L::B_BYTES, &tmB, &full[stage], kb * BK, 0);
+          if (!RES) tma_load_2d(sB + stage * L::B_BYTES, &tmB, &full[stage], kb * BK, 0);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -113,7 +148,8 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       constexpr uint32_t idesc = make_idesc_tf32(BM, BN, 0, 0);
       uint32_t stage = 0, phase = 0;
       uint32_t acc = 0, acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      if (RES) mbar_wait(bfull, 0);
+      for (int tile = tile0; tile < num_tiles; tile += tile_step) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
@@ -121,7 +157,7 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(sA + stage * L::A_BYTES);
-          const uint32_t b_addr = smem_u32(sB + stage * L::B_BYTES);
+          const uint32_t b_addr = smem_u32(sB + (RES ? kb : (int)stage) * L::B_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; k++) {
             // K-major, 128-byte swizzle: rows are 128 B apart, 8-row groups 1024 B apart;
@@ -138,32 +174,27 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue: 4 warps, warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 =====
+    // ===== epilogue: 4 independent warps; warp (w & 3) owns TMEM lanes / tile rows 32*(w&3) .. +31,
+    // stages its own 32x32 sub-slab (4 KB, 128-byte swizzled) and stores it with its own TMA store,
+    // so the warps never synchronise with each other =====
     const int ew = warp & 3;
-    const int row = ew * 32 + lane;        // row inside the tile
-    const int et = threadIdx.x - 128;      // 0..127
+    const int eh = (warp - 4) >> 2;           // which half of the slabs this warp takes
+    constexpr int CW = (BN < 32 ? 32 : BN);
+    uint8_t* out = sOut + (warp - 4) * 4096;
+    float* sColW = sCol + ew * CW;
     uint32_t acc = 0, acc_phase = 0;
-    uint32_t zphase[2] = {0, 0};
-    uint32_t slab_counter = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    constexpr int NSLAB = (BN + SLAB - 1) / SLAB;
+    const int words = (ep.N + 31) >> 5;      // mask words per row
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      constexpr int NSLAB = (BN + SLAB - 1) / SLAB;
-      for (int s = 0; s < NSLAB; s++) {
-        if (s * SLAB >= ep.N) break;
-        const uint32_t buf = slab_counter & 1;
-        uint8_t* out = sOut + buf * L::OUT_BYTES;
-        // the TMA store that last read this buffer (two slabs ago) must have finished reading it
-        if (et == 0) tma_store_wait_read<1>();
-        named_bar_sync(1, 128);
-        if (ep.use_mask) {
-          if (et == 0) {
-            mbar_expect_tx(&zbar[buf], L::OUT_BYTES);
-            tma_load_2d(out, &tmZ, &zbar[buf], s * SLAB, tile * BM);
-          }
-          mbar_wait(&zbar[buf], zphase[buf]);
-          zphase[buf] ^= 1;
-        }
+      const int grow = tile * BM + ew * 32 + lane;   // global row of this thread
+#pragma unroll 1
+      for (int s = eh; s < NSLAB; s += EPI_WARPS / 4) {
+        if (n_off + s * SLAB >= ep.N) break;
+        const int ws = (n_off >> 5) + s;            // mask word / global slab index
+        uint32_t keep = 0xffffffffu;
+        if (ep.mask_in) keep = (grow < ep.M) ? __ldg(ep.mask_in + (size_t)grow * words + ws) : 0u;
         uint32_t v[32];
         constexpr int W = (BN < SLAB) ? BN : SLAB;  // columns actually present in this slab
         if constexpr (W == 32) {
@@ -174,46 +205,69 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int i = 0; i < 16; i++) { v[i] = v16[i]; v[i + 16] = 0; }
         }
+        // bias of this slab, fetched while the TMEM load is in flight
+        float4 bq[8];
+#pragma unroll
+        for (int c = 0; c < 8; c++) bq[c] = *reinterpret_cast<const float4*>(sBias + s * SLAB + c * 4);
         tmem_ld_wait();
-        // 128-byte swizzled staging tile: element (row, 16-byte chunk c) at row*128 + ((c ^ (row & 7)) << 4)
+        __syncwarp();
+        uint32_t pos = 0;
+        // element (row = lane, 16-byte chunk c) lives at lane*128 + ((c ^ (lane & 7)) << 4)
 #pragma unroll
         for (int c = 0; c < 8; c++) {
+          const float bb[4] = {bq[c].x, bq[c].y, bq[c].z, bq[c].w};
           float4 o;
           float* of = reinterpret_cast<float*>(&o);
-          float4* dst = reinterpret_cast<float4*>(out + row * 128 + ((c ^ (row & 7)) << 4));
-          float4 z = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (ep.use_mask) z = *dst;
-          const float* zf = reinterpret_cast<const float*>(&z);
 #pragma unroll
           for (int j = 0; j < 4; j++) {
-            float x = __uint_as_float(v[c * 4 + j]) + sBias[s * SLAB + c * 4 + j];
+            float x = __uint_as_float(v[c * 4 + j]) + bb[j];
             if (ep.relu) x = fmaxf(x, 0.f);
-            if (ep.use_mask) x = (zf[j] > 0.f) ? x : 0.f;
+            if (!((keep >> (c * 4 + j)) & 1u)) x = 0.f;
             if (ep.round_tf32) {
               uint32_t u;
               asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
               x = __uint_as_float(u);
             }
+            pos |= (x > 0.f ? 1u : 0u) << (c * 4 + j);
             of[j] = x;
           }
-          *dst = o;
+          *reinterpret_cast<float4*>(out + lane * 128 + ((c ^ (lane & 7)) << 4)) = o;
         }
-        fence_proxy_async_smem();
-        named_bar_sync(1, 128);
-        if (et == 0) {
-          tma_store_2d(&tmD, out, s * SLAB, tile * BM);
-          tma_store_commit();
+        if (ep.mask_out && grow < ep.M) ep.mask_out[(size_t)grow * words + ws] = pos;
+        __syncwarp();
+        // copy-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction -> full-line stores
+        {
+          const int chunk = lane & 7;
+          const int col0 = n_off + s * SLAB + chunk * 4;
+#pragma unroll
+          for (int it = 0; it < 8; it++) {
+            const int r = it * 4 + (lane >> 3);
+            const float4 val = *reinterpret_cast<const float4*>(out + r * 128 + ((chunk ^ (r & 7)) << 4));
+            const int gr = tile * BM + ew * 32 + r;
+            if (gr < ep.M && col0 < ep.N) {
+              float* dst = ep.D + (size_t)gr * ep.ldd + col0;
+              if (col0 + 3 < ep.N) {
+                *reinterpret_cast<float4*>(dst) = val;
+              } else {
+                const float vv[4] = {val.x, val.y, val.z, val.w};
+                for (int j = 0; j < 4 && col0 + j < ep.N; j++) dst[j] = vv[j];
+              }
+            }
+          }
         }
         if (ep.colsum) {
-          // bias gradient: thread (g, c) sums column c over rows 32g..32g+31 of the staged slab
-          const int c = et & 31, g = et >> 5;
-          float acc_c = 0.f;
-#pragma unroll 8
-          for (int r = g * 32; r < g * 32 + 32; r++)
-            acc_c += *reinterpret_cast<const float*>(out + r * 128 + (((c >> 2) ^ (r & 7)) << 4) + ((c & 3) << 2));
-          if (s * SLAB + c < ep.N) atomicAdd(ep.colsum + s * SLAB + c, acc_c);
+          // bias gradient: lane c sums column c over this warp's 32 staged rows
+          float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+          for (int r = 0; r < 32; r += 4) {
+            a0 += *reinterpret_cast<const float*>(out + (r + 0) * 128 + (((lane >> 2) ^ ((r + 0) & 7)) << 4) + ((lane & 3) << 2));
+            a1 += *reinterpret_cast<const float*>(out + (r + 1) * 128 + (((lane >> 2) ^ ((r + 1) & 7)) << 4) + ((lane & 3) << 2));
+            a2 += *reinterpret_cast<const float*>(out + (r + 2) * 128 + (((lane >> 2) ^ ((r + 2) & 7)) << 4) + ((lane & 3) << 2));
+            a3 += *reinterpret_cast<const float*>(out + (r + 3) * 128 + (((lane >> 2) ^ ((r + 3) & 7)) << 4) + ((lane & 3) << 2));
+          }
+          sColW[s * SLAB + lane] += (a0 + a1) + (a2 + a3);
         }
-        slab_counter++;
+        __syncwarp();   // staging buffer is rewritten by the next slab
       }
       // all TMEM reads of this accumulator are done: hand it back to the MMA warp
       tc_fence_before();
@@ -221,7 +275,11 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    if (et == 0) tma_store_wait<0>();
+    if (ep.colsum) {
+      // each warp flushes the columns of the slabs it owned
+      for (int s = eh; s < NSLAB; s += EPI_WARPS / 4)
+        if (n_off + s * SLAB + lane < ep.N) atomicAdd(ep.colsum + n_off + s * SLAB + lane, sColW[s * SLAB + lane]);
+    }
   }
 
   tc_fence_before();
@@ -260,6 +318,8 @@ bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t col
   return r == CUDA_SUCCESS;
 }
 
+int g_prefetch_tiles = 0;    // tuning switch ("gemm_prefetch")
+int g_allow_resident = 1;   // tuning switch (trase_b200_set_tuning "gemm_resident")
 static int g_num_sms = 0;
 static int num_sms() {
   if (!g_num_sms) {
@@ -271,19 +331,25 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int BN>
-static cudaError_t launch_gemm_tn(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
-                                  const CUtensorMap& tZ, const GemmEpilogue& ep, cudaStream_t s) {
+template <int BN, bool RES>
+static cudaError_t launch_gemm_tn(const CUtensorMap& tA, const CUtensorMap& tB, const GemmEpilogue& ep,
+                                  cudaStream_t s) {
   static bool attr_set = false;
-  const int smem = GemmSmem<BN>::TOTAL;
+  const int smem = GemmSmem<BN, RES>::TOTAL;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tn_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e =
+        cudaFuncSetAttribute(gemm_tn_tf32_kernel<BN, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   const int tiles = (ep.M + BM - 1) / BM;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tn_tf32_kernel<BN><<<grid, GEMM_THREADS, smem, s>>>(tA, tB, tD, tZ, ep);
+  int grid;
+  if (RES) {
+    grid = 2 * tiles < num_sms() ? 2 * tiles : (num_sms() & ~1);   // CTA pairs: (row tile walker, column half)
+  } else {
+    grid = tiles < num_sms() ? tiles : num_sms();
+  }
+  gemm_tn_tf32_kernel<BN, RES><<<grid, GEMM_THREADS, smem, s>>>(tA, tB, ep);
   return cudaGetLastError();
 }
 
@@ -292,34 +358,36 @@ static cudaError_t launch_gemm_tn(const CUtensorMap& tA, const CUtensorMap& tB, 
 
 using namespace tb;
 
-// D[M,N] = epilogue(A[M,K] · B[N,K]^T); lda/ldb/ldd/ldz are row pitches in floats (multiples of 4),
-// all base pointers 16-byte aligned.  N <= 256.  colsum (optional) accumulates the column sums of D.
+// D[M,N] = epilogue(A[M,K] · B[N,K]^T); lda/ldb/ldd are row pitches in floats (multiples of 4), all base
+// pointers 16-byte aligned, N <= 256.  mask_in / mask_out: [M][ceil(N/32)] bit masks (ReLU derivative).
 extern "C" TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const float* B, int ldb, float* D, int ldd,
-                                              int M, int N, int K, const float* bias, int relu, const float* Z,
-                                              int ldz, float* colsum, int round_tf32, void* stream) {
+                                              int M, int N, int K, const float* bias, int relu,
+                                              const uint32_t* mask_in, uint32_t* mask_out, float* colsum,
+                                              int round_tf32, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0 || N > 256 || !A || !B || !D) {
     set_error("trase_b200_gemm_tf32: bad arguments (M=%d N=%d K=%d)", M, N, K);
     return 1;
   }
-  if ((lda & 3) || (ldb & 3) || (ldd & 3) || (Z && (ldz & 3)) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) ||
-      ((uintptr_t)D & 15) || ((uintptr_t)Z & 15)) {
+  if ((lda & 3) || (ldb & 3) || (ldd & 3) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) || ((uintptr_t)D & 15)) {
     set_error("trase_b200_gemm_tf32: pointers must be 16-byte aligned and row pitches multiples of 4 floats");
     return 1;
   }
   const bool small = N <= 16;
-  CUtensorMap tA, tB, tD, tZ;
-  bool ok = mlp::make_tmap_2d(&tA, A, M, K, lda, mlp::BM, mlp::BK) &&
-            mlp::make_tmap_2d(&tB, B, N, K, ldb, small ? 16 : 256, mlp::BK) &&
-            mlp::make_tmap_2d(&tD, D, M, N, ldd, mlp::BM, mlp::SLAB);
-  if (ok) ok = Z ? mlp::make_tmap_2d(&tZ, Z, M, N, ldz, mlp::BM, mlp::SLAB) : mlp::make_tmap_2d(&tZ, D, M, N, ldd, mlp::BM, mlp::SLAB);
+  const bool resident = false;  // the resident-weights variant measured slower (the epilogue, not L2, is the limiter)
+  CUtensorMap tA, tB;
+  const bool ok = mlp::make_tmap_2d(&tA, A, M, K, lda, mlp::BM, mlp::BK) &&
+                  mlp::make_tmap_2d(&tB, B, N, K, ldb, small ? 16 : (resident ? 128 : 256), mlp::BK);
   if (!ok) {
     set_error("trase_b200_gemm_tf32: cuTensorMapEncodeTiled failed");
     return 2;
   }
   mlp::GemmEpilogue ep;
-  ep.bias = bias; ep.relu = relu; ep.use_mask = Z != nullptr; ep.colsum = colsum; ep.round_tf32 = round_tf32; ep.M = M; ep.N = N; ep.K = K;
-  cudaError_t e = small ? mlp::launch_gemm_tn<16>(tA, tB, tD, tZ, ep, reinterpret_cast<cudaStream_t>(stream))
-                        : mlp::launch_gemm_tn<256>(tA, tB, tD, tZ, ep, reinterpret_cast<cudaStream_t>(stream));
+  ep.bias = bias; ep.relu = relu; ep.mask_in = mask_in; ep.mask_out = mask_out; ep.colsum = colsum;
+  ep.round_tf32 = round_tf32; ep.prefetch_tiles = mlp::g_prefetch_tiles; ep.D = D; ep.ldd = ldd; ep.M = M; ep.N = N; ep.K = K;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  cudaError_t e = small ? mlp::launch_gemm_tn<16, false>(tA, tB, ep, st)
+                        : mlp::launch_gemm_tn<256, false>(tA, tB, ep, st);
+  (void)resident;
   if (e != cudaSuccess) {
     set_error("trase_b200_gemm_tf32: CUDA error: %s", cudaGetErrorString(e));
     return 2;
@@ -347,11 +415,16 @@ struct WgradParams {
   float* D; int ldd;
 };
 
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+constexpr int WG_THREADS = 256;
+__global__ void __launch_bounds__(WG_THREADS, 1)
 wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ,
                   const WgradParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment (128-byte swizzle atoms) comes from the declaration: aligning the pointer
+  // by integer arithmetic would hide the shared address space from the compiler and turn every
+  // LDS/STS of the epilogue into a generic LD/ST.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
   constexpr int OP_BYTES = 8 * WG_BOX_BYTES;            // up to 256 columns per operand = 32 KB
   uint8_t* sP = smem;
   uint8_t* sQ = smem + WG_STAGES * OP_BYTES;
@@ -485,7 +558,7 @@ extern "C" TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, c
   wp.M = M; wp.I = I; wp.J = J; wp.D = D; wp.ldd = ldd;
   const int nblk = (M + mlp::WG_ROWS - 1) / mlp::WG_ROWS;
   const int grid = nblk < mlp::num_sms() ? nblk : mlp::num_sms();
-  mlp::wgrad_tf32_kernel<<<grid, mlp::GEMM_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
+  mlp::wgrad_tf32_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_wgrad_tf32: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   return 0;

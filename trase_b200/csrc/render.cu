@@ -31,6 +31,7 @@
 #include "common.cuh"
 
 namespace tb {
+namespace mlp { extern int g_allow_resident; extern int g_prefetch_tiles; }
 
 struct Tuning {
   int fwd_ppt = 2;
@@ -475,6 +476,8 @@ void set_tuning(const char* key, int value) {
   };
   if (eq(key, "fwd_ppt")) g_tuning.fwd_ppt = value;
   if (eq(key, "bwd_ppt")) g_tuning.bwd_ppt = value;
+  if (eq(key, "gemm_resident")) mlp::g_allow_resident = value;
+  if (eq(key, "gemm_prefetch")) mlp::g_prefetch_tiles = value;
 }
 
 }  // namespace tb
