@@ -120,12 +120,9 @@ class Workload:
         self.bg = torch.zeros(3, device=device)
         self.params = list(self.pc.parameters()) + list(self.deform.parameters())
         # one flat gradient arena; every .grad is a view into it (single memset, single all-reduce)
-        n = sum(p.numel() for p in self.params)
-        self.arena = torch.zeros(n, device=device)
-        off = 0
-        for p in self.params:
-            p.grad = self.arena[off:off + p.numel()].view_as(p)
-            off += p.numel()
+        from trase_b200.distributed import GradArena
+        self.grad_arena = GradArena(self.params)
+        self.arena = self.grad_arena.flat
         # e2e leg: ground-truth image + camera block in pinned host memory
         g = torch.Generator().manual_seed(99 + rank)
         self.gt_host = torch.rand(3, H, W, generator=g).pin_memory()

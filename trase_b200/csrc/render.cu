@@ -52,6 +52,24 @@ __device__ __forceinline__ float splat_power(const float2 xy, const float4 co, f
   return __fmaf_rn(S, -0.5f, -__fmul_rn(__fmul_rn(dx, co.y), dy));
 }
 
+// Conservative half-extents (in pixels) of the axis-aligned box outside of which this splat cannot
+// reach alpha >= 1/255:  o*exp(-q/2) >= 1/255  <=>  q = d^T C d <= 2 ln(255 o), and over that ellipse
+// |dx| <= sqrt(2 ln(255 o) * (C^-1)_xx).  Used only to skip whole (warp, splat) pairs early; the exact
+// per-pixel test still decides every pair that is evaluated, so results are unchanged.
+__device__ __forceinline__ float2 splat_reach(const float4 co) {
+  const float t2 = 2.f * __logf(255.f * co.w);
+  const float det = co.x * co.z - co.y * co.y;
+  if (!(t2 > 0.f)) return make_float2(-1.f, -1.f);            // opacity below 1/255: never blends
+  if (!(det > 0.f) || !isfinite(det)) return make_float2(3.0e38f, 3.0e38f);
+  const float inv = 1.f / det;
+  float2 r;
+  r.x = sqrtf(t2 * co.z * inv) * 1.002f + 0.05f;              // generous margin over fp32 rounding
+  r.y = sqrtf(t2 * co.x * inv) * 1.002f + 0.05f;
+  if (!(r.x == r.x)) r.x = 3.0e38f;
+  if (!(r.y == r.y)) r.y = 3.0e38f;
+  return r;
+}
+
 struct RenderFwdParams {
   const uint2* ranges; const uint32_t* point_list;
   int W, H;
@@ -68,12 +86,16 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
   __shared__ float4 s_co[FWD_BATCH];
   __shared__ float4 s_rgbd[FWD_BATCH];
   __shared__ float4 s_feat[FWD_BATCH * 8];
+  __shared__ float2 s_reach[FWD_BATCH];
 
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
   const uint2 range = q.ranges[tile];
   const int px = blockIdx.x * TILE + (threadIdx.x & 15);
   const int py0 = blockIdx.y * TILE + (threadIdx.x >> 4) * PPT;
   const float pxf = (float)px;
+  // pixel rectangle of this warp: 16 columns x (2*PPT) rows
+  const float wx0 = (float)(blockIdx.x * TILE), wx1 = wx0 + 15.f;
+  const float wy0 = (float)(blockIdx.y * TILE + (threadIdx.x >> 5) * 2 * PPT), wy1 = wy0 + (float)(2 * PPT - 1);
 
   float pyf[PPT], T[PPT], C[PPT][3], D[PPT], O[PPT][NUM_OBJECTS];
   bool done[PPT], inside[PPT];
@@ -99,7 +121,9 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
     for (int k = threadIdx.x; k < n; k += NT) {
       const uint32_t id = q.point_list[base + k];
       s_xy[k] = q.means2D[id];
-      s_co[k] = q.conic_opacity[id];
+      const float4 co = q.conic_opacity[id];
+      s_co[k] = co;
+      s_reach[k] = splat_reach(co);
       s_rgbd[k] = q.rgbd[id];
     }
     for (int e = threadIdx.x; e < n * 8; e += NT) {
@@ -111,6 +135,10 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
     if (!all_done) {
       for (int j = 0; j < n; j++) {
         const float2 xy = s_xy[j];
+        const float2 reach = s_reach[j];
+        // warp-uniform: the splat cannot touch this warp's pixel rectangle
+        if (fmaxf(fmaxf(wx0 - xy.x, xy.x - wx1), 0.f) > reach.x || fmaxf(fmaxf(wy0 - xy.y, xy.y - wy1), 0.f) > reach.y)
+          continue;
         const float4 co = s_co[j];
         float w[PPT];
         bool any = false;
@@ -284,13 +312,14 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 }
 
 template <int PPT>
-__global__ void __launch_bounds__(256 / PPT) render_bwd_kernel(const RenderBwdParams q) {
+__global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel(const RenderBwdParams q) {
   constexpr int NT = 256 / PPT;
   __shared__ uint32_t s_id[BWD_BATCH];
   __shared__ float2 s_xy[BWD_BATCH];
   __shared__ float4 s_co[BWD_BATCH];
   __shared__ float4 s_rgbd[BWD_BATCH];
   __shared__ float4 s_feat[BWD_BATCH * 8];
+  __shared__ float2 s_reach[BWD_BATCH];
   __shared__ uint32_t s_max[NT / 32];
 
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
@@ -300,6 +329,8 @@ __global__ void __launch_bounds__(256 / PPT) render_bwd_kernel(const RenderBwdPa
   const int py0 = blockIdx.y * TILE + (threadIdx.x >> 4) * PPT;
   const float pxf = (float)px;
   const size_t HW = (size_t)q.H * q.W;
+  const float wx0 = (float)(blockIdx.x * TILE), wx1 = wx0 + 15.f;
+  const float wy0 = (float)(blockIdx.y * TILE + (threadIdx.x >> 5) * 2 * PPT), wy1 = wy0 + (float)(2 * PPT - 1);
 
   float pyf[PPT], T[PPT], T_final[PPT], S[PPT], last_alpha[PPT], last_dot[PPT], bg_dot[PPT];
   float dLc[PPT][3], dLo[PPT][NUM_OBJECTS];
@@ -324,6 +355,7 @@ __global__ void __launch_bounds__(256 / PPT) render_bwd_kernel(const RenderBwdPa
   // largest contributor count of the tile: nothing behind it received any weight
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) my_max = max(my_max, __shfl_xor_sync(FULL, my_max, o));
+  const uint32_t warp_last = my_max;   // nothing at or beyond this index contributes to any pixel of this warp
   if (lane == 0) s_max[threadIdx.x >> 5] = my_max;
   __syncthreads();
   uint32_t tile_max = 0;
@@ -344,7 +376,9 @@ __global__ void __launch_bounds__(256 / PPT) render_bwd_kernel(const RenderBwdPa
       const uint32_t id = q.point_list[range.x + hi - 1 - k];
       s_id[k] = id;
       s_xy[k] = q.means2D[id];
-      s_co[k] = q.conic_opacity[id];
+      const float4 co = q.conic_opacity[id];
+      s_co[k] = co;
+      s_reach[k] = splat_reach(co);
       s_rgbd[k] = q.rgbd[id];
     }
     for (int e = threadIdx.x; e < n * 8; e += NT) {
@@ -355,7 +389,11 @@ __global__ void __launch_bounds__(256 / PPT) render_bwd_kernel(const RenderBwdPa
 
     for (int k = 0; k < n; k++) {
       const uint32_t e = (uint32_t)(hi - 1 - k);
+      if (e >= warp_last) continue;                         // warp-uniform
       const float2 xy = s_xy[k];
+      const float2 reach = s_reach[k];
+      if (fmaxf(fmaxf(wx0 - xy.x, xy.x - wx1), 0.f) > reach.x || fmaxf(fmaxf(wy0 - xy.y, xy.y - wy1), 0.f) > reach.y)
+        continue;                                           // warp-uniform
       const float4 co = s_co[k];
       float w[PPT], G[PPT], dx[PPT], dy[PPT], alpha[PPT];
       bool act[PPT];
