@@ -291,14 +291,15 @@ def run_ours(args, rank, world, device):
     e2e = world * args.steps / (ms_e2e / 1e3)
 
     line = None
+    # per-stage device times inside the step (second pass with event pairs around each stage); every rank
+    # runs it because the step contains the collective
+    _lib.profile_enable(True)
+    for _ in range(args.steps):
+        step()
+    torch.cuda.synchronize(device)
+    prof = _lib.profile_read()
+    _lib.profile_enable(False)
     if rank == 0:
-        # per-stage device times inside the step (second pass with event pairs around each stage)
-        _lib.profile_enable(True)
-        for _ in range(args.steps):
-            step()
-        torch.cuda.synchronize(device)
-        prof = _lib.profile_read()
-        _lib.profile_enable(False)
         from trase_b200 import _raster
         R = _raster._capacity_hint.get((device.index or 0, cfg["P"], cfg["W"], cfg["H"]), 0)
         P, N = cfg["P"], cfg["W"] * cfg["H"]

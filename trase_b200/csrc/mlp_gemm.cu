@@ -578,31 +578,36 @@ __device__ __forceinline__ float rna_tf32(float x) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
   return __uint_as_float(u);
 }
+// One warp per row, lanes across the output columns (coalesced 128-byte stores); every output needs
+// one sinf or cosf (full-precision: arguments reach 2^9 * x).
 __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* __restrict__ xyz,
                                                            const float* __restrict__ t, int t_stride, int Lx, int Lt,
                                                            float* __restrict__ out, int ld) {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= M) return;
-  float* o = out + (size_t)m * ld;
-  const float x[3] = {xyz[3 * m], xyz[3 * m + 1], xyz[3 * m + 2]};
-  int c = 0;
-  o[c++] = rna_tf32(x[0]); o[c++] = rna_tf32(x[1]); o[c++] = rna_tf32(x[2]);
-  float f = 1.f;
-  for (int k = 0; k < Lx; k++, f *= 2.f) {
-    float s0, c0, s1, c1, s2, c2;
-    sincosf(x[0] * f, &s0, &c0);
-    sincosf(x[1] * f, &s1, &c1);
-    sincosf(x[2] * f, &s2, &c2);
-    o[c++] = rna_tf32(s0); o[c++] = rna_tf32(s1); o[c++] = rna_tf32(s2);
-    o[c++] = rna_tf32(c0); o[c++] = rna_tf32(c1); o[c++] = rna_tf32(c2);
-  }
-  const float tv = t[(size_t)m * t_stride];
-  o[c++] = rna_tf32(tv);
-  f = 1.f;
-  for (int k = 0; k < Lt; k++, f *= 2.f) {
-    float s, cs;
-    sincosf(tv * f, &s, &cs);
-    o[c++] = rna_tf32(s); o[c++] = rna_tf32(cs);
+  const int lane = threadIdx.x & 31;
+  const int warps_per_grid = (gridDim.x * blockDim.x) >> 5;
+  const int nx = 3 + 6 * Lx;           // columns of the xyz part
+  const int ncol = nx + 1 + 2 * Lt;
+  for (int m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < M; m += warps_per_grid) {
+    const float x0 = xyz[3 * m], x1 = xyz[3 * m + 1], x2 = xyz[3 * m + 2];
+    const float tv = t[(size_t)m * t_stride];
+    float* o = out + (size_t)m * ld;
+    for (int c = lane; c < ncol; c += 32) {
+      float v;
+      if (c < 3) {
+        v = c == 0 ? x0 : (c == 1 ? x1 : x2);
+      } else if (c < nx) {
+        const int k = (c - 3) / 6, r = (c - 3) - 6 * k, comp = r % 3;
+        const float a = (comp == 0 ? x0 : (comp == 1 ? x1 : x2)) * exp2f((float)k);
+        v = r < 3 ? sinf(a) : cosf(a);
+      } else if (c == nx) {
+        v = tv;
+      } else {
+        const int j = c - nx - 1, k = j >> 1;
+        const float a = tv * exp2f((float)k);
+        v = (j & 1) ? cosf(a) : sinf(a);
+      }
+      o[c] = rna_tf32(v);
+    }
   }
 }
 
@@ -618,8 +623,9 @@ extern "C" TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const 
     set_error("trase_b200_deform_embed: bad arguments");
     return 1;
   }
-  mlp::deform_embed_kernel<<<(M + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(M, xyz, t, t_stride, Lx,
-                                                                                              Lt, out, ld);
+  const int blocks = (M + 7) / 8 < 148 * 16 ? (M + 7) / 8 : 148 * 16;
+  mlp::deform_embed_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(M, xyz, t, t_stride, Lx, Lt, out,
+                                                                                      ld);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_deform_embed: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   return 0;
