@@ -140,12 +140,13 @@ class Workload:
         if rasterizer_cls is None:
             return R.render(view, self.pc, R.PIPE_DEFAULT, self.bg, d_xyz, d_rot, d_scale)
         # reference arm: identical glue, the reference's own GaussianRasterizer
-        saved = R.GaussianRasterizer, R.GaussianRasterizationSettings
+        saved = R.GaussianRasterizer, R.GaussianRasterizationSettings, R.FUSED_GLUE
         R.GaussianRasterizer, R.GaussianRasterizationSettings = rasterizer_cls
+        R.FUSED_GLUE = False          # the reference's own elementwise torch glue: none of our kernels on this arm
         try:
             return R.render(view, self.pc, R.PIPE_DEFAULT, self.bg, d_xyz, d_rot, d_scale)
         finally:
-            R.GaussianRasterizer, R.GaussianRasterizationSettings = saved
+            R.GaussianRasterizer, R.GaussianRasterizationSettings, R.FUSED_GLUE = saved
 
     def step_resident(self, world_size=1, rasterizer_cls=None):
         """Inputs already in HBM: fwd + bwd with fixed upstream gradients."""

@@ -228,6 +228,29 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
                           void* stream);
 
 /* ------------------------------------------------------------------------
+ * Fused parameter activation + rasterizer-input assembly and its backward
+ * (SURVEY.md §8(f) rank 1).  ref: the elementwise torch glue of
+ * gaussian_renderer/__init__.py:82-121 and scene/gaussian_model.py:181-205:
+ *   means3D = xyz + d_xyz;  scales = exp(scaling) + d_scaling;
+ *   rotations = normalize(rotation) + d_rotation;  opacity = sigmoid(opacity);
+ *   shs = cat(f_dc[P,1,3], f_rest[P,Mrest,3]);  sh_objs = feat / (||feat|| + 1e-9).
+ * Backward takes the six upstream gradients (NULL = zero) and writes the
+ * gradients of the ten inputs.  rotation / feature buffers 16-byte aligned.
+ * ---------------------------------------------------------------------- */
+TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const float* xyz, const float* d_xyz, const float* scaling,
+                                          const float* d_scaling, const float* rotation, const float* d_rotation,
+                                          const float* opacity, const float* f_dc, const float* f_rest,
+                                          const float* feat, float* means3D, float* scales, float* rotations,
+                                          float* opac_out, float* shs, float* sh_objs, void* stream);
+TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const float* scaling, const float* rotation,
+                                           const float* opacity, const float* feat, const float* g_means3D,
+                                           const float* g_scales, const float* g_rotations, const float* g_opac,
+                                           const float* g_shs, const float* g_objs, float* g_xyz, float* g_dxyz,
+                                           float* g_scaling, float* g_dscaling, float* g_rotation, float* g_drotation,
+                                           float* g_opacity, float* g_fdc, float* g_frest, float* g_feat,
+                                           void* stream);
+
+/* ------------------------------------------------------------------------
  * DeformNetwork MLP building block.  ref: the eleven nn.Linear layers of
  * DeformNetwork.forward (utils/time_utils.py:106-131), which the reference runs
  * as cuBLAS SGEMM + separate bias/ReLU kernels, and their autograd backward.

@@ -275,3 +275,34 @@ def test_runs_on_a_side_stream(native_lib):
         side = cuda_forward(a)
     s.synchronize()
     assert torch.equal(base.color, side.color)
+
+
+# ------------------------------------------ fused activation / assembly -----
+def test_fused_assembly_matches_torch_glue(native_lib):
+    """render() with the fused assembly kernels == render() with the reference's torch glue, outputs and
+    gradients of every raw parameter and of the three deformation inputs."""
+    from trase_b200 import synth, render as R
+    sc = synth.make_scene(8000, 96, 80, 41)
+    view = R.make_view(sc["cam"], DEV)
+    up = {k: v.to(DEV) for k, v in synth.make_upstream_grads(96, 80, 41).items()}
+    bg = torch.zeros(3, device=DEV)
+    results = {}
+    for fused in (False, True):
+        R.FUSED_GLUE = fused
+        try:
+            pc = R.GaussianParams.from_activated(sc, DEV)
+            g = torch.Generator(device=DEV).manual_seed(3)
+            deltas = [(torch.randn(8000, k, device=DEV, generator=g) * 1e-3).requires_grad_(True) for k in (3, 4, 3)]
+            out = R.render(view, pc, R.PIPE_DEFAULT, bg, deltas[0], deltas[1], deltas[2])
+            torch.autograd.backward([out["render"], out["render_gaussian_features"]],
+                                    [up["dL_dcolor"], up["dL_dobjects"]])
+            results[fused] = (out, [p.grad.clone() for p in pc.parameters()] + [d.grad.clone() for d in deltas])
+        finally:
+            R.FUSED_GLUE = True
+    o0, g0 = results[False]
+    o1, g1 = results[True]
+    assert torch.equal(o0["radii"], o1["radii"])
+    assert (o0["render"] - o1["render"]).abs().max() <= 1e-5
+    assert (o0["render_gaussian_features"] - o1["render_gaussian_features"]).abs().max() <= 1e-5
+    for a, b in zip(g0, g1):
+        assert rel_err(_np(a), _np(b)) <= 1e-3

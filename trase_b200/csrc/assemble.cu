@@ -1,0 +1,199 @@
+// Fused parameter activation + rasterizer-input assembly, forward and backward
+// (SURVEY.md §8(f) rank 1).  Replaces the ~20 elementwise torch kernels (and as
+// many again in autograd) that the reference's glue launches per view:
+//   means3D  = xyz + d_xyz                                   gaussian_renderer/__init__.py:82
+//   scales   = exp(_scaling) + d_scaling                      :95, scene/gaussian_model.py:183
+//   rotations= normalize(_rotation) + d_rotation              :96, scene/gaussian_model.py:187
+//   opacity  = sigmoid(_opacity)                              scene/gaussian_model.py:201
+//   shs      = cat(f_dc, f_rest, dim=1)                        scene/gaussian_model.py:195-197
+//   sh_objs  = feat / (||feat|| + 1e-9)                        gaussian_renderer/__init__.py:116-121
+// One thread per Gaussian for the small vectors; the 48-float SH row and the
+// 32-float feature row are handled by 4 / 8 cooperating lanes with 16-byte accesses.
+#include "common.cuh"
+
+namespace tb {
+
+struct AssembleFwd {
+  int P, Mrest;   // Mrest = SH coefficients in f_rest (15 for degree 3)
+  const float *xyz, *d_xyz, *scaling, *d_scaling, *rotation, *d_rotation, *opacity, *f_dc, *f_rest, *feat;
+  float *means3D, *scales, *rotations, *opac_out, *shs, *sh_objs;
+};
+
+__global__ void __launch_bounds__(256) assemble_fwd_kernel(const AssembleFwd a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < a.P) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      a.means3D[3 * i + c] = a.xyz[3 * i + c] + a.d_xyz[3 * i + c];
+      a.scales[3 * i + c] = expf(a.scaling[3 * i + c]) + a.d_scaling[3 * i + c];
+    }
+    const float4 q = reinterpret_cast<const float4*>(a.rotation)[i];
+    const float4 dq = reinterpret_cast<const float4*>(a.d_rotation)[i];
+    // F.normalize: v / max(||v||, 1e-12)
+    const float n = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
+    reinterpret_cast<float4*>(a.rotations)[i] = make_float4(q.x / n + dq.x, q.y / n + dq.y, q.z / n + dq.z, q.w / n + dq.w);
+    a.opac_out[i] = 1.f / (1.f + expf(-a.opacity[i]));
+  }
+}
+
+// SH rows: out[i][0] = f_dc[i][0], out[i][1..] = f_rest[i][..]; flat float copy, coalesced
+__global__ void __launch_bounds__(256) assemble_sh_kernel(int P, int Mrest, const float* __restrict__ f_dc,
+                                                          const float* __restrict__ f_rest, float* __restrict__ shs) {
+  const int M3 = (Mrest + 1) * 3;
+  const size_t total = (size_t)P * M3;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t i = e / M3;
+    const int c = (int)(e - i * M3);
+    shs[e] = c < 3 ? f_dc[i * 3 + c] : f_rest[i * (size_t)(Mrest * 3) + (c - 3)];
+  }
+}
+
+// feature rows: 8 lanes per Gaussian, float4 each; norm by shuffle over the 8 lanes
+__global__ void __launch_bounds__(256) assemble_feat_kernel(int P, const float4* __restrict__ feat,
+                                                            float4* __restrict__ out) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = e < (size_t)P * 8;
+  float4 f = valid ? feat[e] : make_float4(0, 0, 0, 0);
+  float s = f.x * f.x + f.y * f.y + f.z * f.z + f.w * f.w;
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  const float inv = 1.f / (sqrtf(s) + 1e-9f);
+  if (valid) out[e] = make_float4(f.x * inv, f.y * inv, f.z * inv, f.w * inv);
+}
+
+struct AssembleBwd {
+  int P, Mrest;
+  const float *scaling, *rotation, *opacity, *feat;                          // raw parameters
+  const float *g_means3D, *g_scales, *g_rotations, *g_opac, *g_shs, *g_objs; // upstream gradients (may be null)
+  float *g_xyz, *g_dxyz, *g_scaling, *g_dscaling, *g_rotation, *g_drotation, *g_opacity, *g_fdc, *g_frest, *g_feat;
+};
+
+__global__ void __launch_bounds__(256) assemble_bwd_kernel(const AssembleBwd a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < a.P) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const float gm = a.g_means3D ? a.g_means3D[3 * i + c] : 0.f;
+      a.g_xyz[3 * i + c] = gm;
+      a.g_dxyz[3 * i + c] = gm;
+      const float gs = a.g_scales ? a.g_scales[3 * i + c] : 0.f;
+      a.g_scaling[3 * i + c] = gs * expf(a.scaling[3 * i + c]);
+      a.g_dscaling[3 * i + c] = gs;
+    }
+    const float4 q = reinterpret_cast<const float4*>(a.rotation)[i];
+    const float4 g = a.g_rotations ? reinterpret_cast<const float4*>(a.g_rotations)[i] : make_float4(0, 0, 0, 0);
+    const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    float4 gq;
+    if (n > 1e-12f) {
+      // d/dq (q/|q|) : (g - r (r.g)) / |q| with r = q/|q|
+      const float inv = 1.f / n;
+      const float rx = q.x * inv, ry = q.y * inv, rz = q.z * inv, rw = q.w * inv;
+      const float rg = rx * g.x + ry * g.y + rz * g.z + rw * g.w;
+      gq = make_float4((g.x - rx * rg) * inv, (g.y - ry * rg) * inv, (g.z - rz * rg) * inv, (g.w - rw * rg) * inv);
+    } else {
+      gq = make_float4(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f, g.w * 1e12f);   // clamped branch of F.normalize
+    }
+    reinterpret_cast<float4*>(a.g_rotation)[i] = gq;
+    reinterpret_cast<float4*>(a.g_drotation)[i] = g;
+    const float sgm = 1.f / (1.f + expf(-a.opacity[i]));
+    a.g_opacity[i] = (a.g_opac ? a.g_opac[i] : 0.f) * sgm * (1.f - sgm);
+  }
+}
+
+__global__ void __launch_bounds__(256) assemble_sh_bwd_kernel(int P, int Mrest, const float* __restrict__ g_shs,
+                                                              float* __restrict__ g_fdc, float* __restrict__ g_frest) {
+  const int M3 = (Mrest + 1) * 3;
+  const size_t total = (size_t)P * M3;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t i = e / M3;
+    const int c = (int)(e - i * M3);
+    const float v = g_shs ? g_shs[e] : 0.f;
+    if (c < 3) g_fdc[i * 3 + c] = v;
+    else g_frest[i * (size_t)(Mrest * 3) + (c - 3)] = v;
+  }
+}
+
+// y = f / (n + eps):  df = g / (n + eps) - f (f.g) / (n (n + eps)^2)
+__global__ void __launch_bounds__(256) assemble_feat_bwd_kernel(int P, const float4* __restrict__ feat,
+                                                                const float4* __restrict__ g_objs,
+                                                                float4* __restrict__ g_feat) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = e < (size_t)P * 8;
+  const float4 f = valid ? feat[e] : make_float4(0, 0, 0, 0);
+  const float4 g = (valid && g_objs) ? g_objs[e] : make_float4(0, 0, 0, 0);
+  float s = f.x * f.x + f.y * f.y + f.z * f.z + f.w * f.w;
+  float d = f.x * g.x + f.y * g.y + f.z * g.z + f.w * g.w;
+#pragma unroll
+  for (int o = 1; o < 8; o <<= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    d += __shfl_xor_sync(0xffffffffu, d, o);
+  }
+  const float n = sqrtf(s);
+  const float inv = 1.f / (n + 1e-9f);
+  const float k = (n > 0.f) ? d * inv * inv / n : 0.f;
+  if (valid) g_feat[e] = make_float4(g.x * inv - f.x * k, g.y * inv - f.y * k, g.z * inv - f.z * k, g.w * inv - f.w * k);
+}
+
+}  // namespace tb
+
+using namespace tb;
+
+extern "C" TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const float* xyz, const float* d_xyz,
+                                                     const float* scaling, const float* d_scaling,
+                                                     const float* rotation, const float* d_rotation,
+                                                     const float* opacity, const float* f_dc, const float* f_rest,
+                                                     const float* feat, float* means3D, float* scales,
+                                                     float* rotations, float* opac_out, float* shs, float* sh_objs,
+                                                     void* stream) {
+  if (P <= 0) return 0;
+  if (!xyz || !d_xyz || !scaling || !d_scaling || !rotation || !d_rotation || !opacity || !f_dc || !feat ||
+      !means3D || !scales || !rotations || !opac_out || !shs || !sh_objs || (Mrest > 0 && !f_rest) || Mrest < 0) {
+    set_error("trase_b200_assemble_forward: null pointer");
+    return 1;
+  }
+  if (((uintptr_t)rotation | (uintptr_t)d_rotation | (uintptr_t)rotations | (uintptr_t)feat | (uintptr_t)sh_objs) & 15) {
+    set_error("trase_b200_assemble_forward: rotation and feature buffers must be 16-byte aligned");
+    return 1;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  AssembleFwd a{P, Mrest, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat,
+                means3D, scales, rotations, opac_out, shs, sh_objs};
+  assemble_fwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+  const size_t tot = (size_t)P * (Mrest + 1) * 3;
+  int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
+  assemble_sh_kernel<<<g, 256, 0, s>>>(P, Mrest, f_dc, f_rest, shs);
+  assemble_feat_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(P, reinterpret_cast<const float4*>(feat),
+                                                                       reinterpret_cast<float4*>(sh_objs));
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_assemble_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  return 0;
+}
+
+extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const float* scaling, const float* rotation,
+                                                      const float* opacity, const float* feat, const float* g_means3D,
+                                                      const float* g_scales, const float* g_rotations,
+                                                      const float* g_opac, const float* g_shs, const float* g_objs,
+                                                      float* g_xyz, float* g_dxyz, float* g_scaling, float* g_dscaling,
+                                                      float* g_rotation, float* g_drotation, float* g_opacity,
+                                                      float* g_fdc, float* g_frest, float* g_feat, void* stream) {
+  if (P <= 0) return 0;
+  if (!scaling || !rotation || !opacity || !feat || !g_xyz || !g_dxyz || !g_scaling || !g_dscaling || !g_rotation ||
+      !g_drotation || !g_opacity || !g_fdc || !g_feat || (Mrest > 0 && !g_frest)) {
+    set_error("trase_b200_assemble_backward: null pointer");
+    return 1;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  AssembleBwd a{P, Mrest, scaling, rotation, opacity, feat, g_means3D, g_scales, g_rotations, g_opac, g_shs, g_objs,
+                g_xyz, g_dxyz, g_scaling, g_dscaling, g_rotation, g_drotation, g_opacity, g_fdc, g_frest, g_feat};
+  assemble_bwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+  const size_t tot = (size_t)P * (Mrest + 1) * 3;
+  int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
+  assemble_sh_bwd_kernel<<<g, 256, 0, s>>>(P, Mrest, g_shs, g_fdc, g_frest);
+  assemble_feat_bwd_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(
+      P, reinterpret_cast<const float4*>(feat), reinterpret_cast<const float4*>(g_objs),
+      reinterpret_cast<float4*>(g_feat));
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_assemble_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  return 0;
+}

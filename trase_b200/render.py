@@ -74,6 +74,8 @@ def make_view(cam: dict, device) -> SimpleNamespace:
                            full_proj_transform=cam["projmatrix"].to(device), camera_center=cam["campos"].to(device))
 
 
+FUSED_GLUE = True   # module switch: set False to run the reference's elementwise torch glue instead
+
 PIPE_DEFAULT = SimpleNamespace(convert_SHs_python=False, compute_cov3D_python=False, debug=False)
 
 
@@ -98,15 +100,25 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
         campos=viewpoint_camera.camera_center, prefiltered=False, debug=pipe.debug)
     rasterizer = GaussianRasterizer(raster_settings=raster_settings)
 
-    means3D = pc.get_xyz + d_xyz
     means2D = screenspace_points
-    opacity = pc.get_opacity
-    scales = pc.get_scaling + d_scaling
-    rotations = pc.get_rotation + d_rotation
-    shs, colors_precomp = (pc.get_features, None) if override_color is None else (None, override_color)
-    sh_objs = pc.get_gaussian_features
-    if norm_gaussian_features:
-        sh_objs = sh_objs / (sh_objs.norm(dim=2, keepdim=True) + 1e-9)
+    fused = (FUSED_GLUE and override_color is None and norm_gaussian_features and isinstance(pc, GaussianParams)
+             and all(torch.is_tensor(d) and d.shape[0] == pc._xyz.shape[0] for d in (d_xyz, d_rotation, d_scaling)))
+    if fused:
+        # one fused kernel group instead of ~20 elementwise torch kernels (and as many in autograd)
+        from ._assemble import assemble_inputs
+        means3D, scales, rotations, opacity, shs, sh_objs = assemble_inputs(
+            pc._xyz, d_xyz, pc._scaling, d_scaling, pc._rotation, d_rotation, pc._opacity, pc._features_dc,
+            pc._features_rest, pc._gaussian_features)
+        colors_precomp = None
+    else:
+        means3D = pc.get_xyz + d_xyz
+        opacity = pc.get_opacity
+        scales = pc.get_scaling + d_scaling
+        rotations = pc.get_rotation + d_rotation
+        shs, colors_precomp = (pc.get_features, None) if override_color is None else (None, override_color)
+        sh_objs = pc.get_gaussian_features
+        if norm_gaussian_features:
+            sh_objs = sh_objs / (sh_objs.norm(dim=2, keepdim=True) + 1e-9)
     if mask is not None:
         means3D, means2D, opacity, sh_objs = means3D[mask], means2D[mask], opacity[mask], sh_objs[mask]
         scales, rotations = scales[mask], rotations[mask]
