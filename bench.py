@@ -315,10 +315,16 @@ def run_ours(args, rank, world, device):
         dom = max(stages, key=lambda k: stages[k]["ms"]) if stages else None
         peak, peak_src = measured_peaks()
         roof = None
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom, {}).get("bytes")
+        except Exception:
+            pass
         if dom:
             ach = stages[dom]["GBps"]
             roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                    "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
+                    "frac": round(ach / peak, 4), "traffic": traffic, "traffic_unit": "bytes per launch (ncu --set full, profiles/traffic.json)",
+                    "peak_source": peak_src,
                     "algorithmic_bytes": algorithmic_bytes(dom, P, R, N, 16, n_pass),
                     "launch_ms": stages[dom]["ms"],
                     "note": "compositing kernels are FP32/shuffle-bound on (pixel,Gaussian) pairs, not HBM-bound "
