@@ -283,6 +283,21 @@ TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const float* B, int 
 TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt,
                                       float* out, int ld, void* stream);
 
+/* Helpers around the MLP GEMMs (each replaces several elementwise torch kernels of
+ * the reference's eager path, utils/time_utils.py:106-131 and its autograd):
+ *  round_transpose: Wr = tf32-round(W) [rows][cols] and WrT = tf32-round(W[:, col0:col0+ncols])^T
+ *                   [ncols][rows] (either output may be NULL);
+ *  pack_heads:      the three head weights [3|4|3][K] and biases -> wh [16][K], whT [K][16], bh [16];
+ *  pack_dout:       the three upstream gradients [M][3|4|3] (NULL = zero) -> dout [M][16] (tf32-rounded),
+ *                   colsum[16] += their column sums (= head bias gradients). */
+TRASE_API int trase_b200_mlp_round_transpose(const float* W, int rows, int cols, int col0, int ncols, float* Wr,
+                                             float* WrT, void* stream);
+TRASE_API int trase_b200_mlp_pack_heads(const float* w0, const float* b0, const float* w1, const float* b1,
+                                        const float* w2, const float* b2, int K, float* wh, float* whT, float* bh,
+                                        void* stream);
+TRASE_API int trase_b200_mlp_pack_dout(int M, const float* g0, const float* g1, const float* g2, float* dout,
+                                       float* colsum, void* stream);
+
 /* Weight gradient of one nn.Linear: D[i][j] += sum_m P[m][i] * Q[m][j]
  * (dW = dZ^T X; ref: autograd backward of utils/time_utils.py:113, cuBLAS SGEMM
  * in the reference).  P [M][I], Q [M][J], D [I][J] row-major fp32; I, J <= 256,

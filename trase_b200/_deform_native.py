@@ -5,8 +5,9 @@ the epilogue, wgrad straight from the row-major activations).
 
 Mirrors DeformNetwork.forward (utils/time_utils.py:106-131) for the default
 non-blender, non-6DoF model.  Numerics: TF32 products (10-bit mantissa
-operands), fp32 accumulation; the reference runs fp32 SGEMM.  xyz and t carry
-no gradient (train.py:202-204 detaches xyz).
+operands, rounded to nearest by every producer), fp32 accumulation; the
+reference runs fp32 SGEMM.  xyz and t carry no gradient (train.py:202-204
+detaches xyz).
 """
 from __future__ import annotations
 
@@ -22,6 +23,10 @@ def tf32_round(w: torch.Tensor) -> torch.Tensor:
     return ((w.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
 
 
+def _stream(dev):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
 def _gemm(lib, A, B, D, bias=None, relu=False, mask_in=None, mask_out=None, colsum=None, round_tf32=True):
     M, K = A.shape
     N = B.shape[0]
@@ -29,15 +34,14 @@ def _gemm(lib, A, B, D, bias=None, relu=False, mask_in=None, mask_out=None, cols
         A.data_ptr(), A.stride(0), B.data_ptr(), B.stride(0), D.data_ptr(), D.stride(0), M, N, K,
         bias.data_ptr() if bias is not None else None, int(relu),
         mask_in.data_ptr() if mask_in is not None else None, mask_out.data_ptr() if mask_out is not None else None,
-        colsum.data_ptr() if colsum is not None else None, int(round_tf32),
-        torch.cuda.current_stream(A.device).cuda_stream))
+        colsum.data_ptr() if colsum is not None else None, int(round_tf32), _stream(A.device)))
 
 
 def _wgrad(lib, P, Q, D):
     """D[i, j] += sum_m P[m, i] Q[m, j]; Q wider than 256 columns goes in chunks."""
     M, I = P.shape
     J = Q.shape[1]
-    s = torch.cuda.current_stream(P.device).cuda_stream
+    s = _stream(P.device)
     for j0 in range(0, J, 256):
         j1 = min(J, j0 + 256)
         _lib.check(lib.trase_b200_wgrad_tf32(P.data_ptr(), P.stride(0), I, Q[:, j0:].data_ptr(), Q.stride(0), j1 - j0,
@@ -50,91 +54,104 @@ class _DeformMLP(torch.autograd.Function):
         lib = _lib.load()
         nl = (len(params) - 6) // 2
         Ws, bs = params[0:2 * nl:2], params[1:2 * nl:2]
-        heads_w, heads_b = params[2 * nl::2], params[2 * nl + 1::2]
+        heads = params[2 * nl:]
         dev = x.device
         M = x.shape[0]
         E = 3 + 6 * Lx + 1 + 2 * Lt                       # 84
         with torch.cuda.device(dev):
+            s = _stream(dev)
             x = x.detach().contiguous().float()
             t = t.detach().float()
             t_stride = 0 if (t.numel() == 1 or t.stride(0) == 0) else 1
             t_c = t if t_stride == 0 else t.contiguous()
             f32 = dict(dtype=torch.float32, device=dev)
+            # TF32-rounded weights (forward operand) and their transposes (backward operand), one small
+            # kernel per layer; the layer after the skip only back-propagates through its hidden columns
+            sizes = [(w.shape[0], w.shape[1]) for w in Ws]
+            wbuf = torch.empty(sum(r * c for r, c in sizes) + sum(r * (c - E if i - 1 == skip else c)
+                                                                  for i, (r, c) in enumerate(sizes) if i > 0), **f32)
+            Wr, WrT, off = [], [None] * nl, 0
+            for i, (r, c) in enumerate(sizes):
+                wr = wbuf[off:off + r * c].view(r, c)
+                off += r * c
+                wt = None
+                if i > 0:
+                    c0 = E if i - 1 == skip else 0
+                    wt = wbuf[off:off + r * (c - c0)].view(c - c0, r)
+                    off += r * (c - c0)
+                    WrT[i] = wt
+                _lib.check(lib.trase_b200_mlp_round_transpose(
+                    Ws[i].detach().contiguous().data_ptr(), r, c, E if (i > 0 and i - 1 == skip) else 0,
+                    (c - E) if (i > 0 and i - 1 == skip) else (c if i > 0 else 0), wr.data_ptr(),
+                    wt.data_ptr() if wt is not None else None, s))
+                Wr.append(wr)
+            hb = torch.empty(16 * W * 2 + 16, **f32)
+            wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
+            _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
+                                                     wh.data_ptr(), whT.data_ptr(), bh.data_ptr(), s))
             # skip buffer [M, E + W]: embedding in [:, :E], output of layer `skip` in [:, E:]
             skipbuf = torch.empty((M, E + W), **f32)
             _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt, skipbuf.data_ptr(),
-                                                   skipbuf.stride(0), torch.cuda.current_stream(dev).cuda_stream))
-            emb = skipbuf[:, :E]
-            Wr = [tf32_round(w.detach()) for w in Ws]
-            acts, masks = [], []
-            inp = emb
+                                                   skipbuf.stride(0), s))
+            masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
+            acts = []
+            inp = skipbuf[:, :E]
             for i in range(nl):
                 out = skipbuf[:, E:] if i == skip else torch.empty((M, W), **f32)
-                mk = torch.empty((M, W // 32), dtype=torch.int32, device=dev)
-                _gemm(lib, inp, Wr[i], out, bias=bs[i].detach(), relu=True, mask_out=mk)
+                _gemm(lib, inp, Wr[i], out, bias=bs[i].detach(), relu=True, mask_out=masks[i])
                 acts.append(out)
-                masks.append(mk)
                 inp = skipbuf if i == skip else out
-            # the three heads as one [16, W] GEMM (10 real rows)
-            wh = torch.zeros((16, W), **f32)
-            bh = torch.zeros((16,), **f32)
-            wh[0:3], wh[3:7], wh[7:10] = heads_w[0].detach(), heads_w[1].detach(), heads_w[2].detach()
-            bh[0:3], bh[3:7], bh[7:10] = heads_b[0].detach(), heads_b[1].detach(), heads_b[2].detach()
             out16 = torch.empty((M, 16), **f32)
-            wh = tf32_round(wh)
             _gemm(lib, acts[-1], wh, out16, bias=bh, round_tf32=False)
-        ctx.save_for_backward(skipbuf, wh, *acts, *Wr, *masks)
-        ctx.meta = (nl, skip, E, M)
+        ctx.save_for_backward(skipbuf, whT, masks, *acts, *[w for w in WrT if w is not None])
+        ctx.meta = (nl, skip, E, M, sizes)
         return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
 
     @staticmethod
     def backward(ctx, g_xyz, g_rot, g_scale):
         lib = _lib.load()
-        nl, skip, E, M = ctx.meta
+        nl, skip, E, M, sizes = ctx.meta
         saved = ctx.saved_tensors
-        skipbuf, wh = saved[0], saved[1]
-        acts = saved[2:2 + nl]
-        Ws = saved[2 + nl:2 + 2 * nl]
-        masks = saved[2 + 2 * nl:2 + 3 * nl]
+        skipbuf, whT, masks = saved[0], saved[1], saved[2]
+        acts = saved[3:3 + nl]
+        WrT = [None] + list(saved[3 + nl:])
         dev = skipbuf.device
         f32 = dict(dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
-            dout = torch.zeros((M, 16), **f32)
-            if g_xyz is not None:
-                dout[:, 0:3] = g_xyz
-            if g_rot is not None:
-                dout[:, 3:7] = g_rot
-            if g_scale is not None:
-                dout[:, 7:10] = g_scale
-            dbh = dout.sum(0)
-            dout = tf32_round(dout)
-            # heads: dWh^T = h_last^T dout ; db = colsum(dout)
-            dwhT = torch.zeros((W, 16), **f32)
+            s = _stream(dev)
+            # every weight / bias gradient lives in one zero-initialised buffer (one memset)
+            n_w = sum(r * c for r, c in sizes)
+            gbuf = torch.zeros(n_w + nl * W + W * 16 + 16, **f32)
+            grads_w, grads_b, off = [], [], 0
+            for r, c in sizes:
+                grads_w.append(gbuf[off:off + r * c].view(r, c))
+                off += r * c
+            for _ in range(nl):
+                grads_b.append(gbuf[off:off + W])
+                off += W
+            dwhT = gbuf[off:off + W * 16].view(W, 16)
+            dbh = gbuf[off + W * 16:off + W * 16 + 16]
+            dout = torch.empty((M, 16), **f32)
+            gs = [None if g is None else g.contiguous() for g in (g_xyz, g_rot, g_scale)]
+            _lib.check(lib.trase_b200_mlp_pack_dout(M, *[None if g is None else g.data_ptr() for g in gs],
+                                                    dout.data_ptr(), dbh.data_ptr(), s))
+            # heads: dWh^T = h_last^T dout
             _wgrad(lib, acts[-1], dout, dwhT)
-            grads_w = [None] * nl
-            grads_b = [None] * nl
-            # dZ_{nl-1} = (dout Wh) * relu'(h_last)
+            # dZ_{nl-1} = (dout Wh) * relu'(h_last); its column sums are the bias gradient of layer nl-1
             dz = torch.empty((M, W), **f32)
-            db = torch.zeros((W,), **f32)
-            _gemm(lib, dout, wh.t().contiguous(), dz, mask_in=masks[-1], colsum=db)
+            _gemm(lib, dout, whT, dz, mask_in=masks[nl - 1], colsum=grads_b[nl - 1])
             for i in range(nl - 1, -1, -1):
-                grads_b[i] = db
                 inp = skipbuf[:, :E] if i == 0 else (skipbuf if i - 1 == skip else acts[i - 1])
-                dw = torch.zeros((W, inp.shape[1]), **f32)
-                _wgrad(lib, dz, inp, dw)
-                grads_w[i] = dw
+                _wgrad(lib, dz, inp, grads_w[i])
                 if i > 0:
-                    wt = Ws[i][:, E:] if i - 1 == skip else Ws[i]      # only the hidden part carries gradient
                     dz_prev = torch.empty((M, W), **f32)
-                    db = torch.zeros((W,), **f32)
-                    _gemm(lib, dz, wt.t().contiguous(), dz_prev, mask_in=masks[i - 1], colsum=db)
+                    _gemm(lib, dz, WrT[i], dz_prev, mask_in=masks[i - 1], colsum=grads_b[i - 1])
                     dz = dz_prev
             dwh = dwhT.t()
             out = [None, None, None, None, None]
             for i in range(nl):
                 out += [grads_w[i], grads_b[i]]
-            out += [dwh[0:3].contiguous(), dbh[0:3].contiguous(), dwh[3:7].contiguous(), dbh[3:7].contiguous(),
-                    dwh[7:10].contiguous(), dbh[7:10].contiguous()]
+            out += [dwh[0:3], dbh[0:3], dwh[3:7], dbh[3:7], dwh[7:10], dbh[7:10]]
         return tuple(out)
 
 

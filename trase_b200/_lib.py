@@ -66,7 +66,8 @@ EXPORTS = [
     "trase_b200_rasterize_forward_rebin", "trase_b200_rasterize_backward", "trase_b200_mark_visible",
     "trase_b200_sort_scratch_bytes", "trase_b200_sort_pairs", "trase_b200_higher_msb",
     "trase_b200_set_tuning", "trase_b200_rasterize_backward_stages", "trase_b200_profile_enable",
-    "trase_b200_profile_read", "trase_b200_sort_pairs_static", "trase_b200_gemm_tf32", "trase_b200_wgrad_tf32", "trase_b200_deform_embed", "trase_b200_assemble_forward", "trase_b200_assemble_backward",
+    "trase_b200_profile_read", "trase_b200_sort_pairs_static", "trase_b200_gemm_tf32", "trase_b200_wgrad_tf32", "trase_b200_deform_embed", "trase_b200_assemble_forward", "trase_b200_assemble_backward", "trase_b200_mlp_round_transpose", "trase_b200_mlp_pack_heads",
+    "trase_b200_mlp_pack_dout",
 ]
 
 _lib = None
@@ -128,6 +129,13 @@ def load() -> C.CDLL:
     lib.trase_b200_assemble_forward.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 17
     lib.trase_b200_assemble_backward.restype = C.c_int
     lib.trase_b200_assemble_backward.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 21
+    lib.trase_b200_mlp_round_transpose.restype = C.c_int
+    lib.trase_b200_mlp_round_transpose.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                   C.c_void_p]
+    lib.trase_b200_mlp_pack_heads.restype = C.c_int
+    lib.trase_b200_mlp_pack_heads.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 4
+    lib.trase_b200_mlp_pack_dout.restype = C.c_int
+    lib.trase_b200_mlp_pack_dout.argtypes = [C.c_int] + [C.c_void_p] * 6
     lib.trase_b200_higher_msb.restype = C.c_uint32
     lib.trase_b200_higher_msb.argtypes = [C.c_uint32]
     lib.trase_b200_rasterize_backward_stages.restype = C.c_int

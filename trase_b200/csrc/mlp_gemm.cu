@@ -38,6 +38,7 @@ struct GemmEpilogue {
   uint32_t* mask_out;        // [M][N/32] written as (output > 0), or null
   float* colsum;      // [N] or null: += column sums of the written values (bias gradient)
   float* D; int ldd;  // output, row pitch in floats
+  int reverse;        // walk the row tiles from the last to the first (see trase_b200_set_tuning "gemm_snake")
   int prefetch_tiles; // L2 prefetch distance of the activation stream, in tiles per CTA
   int round_tf32;     // round outputs to TF32 (nearest) so the next GEMM's operand truncation is exact
   int M, N, K;
@@ -94,6 +95,9 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int n_off = RES ? (int)(blockIdx.x & 1) * BN : 0;
   const int tile0 = RES ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int tile_step = RES ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  // consecutive layers walk the rows in opposite directions so that the rows the previous kernel wrote last
+  // (still in the 126 MB L2) are the ones this kernel reads first
+#define TB_TILE(t) (ep.reverse ? (num_tiles - 1 - (t)) : (t))
   constexpr uint32_t TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // power of two >= 32 (BN = 16 -> 32, 256 -> 512)
 
   if (warp == 0 && lane == 0) {
@@ -128,15 +132,15 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int i = 0; i < pf; i++) {
         const int t = tile0 + i * tile_step;
         if (t < num_tiles)
-          for (int kb = 0; kb < num_kb; kb++) tma_prefetch_l2_2d(&tmA, kb * BK, t * BM);
+          for (int kb = 0; kb < num_kb; kb++) tma_prefetch_l2_2d(&tmA, kb * BK, TB_TILE(t) * BM);
       }
       for (int tile = tile0; tile < num_tiles; tile += tile_step) {
         const int tpf = tile + pf * tile_step;
         for (int kb = 0; kb < num_kb; kb++) {
-          if (pf && tpf < num_tiles) tma_prefetch_l2_2d(&tmA, kb * BK, tpf * BM);
+          if (pf && tpf < num_tiles) tma_prefetch_l2_2d(&tmA, kb * BK, TB_TILE(tpf) * BM);
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_expect_tx(&full[stage], RES ? L::A_BYTES : L::A_BYTES + L::B_BYTES);
-          tma_load_2d(sA + stage * L::A_BYTES, &tmA, &full[stage], kb * BK, tile * BM);
+          tma_load_2d(sA + stage * L::A_BYTES, &tmA, &full[stage], kb * BK, TB_TILE(tile) * BM);
           if (!RES) tma_load_2d(sB + stage * L::B_BYTES, &tmB, &full[stage], kb * BK, 0);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -188,7 +192,8 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int tile = tile0; tile < num_tiles; tile += tile_step) {
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const int grow = tile * BM + ew * 32 + lane;   // global row of this thread
+      const int rtile = TB_TILE(tile);
+      const int grow = rtile * BM + ew * 32 + lane;   // global row of this thread
 #pragma unroll 1
       for (int s = eh; s < NSLAB; s += EPI_WARPS / 4) {
         if (n_off + s * SLAB >= ep.N) break;
@@ -243,7 +248,7 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int it = 0; it < 8; it++) {
             const int r = it * 4 + (lane >> 3);
             const float4 val = *reinterpret_cast<const float4*>(out + r * 128 + ((chunk ^ (r & 7)) << 4));
-            const int gr = tile * BM + ew * 32 + r;
+            const int gr = rtile * BM + ew * 32 + r;
             if (gr < ep.M && col0 < ep.N) {
               float* dst = ep.D + (size_t)gr * ep.ldd + col0;
               if (col0 + 3 < ep.N) {
@@ -285,6 +290,7 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+#undef TB_TILE
 }
 
 // ---------------------------------------------------------------------------
@@ -318,7 +324,9 @@ bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t col
   return r == CUDA_SUCCESS;
 }
 
-int g_prefetch_tiles = 0;    // tuning switch ("gemm_prefetch")
+int g_prefetch_tiles = 0;
+int g_snake = 0;              // alternate the row-tile direction between consecutive GEMM launches
+int g_snake_phase = 0;    // tuning switch ("gemm_prefetch")
 int g_allow_resident = 1;   // tuning switch (trase_b200_set_tuning "gemm_resident")
 static int g_num_sms = 0;
 static int num_sms() {
@@ -383,7 +391,7 @@ extern "C" TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const flo
   }
   mlp::GemmEpilogue ep;
   ep.bias = bias; ep.relu = relu; ep.mask_in = mask_in; ep.mask_out = mask_out; ep.colsum = colsum;
-  ep.round_tf32 = round_tf32; ep.prefetch_tiles = mlp::g_prefetch_tiles; ep.D = D; ep.ldd = ldd; ep.M = M; ep.N = N; ep.K = K;
+  ep.round_tf32 = round_tf32; ep.prefetch_tiles = mlp::g_prefetch_tiles; ep.reverse = mlp::g_snake ? (mlp::g_snake_phase++ & 1) : 0; ep.D = D; ep.ldd = ldd; ep.M = M; ep.N = N; ep.K = K;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   cudaError_t e = small ? mlp::launch_gemm_tn<16, false>(tA, tB, ep, st)
                         : mlp::launch_gemm_tn<256, false>(tA, tB, ep, st);
@@ -413,6 +421,7 @@ constexpr int WG_BOX_BYTES = WG_ROWS * 128;  // one 32-row x 32-col fp32 box
 struct WgradParams {
   int M, I, J;      // reduction length, output rows (<= 256), output cols (<= 256)
   float* D; int ldd;
+  int reverse;
 };
 
 constexpr int WG_THREADS = 256;
@@ -443,6 +452,9 @@ wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
   const int per = (nblk + gridDim.x - 1) / gridDim.x;
   const int blk0 = blockIdx.x * per;
   const int blk1 = min(nblk, blk0 + per);
+  // CTA c owns row blocks [blk0, blk1); with `reverse` the ownership is mirrored so that the CTAs which start
+  // first take the rows written last by the producer kernel
+#define WG_BLK(b) (p.reverse ? (nblk - 1 - (b)) : (b))
   constexpr uint32_t TMEM_COLS = 512;
 
   if (warp == 0 && lane == 0) {
@@ -464,9 +476,9 @@ wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
         mbar_wait(&empty[stage], phase ^ 1);
         mbar_expect_tx(&full[stage], (i_boxes + j_boxes) * WG_BOX_BYTES);
         for (int c = 0; c < i_boxes; c++)
-          tma_load_2d(sP + stage * OP_BYTES + c * WG_BOX_BYTES, &tmP, &full[stage], c * 32, b * WG_ROWS);
+          tma_load_2d(sP + stage * OP_BYTES + c * WG_BOX_BYTES, &tmP, &full[stage], c * 32, WG_BLK(b) * WG_ROWS);
         for (int c = 0; c < j_boxes; c++)
-          tma_load_2d(sQ + stage * OP_BYTES + c * WG_BOX_BYTES, &tmQ, &full[stage], c * 32, b * WG_ROWS);
+          tma_load_2d(sQ + stage * OP_BYTES + c * WG_BOX_BYTES, &tmQ, &full[stage], c * 32, WG_BLK(b) * WG_ROWS);
         if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -556,6 +568,7 @@ extern "C" TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, c
   }
   mlp::WgradParams wp;
   wp.M = M; wp.I = I; wp.J = J; wp.D = D; wp.ldd = ldd;
+  wp.reverse = 0;
   const int nblk = (M + mlp::WG_ROWS - 1) / mlp::WG_ROWS;
   const int grid = nblk < mlp::num_sms() ? nblk : mlp::num_sms();
   mlp::wgrad_tf32_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
@@ -578,36 +591,40 @@ __device__ __forceinline__ float rna_tf32(float x) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
   return __uint_as_float(u);
 }
-// One warp per row, lanes across the output columns (coalesced 128-byte stores); every output needs
-// one sinf or cosf (full-precision: arguments reach 2^9 * x).
+// One warp per row.  Lane (k, comp) evaluates one full-precision sincosf (arguments reach 2^9 * x) and
+// drops sin and cos into the warp's staging row; the row is then written with coalesced stores.
+constexpr int EMB_MAX_COLS = 128;
 __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* __restrict__ xyz,
                                                            const float* __restrict__ t, int t_stride, int Lx, int Lt,
                                                            float* __restrict__ out, int ld) {
-  const int lane = threadIdx.x & 31;
+  __shared__ float s_row[8][EMB_MAX_COLS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int warps_per_grid = (gridDim.x * blockDim.x) >> 5;
   const int nx = 3 + 6 * Lx;           // columns of the xyz part
   const int ncol = nx + 1 + 2 * Lt;
+  float* row = s_row[w];
   for (int m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < M; m += warps_per_grid) {
     const float x0 = xyz[3 * m], x1 = xyz[3 * m + 1], x2 = xyz[3 * m + 2];
     const float tv = t[(size_t)m * t_stride];
-    float* o = out + (size_t)m * ld;
-    for (int c = lane; c < ncol; c += 32) {
-      float v;
-      if (c < 3) {
-        v = c == 0 ? x0 : (c == 1 ? x1 : x2);
-      } else if (c < nx) {
-        const int k = (c - 3) / 6, r = (c - 3) - 6 * k, comp = r % 3;
-        const float a = (comp == 0 ? x0 : (comp == 1 ? x1 : x2)) * exp2f((float)k);
-        v = r < 3 ? sinf(a) : cosf(a);
-      } else if (c == nx) {
-        v = tv;
-      } else {
-        const int j = c - nx - 1, k = j >> 1;
-        const float a = tv * exp2f((float)k);
-        v = (j & 1) ? cosf(a) : sinf(a);
-      }
-      o[c] = rna_tf32(v);
+    if (lane < 3) row[lane] = lane == 0 ? x0 : (lane == 1 ? x1 : x2);
+    if (lane == 3) row[nx] = tv;
+    for (int e = lane; e < 3 * Lx; e += 32) {       // (k, comp) pairs of the xyz part
+      const int k = e / 3, comp = e - 3 * k;
+      float sv, cv;
+      sincosf((comp == 0 ? x0 : (comp == 1 ? x1 : x2)) * exp2f((float)k), &sv, &cv);
+      row[3 + 6 * k + comp] = sv;
+      row[3 + 6 * k + 3 + comp] = cv;
     }
+    for (int k = lane; k < Lt; k += 32) {
+      float sv, cv;
+      sincosf(tv * exp2f((float)k), &sv, &cv);
+      row[nx + 1 + 2 * k] = sv;
+      row[nx + 2 + 2 * k] = cv;
+    }
+    __syncwarp();
+    float* o = out + (size_t)m * ld;
+    for (int c = lane; c < ncol; c += 32) o[c] = rna_tf32(row[c]);
+    __syncwarp();
   }
 }
 
@@ -619,7 +636,8 @@ extern "C" TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const 
                                                  float* out, int ld, void* stream) {
   using namespace tb;
   if (M <= 0) return 0;
-  if (!xyz || !t || !out || Lx < 0 || Lt < 0 || ld < 3 + 6 * Lx + 1 + 2 * Lt) {
+  if (!xyz || !t || !out || Lx < 0 || Lt < 0 || ld < 3 + 6 * Lx + 1 + 2 * Lt ||
+      3 + 6 * Lx + 1 + 2 * Lt > mlp::EMB_MAX_COLS) {
     set_error("trase_b200_deform_embed: bad arguments");
     return 1;
   }

@@ -31,7 +31,7 @@
 #include "common.cuh"
 
 namespace tb {
-namespace mlp { extern int g_allow_resident; extern int g_prefetch_tiles; }
+namespace mlp { extern int g_allow_resident; extern int g_prefetch_tiles; extern int g_snake; }
 
 struct Tuning {
   int fwd_ppt = 2;
@@ -41,7 +41,7 @@ static Tuning g_tuning;
 void set_tuning(const char* key, int value);
 
 constexpr int FWD_BATCH = 128;
-constexpr int BWD_BATCH = 64;
+constexpr int BWD_BATCH = 256;
 constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ float splat_power(const float2 xy, const float4 co, float pxf, float pyf, float& dx,
@@ -56,13 +56,18 @@ __device__ __forceinline__ float splat_power(const float2 xy, const float4 co, f
 // reach alpha >= 1/255:  o*exp(-q/2) >= 1/255  <=>  q = d^T C d <= 2 ln(255 o), and over that ellipse
 // |dx| <= sqrt(2 ln(255 o) * (C^-1)_xx).  Used only to skip whole (warp, splat) pairs early; the exact
 // per-pixel test still decides every pair that is evaluated, so results are unchanged.
-__device__ __forceinline__ float2 splat_reach(const float4 co) {
-  const float t2 = 2.f * __logf(255.f * co.w);
+// .z = a power threshold: o*exp(power) < 1/255 for every power below it (with slack), so such pairs skip
+// the expf; pairs at or above it go through the exact test.
+__device__ __forceinline__ float3 splat_reach(const float4 co) {
+  const float t = __logf(255.f * co.w);
+  const float t2 = 2.f * t;
   const float det = co.x * co.z - co.y * co.y;
-  if (!(t2 > 0.f)) return make_float2(-1.f, -1.f);            // opacity below 1/255: never blends
-  if (!(det > 0.f) || !isfinite(det)) return make_float2(3.0e38f, 3.0e38f);
+  const float thr = (t == t) ? -(t + 1e-3f * (1.f + fabsf(t))) : -3.0e38f;
+  if (!(t2 > 0.f)) return make_float3(-1.f, -1.f, thr);       // opacity below 1/255: never blends
+  if (!(det > 0.f) || !isfinite(det)) return make_float3(3.0e38f, 3.0e38f, thr);
   const float inv = 1.f / det;
-  float2 r;
+  float3 r;
+  r.z = thr;
   r.x = sqrtf(t2 * co.z * inv) * 1.002f + 0.05f;              // generous margin over fp32 rounding
   r.y = sqrtf(t2 * co.x * inv) * 1.002f + 0.05f;
   if (!(r.x == r.x)) r.x = 3.0e38f;
@@ -86,7 +91,7 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
   __shared__ float4 s_co[FWD_BATCH];
   __shared__ float4 s_rgbd[FWD_BATCH];
   __shared__ float4 s_feat[FWD_BATCH * 8];
-  __shared__ float2 s_reach[FWD_BATCH];
+  __shared__ float3 s_reach[FWD_BATCH];
 
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
   const uint2 range = q.ranges[tile];
@@ -135,7 +140,7 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
     if (!all_done) {
       for (int j = 0; j < n; j++) {
         const float2 xy = s_xy[j];
-        const float2 reach = s_reach[j];
+        const float3 reach = s_reach[j];
         // warp-uniform: the splat cannot touch this warp's pixel rectangle
         if (fmaxf(fmaxf(wx0 - xy.x, xy.x - wx1), 0.f) > reach.x || fmaxf(fmaxf(wy0 - xy.y, xy.y - wy1), 0.f) > reach.y)
           continue;
@@ -149,7 +154,7 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
           if (!done[p]) {
             float dx, dy;
             const float power = splat_power(xy, co, pxf, pyf[p], dx, dy);
-            if (!(power > 0.0f)) {
+            if (!(power > 0.0f) && !(power < reach.z)) {
               const float alpha = fminf(0.99f, co.w * expf(power));
               if (!(alpha < 1.0f / 255.0f)) {
                 const float test_T = T[p] * (1 - alpha);
@@ -319,7 +324,7 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
   __shared__ float4 s_co[BWD_BATCH];
   __shared__ float4 s_rgbd[BWD_BATCH];
   __shared__ float4 s_feat[BWD_BATCH * 8];
-  __shared__ float2 s_reach[BWD_BATCH];
+  __shared__ float3 s_reach[BWD_BATCH];
   __shared__ uint32_t s_max[NT / 32];
 
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
@@ -391,7 +396,7 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
       const uint32_t e = (uint32_t)(hi - 1 - k);
       if (e >= warp_last) continue;                         // warp-uniform
       const float2 xy = s_xy[k];
-      const float2 reach = s_reach[k];
+      const float3 reach = s_reach[k];
       if (fmaxf(fmaxf(wx0 - xy.x, xy.x - wx1), 0.f) > reach.x || fmaxf(fmaxf(wy0 - xy.y, xy.y - wy1), 0.f) > reach.y)
         continue;                                           // warp-uniform
       const float4 co = s_co[k];
@@ -403,7 +408,7 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
         act[p] = false;
         if (e < last[p]) {
           const float power = splat_power(xy, co, pxf, pyf[p], dx[p], dy[p]);
-          if (!(power > 0.0f)) {
+          if (!(power > 0.0f) && !(power < reach.z)) {
             G[p] = expf(power);
             alpha[p] = fminf(0.99f, co.w * G[p]);
             if (!(alpha[p] < 1.0f / 255.0f)) {
@@ -516,6 +521,7 @@ void set_tuning(const char* key, int value) {
   if (eq(key, "bwd_ppt")) g_tuning.bwd_ppt = value;
   if (eq(key, "gemm_resident")) mlp::g_allow_resident = value;
   if (eq(key, "gemm_prefetch")) mlp::g_prefetch_tiles = value;
+  if (eq(key, "gemm_snake")) mlp::g_snake = value;
 }
 
 }  // namespace tb
