@@ -33,6 +33,8 @@ WORKLOADS = {  # BASELINE.json configs
     "neu3d": dict(P=300_000, W=1352, H=1014, seed=2, desc="configs[1]: Neu3D-shaped 300k Gaussians 1352x1014, "
                   "DeformNetwork MLP + RGB+feature fwd+bwd"),
     "tiny": dict(P=20_000, W=128, H=128, seed=1, desc="configs[0]: tiny 20k Gaussians 128x128"),
+    "inference2m": dict(P=2_000_000, W=1920, H=1080, seed=4, desc="configs[3]: 2M Gaussians 1920x1080 feature-field "
+                        "inference (DeformNetwork + RGB+feature+depth forward, no backward)"),
 }
 
 
@@ -283,7 +285,12 @@ def run_ours(args, rank, world, device):
     cfg = wl.cfg
     step = lambda: wl.step_resident(world)
     sampler = ClockSampler(device.index) if rank == 0 else None
-    ms = timed_region(step, args.steps, args.warmup, world, device, sampler)
+    # launches of OUR kernels in the timed region (counted by the library itself); warm-up excluded
+    for _ in range(args.warmup):
+        step()
+    l0 = _lib.launch_count()
+    ms = timed_region(step, args.steps, 0, world, device, sampler)
+    launches = _lib.launch_count() - l0
     value = world * args.steps / (ms / 1e3)
     clocks = sampler.summary() if sampler else None
 
@@ -329,7 +336,6 @@ def run_ours(args, rank, world, device):
                     "launch_ms": stages[dom]["ms"],
                     "note": "compositing kernels are FP32/shuffle-bound on (pixel,Gaussian) pairs, not HBM-bound "
                             "(SURVEY.md §8d); HBM fraction is low by construction"}
-        launches_per_step = 3 + 3 * n_pass + 2 + 2  # preprocess, scan, duplicate, sort passes, ranges, render; bwd x2
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
@@ -342,12 +348,32 @@ def run_ours(args, rank, world, device):
                        "+ workspaces) exceeds the 126 MB L2"},
             "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": wl.h2d_bytes(),
                     "d2h_bytes_per_step": wl.d2h_bytes(), "ms_per_step": round(ms_e2e / args.steps, 4)},
-            "gpu_launches": launches_per_step * args.steps,
+            "gpu_launches": launches,
             "clocks": clocks, "roofline": roof, "stages": stages,
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(args.workload)
     return line
+
+
+def run_inference(args, rank, world, device):
+    """Extra, not the headline line: views/s of inference rendering (configs[3] shape); views shard
+    round-robin over the ranks with no collective."""
+    from trase_b200 import _lib
+    _lib.load()
+    wl = Workload(args.workload, device, rank, mlp_backend="native" if args.mlp == "native" else "torch")
+
+    def step():
+        with torch.no_grad():
+            return wl.render(wl.view, wl.time)
+
+    ms = timed_region(step, args.steps, args.warmup, world, device)
+    if rank != 0:
+        return None
+    return {"metric": "inference views/sec (RGB+feature+depth)", "value": round(world * args.steps / (ms / 1e3), 3),
+            "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": wl.cfg["desc"], "mlp": args.mlp}}
 
 
 def run_reference(args, rank, world, device):
@@ -416,7 +442,8 @@ def main():
             if not have_gpu:
                 raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
                                  "(use --impl reference for the CPU port)")
-            line = run_ours(args, rank, world, device)
+            line = run_inference(args, rank, world, device) if args.workload == "inference2m" else \
+                run_ours(args, rank, world, device)
         if rank == 0 and line is not None:
             print(json.dumps(line), flush=True)
     finally:

@@ -204,6 +204,9 @@ TRASE_API int trase_b200_rasterize_backward_stages(const trase_b200_bwd_args* ar
  * recorded events, returns the number of stages and fills total_ms[i] /
  * count[i] (i: 0 preprocess_fwd, 1 scan+duplicate, 2 sort, 3 ranges,
  * 4 render_fwd, 5 render_bwd, 6 preprocess_bwd, 7 unused), then clears. */
+/* Number of CUDA kernels this library has launched in this process so far (no
+ * reference counterpart; bench.py reports the difference over its timed region). */
+TRASE_API unsigned long long trase_b200_launch_count(void);
 TRASE_API void trase_b200_profile_enable(int on);
 TRASE_API int trase_b200_profile_read(double* total_ms, int* count);
 

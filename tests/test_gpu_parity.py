@@ -306,3 +306,55 @@ def test_fused_assembly_matches_torch_glue(native_lib):
     assert (o0["render_gaussian_features"] - o1["render_gaussian_features"]).abs().max() <= 1e-5
     for a, b in zip(g0, g1):
         assert rel_err(_np(a), _np(b)) <= 1e-3
+
+
+def test_config4_inference_shape_against_compiled_reference(native_lib):
+    """BASELINE.json configs[3]: 2 M Gaussians, 1920x1080, forward only (feature-field inference)."""
+    ref_loader = _ref_or_skip()
+    from trase_b200 import synth
+    P, W, H = 2_000_000, 1920, 1080
+    sc = synth.scene_to(synth.make_scene(P, W, H, 4), DEV)
+    bgt = torch.zeros(3, device=DEV)
+    with torch.no_grad():
+        ref = ref_loader.run_forward(sc, bgt)
+        a = scene_args(sc, 0.0, DEV)
+        res = cuda_forward(a)
+    v = views(res, a)
+    assert res.num_rendered == int(ref["num_rendered"])
+    assert torch.equal(res.radii, ref["radii"])
+    assert torch.equal(v["point_list_keys"], ref["point_list_keys"])
+    assert torch.equal(v["point_list"], ref["point_list"])
+    assert torch.equal(v["ranges"], ref["ranges"])
+    assert torch.equal(v["n_contrib"], ref["n_contrib"])
+    assert (res.color - ref["color"]).abs().max() <= 1e-4
+    assert (res.objects - ref["objects"]).abs().max() <= 1e-4
+    assert (res.depth - ref["depth"]).abs().max() <= 1e-4
+
+
+def test_override_color_and_mask_paths_of_render(native_lib):
+    """render() with override_color (render.py's PCA / cluster colour passes) and a boolean mask
+    (gaussian_renderer/__init__.py:123-135) against the oracle on the compacted inputs."""
+    from oracle import oracle
+    from trase_b200 import synth, render as R
+    sc = synth.make_scene(5000, 72, 56, 17)
+    view = R.make_view(sc["cam"], DEV)
+    pc = R.GaussianParams.from_activated(sc, DEV)
+    g = torch.Generator().manual_seed(1)
+    color = torch.rand(5000, 3, generator=g)
+    mask = torch.rand(5000, generator=g) > 0.4
+    z3, z4 = torch.zeros(5000, 3, device=DEV), torch.zeros(5000, 4, device=DEV)
+    with torch.no_grad():
+        out = R.render(view, pc, R.PIPE_DEFAULT, torch.ones(3, device=DEV), z3, z4, z3, override_color=color.to(DEV),
+                       mask=mask.to(DEV))
+    cam = sc["cam"]
+    m = mask.numpy()
+    f = oracle.forward(sc["means3D"].numpy()[m], pc.get_opacity.detach().cpu().numpy()[m],
+                       sc["sh_objs"].numpy()[m], cam["viewmatrix"].numpy(), cam["projmatrix"].numpy(),
+                       cam["campos"].numpy(), 72, 56, cam["tanfovx"], cam["tanfovy"], np.ones(3, np.float32),
+                       colors_precomp=color.numpy()[m], scales=pc.get_scaling.detach().cpu().numpy()[m],
+                       rotations=pc.get_rotation.detach().cpu().numpy()[m])
+    assert out["radii"].shape[0] == int(m.sum())
+    assert np.array_equal(_np(out["radii"]), f["radii"])
+    assert np.abs(_np(out["render"]) - f["color"]).max() <= 1e-4
+    assert np.abs(_np(out["render_gaussian_features"]) - f["objects"]).max() <= 1e-4
+    assert set(out) == {"render", "viewspace_points", "visibility_filter", "radii", "render_gaussian_features", "depth"}

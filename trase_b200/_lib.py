@@ -67,7 +67,7 @@ EXPORTS = [
     "trase_b200_sort_scratch_bytes", "trase_b200_sort_pairs", "trase_b200_higher_msb",
     "trase_b200_set_tuning", "trase_b200_rasterize_backward_stages", "trase_b200_profile_enable",
     "trase_b200_profile_read", "trase_b200_sort_pairs_static", "trase_b200_gemm_tf32", "trase_b200_wgrad_tf32", "trase_b200_deform_embed", "trase_b200_assemble_forward", "trase_b200_assemble_backward", "trase_b200_mlp_round_transpose", "trase_b200_mlp_pack_heads",
-    "trase_b200_mlp_pack_dout",
+    "trase_b200_mlp_pack_dout", "trase_b200_launch_count",
 ]
 
 _lib = None
@@ -136,6 +136,7 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_pack_heads.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 4
     lib.trase_b200_mlp_pack_dout.restype = C.c_int
     lib.trase_b200_mlp_pack_dout.argtypes = [C.c_int] + [C.c_void_p] * 6
+    lib.trase_b200_launch_count.restype = C.c_ulonglong
     lib.trase_b200_higher_msb.restype = C.c_uint32
     lib.trase_b200_higher_msb.argtypes = [C.c_uint32]
     lib.trase_b200_rasterize_backward_stages.restype = C.c_int
@@ -185,6 +186,10 @@ def profile_read() -> dict:
     cnt = (C.c_int * 8)()
     load().trase_b200_profile_read(ms, cnt)
     return {STAGES[i]: (ms[i], cnt[i]) for i in range(8)}
+
+
+def launch_count() -> int:
+    return int(load().trase_b200_launch_count())
 
 
 def set_tuning(key: str, value: int) -> None:

@@ -12,6 +12,7 @@
 namespace tb {
 
 static thread_local char g_err[512] = {0};
+unsigned long long g_launch_count = 0;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -193,6 +194,8 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
                                                p.sort_scratch, p.sort_scratch_bytes, stream));
   TB_STEP_ST(ST_RANGES, "identify_ranges", launch_identify_ranges(*a, p, stream));
   TB_STEP_ST(ST_RENDER_FWD, "render_forward", launch_render_forward(*a, p, stream));
+  // preprocess, block-sum scan, key duplication, 3 kernels per radix pass, ranges, compositing
+  count_launches((with_preprocess ? 1 : 0) + 2 + (a->capacity > 0 ? 3 * sort_num_passes(end_bit) + 1 : 0) + 1);
   return 0;
 }
 
@@ -253,11 +256,14 @@ static int backward_impl(const trase_b200_bwd_args* a, int stages) {
                         const_cast<void*>(a->binning), a->capacity, nullptr);
   if (stages & 1) TB_STEP_ST(ST_RENDER_BWD, "render_backward", launch_render_backward(*a, p, stream));
   if (stages & 2) TB_STEP_ST(ST_PREPROCESS_BWD, "preprocess_backward", launch_preprocess_backward(*a, p, stream));
+  count_launches(((stages & 1) ? 1 : 0) + ((stages & 2) ? 1 : 0));
   return 0;
 }
 
 int trase_b200_rasterize_backward(const trase_b200_bwd_args* a) { return backward_impl(a, 3); }
 int trase_b200_rasterize_backward_stages(const trase_b200_bwd_args* a, int stages) { return backward_impl(a, stages); }
+
+unsigned long long trase_b200_launch_count(void) { return g_launch_count; }
 
 void trase_b200_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(g_prof_mu);

@@ -167,6 +167,7 @@ extern "C" TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const flo
                                                                        reinterpret_cast<float4*>(sh_objs));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_assemble_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(3);
   return 0;
 }
 
@@ -195,5 +196,6 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
       reinterpret_cast<float4*>(g_feat));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_assemble_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(3);
   return 0;
 }

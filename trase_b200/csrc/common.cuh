@@ -111,6 +111,10 @@ inline ScratchLayout scratch_layout(int64_t capacity) {
   return L;
 }
 
+// number of kernels this library has launched (bench.py's gpu_launches)
+extern unsigned long long g_launch_count;
+inline void count_launches(int n) { g_launch_count += (unsigned long long)n; }
+
 // host-side error recording (api.cu)
 void set_error(const char* fmt, ...);
 

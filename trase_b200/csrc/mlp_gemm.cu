@@ -400,6 +400,7 @@ extern "C" TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const flo
     set_error("trase_b200_gemm_tf32: CUDA error: %s", cudaGetErrorString(e));
     return 2;
   }
+  count_launches(1);
   return 0;
 }
 
@@ -574,6 +575,7 @@ extern "C" TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, c
   mlp::wgrad_tf32_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_wgrad_tf32: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
   return 0;
 }
 
@@ -646,5 +648,6 @@ extern "C" TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const 
                                                                                       ld);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_deform_embed: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
   return 0;
 }

@@ -101,6 +101,7 @@ extern "C" TRASE_API int trase_b200_mlp_round_transpose(const float* W, int rows
   mlp::round_transpose_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(W, rows, cols, col0, ncols, Wr, WrT);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_round_transpose: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
   return 0;
 }
 
@@ -115,6 +116,7 @@ extern "C" TRASE_API int trase_b200_mlp_pack_heads(const float* w0, const float*
                                                                                                wh, whT, bh);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_heads: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
   return 0;
 }
 
@@ -127,5 +129,6 @@ extern "C" TRASE_API int trase_b200_mlp_pack_dout(int M, const float* g0, const 
   mlp::pack_dout_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(M, g0, g1, g2, dout, colsum);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_dout: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
   return 0;
 }
