@@ -75,6 +75,34 @@ __device__ __forceinline__ float3 splat_reach(const float4 co) {
   return r;
 }
 
+// Smallest value of q(d) = a dx^2 + 2 b dx dy + c dy^2 (power = -q/2) over the axis-aligned rectangle
+// dx in [u0,u1], dy in [v0,v1] (offsets of a warp's pixel block from the splat centre), for a positive
+// definite conic.  A pair can blend only if q <= -2*thr somewhere in the block, so a splat whose minimum
+// exceeds that can be dropped for the whole warp before any per-pixel work.
+__device__ __forceinline__ float min_q_over_rect(float a, float b, float c, float u0, float u1, float v0, float v1) {
+  if (u0 <= 0.f && u1 >= 0.f && v0 <= 0.f && v1 >= 0.f) return 0.f;
+  float best = 3.0e38f;
+#pragma unroll
+  for (int s = 0; s < 2; s++) {
+    const float U = s ? u1 : u0;                       // edge dx = U
+    const float v = fminf(fmaxf(-b * U / c, v0), v1);
+    best = fminf(best, a * U * U + 2.f * b * U * v + c * v * v);
+    const float V = s ? v1 : v0;                       // edge dy = V
+    const float u = fminf(fmaxf(-b * V / a, u0), u1);
+    best = fminf(best, a * u * u + 2.f * b * u * V + c * V * V);
+  }
+  return best;
+}
+// true if the splat may blend into some pixel of the block [wx0,wx1] x [wy0,wy1]
+__device__ __forceinline__ bool splat_may_touch(const float2 xy, const float4 co, const float3 reach, float wx0,
+                                                float wx1, float wy0, float wy1) {
+  if (fmaxf(fmaxf(wx0 - xy.x, xy.x - wx1), 0.f) > reach.x || fmaxf(fmaxf(wy0 - xy.y, xy.y - wy1), 0.f) > reach.y)
+    return false;
+  if (reach.x > 1.0e37f) return true;                  // degenerate conic: no tight test
+  const float qmin = min_q_over_rect(co.x, co.y, co.z, wx0 - xy.x, wx1 - xy.x, wy0 - xy.y, wy1 - xy.y);
+  return qmin * 0.998f <= -2.f * reach.z + 1e-3f;
+}
+
 struct RenderFwdParams {
   const uint2* ranges; const uint32_t* point_list;
   int W, H;
@@ -95,12 +123,14 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
 
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
   const uint2 range = q.ranges[tile];
-  const int px = blockIdx.x * TILE + (threadIdx.x & 15);
-  const int py0 = blockIdx.y * TILE + (threadIdx.x >> 4) * PPT;
+  // each warp owns a compact 8 x (4*PPT) pixel block (small extent = few splats survive the per-warp
+  // test); lane l sits in column l&7 and owns PPT vertically adjacent pixels
+  const int wbx = ((threadIdx.x >> 5) & 1) * 8, wby = (threadIdx.x >> 6) * 4 * PPT;
+  const int px = blockIdx.x * TILE + wbx + (threadIdx.x & 7);
+  const int py0 = blockIdx.y * TILE + wby + ((threadIdx.x >> 3) & 3) * PPT;
   const float pxf = (float)px;
-  // pixel rectangle of this warp: 16 columns x (2*PPT) rows
-  const float wx0 = (float)(blockIdx.x * TILE), wx1 = wx0 + 15.f;
-  const float wy0 = (float)(blockIdx.y * TILE + (threadIdx.x >> 5) * 2 * PPT), wy1 = wy0 + (float)(2 * PPT - 1);
+  const float wx0 = (float)(blockIdx.x * TILE + wbx), wx1 = wx0 + 7.f;
+  const float wy0 = (float)(blockIdx.y * TILE + wby), wy1 = wy0 + (float)(4 * PPT - 1);
 
   float pyf[PPT], T[PPT], C[PPT][3], D[PPT], O[PPT][NUM_OBJECTS];
   bool done[PPT], inside[PPT];
@@ -137,17 +167,25 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
     }
     __syncthreads();
 
-    if (!all_done) {
-      for (int j = 0; j < n; j++) {
+    if (!__all_sync(0xffffffffu, all_done)) {   // warp-uniform: the block below uses full-warp ballots
+      // 32 splats at a time: lane l tests splat sub+l against this warp's pixel block, survivors are
+      // then composited pixel-parallel in list order
+      const int lane = threadIdx.x & 31;
+      bool still = true;
+      for (int sub = 0; sub < n && still; sub += 32) {
+        const int jj = sub + lane;
+        bool cand = false;
+        if (jj < n) cand = splat_may_touch(s_xy[jj], s_co[jj], s_reach[jj], wx0, wx1, wy0, wy1);
+        unsigned cmask = __ballot_sync(0xffffffffu, cand);
+        while (cmask) {
+          const int j = sub + __ffs(cmask) - 1;
+          cmask &= cmask - 1;
         const float2 xy = s_xy[j];
         const float3 reach = s_reach[j];
-        // warp-uniform: the splat cannot touch this warp's pixel rectangle
-        if (fmaxf(fmaxf(wx0 - xy.x, xy.x - wx1), 0.f) > reach.x || fmaxf(fmaxf(wy0 - xy.y, xy.y - wy1), 0.f) > reach.y)
-          continue;
         const float4 co = s_co[j];
         float w[PPT];
         bool any = false;
-        bool still = false;
+        still = false;
 #pragma unroll
         for (int p = 0; p < PPT; p++) {
           w[p] = 0.f;
@@ -192,7 +230,10 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
             }
           }
         }
+        // the candidate loop is warp-uniform (ballots): leave it only when the whole warp is finished
+        still = __any_sync(0xffffffffu, still);
         if (!still) break;
+        }
       }
     }
   }
@@ -330,12 +371,15 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
   const uint2 range = q.ranges[tile];
   const int lane = threadIdx.x & 31;
-  const int px = blockIdx.x * TILE + (threadIdx.x & 15);
-  const int py0 = blockIdx.y * TILE + (threadIdx.x >> 4) * PPT;
+  // each warp owns a compact 8 x (4*PPT) pixel block (small extent = few splats survive the per-warp
+  // test); lane l sits in column l&7 and owns PPT vertically adjacent pixels
+  const int wbx = ((threadIdx.x >> 5) & 1) * 8, wby = (threadIdx.x >> 6) * 4 * PPT;
+  const int px = blockIdx.x * TILE + wbx + (threadIdx.x & 7);
+  const int py0 = blockIdx.y * TILE + wby + ((threadIdx.x >> 3) & 3) * PPT;
   const float pxf = (float)px;
   const size_t HW = (size_t)q.H * q.W;
-  const float wx0 = (float)(blockIdx.x * TILE), wx1 = wx0 + 15.f;
-  const float wy0 = (float)(blockIdx.y * TILE + (threadIdx.x >> 5) * 2 * PPT), wy1 = wy0 + (float)(2 * PPT - 1);
+  const float wx0 = (float)(blockIdx.x * TILE + wbx), wx1 = wx0 + 7.f;
+  const float wy0 = (float)(blockIdx.y * TILE + wby), wy1 = wy0 + (float)(4 * PPT - 1);
 
   float pyf[PPT], T[PPT], T_final[PPT], S[PPT], last_alpha[PPT], last_dot[PPT], bg_dot[PPT];
   float dLc[PPT][3], dLo[PPT][NUM_OBJECTS];
@@ -392,13 +436,21 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
     }
     __syncthreads();
 
-    for (int k = 0; k < n; k++) {
+    for (int sub = 0; sub < n; sub += 32) {
+      // lane l tests splat sub+l (list element e = hi-1-(sub+l)) against this warp's pixel block
+      bool cand = false;
+      {
+        const int kk = sub + lane;
+        if (kk < n && (uint32_t)(hi - 1 - kk) < warp_last)
+          cand = splat_may_touch(s_xy[kk], s_co[kk], s_reach[kk], wx0, wx1, wy0, wy1);
+      }
+      unsigned cmask = __ballot_sync(FULL, cand);
+      while (cmask) {
+      const int k = sub + __ffs(cmask) - 1;
+      cmask &= cmask - 1;
       const uint32_t e = (uint32_t)(hi - 1 - k);
-      if (e >= warp_last) continue;                         // warp-uniform
       const float2 xy = s_xy[k];
       const float3 reach = s_reach[k];
-      if (fmaxf(fmaxf(wx0 - xy.x, xy.x - wx1), 0.f) > reach.x || fmaxf(fmaxf(wy0 - xy.y, xy.y - wy1), 0.f) > reach.y)
-        continue;                                           // warp-uniform
       const float4 co = s_co[k];
       float w[PPT], G[PPT], dx[PPT], dy[PPT], alpha[PPT];
       bool act[PPT];
@@ -490,6 +542,7 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
         else if (lane == 7) dst = q.dL_dconic + (size_t)id * 4 + 3;
         else dst = q.dL_dopacity + id;
         atomicAdd(dst, tot_s);
+      }
       }
     }
   }

@@ -67,13 +67,17 @@ def make_scene(P: int, W: int, H: int, seed: int = 1, sh_degree: int = 3, target
     means3D = torch.stack([x, y, z], 1).contiguous()
 
     s0 = (target_radius_px / 3.0) * 4.75 / f
-    scales = torch.exp(math.log(s0) + 0.6 * N(P, 3)).contiguous()
+    # transcendental / reduction steps run in float64 and are narrowed once, so that the fp32 scene does not
+    # depend on how the CPU vectorises (thread count, SIMD tails)
+    scales = torch.exp(math.log(s0) + 0.6 * N(P, 3).double()).float().contiguous()
     q = N(P, 4)
-    rotations = (q / q.norm(dim=1, keepdim=True) + 0.01 * N(P, 4)).contiguous()  # deliberately non-unit
-    opacities = torch.sigmoid(2.0 * N(P, 1)).contiguous()
+    qd = q.double()
+    rotations = ((qd / qd.norm(dim=1, keepdim=True)).float() + 0.01 * N(P, 4)).contiguous()  # deliberately non-unit
+    opacities = torch.sigmoid(2.0 * N(P, 1).double()).float().contiguous()
     shs = torch.cat([N(P, 1, 3), 0.1 * N(P, 15, 3)], 1).contiguous()
     feats = N(P, 1, 32)
-    sh_objs = (feats / (feats.norm(dim=2, keepdim=True) + 1e-9)).contiguous()
+    fd = feats.double()
+    sh_objs = (fd / (fd.norm(dim=2, keepdim=True) + 1e-9)).float().contiguous()
     return dict(P=P, sh_degree=sh_degree, means3D=means3D, scales=scales, rotations=rotations,
                 opacities=opacities, shs=shs, sh_objs=sh_objs, cam=cam, seed=seed)
 
