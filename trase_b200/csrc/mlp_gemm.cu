@@ -327,7 +327,7 @@ bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t col
 int g_prefetch_tiles = 0;
 int g_snake = 0;              // alternate the row-tile direction between consecutive GEMM launches
 int g_snake_phase = 0;    // tuning switch ("gemm_prefetch")
-int g_allow_resident = 1;   // tuning switch (trase_b200_set_tuning "gemm_resident")
+int g_allow_resident = 0;   // tuning switch (trase_b200_set_tuning "gemm_resident")
 static int g_num_sms = 0;
 static int num_sms() {
   if (!g_num_sms) {
@@ -381,7 +381,7 @@ extern "C" TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const flo
     return 1;
   }
   const bool small = N <= 16;
-  const bool resident = false;  // the resident-weights variant measured slower (the epilogue, not L2, is the limiter)
+  const bool resident = !small && N == 256 && K <= mlp::RES_MAX_KB * mlp::BK && mlp::g_allow_resident;
   CUtensorMap tA, tB;
   const bool ok = mlp::make_tmap_2d(&tA, A, M, K, lda, mlp::BM, mlp::BK) &&
                   mlp::make_tmap_2d(&tB, B, N, K, ldb, small ? 16 : (resident ? 128 : 256), mlp::BK);
@@ -394,8 +394,8 @@ extern "C" TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const flo
   ep.round_tf32 = round_tf32; ep.prefetch_tiles = mlp::g_prefetch_tiles; ep.reverse = mlp::g_snake ? (mlp::g_snake_phase++ & 1) : 0; ep.D = D; ep.ldd = ldd; ep.M = M; ep.N = N; ep.K = K;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   cudaError_t e = small ? mlp::launch_gemm_tn<16, false>(tA, tB, ep, st)
-                        : mlp::launch_gemm_tn<256, false>(tA, tB, ep, st);
-  (void)resident;
+                        : (resident ? mlp::launch_gemm_tn<128, true>(tA, tB, ep, st)
+                                    : mlp::launch_gemm_tn<256, false>(tA, tB, ep, st));
   if (e != cudaSuccess) {
     set_error("trase_b200_gemm_tf32: CUDA error: %s", cudaGetErrorString(e));
     return 2;
