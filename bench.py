@@ -123,7 +123,8 @@ class Workload:
         self.params = list(self.pc.parameters()) + list(self.deform.parameters())
         # one flat gradient arena; every .grad is a view into it (single memset, single all-reduce)
         from trase_b200.distributed import GradArena
-        self.grad_arena = GradArena(self.params)
+        # the Gaussians' own gradients are final before the MLP backward starts: early segment, reduced under it
+        self.grad_arena = GradArena(self.params, early=list(self.pc.parameters()))
         self.arena = self.grad_arena.flat
         # e2e leg: ground-truth image + camera block in pinned host memory
         g = torch.Generator().manual_seed(99 + rank)
@@ -134,6 +135,7 @@ class Workload:
         self.gt_dev = torch.empty(3, H, W, device=device)
         self.cam_dev = torch.empty_like(cam_block, device=device)
         self.loss_host = torch.zeros(1).pin_memory()
+        self.copy_stream = torch.cuda.Stream(device=device)
         self.last_R = None
 
     def render(self, view, time_t, rasterizer_cls=None):
@@ -154,10 +156,10 @@ class Workload:
         """Inputs already in HBM: fwd + bwd with fixed upstream gradients."""
         self.arena.zero_()
         out = self.render(self.view, self.time, rasterizer_cls)
+        self.grad_arena.arm()
         torch.autograd.backward([out["render"], out["render_gaussian_features"]],
                                 [self.dL_dcolor, self.dL_dobjects])
-        if world_size > 1:
-            dist.all_reduce(self.arena)
+        self.grad_arena.all_reduce()
         return out
 
     def step_e2e(self, world_size=1, rasterizer_cls=None):
@@ -165,8 +167,13 @@ class Workload:
         block and ground-truth image, L1 colour loss + feature-norm regulariser
         (train.py:235-243, 280), backward, D2H of the loss."""
         from types import SimpleNamespace
-        self.gt_dev.copy_(self.gt_host, non_blocking=True)
+        # the camera block is needed at once; the ground-truth image is only read by the loss, so its
+        # copy runs on a side stream under this step's forward pass and the loss waits for it
+        main = torch.cuda.current_stream()
         self.cam_dev.copy_(self.cam_host, non_blocking=True)
+        self.copy_stream.wait_stream(main)      # the previous step's loss has finished reading gt_dev
+        with torch.cuda.stream(self.copy_stream):
+            self.gt_dev.copy_(self.gt_host, non_blocking=True)
         v = self.view
         view = SimpleNamespace(FoVx=v.FoVx, FoVy=v.FoVy, image_height=v.image_height, image_width=v.image_width,
                                world_view_transform=self.cam_dev[0:16].view(4, 4),
@@ -174,11 +181,12 @@ class Workload:
         t = self.cam_dev[35:36].expand(self.cfg["P"], 1)
         self.arena.zero_()
         out = self.render(view, t, rasterizer_cls)
+        main.wait_stream(self.copy_stream)
         loss = (out["render"] - self.gt_dev).abs().mean() + \
             ((out["render_gaussian_features"].norm(dim=0) - 1.0) ** 2).mean()
+        self.grad_arena.arm()
         loss.backward()
-        if world_size > 1:
-            dist.all_reduce(self.arena)
+        self.grad_arena.all_reduce()
         self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return float(self.loss_host[0])

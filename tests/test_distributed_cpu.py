@@ -32,21 +32,28 @@ def _view_loss(model, v):
     return (model(x) ** 2).sum() * (1.0 + 0.1 * v)
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, overlap=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         model = _model()
-        arena = GradArena(model.parameters())
+        # overlap: the LAST layer's gradients are final first in backward; they form the early segment
+        arena = GradArena(model.parameters(), early=list(model[2].parameters()) if overlap else ())
         arena.zero()
-        for v in shard_views(5, rank, world):
+        views = shard_views(5, rank, world)
+        for k, v in enumerate(views):
+            if overlap and k == len(views) - 1:
+                arena.arm()
             _view_loss(model, v).backward()          # accumulates into the arena views in place
+        if overlap:
+            assert arena._work is not None and arena.n_early == 8 * 3 + 3
         stats = torch.tensor([float(rank + 1)]), torch.tensor([1.0]), torch.tensor([3 + 4 * rank], dtype=torch.int32)
         arena.all_reduce()
         reduce_densification_stats(*stats)
         if rank == 0:
-            torch.save({"flat": arena.flat.clone(), "stats": [s.clone() for s in stats]}, out)
+            flat = torch.cat([arena.view_of(p).reshape(-1) for p in model.parameters()])   # model order
+            torch.save({"flat": flat, "stats": [s.clone() for s in stats]}, out)
     finally:
         dist.destroy_process_group()
 
@@ -69,9 +76,10 @@ def test_arena_views_alias_flat_buffer():
     assert all(not p.grad.any() for p in model.parameters())
 
 
-def test_two_rank_allreduce_equals_sum_of_views(tmp_path):
+@pytest.mark.parametrize("overlap", [False, True])
+def test_two_rank_allreduce_equals_sum_of_views(tmp_path, overlap):
     out = str(tmp_path / "rank0.pt")
-    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), out, overlap), nprocs=2, join=True)
     got = torch.load(out)
     model = _model()
     arena = GradArena(model.parameters())

@@ -7,6 +7,14 @@ fp32 arena (each `.grad` is a view into it), so a step needs one memset and
 one `all_reduce` (NCCL over NVLink on GPUs, gloo in the CPU tests).  The
 arena after the all-reduce equals the sum over views of the single-GPU
 gradients, which is the parity definition for this path.
+
+Overlap: the Gaussians' own gradients (the bulk of the arena: ~90 floats per
+Gaussian) are final as soon as the rasterizer backward and the activation
+glue have run, while the DeformNetwork backward (about 40 % of a step) is
+still ahead.  Parameters passed as `early` are laid out first in the arena;
+once `arm()` has been called, the hook of the last early parameter to
+accumulate starts an asynchronous all-reduce of that segment, which then runs
+under the MLP backward, and `all_reduce()` only has the small tail left.
 """
 from __future__ import annotations
 
@@ -19,10 +27,16 @@ import torch.distributed as dist
 class GradArena:
     """Flat gradient buffer shared by a list of parameters."""
 
-    def __init__(self, params: Iterable[torch.nn.Parameter]):
-        self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
+    def __init__(self, params: Iterable[torch.nn.Parameter], early: Iterable[torch.nn.Parameter] = ()):
+        params = [p for p in params if p.requires_grad]
+        early_ids = {id(p) for p in early}
+        first = [p for p in params if id(p) in early_ids]
+        self.params: List[torch.nn.Parameter] = first + [p for p in params if id(p) not in early_ids]
         if not self.params:
             raise ValueError("GradArena needs at least one parameter that requires grad")
+        self.n_early_params = len(first)
+        self.n_early = sum(p.numel() for p in first)
+        self._armed, self._seen, self._work, self._group = False, 0, None, None
         dev, dt = self.params[0].device, self.params[0].dtype
         if any(p.device != dev or p.dtype != dt for p in self.params):
             raise ValueError("all parameters of an arena must share device and dtype")
@@ -34,13 +48,42 @@ class GradArena:
         self.flat = torch.zeros(n, device=dev, dtype=dt)
         for p, off in zip(self.params, self.offsets):
             p.grad = self.flat[off:off + p.numel()].view_as(p)
+        for p in first:
+            p.register_post_accumulate_grad_hook(self._early_hook)
 
     def zero(self) -> None:
         self.flat.zero_()
 
+    @staticmethod
+    def _multi_rank(group) -> bool:
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+
+    def arm(self, group=None) -> None:
+        """Call before the LAST backward of a step (earlier views of the same step still accumulate
+        into the early segment, so it is not final before that)."""
+        self._armed, self._seen, self._group = self.n_early > 0 and self._multi_rank(group), 0, group
+
+    def _early_hook(self, _param) -> None:
+        if not self._armed:
+            return
+        self._seen += 1
+        if self._seen == self.n_early_params:
+            self._armed = False
+            self._work = dist.all_reduce(self.flat[:self.n_early], op=dist.ReduceOp.SUM, group=self._group,
+                                         async_op=True)
+
     def all_reduce(self, group=None) -> None:
-        """Sum over ranks (sum, not mean: parity is defined against the sum of per-view gradients)."""
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        """Sum over ranks (sum, not mean: parity is defined against the sum of per-view gradients).
+        Finishes an overlapped early-segment reduction if one was started by `arm()`."""
+        if not self._multi_rank(group):
+            return
+        if self._work is not None:
+            self._work.wait()
+            self._work = None
+            if self.n_early < self.flat.numel():
+                dist.all_reduce(self.flat[self.n_early:], op=dist.ReduceOp.SUM, group=group)
+        else:
+            self._armed = False        # armed but some early parameter got no gradient: reduce everything
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
 
     def view_of(self, p: torch.nn.Parameter) -> torch.Tensor:
