@@ -164,8 +164,8 @@ class Workload:
 
     def step_e2e(self, world_size=1, rasterizer_cls=None):
         """Through the public API with HOST buffers: H2D of this view's camera
-        block and ground-truth image, L1 colour loss + feature-norm regulariser
-        (train.py:235-243, 280), backward, D2H of the loss."""
+        block and ground-truth image, the reference's L1 + SSIM colour loss and
+        feature-norm regulariser (train.py:235-238, 280-281), backward, D2H of the loss."""
         from types import SimpleNamespace
         # the camera block is needed at once; the ground-truth image is only read by the loss, so its
         # copy runs on a side stream under this step's forward pass and the loss waits for it
@@ -182,8 +182,16 @@ class Workload:
         self.arena.zero_()
         out = self.render(view, t, rasterizer_cls)
         main.wait_stream(self.copy_stream)
-        loss = (out["render"] - self.gt_dev).abs().mean() + \
-            ((out["render_gaussian_features"].norm(dim=0) - 1.0) ** 2).mean()
+        # the reference's two losses on the path's outputs: GAUSSIAN state (train.py:235-238)
+        # (1 - l) * L1 + l * (1 - SSIM), l = 0.2, and the FEATURE state's norm regulariser (train.py:280-281)
+        if rasterizer_cls is None:
+            from trase_b200 import loss_utils          # fused kernels (csrc/loss.cu)
+            loss = loss_utils.l1_ssim_loss(out["render"], self.gt_dev, 0.2) + \
+                loss_utils.feature_norm_reg(out["render_gaussian_features"])
+        else:
+            from oracle import loss_oracle             # reference arm: the reference's torch formulation
+            loss = loss_oracle.l1_ssim_ref(out["render"], self.gt_dev, 0.2) + \
+                (1.0 - out["render_gaussian_features"].norm(dim=0, p=2).mean()) ** 2
         self.grad_arena.arm()
         loss.backward()
         self.grad_arena.all_reduce()

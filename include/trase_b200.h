@@ -337,6 +337,47 @@ TRASE_API int trase_b200_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in,
                                            uint32_t* vals_out, const uint32_t* count_dev, int64_t capacity,
                                            int end_bit, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Fused L1 + SSIM image loss and its backward.
+ * ref: l1_loss (utils/loss_utils.py:30-31), ssim / _ssim with the 11x11
+ * Gaussian window, sigma 1.5, zero padding 5, C1 = 0.01^2, C2 = 0.03^2
+ * (utils/loss_utils.py:46-86), and the GAUSSIAN-state loss of train.py:235-243,
+ * (1 - l) * L1 + l * (1 - SSIM).  The reference runs five depthwise cuDNN
+ * convolutions plus ~15 elementwise kernels forward and as many again in
+ * autograd.
+ *
+ * img, gt: [C][H][W] fp32 on the device.
+ * forward writes out3 = { mean|img-gt|, mean SSIM, w_l1*L1 + w_ssim*SSIM + bias }
+ * (device floats; fixed-order reduction, deterministic).  `maps` (3*C*H*W
+ * floats, may be NULL when w_ssim == 0) receives the SSIM map's partial
+ * derivatives for backward; `scratch` holds trase_b200_loss_scratch_bytes().
+ * backward writes d_img = sum_k grad_out3[k] * d(out3[k])/d(img) (grad_out3:
+ * three device floats, NULL = {0,0,1}; a term evaluated with w_ssim == 0 and
+ * maps == NULL has no SSIM gradient).  No gradient is produced for gt (the
+ * reference never asks for one).
+ * ---------------------------------------------------------------------- */
+TRASE_API size_t trase_b200_loss_scratch_bytes(int C, int H, int W);
+TRASE_API int trase_b200_l1_ssim_forward(int C, int H, int W, const float* img, const float* gt, float w_l1,
+                                         float w_ssim, float bias, float* maps, float* scratch, float* out3,
+                                         void* stream);
+TRASE_API int trase_b200_l1_ssim_backward(int C, int H, int W, const float* img, const float* gt, const float* maps,
+                                          float w_l1, float w_ssim, const float* grad_out3, float* d_img,
+                                          void* stream);
+
+/* Feature-norm regulariser of the FEATURE training state (SURVEY.md §8(f) rank 3,
+ * first part).  ref: train.py:280-281,
+ *   rendered_feature_norm = rendered_features.norm(dim=0, p=2).mean();  reg = (1 - that)^2.
+ * feat: [C][N] fp32 (N = H*W pixels).  forward writes the per-pixel norm (N
+ * floats, kept for backward) and out2 = { mean norm, reg }; backward writes
+ * d_feat = grad_out2[0] * d(mean)/dF + grad_out2[1] * d(reg)/dF (NULL = {0,1}),
+ * zero where a pixel's norm is zero (as torch's norm backward). */
+TRASE_API size_t trase_b200_feature_norm_scratch_bytes(int64_t N);
+TRASE_API int trase_b200_feature_norm_reg_forward(int C, int64_t N, const float* feat, float* norm, float* scratch,
+                                                  float* out2, void* stream);
+TRASE_API int trase_b200_feature_norm_reg_backward(int C, int64_t N, const float* feat, const float* norm,
+                                                   const float* out2, const float* grad_out2, float* d_feat,
+                                                   void* stream);
+
 /* ref: getHigherMsb (DGR/cuda_rasterizer/rasterizer_impl.cu:38-53). */
 TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);
 

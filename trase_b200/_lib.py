@@ -67,7 +67,9 @@ EXPORTS = [
     "trase_b200_sort_scratch_bytes", "trase_b200_sort_pairs", "trase_b200_higher_msb",
     "trase_b200_set_tuning", "trase_b200_rasterize_backward_stages", "trase_b200_profile_enable",
     "trase_b200_profile_read", "trase_b200_sort_pairs_static", "trase_b200_gemm_tf32", "trase_b200_wgrad_tf32", "trase_b200_deform_embed", "trase_b200_assemble_forward", "trase_b200_assemble_backward", "trase_b200_mlp_round_transpose", "trase_b200_mlp_pack_heads",
-    "trase_b200_mlp_pack_dout", "trase_b200_launch_count",
+    "trase_b200_mlp_pack_dout", "trase_b200_launch_count", "trase_b200_loss_scratch_bytes",
+    "trase_b200_l1_ssim_forward", "trase_b200_l1_ssim_backward", "trase_b200_feature_norm_scratch_bytes",
+    "trase_b200_feature_norm_reg_forward", "trase_b200_feature_norm_reg_backward",
 ]
 
 _lib = None
@@ -136,6 +138,18 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_pack_heads.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 4
     lib.trase_b200_mlp_pack_dout.restype = C.c_int
     lib.trase_b200_mlp_pack_dout.argtypes = [C.c_int] + [C.c_void_p] * 6
+    lib.trase_b200_loss_scratch_bytes.restype = C.c_size_t
+    lib.trase_b200_loss_scratch_bytes.argtypes = [C.c_int] * 3
+    lib.trase_b200_l1_ssim_forward.restype = C.c_int
+    lib.trase_b200_l1_ssim_forward.argtypes = [C.c_int] * 3 + [C.c_void_p] * 2 + [C.c_float] * 3 + [C.c_void_p] * 4
+    lib.trase_b200_feature_norm_scratch_bytes.restype = C.c_size_t
+    lib.trase_b200_feature_norm_scratch_bytes.argtypes = [C.c_int64]
+    lib.trase_b200_feature_norm_reg_forward.restype = C.c_int
+    lib.trase_b200_feature_norm_reg_forward.argtypes = [C.c_int, C.c_int64] + [C.c_void_p] * 5
+    lib.trase_b200_feature_norm_reg_backward.restype = C.c_int
+    lib.trase_b200_feature_norm_reg_backward.argtypes = [C.c_int, C.c_int64] + [C.c_void_p] * 6
+    lib.trase_b200_l1_ssim_backward.restype = C.c_int
+    lib.trase_b200_l1_ssim_backward.argtypes = [C.c_int] * 3 + [C.c_void_p] * 3 + [C.c_float] * 2 + [C.c_void_p] * 3
     lib.trase_b200_launch_count.restype = C.c_ulonglong
     lib.trase_b200_higher_msb.restype = C.c_uint32
     lib.trase_b200_higher_msb.argtypes = [C.c_uint32]

@@ -1,0 +1,367 @@
+// Fused L1 + SSIM image loss, forward and backward.
+// ref: utils/loss_utils.py:30-31 (l1_loss), :46-86 (gaussian / create_window / ssim / _ssim) and the
+// GAUSSIAN-state loss of train.py:235-243, loss = (1 - l) * L1 + l * (1 - SSIM).
+//
+// The reference evaluates SSIM with five 11x11 depthwise convolutions (zero padding 5) plus ~15
+// image-sized elementwise kernels, and autograd runs as many again.  Here one kernel per direction:
+//   forward : per 32x32 tile, stage the 42x42 halo of both images in shared memory, run the separable
+//             11-tap Gaussian over {x, y, x^2, y^2, xy}, form the SSIM map and its three partial
+//             derivatives (w.r.t. mu1, E[x^2], E[xy]) and reduce |x-y| and SSIM to per-block partials;
+//   backward: convolve the three derivative maps with the same (symmetric) window and combine:
+//             dL/dx = k_l1 * sign(x-y) + k_ssim * (G*Dmu + 2x * G*D11 + y * G*D12),
+//             k_* = (upstream gradient of each term) / N.
+// Partials are reduced in a fixed order by a one-block kernel, so the loss value is deterministic.
+#include "common.cuh"
+
+#include <math.h>
+
+namespace tb {
+
+constexpr int LW = 11, LR = 5;                           // window size and radius
+constexpr int LTX = 32, LTY = 32;                        // output tile
+constexpr int LHX = LTX + 2 * LR, LHY = LTY + 2 * LR;    // tile + halo
+constexpr int LOSS_THREADS = 256;
+constexpr float SSIM_C1 = 0.01f * 0.01f, SSIM_C2 = 0.03f * 0.03f;
+
+struct LossWindow {
+  float g[LW];
+};
+
+// the reference's window: fp32 of exp(-(x-5)^2 / (2 * 1.5^2)), normalised by its fp32 sum
+static LossWindow make_window() {
+  LossWindow w;
+  float sum = 0.f;
+  for (int i = 0; i < LW; i++) {
+    w.g[i] = (float)exp(-(double)((i - LR) * (i - LR)) / (2.0 * 1.5 * 1.5));
+    sum += w.g[i];
+  }
+  for (int i = 0; i < LW; i++) w.g[i] /= sum;
+  return w;
+}
+
+__device__ __forceinline__ float block_sum(float v, float* s_red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();
+  if (lane == 0) s_red[warp] = v;
+  __syncthreads();
+  float t = 0.f;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 0; w < LOSS_THREADS / 32; w++) t += s_red[w];
+  }
+  return t;   // valid on thread 0
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, const LossWindow win,
+                   int do_ssim, float* __restrict__ maps, float* __restrict__ partials) {
+  __shared__ float sx[LHY][LHX + 1], sy[LHY][LHX + 1];
+  __shared__ float sh[5][LHY][LTX];
+  __shared__ float s_red[LOSS_THREADS / 32];
+  const int tx0 = blockIdx.x * LTX, ty0 = blockIdx.y * LTY;
+  const size_t plane = (size_t)H * W;
+  const float* x = img + blockIdx.z * plane;
+  const float* y = gt + blockIdx.z * plane;
+
+  for (int i = threadIdx.x; i < LHY * LHX; i += LOSS_THREADS) {
+    const int r = i / LHX, c = i - r * LHX;
+    const int gy = ty0 + r - LR, gx = tx0 + c - LR;
+    const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+    sx[r][c] = in ? x[(size_t)gy * W + gx] : 0.f;
+    sy[r][c] = in ? y[(size_t)gy * W + gx] : 0.f;
+  }
+  __syncthreads();
+  if (do_ssim) {
+    for (int i = threadIdx.x; i < LHY * LTX; i += LOSS_THREADS) {
+      const int r = i / LTX, c = i - r * LTX;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll
+      for (int k = 0; k < LW; k++) {
+        const float g = win.g[k], xv = sx[r][c + k], yv = sy[r][c + k];
+        a0 = fmaf(g, xv, a0);
+        a1 = fmaf(g, yv, a1);
+        a2 = fmaf(g, xv * xv, a2);
+        a3 = fmaf(g, yv * yv, a3);
+        a4 = fmaf(g, xv * yv, a4);
+      }
+      sh[0][r][c] = a0; sh[1][r][c] = a1; sh[2][r][c] = a2; sh[3][r][c] = a3; sh[4][r][c] = a4;
+    }
+    __syncthreads();
+  }
+  float l1 = 0.f, ss = 0.f;
+  const int c = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < LTY / (LOSS_THREADS / 32); j++) {
+    const int r = (threadIdx.x >> 5) + j * (LOSS_THREADS / 32);
+    const int gy = ty0 + r, gx = tx0 + c;
+    if (gy >= H || gx >= W) continue;
+    const float xv = sx[r + LR][c + LR], yv = sy[r + LR][c + LR];
+    l1 += fabsf(xv - yv);
+    if (!do_ssim) continue;
+    float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int k = 0; k < LW; k++) {
+      const float g = win.g[k];
+      mu1 = fmaf(g, sh[0][r + k][c], mu1);
+      mu2 = fmaf(g, sh[1][r + k][c], mu2);
+      e11 = fmaf(g, sh[2][r + k][c], e11);
+      e22 = fmaf(g, sh[3][r + k][c], e22);
+      e12 = fmaf(g, sh[4][r + k][c], e12);
+    }
+    const float mu1sq = mu1 * mu1, mu2sq = mu2 * mu2, mu12 = mu1 * mu2;
+    const float s1 = e11 - mu1sq, s2 = e22 - mu2sq, s12 = e12 - mu12;
+    const float A1 = 2.f * mu12 + SSIM_C1, A2 = 2.f * s12 + SSIM_C2;
+    const float B1 = mu1sq + mu2sq + SSIM_C1, B2 = s1 + s2 + SSIM_C2;
+    const float inv = 1.f / (B1 * B2);
+    const float S = A1 * A2 * inv;
+    ss += S;
+    if (maps) {
+      // S as a function of (mu1, E[x^2], E[xy]) with s1 = E[x^2] - mu1^2, s12 = E[xy] - mu1 mu2
+      const size_t o = blockIdx.z * plane + (size_t)gy * W + gx;
+      const size_t n = (size_t)gridDim.z * plane;
+      maps[o] = 2.f * (mu2 * (A2 - A1) - mu1 * S * (B2 - B1)) * inv;
+      maps[n + o] = -S / B2;
+      maps[2 * n + o] = 2.f * A1 * inv;
+    }
+  }
+  const float tl1 = block_sum(l1, s_red);
+  const float tss = block_sum(ss, s_red);
+  if (threadIdx.x == 0) {
+    const size_t b = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    partials[2 * b] = tl1;
+    partials[2 * b + 1] = tss;
+  }
+}
+
+// fixed-order reduction of the per-block partials: out = {mean |x-y|, mean SSIM, w_l1 * L1 + w_ssim * SSIM + bias}
+__global__ void __launch_bounds__(LOSS_THREADS)
+l1_ssim_finalize_kernel(int nblocks, const float* __restrict__ partials, double inv_n, float w_l1, float w_ssim,
+                        float bias, float* __restrict__ out) {
+  __shared__ double s0[LOSS_THREADS], s1[LOSS_THREADS];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < nblocks; i += LOSS_THREADS) {
+    a += (double)partials[2 * i];
+    b += (double)partials[2 * i + 1];
+  }
+  s0[threadIdx.x] = a;
+  s1[threadIdx.x] = b;
+  __syncthreads();
+  for (int o = LOSS_THREADS / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) {
+      s0[threadIdx.x] += s0[threadIdx.x + o];
+      s1[threadIdx.x] += s1[threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const float l1 = (float)(s0[0] * inv_n), ss = (float)(s1[0] * inv_n);
+    out[0] = l1;
+    out[1] = ss;
+    out[2] = w_l1 * l1 + w_ssim * ss + bias;
+  }
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt,
+                   const float* __restrict__ maps, const LossWindow win, float w_l1, float w_ssim, float inv_n,
+                   const float* __restrict__ grad_out3, float* __restrict__ d_img) {
+  __shared__ float sm[3][LHY][LHX + 1];
+  __shared__ float sh[3][LHY][LTX];
+  const int tx0 = blockIdx.x * LTX, ty0 = blockIdx.y * LTY;
+  const size_t plane = (size_t)H * W;
+  const size_t n = (size_t)gridDim.z * plane;
+  const size_t base = blockIdx.z * plane;
+  // upstream gradients of {L1, SSIM, combined}: effective weights of the two terms
+  const float g0 = grad_out3 ? grad_out3[0] : 0.f, g1 = grad_out3 ? grad_out3[1] : 0.f;
+  const float g2 = grad_out3 ? grad_out3[2] : 1.f;
+  const float k_l1 = (g2 * w_l1 + g0) * inv_n, k_ssim = (g2 * w_ssim + g1) * inv_n;
+  const bool do_ssim = maps != nullptr;
+  if (do_ssim) {
+    for (int i = threadIdx.x; i < LHY * LHX; i += LOSS_THREADS) {
+      const int r = i / LHX, c = i - r * LHX;
+      const int gy = ty0 + r - LR, gx = tx0 + c - LR;
+      const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      const size_t o = base + (size_t)gy * W + gx;
+      sm[0][r][c] = in ? maps[o] : 0.f;
+      sm[1][r][c] = in ? maps[n + o] : 0.f;
+      sm[2][r][c] = in ? maps[2 * n + o] : 0.f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < LHY * LTX; i += LOSS_THREADS) {
+      const int r = i / LTX, c = i - r * LTX;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < LW; k++) {
+        const float g = win.g[k];
+        a0 = fmaf(g, sm[0][r][c + k], a0);
+        a1 = fmaf(g, sm[1][r][c + k], a1);
+        a2 = fmaf(g, sm[2][r][c + k], a2);
+      }
+      sh[0][r][c] = a0; sh[1][r][c] = a1; sh[2][r][c] = a2;
+    }
+    __syncthreads();
+  }
+  const int c = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < LTY / (LOSS_THREADS / 32); j++) {
+    const int r = (threadIdx.x >> 5) + j * (LOSS_THREADS / 32);
+    const int gy = ty0 + r, gx = tx0 + c;
+    if (gy >= H || gx >= W) continue;
+    const size_t o = base + (size_t)gy * W + gx;
+    const float xv = img[o], yv = gt[o];
+    const float d = xv - yv;
+    float g = k_l1 * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));
+    if (do_ssim) {
+      float cm = 0.f, c11 = 0.f, c12 = 0.f;
+#pragma unroll
+      for (int k = 0; k < LW; k++) {
+        const float w = win.g[k];
+        cm = fmaf(w, sh[0][r + k][c], cm);
+        c11 = fmaf(w, sh[1][r + k][c], c11);
+        c12 = fmaf(w, sh[2][r + k][c], c12);
+      }
+      g += k_ssim * (cm + 2.f * xv * c11 + yv * c12);
+    }
+    d_img[o] = g;
+  }
+}
+
+// ---- feature-norm regulariser (train.py:280-281): reg = (1 - mean_p ||F[:, p]||_2)^2 ------------------
+constexpr int FN_MAX_BLOCKS = 148 * 8;
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+feat_norm_fwd_kernel(int C, long long N, const float* __restrict__ feat, float* __restrict__ norm,
+                     float* __restrict__ partials) {
+  __shared__ float s_red[LOSS_THREADS / 32];
+  float acc = 0.f;
+  for (long long p = (long long)blockIdx.x * LOSS_THREADS + threadIdx.x; p < N; p += (long long)gridDim.x * LOSS_THREADS) {
+    float s = 0.f;
+    for (int c = 0; c < C; c++) {
+      const float f = feat[(size_t)c * N + p];
+      s = fmaf(f, f, s);
+    }
+    const float n = sqrtf(s);
+    norm[p] = n;
+    acc += n;
+  }
+  const float t = block_sum(acc, s_red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+feat_norm_finalize_kernel(int nblocks, const float* __restrict__ partials, double inv_n, float* __restrict__ out2) {
+  __shared__ double s0[LOSS_THREADS];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < nblocks; i += LOSS_THREADS) a += (double)partials[i];
+  s0[threadIdx.x] = a;
+  __syncthreads();
+  for (int o = LOSS_THREADS / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s0[threadIdx.x] += s0[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const float m = (float)(s0[0] * inv_n);
+    out2[0] = m;
+    out2[1] = (1.f - m) * (1.f - m);
+  }
+}
+
+// d reg / d F[c, p] = (g_mean + g_reg * 2 (mean - 1)) / N * F[c, p] / ||F[:, p]||   (0 where the norm is 0)
+__global__ void __launch_bounds__(LOSS_THREADS)
+feat_norm_bwd_kernel(int C, long long N, const float* __restrict__ feat, const float* __restrict__ norm,
+                     const float* __restrict__ out2, const float* __restrict__ grad_out2, float inv_n,
+                     float* __restrict__ d_feat) {
+  const float g_mean = grad_out2 ? grad_out2[0] : 0.f, g_reg = grad_out2 ? grad_out2[1] : 1.f;
+  const float k = (g_mean + g_reg * 2.f * (out2[0] - 1.f)) * inv_n;
+  for (long long p = (long long)blockIdx.x * LOSS_THREADS + threadIdx.x; p < N; p += (long long)gridDim.x * LOSS_THREADS) {
+    const float n = norm[p];
+    const float w = n > 0.f ? k / n : 0.f;
+    for (int c = 0; c < C; c++) d_feat[(size_t)c * N + p] = w * feat[(size_t)c * N + p];
+  }
+}
+
+static int feat_norm_blocks(long long N) {
+  const long long b = (N + LOSS_THREADS - 1) / LOSS_THREADS;
+  return (int)(b < FN_MAX_BLOCKS ? (b > 0 ? b : 1) : FN_MAX_BLOCKS);
+}
+
+static bool loss_dims_ok(int C, int H, int W) {
+  return C > 0 && H > 0 && W > 0 && C <= 65535 && (H + LTY - 1) / LTY <= 65535;
+}
+
+}  // namespace tb
+
+using namespace tb;
+
+extern "C" TRASE_API size_t trase_b200_loss_scratch_bytes(int C, int H, int W) {
+  if (!loss_dims_ok(C, H, W)) return 0;
+  return (size_t)C * ((H + LTY - 1) / LTY) * ((W + LTX - 1) / LTX) * 2 * sizeof(float);
+}
+
+extern "C" TRASE_API int trase_b200_l1_ssim_forward(int C, int H, int W, const float* img, const float* gt, float w_l1,
+                                                    float w_ssim, float bias, float* maps, float* scratch,
+                                                    float* out3, void* stream) {
+  if (!loss_dims_ok(C, H, W)) { set_error("trase_b200_l1_ssim_forward: bad image shape %dx%dx%d", C, H, W); return 1; }
+  if (!img || !gt || !scratch || !out3) { set_error("trase_b200_l1_ssim_forward: null pointer"); return 1; }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  static const LossWindow win = make_window();
+  const dim3 grid((W + LTX - 1) / LTX, (H + LTY - 1) / LTY, C);
+  const int nblocks = (int)(grid.x * grid.y * grid.z);
+  l1_ssim_fwd_kernel<<<grid, LOSS_THREADS, 0, s>>>(H, W, img, gt, win, w_ssim != 0.f ? 1 : 0, maps, scratch);
+  l1_ssim_finalize_kernel<<<1, LOSS_THREADS, 0, s>>>(nblocks, scratch, 1.0 / ((double)C * H * W), w_l1, w_ssim, bias,
+                                                     out3);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_l1_ssim_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(2);
+  return 0;
+}
+
+extern "C" TRASE_API int trase_b200_l1_ssim_backward(int C, int H, int W, const float* img, const float* gt,
+                                                     const float* maps, float w_l1, float w_ssim,
+                                                     const float* grad_out3, float* d_img, void* stream) {
+  if (!loss_dims_ok(C, H, W)) { set_error("trase_b200_l1_ssim_backward: bad image shape %dx%dx%d", C, H, W); return 1; }
+  if (!img || !gt || !d_img || (w_ssim != 0.f && !maps)) { set_error("trase_b200_l1_ssim_backward: null pointer"); return 1; }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  static const LossWindow win = make_window();
+  const dim3 grid((W + LTX - 1) / LTX, (H + LTY - 1) / LTY, C);
+  l1_ssim_bwd_kernel<<<grid, LOSS_THREADS, 0, s>>>(H, W, img, gt, maps, win, w_l1, w_ssim,
+                                                   (float)(1.0 / ((double)C * H * W)), grad_out3, d_img);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_l1_ssim_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+extern "C" TRASE_API size_t trase_b200_feature_norm_scratch_bytes(int64_t N) {
+  return N > 0 ? (size_t)feat_norm_blocks(N) * sizeof(float) : 0;
+}
+
+extern "C" TRASE_API int trase_b200_feature_norm_reg_forward(int C, int64_t N, const float* feat, float* norm,
+                                                             float* scratch, float* out2, void* stream) {
+  if (C <= 0 || N <= 0) { set_error("trase_b200_feature_norm_reg_forward: empty feature image"); return 1; }
+  if (!feat || !norm || !scratch || !out2) { set_error("trase_b200_feature_norm_reg_forward: null pointer"); return 1; }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int nb = feat_norm_blocks(N);
+  feat_norm_fwd_kernel<<<nb, LOSS_THREADS, 0, s>>>(C, N, feat, norm, scratch);
+  feat_norm_finalize_kernel<<<1, LOSS_THREADS, 0, s>>>(nb, scratch, 1.0 / (double)N, out2);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_feature_norm_reg_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(2);
+  return 0;
+}
+
+extern "C" TRASE_API int trase_b200_feature_norm_reg_backward(int C, int64_t N, const float* feat, const float* norm,
+                                                              const float* out2, const float* grad_out2,
+                                                              float* d_feat, void* stream) {
+  if (C <= 0 || N <= 0) { set_error("trase_b200_feature_norm_reg_backward: empty feature image"); return 1; }
+  if (!feat || !norm || !out2 || !d_feat) { set_error("trase_b200_feature_norm_reg_backward: null pointer"); return 1; }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  feat_norm_bwd_kernel<<<feat_norm_blocks(N), LOSS_THREADS, 0, s>>>(C, N, feat, norm, out2, grad_out2,
+                                                                    (float)(1.0 / (double)N), d_feat);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_feature_norm_reg_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
