@@ -378,6 +378,31 @@ TRASE_API int trase_b200_feature_norm_reg_backward(int C, int64_t N, const float
                                                    const float* out2, const float* grad_out2, float* d_feat,
                                                    void* stream);
 
+/* ------------------------------------------------------------------------
+ * DeformNetwork forward as one persistent kernel.  ref: DeformNetwork.forward
+ * (utils/time_utils.py:106-131): nl hidden nn.Linear(256) + ReLU layers, the
+ * input embedding re-concatenated after layer `skip` (embedding columns first,
+ * time_utils.py:117), then the three linear heads (:119-129).
+ * A 128-row tile is carried through all layers on chip; activations are written
+ * to HBM once (for the backward pass) and never read back.
+ *   trase_b200_mlp_fused_pack_floats: size of the packed weight buffer.
+ *   trase_b200_mlp_pack_fused: weights[i] (host array of nl device pointers) =
+ *     layer i's [256][in_i] matrix, wh = the packed [16][256] head matrix
+ *     (trase_b200_mlp_pack_heads) -> TF32-rounded k-block layout.
+ *   trase_b200_mlp_forward_fused: emb [M][ld_emb] (E columns used), bias =
+ *     nl*256 hidden biases then 16 head biases; writes acts [nl][M][256]
+ *     (TF32-rounded post-ReLU activations), masks [nl][M][8] (bit = output > 0)
+ *     and out16 [M][16] (heads: 3 warp, 4 rotation, 3 scaling, 6 zero).
+ * Restrictions: width 256, 2 <= nl <= 11, E <= 96 and a multiple of 4,
+ * skip < nl - 1 (or -1 for none).
+ * ---------------------------------------------------------------------- */
+TRASE_API size_t trase_b200_mlp_fused_pack_floats(int nl, int skip, int E);
+TRASE_API int trase_b200_mlp_pack_fused(int nl, int skip, int E, const float* const* weights, const float* wh,
+                                        float* wpack, void* stream);
+TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const float* emb, int ld_emb,
+                                           const float* wpack, const float* bias, float* acts, uint32_t* masks,
+                                           float* out16, void* stream);
+
 /* ref: getHigherMsb (DGR/cuda_rasterizer/rasterizer_impl.cu:38-53). */
 TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);
 

@@ -11,11 +11,14 @@ detaches xyz).
 """
 from __future__ import annotations
 
+import ctypes
+
 import torch
 
 from . import _lib
 
 W = 256
+FUSED_FORWARD = True   # module switch: False runs the layer-by-layer GEMM chain (csrc/mlp_gemm.cu)
 
 
 def tf32_round(w: torch.Tensor) -> torch.Tensor:
@@ -89,28 +92,46 @@ class _DeformMLP(torch.autograd.Function):
             wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
             _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
                                                      wh.data_ptr(), whT.data_ptr(), bh.data_ptr(), s))
-            # skip buffer [M, E + W]: embedding in [:, :E], output of layer `skip` in [:, E:]
-            skipbuf = torch.empty((M, E + W), **f32)
-            _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt, skipbuf.data_ptr(),
-                                                   skipbuf.stride(0), s))
             masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
-            acts = []
-            inp = skipbuf[:, :E]
-            for i in range(nl):
-                out = skipbuf[:, E:] if i == skip else torch.empty((M, W), **f32)
-                _gemm(lib, inp, Wr[i], out, bias=bs[i].detach(), relu=True, mask_out=masks[i])
-                acts.append(out)
-                inp = skipbuf if i == skip else out
             out16 = torch.empty((M, 16), **f32)
-            _gemm(lib, acts[-1], wh, out16, bias=bh, round_tf32=False)
+            fused = FUSED_FORWARD and lib.trase_b200_mlp_fused_pack_floats(nl, skip, E) > 0 and \
+                all(r == W for r, _ in sizes)
+            if fused:
+                # one persistent kernel carries each 128-row tile through all layers (csrc/mlp_fused.cu)
+                emb = torch.empty((M, E), **f32)
+                _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt, emb.data_ptr(),
+                                                       emb.stride(0), s))
+                wpack = torch.empty(lib.trase_b200_mlp_fused_pack_floats(nl, skip, E), **f32)
+                wptrs = (ctypes.c_void_p * nl)(*[w.detach().contiguous().data_ptr() for w in Ws])
+                _lib.check(lib.trase_b200_mlp_pack_fused(nl, skip, E, wptrs, wh.data_ptr(), wpack.data_ptr(), s))
+                ball = torch.cat([b.detach().reshape(-1) for b in bs] + [bh])
+                acts_all = torch.empty((nl, M, W), **f32)
+                _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
+                                                            wpack.data_ptr(), ball.data_ptr(), acts_all.data_ptr(),
+                                                            masks.data_ptr(), out16.data_ptr(), s))
+                acts = list(acts_all.unbind(0))
+                skipbuf = emb
+            else:
+                # skip buffer [M, E + W]: embedding in [:, :E], output of layer `skip` in [:, E:]
+                skipbuf = torch.empty((M, E + W), **f32)
+                _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt,
+                                                       skipbuf.data_ptr(), skipbuf.stride(0), s))
+                acts = []
+                inp = skipbuf[:, :E]
+                for i in range(nl):
+                    out = skipbuf[:, E:] if i == skip else torch.empty((M, W), **f32)
+                    _gemm(lib, inp, Wr[i], out, bias=bs[i].detach(), relu=True, mask_out=masks[i])
+                    acts.append(out)
+                    inp = skipbuf if i == skip else out
+                _gemm(lib, acts[-1], wh, out16, bias=bh, round_tf32=False)
         ctx.save_for_backward(skipbuf, whT, masks, *acts, *[w for w in WrT if w is not None])
-        ctx.meta = (nl, skip, E, M, sizes)
+        ctx.meta = (nl, skip, E, M, sizes, fused)
         return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
 
     @staticmethod
     def backward(ctx, g_xyz, g_rot, g_scale):
         lib = _lib.load()
-        nl, skip, E, M, sizes = ctx.meta
+        nl, skip, E, M, sizes, fused = ctx.meta
         saved = ctx.saved_tensors
         skipbuf, whT, masks = saved[0], saved[1], saved[2]
         acts = saved[3:3 + nl]
@@ -141,8 +162,13 @@ class _DeformMLP(torch.autograd.Function):
             dz = torch.empty((M, W), **f32)
             _gemm(lib, dout, whT, dz, mask_in=masks[nl - 1], colsum=grads_b[nl - 1])
             for i in range(nl - 1, -1, -1):
-                inp = skipbuf[:, :E] if i == 0 else (skipbuf if i - 1 == skip else acts[i - 1])
-                _wgrad(lib, dz, inp, grads_w[i])
+                if fused and i > 0 and i - 1 == skip:
+                    # the skip layer's input was never concatenated: embedding columns, then the hidden ones
+                    _wgrad(lib, dz, skipbuf, grads_w[i][:, :E])
+                    _wgrad(lib, dz, acts[i - 1], grads_w[i][:, E:])
+                else:
+                    inp = skipbuf[:, :E] if i == 0 else (skipbuf if i - 1 == skip else acts[i - 1])
+                    _wgrad(lib, dz, inp, grads_w[i])
                 if i > 0:
                     dz_prev = torch.empty((M, W), **f32)
                     _gemm(lib, dz, WrT[i], dz_prev, mask_in=masks[i - 1], colsum=grads_b[i - 1])

@@ -70,6 +70,7 @@ EXPORTS = [
     "trase_b200_mlp_pack_dout", "trase_b200_launch_count", "trase_b200_loss_scratch_bytes",
     "trase_b200_l1_ssim_forward", "trase_b200_l1_ssim_backward", "trase_b200_feature_norm_scratch_bytes",
     "trase_b200_feature_norm_reg_forward", "trase_b200_feature_norm_reg_backward",
+    "trase_b200_mlp_fused_pack_floats", "trase_b200_mlp_pack_fused", "trase_b200_mlp_forward_fused",
 ]
 
 _lib = None
@@ -148,6 +149,12 @@ def load() -> C.CDLL:
     lib.trase_b200_feature_norm_reg_forward.argtypes = [C.c_int, C.c_int64] + [C.c_void_p] * 5
     lib.trase_b200_feature_norm_reg_backward.restype = C.c_int
     lib.trase_b200_feature_norm_reg_backward.argtypes = [C.c_int, C.c_int64] + [C.c_void_p] * 6
+    lib.trase_b200_mlp_fused_pack_floats.restype = C.c_size_t
+    lib.trase_b200_mlp_fused_pack_floats.argtypes = [C.c_int] * 3
+    lib.trase_b200_mlp_pack_fused.restype = C.c_int
+    lib.trase_b200_mlp_pack_fused.argtypes = [C.c_int] * 3 + [C.POINTER(C.c_void_p)] + [C.c_void_p] * 3
+    lib.trase_b200_mlp_forward_fused.restype = C.c_int
+    lib.trase_b200_mlp_forward_fused.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 6
     lib.trase_b200_l1_ssim_backward.restype = C.c_int
     lib.trase_b200_l1_ssim_backward.argtypes = [C.c_int] * 3 + [C.c_void_p] * 3 + [C.c_float] * 2 + [C.c_void_p] * 3
     lib.trase_b200_launch_count.restype = C.c_ulonglong

@@ -1,0 +1,460 @@
+// DeformNetwork forward as ONE persistent kernel (reference: utils/time_utils.py:106-131 — eight
+// nn.Linear + ReLU with a skip concatenation, then three linear heads; the reference launches one
+// cuBLAS SGEMM and two elementwise kernels per layer).
+//
+// The layer-by-layer path (mlp_gemm.cu) is bound by HBM: every layer reads the previous activations
+// (M x 256 fp32) and writes its own.  Here a CTA carries a 128-row tile through all layers: the
+// activations stay in shared memory as the next layer's A operand and are written to HBM only once
+// (they are needed by the backward pass); nothing is read back.  Per tile and layer:
+//   * the weight k-blocks (pre-packed, TF32-rounded, [k-block][256 rows][32]) stream from L2 through a
+//     3-stage TMA ring (32 KB per stage);
+//   * one thread issues tcgen05.mma.kind::tf32 128x256x8 into one of two TMEM accumulators;
+//   * eight epilogue warps drain the accumulator (tcgen05.ld), add the bias, apply ReLU, round to TF32,
+//     record the ReLU bit mask and write the result IN PLACE over the previous activations, already in
+//     the 128-byte-swizzled K-major layout the next layer's MMA reads;
+//   * each 32-column chunk is released to the MMA thread through its own mbarrier, so the next layer's
+//     MMAs start on chunk 0 while chunks 1..7 are still being drained (the two accumulators alternate);
+//   * the MMA thread also TMA-stores each finished chunk to the activation tensor in HBM (direct 16-byte
+//     stores from the epilogue registers were measured 50 % slower).
+// The positional encoding (84 columns -> three zero-padded chunks) is the A operand of layer 0 and of
+// the first k-blocks of the layer after the skip; its chunks travel through the same TMA ring.  The heads run as a last half-width pseudo-layer whose 16
+// output columns go straight to global memory.
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace tb {
+namespace mlp {
+
+using namespace ptx;
+
+bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                  uint32_t box_cols, CUtensorMapSwizzle swz);
+
+constexpr int FU_BM = 128;
+constexpr int FU_W = 256;                 // hidden width
+constexpr int FU_CHUNK = FU_BM * 128;     // 128 rows x 32 fp32 = 16 KB: one A chunk, or half a weight k-block
+constexpr int FU_HCH = FU_W / 32;         // 8 chunks of hidden activations
+constexpr int FU_ECH = 3;                 // up to 96 embedding columns
+constexpr int FU_STAGES = 3;
+constexpr int FU_STAGE_BYTES = 2 * FU_CHUNK;   // a whole weight k-block (256 output features x 32)
+constexpr int FU_EPI_WARPS = 8;
+constexpr int FU_THREADS = 128 + 32 * FU_EPI_WARPS;
+constexpr int FU_MAX_LAYERS = 12;
+constexpr int FU_CLUSTER = 2;             // CTAs sharing every weight k-block through TMA multicast         // hidden layers + the head pseudo-layer
+
+constexpr int FU_OFF_H = 0;
+constexpr int FU_OFF_W = FU_OFF_H + FU_HCH * FU_CHUNK;
+constexpr int FU_OFF_BAR = FU_OFF_W + FU_STAGES * FU_STAGE_BYTES;
+constexpr int FU_SMEM = FU_OFF_BAR + 256;
+
+struct FusedParams {
+  int M, nl, skip, eb;               // rows, hidden layers, index of the skip layer, embedding chunks
+  int blk_base[FU_MAX_LAYERS + 1];   // first packed k-block of each layer (layer nl = heads)
+  const float* bias;                 // [nl][256], then the 16 head biases
+  uint32_t* masks;                   // [nl][M][8]  ReLU bit masks
+  float* out16;                      // [M][16]
+  float* acts;                       // [nl][M][256]
+  unsigned long long* prof;          // optional [grid][8] stall-cycle counters (tools/check_fused_mlp.py)
+};
+
+__device__ __forceinline__ int fu_emb_blocks(const FusedParams& p, int L) {
+  return (L == 0 || (L < p.nl && L - 1 == p.skip)) ? p.eb : 0;
+}
+__device__ __forceinline__ int fu_h_blocks(int L) { return L == 0 ? 0 : FU_HCH; }
+
+__global__ void __launch_bounds__(FU_THREADS, 1)
+mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constant__ CUtensorMap tmW,
+                         const __grid_constant__ CUtensorMap tmActs, const FusedParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
+  uint8_t* sH = smem + FU_OFF_H;
+  uint8_t* sW = smem + FU_OFF_W;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FU_OFF_BAR);
+  uint64_t* full = bars;                        // [STAGES] weight stage landed
+  uint64_t* empty = full + FU_STAGES;           // [STAGES] weight stage consumed
+  uint64_t* a_ready = empty + FU_STAGES;        // [8] activation chunk written by the epilogue
+  uint64_t* tmem_full = a_ready + FU_HCH;       // [2]
+  uint64_t* tmem_empty = tmem_full + 2;         // [2]
+  uint64_t* h_free = tmem_empty + 2;            // activation chunks may be overwritten (their HBM stores have read them)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_free + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_tiles = (p.M + FU_BM - 1) / FU_BM;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmEmb); prefetch_tmap(&tmW); prefetch_tmap(&tmActs);
+    // a stage is released by the MMA threads of BOTH CTAs of the cluster (the peer multicasts into it)
+    for (int i = 0; i < FU_STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], FU_CLUSTER); }
+    for (int i = 0; i < FU_HCH; i++) mbar_init(&a_ready[i], 4);
+    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], FU_EPI_WARPS); }
+    mbar_init(h_free, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();            // the peer's barriers exist before anything is multicast to them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t crank = cluster_ctarank();
+  constexpr uint16_t CMASK = (1u << FU_CLUSTER) - 1;
+  // both CTAs of a cluster walk the same number of tiles (a tile index past the end is a dummy: its loads are
+  // zero-filled and its stores clipped), because each streams half of every weight k-block to the other
+  const int iters = (num_tiles + gridDim.x - 1) / gridDim.x;
+
+  if (warp == 0) {
+    // ===== TMA producer: embedding chunks once per tile, weight half-k-blocks in consumption order =====
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
+        for (int L = 0; L <= p.nl; L++) {
+          const int ne = fu_emb_blocks(p, L), nkb = ne + fu_h_blocks(L);
+          const int halves = L == p.nl ? 1 : 2;
+          for (int kb = 0; kb < nkb; kb++) {
+            if (kb < ne) {
+              // embedding chunk (A operand of this k-block) travels through the same ring
+              mbar_wait(&empty[stage], phase ^ 1);
+              mbar_expect_tx(&full[stage], FU_CHUNK);
+              tma_load_2d(sW + stage * FU_STAGE_BYTES, &tmEmb, &full[stage], kb * 32, tile * FU_BM);
+              if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
+            }
+            mbar_wait(&empty[stage], phase ^ 1);
+            mbar_expect_tx(&full[stage], halves * FU_CHUNK);
+            if (halves == 2) {
+              // this CTA fetches its half of the k-block once from L2 and delivers it to both CTAs
+              tma_load_2d_multicast(sW + stage * FU_STAGE_BYTES + crank * FU_CHUNK, &tmW, &full[stage], 0,
+                                    (p.blk_base[L] + kb) * FU_W + crank * 128, CMASK);
+            } else {
+              tma_load_2d(sW + stage * FU_STAGE_BYTES, &tmW, &full[stage], 0, (p.blk_base[L] + kb) * FU_W);
+            }
+            if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer; also stores each finished activation chunk to HBM =====
+    if (lane == 0) {
+      constexpr uint32_t idesc256 = make_idesc_tf32(FU_BM, 256, 0, 0);
+      constexpr uint32_t idesc128 = make_idesc_tf32(FU_BM, 128, 0, 0);
+      uint32_t stage = 0, phase = 0, a_phase = 0, lc = 0;
+      long long w_acc = 0, w_a = 0, w_full = 0, w_st = 0, t_all = clock64(), t0;
+#define FU_T0() (t0 = clock64())
+#define FU_ADD(x) ((x) += clock64() - t0)
+      for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
+        for (int L = 0; L <= p.nl; L++, lc++) {
+          const uint32_t acc = lc & 1, acc_phase = (lc >> 1) & 1;
+          FU_T0();
+          mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+          FU_ADD(w_acc);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + acc * FU_W;
+          const int ne = fu_emb_blocks(p, L), nkb = ne + fu_h_blocks(L);
+          const int halves = L == p.nl ? 1 : 2;
+          for (int kb = 0; kb < nkb; kb++) {
+            uint32_t a_addr;
+            int a_stage = -1;
+            if (kb < ne) {
+              mbar_wait(&full[stage], phase);
+              tc_fence_after();
+              a_stage = (int)stage;
+              a_addr = smem_u32(sW + stage * FU_STAGE_BYTES);
+              if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
+            } else {
+              const int j = kb - ne;
+              FU_T0();
+              mbar_wait(&a_ready[j], a_phase);
+              FU_ADD(w_a);
+              tc_fence_after();
+              a_addr = smem_u32(sH + j * FU_CHUNK);
+              tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
+            }
+            FU_T0();
+            mbar_wait(&full[stage], phase);
+            FU_ADD(w_full);
+            tc_fence_after();
+            const uint32_t b_addr = smem_u32(sW + stage * FU_STAGE_BYTES);
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              // B: 256 rows x 128 B, 8-row groups 1024 B apart (the two 128-row TMA boxes are contiguous)
+              const uint64_t da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+              const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+              mma_tf32_ss(tmem_d, da, db, halves == 2 ? idesc256 : idesc128, (kb | k) != 0);
+            }
+            mma_commit_multicast(&empty[stage], CMASK);
+            if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
+            if (a_stage >= 0) mma_commit_multicast(&empty[a_stage], CMASK);   // the embedding chunk's stage is free again
+          }
+          if (L > 0) a_phase ^= 1;
+          mma_commit(&tmem_full[acc]);
+          // the epilogue of this layer overwrites the chunks in place: the stores above must have read them first
+          // (the epilogue waits for h_free only before its first shared-memory write)
+          tma_store_commit();
+          FU_T0();
+          tma_store_wait_read<0>();
+          FU_ADD(w_st);
+          mbar_arrive(h_free);
+        }
+      }
+      tma_store_wait<0>();
+      if (p.prof) {
+        unsigned long long* q = p.prof + blockIdx.x * 8;
+        q[0] = clock64() - t_all; q[1] = w_acc; q[2] = w_a; q[3] = w_full; q[4] = w_st;
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: warp (w & 3) owns TMEM lanes / tile rows 32 (w & 3) .. +31; the two warps of a lane
+    // quarter take alternate 32-column slabs =====
+    const int ew = warp & 3, eh = (warp - 4) >> 2;
+    const int r = ew * 32 + lane;                 // row inside the tile
+    uint32_t lc = 0;
+    long long e_full = 0, e_free = 0, t0;
+    for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
+      const int grow = tile * FU_BM + r;
+      for (int L = 0; L <= p.nl; L++, lc++) {
+        const uint32_t acc = lc & 1, acc_phase = (lc >> 1) & 1;
+        FU_T0();
+        mbar_wait(&tmem_full[acc], acc_phase);
+        FU_ADD(e_full);
+        tc_fence_after();
+        const uint32_t t_addr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc * FU_W;
+        if (L < p.nl) {
+          const float* bias = p.bias + L * FU_W;
+          uint32_t* mask = p.masks + ((size_t)L * p.M + (grow < p.M ? grow : 0)) * (FU_W / 32);
+#pragma unroll 1
+          for (int s = eh; s < FU_HCH; s += 2) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_addr + s * 32, v);
+            float4 bq[8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) bq[c] = __ldg(reinterpret_cast<const float4*>(bias + s * 32) + c);
+            tmem_ld_wait();
+            uint8_t* dst = sH + s * FU_CHUNK + r * 128;
+            if (s == eh) { FU_T0(); mbar_wait(h_free, lc & 1); FU_ADD(e_free); }
+            uint32_t pos = 0;
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+              const float bb[4] = {bq[c].x, bq[c].y, bq[c].z, bq[c].w};
+              float4 o;
+              float* of = reinterpret_cast<float*>(&o);
+#pragma unroll
+              for (int j = 0; j < 4; j++) {
+                // ReLU, then round to TF32 (nearest, ties away: + half ulp, truncate — what cvt.rna.tf32
+                // computes for finite values, on the integer pipe instead of the quarter-rate converter)
+                const float x = fmaxf(__uint_as_float(v[c * 4 + j]) + bb[j], 0.f);
+                const uint32_t u = (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u;
+                pos |= (u != 0u ? 1u : 0u) << (c * 4 + j);
+                of[j] = __uint_as_float(u);
+              }
+              *reinterpret_cast<float4*>(dst + ((c ^ (r & 7)) << 4)) = o;
+            }
+            if (grow < p.M) mask[s] = pos;
+            fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&a_ready[s]);
+          }
+        } else if (eh == 0) {
+          uint32_t v[16];
+          tmem_ld_32x16(t_addr, v);
+          const float* bias = p.bias + p.nl * FU_W;
+          float4 bq[4];
+#pragma unroll
+          for (int c = 0; c < 4; c++) bq[c] = __ldg(reinterpret_cast<const float4*>(bias) + c);
+          tmem_ld_wait();
+          if (grow < p.M) {
+            float4* o = reinterpret_cast<float4*>(p.out16 + (size_t)grow * 16);
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+              o[c] = make_float4(__uint_as_float(v[c * 4]) + bq[c].x, __uint_as_float(v[c * 4 + 1]) + bq[c].y,
+                                 __uint_as_float(v[c * 4 + 2]) + bq[c].z, __uint_as_float(v[c * 4 + 3]) + bq[c].w);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      }
+    }
+    if (p.prof && warp == 4 && lane == 0) { p.prof[blockIdx.x * 8 + 5] = e_full; p.prof[blockIdx.x * 8 + 6] = e_free; }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();            // no CTA leaves while its peer may still signal its barriers
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+unsigned long long* g_fused_prof = nullptr;   // set through trase_b200_set_tuning_ptr (debug)
+
+// ---- weight packing: [k-block][256 rows][32] fp32, TF32-rounded, zero-padded ---------------------------
+constexpr int FU_MAX_SEGS = 16;
+struct PackSeg {
+  const float* src;   // [rows][ld]
+  int rows, ld, k0, kcount, blk0, nblk;
+};
+struct PackTable {
+  PackSeg seg[FU_MAX_SEGS];
+  int nseg;
+};
+
+__global__ void __launch_bounds__(256) mlp_pack_fused_kernel(const PackTable t, float* __restrict__ out) {
+  const int blk = blockIdx.x;
+  int si = 0;
+  while (si + 1 < t.nseg && blk >= t.seg[si + 1].blk0) si++;
+  const PackSeg sg = t.seg[si];
+  const int b = blk - sg.blk0;
+  for (int e = threadIdx.x; e < FU_W * 32; e += 256) {
+    const int n = e >> 5, c = e & 31;
+    const int k = b * 32 + c;
+    float v = 0.f;
+    if (n < sg.rows && k < sg.kcount) {
+      uint32_t u;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(sg.src[(size_t)n * sg.ld + sg.k0 + k]));
+      v = __uint_as_float(u);
+    }
+    out[(size_t)blk * FU_W * 32 + e] = v;
+  }
+}
+
+static int fu_layout(int nl, int skip, int E, int* blk_base) {
+  const int eb = (E + 31) / 32;
+  int n = 0;
+  for (int L = 0; L <= nl; L++) {
+    blk_base[L] = n;
+    n += (L == 0) ? eb : ((L < nl && L - 1 == skip) ? eb + FU_HCH : FU_HCH);
+  }
+  blk_base[nl + 1] = n;
+  return n;
+}
+static bool fu_shape_ok(int nl, int skip, int E) {
+  return nl >= 2 && nl + 1 <= FU_MAX_LAYERS && E > 0 && E <= 32 * FU_ECH && (E & 3) == 0 && skip < nl - 1;
+}
+
+typedef CUresult (*EncodeTiledFn3)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static bool make_tmap_acts(CUtensorMap* m, float* base, uint64_t M, uint64_t nl) {
+  static EncodeTiledFn3 fn = nullptr;
+  if (!fn) {
+    void* q = nullptr;
+    cudaDriverEntryPointQueryResult r;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &q, cudaEnableDefault, &r) != cudaSuccess ||
+        r != cudaDriverEntryPointSuccess)
+      return false;
+    fn = reinterpret_cast<EncodeTiledFn3>(q);
+  }
+  cuuint64_t dims[3] = {(cuuint64_t)FU_W, M, nl};
+  cuuint64_t strides[2] = {(cuuint64_t)FU_W * 4, M * FU_W * 4};
+  cuuint32_t box[3] = {32, FU_BM, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace mlp
+}  // namespace tb
+
+using namespace tb;
+
+// number of floats of the packed weight buffer for a network of nl hidden layers of width 256, skip
+// concatenation after layer `skip` (-1: none), embedding width E (multiple of 4, <= 96)
+extern "C" TRASE_API size_t trase_b200_mlp_fused_pack_floats(int nl, int skip, int E) {
+  if (!mlp::fu_shape_ok(nl, skip, E)) return 0;
+  int base[mlp::FU_MAX_LAYERS + 2];
+  return (size_t)mlp::fu_layout(nl, skip, E, base) * mlp::FU_W * 32;
+}
+
+// weights: host array of nl device pointers, weights[i] = nn.Linear weight of layer i, [256][in_i] with
+// in_0 = E, in_{skip+1} = E + 256 (embedding columns first), 256 otherwise; wh: [16][256] packed heads.
+extern "C" TRASE_API int trase_b200_mlp_pack_fused(int nl, int skip, int E, const float* const* weights,
+                                                   const float* wh, float* wpack, void* stream) {
+  if (!mlp::fu_shape_ok(nl, skip, E) || !weights || !wh || !wpack) {
+    set_error("trase_b200_mlp_pack_fused: unsupported network shape (nl=%d skip=%d E=%d) or null pointer", nl, skip, E);
+    return 1;
+  }
+  int base[mlp::FU_MAX_LAYERS + 2];
+  const int total = mlp::fu_layout(nl, skip, E, base);
+  const int eb = (E + 31) / 32;
+  mlp::PackTable t;
+  t.nseg = 0;
+  for (int L = 0; L <= nl; L++) {
+    const float* src = L < nl ? weights[L] : wh;
+    if (!src) { set_error("trase_b200_mlp_pack_fused: null weight pointer"); return 1; }
+    const int rows = L < nl ? mlp::FU_W : 16;
+    if (L == 0) {
+      t.seg[t.nseg++] = {src, rows, E, 0, E, base[L], eb};
+    } else if (L < nl && L - 1 == skip) {
+      t.seg[t.nseg++] = {src, rows, E + mlp::FU_W, 0, E, base[L], eb};
+      t.seg[t.nseg++] = {src, rows, E + mlp::FU_W, E, mlp::FU_W, base[L] + eb, mlp::FU_HCH};
+    } else {
+      t.seg[t.nseg++] = {src, rows, mlp::FU_W, 0, mlp::FU_W, base[L], mlp::FU_HCH};
+    }
+  }
+  mlp::mlp_pack_fused_kernel<<<total, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(t, wpack);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_fused: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+// emb: [M][ld_emb] (first E columns used, ld_emb multiple of 4), bias: nl*256 + 16 floats,
+// acts: [nl][M][256] (written), masks: [nl][M][8] (written), out16: [M][16] (written).
+extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const float* emb, int ld_emb,
+                                                      const float* wpack, const float* bias, float* acts,
+                                                      uint32_t* masks, float* out16, void* stream) {
+  if (M <= 0) return 0;
+  if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || !acts || !masks || !out16 || (ld_emb & 3) ||
+      ld_emb < E || ((uintptr_t)emb & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)acts & 15) ||
+      ((uintptr_t)bias & 15) || ((uintptr_t)out16 & 15)) {
+    set_error("trase_b200_mlp_forward_fused: bad arguments (M=%d nl=%d skip=%d E=%d)", M, nl, skip, E);
+    return 1;
+  }
+  mlp::FusedParams p;
+  p.M = M; p.nl = nl; p.skip = skip; p.eb = (E + 31) / 32;
+  int base[mlp::FU_MAX_LAYERS + 2];
+  const int total = mlp::fu_layout(nl, skip, E, base);
+  for (int L = 0; L <= nl; L++) p.blk_base[L] = base[L];
+  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.prof = mlp::g_fused_prof;
+  CUtensorMap tE, tW, tA;
+  if (!mlp::make_tmap_2d(&tE, emb, M, E, ld_emb, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
+      !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
+      !mlp::make_tmap_acts(&tA, acts, M, nl)) {
+    set_error("trase_b200_mlp_forward_fused: cuTensorMapEncodeTiled failed");
+    return 2;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp::mlp_forward_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         mlp::FU_SMEM);
+    if (e != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: %s", cudaGetErrorString(e)); return 2; }
+    attr_set = true;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int tiles = (M + mlp::FU_BM - 1) / mlp::FU_BM;
+  int grid = tiles < sms ? tiles : sms;
+  grid = (grid + mlp::FU_CLUSTER - 1) / mlp::FU_CLUSTER * mlp::FU_CLUSTER;
+  if (grid > sms) grid -= mlp::FU_CLUSTER;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(mlp::FU_THREADS);
+  cfg.dynamicSmemBytes = mlp::FU_SMEM;
+  cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = mlp::FU_CLUSTER;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, mlp::mlp_forward_fused_kernel, tE, tW, tA, p);
+  if (le != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: launch failed: %s", cudaGetErrorString(le)); return 2; }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+// debug: device buffer of [grid][8] cycle counters filled by the fused kernel (NULL = off)
+extern "C" TRASE_API void trase_b200_mlp_fused_set_prof(unsigned long long* dev_buf) { tb::mlp::g_fused_prof = dev_buf; }
