@@ -127,3 +127,37 @@ def test_native_deform_network_matches_torch(native_lib):
     for (n, q), b, y in zip(nat.named_parameters(), base, yard):
         err = ((q.grad - b).norm() / b.norm()).item()
         assert err <= 2.0 * y + 2e-3, (n, err, y)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M", [1, 127, 129, 1000, 128 * 148 + 5, 128 * 149 * 2 + 77])
+def test_fused_forward_matches_layer_chain(M):
+    """The single-kernel forward (csrc/mlp_fused.cu, CTA pairs) against the layer-by-layer GEMM chain: same
+    TF32 arithmetic, so outputs agree to TF32 rounding noise and the backward (which consumes the stored
+    activations and ReLU masks of either path) gives the same gradients.  Sizes cover a single partial tile
+    (the pair's second CTA walks a dummy tile), ragged last tiles, and odd tile counts per CTA."""
+    import torch
+    from trase_b200 import _deform_native as dn
+    from trase_b200.deform import DeformNetwork
+    torch.manual_seed(3)
+    net = DeformNetwork(backend="native").cuda()
+    g = torch.Generator(device="cuda").manual_seed(M)
+    x = (torch.rand(M, 3, device="cuda", generator=g) - 0.5) * 3
+    t = torch.full((M, 1), 0.41, device="cuda")
+    go = [torch.randn(M, k, device="cuda", generator=g) for k in (3, 4, 3)]
+    res = {}
+    saved = dn.FUSED_FORWARD
+    try:
+        for fused in (False, True):
+            dn.FUSED_FORWARD = fused
+            net.zero_grad()
+            outs = net(x, t)
+            torch.autograd.backward(list(outs), go)
+            res[fused] = ([o.detach().clone() for o in outs], [p.grad.detach().clone() for p in net.parameters()])
+    finally:
+        dn.FUSED_FORWARD = saved
+    for a, b in zip(res[False][0], res[True][0]):
+        assert torch.isfinite(b).all()
+        assert (a - b).abs().max() <= 2e-3 * a.abs().max() + 1e-7
+    for a, b in zip(res[False][1], res[True][1]):
+        assert (a - b).abs().max() <= 1e-2 * a.abs().max() + 1e-7

@@ -51,5 +51,6 @@ with torch.no_grad():
     net(x, t)
 torch.cuda.synchronize()
 lib.trase_b200_mlp_fused_set_prof(None)
-b = buf.view(148, 8).double().mean(0).tolist()
-print("cycles/CTA: total %.0f | MMA thread waits: tmem_empty %.0f a_ready %.0f w_full %.0f store %.0f | epilogue warp4 waits: tmem_full %.0f h_free %.0f" % tuple(b[:7]))
+for name, sl in (("leader", slice(0, 148, 2)), ("follower", slice(1, 148, 2))):
+    b = buf.view(148, 8)[sl].double().mean(0).tolist()
+    print(name, "cycles/CTA: total %.0f | warp-1 thread waits: tmem_empty %.0f a_ready %.0f w_full %.0f store %.0f | epilogue warp4 waits: tmem_full %.0f h_free %.0f" % tuple(b[:7]))

@@ -3,22 +3,30 @@
 // cuBLAS SGEMM and two elementwise kernels per layer).
 //
 // The layer-by-layer path (mlp_gemm.cu) is bound by HBM: every layer reads the previous activations
-// (M x 256 fp32) and writes its own.  Here a CTA carries a 128-row tile through all layers: the
+// (M x 256 fp32) and writes its own.  Here each CTA carries a 128-row tile through all layers: the
 // activations stay in shared memory as the next layer's A operand and are written to HBM only once
-// (they are needed by the backward pass); nothing is read back.  Per tile and layer:
-//   * the weight k-blocks (pre-packed, TF32-rounded, [k-block][256 rows][32]) stream from L2 through a
-//     3-stage TMA ring (32 KB per stage);
-//   * one thread issues tcgen05.mma.kind::tf32 128x256x8 into one of two TMEM accumulators;
-//   * eight epilogue warps drain the accumulator (tcgen05.ld), add the bias, apply ReLU, round to TF32,
-//     record the ReLU bit mask and write the result IN PLACE over the previous activations, already in
-//     the 128-byte-swizzled K-major layout the next layer's MMA reads;
-//   * each 32-column chunk is released to the MMA thread through its own mbarrier, so the next layer's
-//     MMAs start on chunk 0 while chunks 1..7 are still being drained (the two accumulators alternate);
-//   * the MMA thread also TMA-stores each finished chunk to the activation tensor in HBM (direct 16-byte
-//     stores from the epilogue registers were measured 50 % slower).
+// (the backward pass needs them); nothing is read back.
+//
+// CTA pairs (cluster of 2, tcgen05 cta_group::2): one MMA spans both SMs — M = 256 (each CTA's own
+// 128-row tile), N = 256 with each CTA holding only ITS half of the weight k-block.  With fp32 (TF32)
+// operands a single-CTA 128x256x8 MMA reads 12 KB of shared memory, which together with the TMA writes
+// and the epilogue saturates the 128 B/clk port; the pair halves the B traffic and the weight bytes
+// each SM pulls from L2, and lets a 6-deep ring of 16 KB stages cover the L2 latency (a single-CTA
+// version with 32 KB stages spent 30 % of its time waiting for weights).  Per pair, tile and layer:
+//   * both CTAs' producers TMA their half of every pre-packed, TF32-rounded weight k-block
+//     ([k-block][256 rows][32]) into their ring; the follower relays "landed" to the leader;
+//   * the leader's MMA thread issues tcgen05.mma.cta_group::2.kind::tf32 256x256x8 into one of two
+//     TMEM accumulators (each CTA's TMEM receives its own 128 rows) and commits to both CTAs' barriers;
+//   * eight epilogue warps per CTA drain the accumulator (tcgen05.ld), add the bias, apply ReLU, round to
+//     TF32, record the ReLU bit mask and write the result IN PLACE over the previous activations, already
+//     in the 128-byte-swizzled K-major layout the next layer's MMA reads;
+//   * each 32-column chunk is released to the MMA thread through its own mbarrier (arrivals from both
+//     CTAs), so the next layer's MMAs start on chunk 0 while chunks 1..7 are still being drained;
+//   * warp 1 of each CTA also TMA-stores every finished chunk to the activation tensor in HBM (direct
+//     16-byte stores from the epilogue registers were measured 50 % slower).
 // The positional encoding (84 columns -> three zero-padded chunks) is the A operand of layer 0 and of
-// the first k-blocks of the layer after the skip; its chunks travel through the same TMA ring.  The heads run as a last half-width pseudo-layer whose 16
-// output columns go straight to global memory.
+// the first k-blocks of the layer after the skip; its chunks travel through the same ring.  The heads
+// run as a last pseudo-layer with N = 32 whose first 16 output columns go straight to global memory.
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -35,17 +43,16 @@ constexpr int FU_W = 256;                 // hidden width
 constexpr int FU_CHUNK = FU_BM * 128;     // 128 rows x 32 fp32 = 16 KB: one A chunk, or half a weight k-block
 constexpr int FU_HCH = FU_W / 32;         // 8 chunks of hidden activations
 constexpr int FU_ECH = 3;                 // up to 96 embedding columns
-constexpr int FU_STAGES = 3;
-constexpr int FU_STAGE_BYTES = 2 * FU_CHUNK;   // a whole weight k-block (256 output features x 32)
+constexpr int FU_STAGES = 6;               // 16 KB each: this CTA's half of a weight k-block, or an embedding chunk
 constexpr int FU_EPI_WARPS = 8;
 constexpr int FU_THREADS = 128 + 32 * FU_EPI_WARPS;
 constexpr int FU_MAX_LAYERS = 12;
-constexpr int FU_CLUSTER = 2;             // CTAs sharing every weight k-block through TMA multicast         // hidden layers + the head pseudo-layer
+constexpr int FU_CLUSTER = 2;             // CTA pair: one tcgen05.mma.cta_group::2 spans both         // hidden layers + the head pseudo-layer
 
 constexpr int FU_OFF_H = 0;
 constexpr int FU_OFF_W = FU_OFF_H + FU_HCH * FU_CHUNK;
-constexpr int FU_OFF_BAR = FU_OFF_W + FU_STAGES * FU_STAGE_BYTES;
-constexpr int FU_SMEM = FU_OFF_BAR + 256;
+constexpr int FU_OFF_BAR = FU_OFF_W + FU_STAGES * FU_CHUNK;
+constexpr int FU_SMEM = FU_OFF_BAR + 512;   // 33 mbarriers + the TMEM slot
 
 struct FusedParams {
   int M, nl, skip, eb;               // rows, hidden layers, index of the skip layer, embedding chunks
@@ -64,69 +71,74 @@ __device__ __forceinline__ int fu_h_blocks(int L) { return L == 0 ? 0 : FU_HCH; 
 
 __global__ void __launch_bounds__(FU_THREADS, 1)
 mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constant__ CUtensorMap tmW,
-                         const __grid_constant__ CUtensorMap tmActs, const FusedParams p) {
+                         const __grid_constant__ CUtensorMap tmWh, const __grid_constant__ CUtensorMap tmActs,
+                         const FusedParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
   uint8_t* sH = smem + FU_OFF_H;
   uint8_t* sW = smem + FU_OFF_W;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FU_OFF_BAR);
-  uint64_t* full = bars;                        // [STAGES] weight stage landed
-  uint64_t* empty = full + FU_STAGES;           // [STAGES] weight stage consumed
-  uint64_t* a_ready = empty + FU_STAGES;        // [8] activation chunk written by the epilogue
-  uint64_t* tmem_full = a_ready + FU_HCH;       // [2]
-  uint64_t* tmem_empty = tmem_full + 2;         // [2]
+  uint64_t* full = bars;                        // [STAGES] ring stage landed (leader: in both CTAs)
+  uint64_t* empty = full + FU_STAGES;           // [STAGES] ring stage consumed by the pair's MMAs
+  uint64_t* a_ready = empty + FU_STAGES;        // [8] leader only: activation chunk written in both CTAs
+  uint64_t* a_local = a_ready + FU_HCH;         // [8] activation chunk written in this CTA (for its HBM store)
+  uint64_t* tmem_full = a_local + FU_HCH;       // [2]
+  uint64_t* tmem_empty = tmem_full + 2;         // [2] leader only: accumulator drained in both CTAs
   uint64_t* h_free = tmem_empty + 2;            // activation chunks may be overwritten (their HBM stores have read them)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_free + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = (p.M + FU_BM - 1) / FU_BM;
+  const uint32_t crank = cluster_ctarank();
+  const bool leader = crank == 0;
 
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmEmb); prefetch_tmap(&tmW); prefetch_tmap(&tmActs);
-    // a stage is released by the MMA threads of BOTH CTAs of the cluster (the peer multicasts into it)
-    for (int i = 0; i < FU_STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], FU_CLUSTER); }
-    for (int i = 0; i < FU_HCH; i++) mbar_init(&a_ready[i], 4);
-    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], FU_EPI_WARPS); }
+    prefetch_tmap(&tmEmb); prefetch_tmap(&tmW); prefetch_tmap(&tmWh); prefetch_tmap(&tmActs);
+    for (int i = 0; i < FU_STAGES; i++) {
+      // leader: its own TMA (expect_tx arrival) + the follower's relay; follower: its own TMA
+      mbar_init(&full[i], leader ? 2 : 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < FU_HCH; i++) { mbar_init(&a_ready[i], 4 * FU_CLUSTER); mbar_init(&a_local[i], 4); }
+    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], FU_EPI_WARPS * FU_CLUSTER); }
     mbar_init(h_free, 1);
     fence_barrier_init();
   }
-  if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  if (warp == 2) { tmem_alloc_2cta(tmem_slot, 512); tmem_relinquish_2cta(); }
   tc_fence_before();
   __syncthreads();
-  cluster_sync();            // the peer's barriers exist before anything is multicast to them
+  cluster_sync();            // the peer's barriers exist before anything is signalled on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t crank = cluster_ctarank();
   constexpr uint16_t CMASK = (1u << FU_CLUSTER) - 1;
-  // both CTAs of a cluster walk the same number of tiles (a tile index past the end is a dummy: its loads are
-  // zero-filled and its stores clipped), because each streams half of every weight k-block to the other
+  // the two CTAs of a pair walk the same number of tiles (a tile index past the end is a dummy: its loads are
+  // zero-filled and its stores clipped): every MMA spans both
   const int iters = (num_tiles + gridDim.x - 1) / gridDim.x;
 
   if (warp == 0) {
-    // ===== TMA producer: embedding chunks once per tile, weight half-k-blocks in consumption order =====
+    // ===== TMA producer: this CTA's half of every weight k-block, and its own embedding chunks =====
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
         for (int L = 0; L <= p.nl; L++) {
           const int ne = fu_emb_blocks(p, L), nkb = ne + fu_h_blocks(L);
-          const int halves = L == p.nl ? 1 : 2;
           for (int kb = 0; kb < nkb; kb++) {
             if (kb < ne) {
-              // embedding chunk (A operand of this k-block) travels through the same ring
               mbar_wait(&empty[stage], phase ^ 1);
               mbar_expect_tx(&full[stage], FU_CHUNK);
-              tma_load_2d(sW + stage * FU_STAGE_BYTES, &tmEmb, &full[stage], kb * 32, tile * FU_BM);
+              tma_load_2d(sW + stage * FU_CHUNK, &tmEmb, &full[stage], kb * 32, tile * FU_BM);
               if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
             }
             mbar_wait(&empty[stage], phase ^ 1);
-            mbar_expect_tx(&full[stage], halves * FU_CHUNK);
-            if (halves == 2) {
-              // this CTA fetches its half of the k-block once from L2 and delivers it to both CTAs
-              tma_load_2d_multicast(sW + stage * FU_STAGE_BYTES + crank * FU_CHUNK, &tmW, &full[stage], 0,
-                                    (p.blk_base[L] + kb) * FU_W + crank * 128, CMASK);
+            if (L < p.nl) {
+              // output features [128 crank, 128 crank + 128) of this k-block
+              mbar_expect_tx(&full[stage], FU_CHUNK);
+              tma_load_2d(sW + stage * FU_CHUNK, &tmW, &full[stage], 0, (p.blk_base[L] + kb) * FU_W + crank * 128);
             } else {
-              tma_load_2d(sW + stage * FU_STAGE_BYTES, &tmW, &full[stage], 0, (p.blk_base[L] + kb) * FU_W);
+              // heads: N = 32 over the pair, 16 rows per CTA (rows 16..31 of the packed block are zero)
+              mbar_expect_tx(&full[stage], 16 * 128);
+              tma_load_2d(sW + stage * FU_CHUNK, &tmWh, &full[stage], 0, (p.blk_base[L] + kb) * FU_W + crank * 16);
             }
             if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
           }
@@ -134,10 +146,11 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer; also stores each finished activation chunk to HBM =====
+    // ===== leader: MMA issuer for the pair.  follower: relays "stage landed" to the leader.
+    // Both: TMA-store each finished activation chunk of their own tile to HBM =====
     if (lane == 0) {
-      constexpr uint32_t idesc256 = make_idesc_tf32(FU_BM, 256, 0, 0);
-      constexpr uint32_t idesc128 = make_idesc_tf32(FU_BM, 128, 0, 0);
+      constexpr uint32_t idesc_h = make_idesc_tf32(2 * FU_BM, 256, 0, 0);
+      constexpr uint32_t idesc_o = make_idesc_tf32(2 * FU_BM, 32, 0, 0);
       uint32_t stage = 0, phase = 0, a_phase = 0, lc = 0;
       long long w_acc = 0, w_a = 0, w_full = 0, w_st = 0, t_all = clock64(), t0;
 #define FU_T0() (t0 = clock64())
@@ -145,49 +158,55 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
       for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
         for (int L = 0; L <= p.nl; L++, lc++) {
           const uint32_t acc = lc & 1, acc_phase = (lc >> 1) & 1;
-          FU_T0();
-          mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
-          FU_ADD(w_acc);
-          tc_fence_after();
+          if (leader) {
+            FU_T0();
+            mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            FU_ADD(w_acc);
+            tc_fence_after();
+          }
           const uint32_t tmem_d = tmem_base + acc * FU_W;
           const int ne = fu_emb_blocks(p, L), nkb = ne + fu_h_blocks(L);
-          const int halves = L == p.nl ? 1 : 2;
           for (int kb = 0; kb < nkb; kb++) {
             uint32_t a_addr;
             int a_stage = -1;
             if (kb < ne) {
-              mbar_wait(&full[stage], phase);
-              tc_fence_after();
+              if (leader) {
+                FU_T0();
+                mbar_wait(&full[stage], phase);
+                FU_ADD(w_full);
+                tc_fence_after();
+              }
               a_stage = (int)stage;
-              a_addr = smem_u32(sW + stage * FU_STAGE_BYTES);
+              a_addr = smem_u32(sW + stage * FU_CHUNK);
               if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
             } else {
               const int j = kb - ne;
               FU_T0();
-              mbar_wait(&a_ready[j], a_phase);
+              mbar_wait(leader ? &a_ready[j] : &a_local[j], a_phase);
               FU_ADD(w_a);
               tc_fence_after();
               a_addr = smem_u32(sH + j * FU_CHUNK);
               tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
             }
-            FU_T0();
-            mbar_wait(&full[stage], phase);
-            FU_ADD(w_full);
-            tc_fence_after();
-            const uint32_t b_addr = smem_u32(sW + stage * FU_STAGE_BYTES);
+            if (leader) {
+              FU_T0();
+              mbar_wait(&full[stage], phase);
+              FU_ADD(w_full);
+              tc_fence_after();
+              const uint32_t b_addr = smem_u32(sW + stage * FU_CHUNK);
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-              // B: 256 rows x 128 B, 8-row groups 1024 B apart (the two 128-row TMA boxes are contiguous)
-              const uint64_t da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
-              const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-              mma_tf32_ss(tmem_d, da, db, halves == 2 ? idesc256 : idesc128, (kb | k) != 0);
+              for (int k = 0; k < 4; k++) {
+                const uint64_t da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+                const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+                mma_tf32_ss_2cta(tmem_d, da, db, L < p.nl ? idesc_h : idesc_o, (kb | k) != 0);
+              }
+              mma_commit_2cta(&empty[stage], CMASK);
+              if (a_stage >= 0) mma_commit_2cta(&empty[a_stage], CMASK);   // the embedding chunks' stages
             }
-            mma_commit_multicast(&empty[stage], CMASK);
             if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
-            if (a_stage >= 0) mma_commit_multicast(&empty[a_stage], CMASK);   // the embedding chunk's stage is free again
           }
           if (L > 0) a_phase ^= 1;
-          mma_commit(&tmem_full[acc]);
+          if (leader) mma_commit_2cta(&tmem_full[acc], CMASK);
           // the epilogue of this layer overwrites the chunks in place: the stores above must have read them first
           // (the epilogue waits for h_free only before its first shared-memory write)
           tma_store_commit();
@@ -202,6 +221,20 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
         unsigned long long* q = p.prof + blockIdx.x * 8;
         q[0] = clock64() - t_all; q[1] = w_acc; q[2] = w_a; q[3] = w_full; q[4] = w_st;
       }
+    }
+  } else if (warp == 3) {
+    // ===== follower only: tell the leader's MMA thread, stage by stage, that this CTA's operands have landed =====
+    if (lane == 0 && !leader) {
+      uint32_t stage = 0, phase = 0;
+      for (int it = 0; it < iters; it++)
+        for (int L = 0; L <= p.nl; L++) {
+          const int n = 2 * fu_emb_blocks(p, L) + fu_h_blocks(L);     // ring entries of this layer
+          for (int e = 0; e < n; e++) {
+            mbar_wait(&full[stage], phase);
+            mbar_arrive_cluster(&full[stage], 0);
+            if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
     }
   } else if (warp >= 4) {
     // ===== epilogue: warp (w & 3) owns TMEM lanes / tile rows 32 (w & 3) .. +31; the two warps of a lane
@@ -230,8 +263,8 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
 #pragma unroll
             for (int c = 0; c < 8; c++) bq[c] = __ldg(reinterpret_cast<const float4*>(bias + s * 32) + c);
             tmem_ld_wait();
-            uint8_t* dst = sH + s * FU_CHUNK + r * 128;
             if (s == eh) { FU_T0(); mbar_wait(h_free, lc & 1); FU_ADD(e_free); }
+            uint8_t* dst = sH + s * FU_CHUNK + r * 128;
             uint32_t pos = 0;
 #pragma unroll
             for (int c = 0; c < 8; c++) {
@@ -252,7 +285,10 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
             if (grow < p.M) mask[s] = pos;
             fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
             __syncwarp();
-            if (lane == 0) mbar_arrive(&a_ready[s]);
+            if (lane == 0) {
+              mbar_arrive(&a_local[s]);
+              if (leader) mbar_arrive(&a_ready[s]); else mbar_arrive_cluster(&a_ready[s], 0);
+            }
           }
         } else if (eh == 0) {
           uint32_t v[16];
@@ -272,15 +308,15 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) { if (leader) mbar_arrive(&tmem_empty[acc]); else mbar_arrive_cluster(&tmem_empty[acc], 0); }
       }
     }
     if (p.prof && warp == 4 && lane == 0) { p.prof[blockIdx.x * 8 + 5] = e_full; p.prof[blockIdx.x * 8 + 6] = e_free; }
   }
   tc_fence_before();
   __syncthreads();
-  cluster_sync();            // no CTA leaves while its peer may still signal its barriers
-  if (warp == 2) tmem_dealloc(tmem_base, 512);
+  cluster_sync();            // no CTA leaves while its peer may still signal its barriers or read its shared memory
+  if (warp == 2) tmem_dealloc_2cta(tmem_base, 512);
 }
 
 unsigned long long* g_fused_prof = nullptr;   // set through trase_b200_set_tuning_ptr (debug)
@@ -415,9 +451,10 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
   const int total = mlp::fu_layout(nl, skip, E, base);
   for (int L = 0; L <= nl; L++) p.blk_base[L] = base[L];
   p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.prof = mlp::g_fused_prof;
-  CUtensorMap tE, tW, tA;
+  CUtensorMap tE, tW, tWh, tA;
   if (!mlp::make_tmap_2d(&tE, emb, M, E, ld_emb, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
+      !mlp::make_tmap_2d(&tWh, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 16, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_acts(&tA, acts, M, nl)) {
     set_error("trase_b200_mlp_forward_fused: cuTensorMapEncodeTiled failed");
     return 2;
@@ -448,7 +485,7 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, mlp::mlp_forward_fused_kernel, tE, tW, tA, p);
+  cudaError_t le = cudaLaunchKernelEx(&cfg, mlp::mlp_forward_fused_kernel, tE, tW, tWh, tA, p);
   if (le != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: launch failed: %s", cudaGetErrorString(le)); return 2; }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: CUDA error: %s", cudaGetErrorString(e)); return 2; }
