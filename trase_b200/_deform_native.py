@@ -19,6 +19,7 @@ from . import _lib
 
 W = 256
 FUSED_FORWARD = True   # module switch: False runs the layer-by-layer GEMM chain (csrc/mlp_gemm.cu)
+FUSED_BACKWARD = True  # same for the data-gradient chain of the backward pass
 
 
 def tf32_round(w: torch.Tensor) -> torch.Tensor:
@@ -158,10 +159,25 @@ class _DeformMLP(torch.autograd.Function):
                                                     dout.data_ptr(), dbh.data_ptr(), s))
             # heads: dWh^T = h_last^T dout
             _wgrad(lib, acts[-1], dout, dwhT)
-            # dZ_{nl-1} = (dout Wh) * relu'(h_last); its column sums are the bias gradient of layer nl-1
-            dz = torch.empty((M, W), **f32)
-            _gemm(lib, dout, whT, dz, mask_in=masks[nl - 1], colsum=grads_b[nl - 1])
+            fused_bwd = FUSED_BACKWARD and all(r == W for r, _ in sizes) and \
+                lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
+            if fused_bwd:
+                # the whole data-gradient chain in one persistent kernel (csrc/mlp_fused.cu): dzs[L] = dZ of
+                # layer nl-1-L, bias gradients straight into the gradient buffer
+                wpack_b = torch.empty(lib.trase_b200_mlp_fused_pack_bwd_floats(nl), **f32)
+                wT = (ctypes.c_void_p * (nl - 1))(*[WrT[i].data_ptr() for i in range(1, nl)])
+                _lib.check(lib.trase_b200_mlp_pack_fused_bwd(nl, whT.data_ptr(), wT, wpack_b.data_ptr(), s))
+                dzs = torch.empty((nl, M, W), **f32)
+                _lib.check(lib.trase_b200_mlp_backward_fused(M, nl, dout.data_ptr(), wpack_b.data_ptr(),
+                                                             masks.data_ptr(), dzs.data_ptr(),
+                                                             grads_b[0].data_ptr(), s))
+            else:
+                # dZ_{nl-1} = (dout Wh) * relu'(h_last); its column sums are the bias gradient of layer nl-1
+                dz = torch.empty((M, W), **f32)
+                _gemm(lib, dout, whT, dz, mask_in=masks[nl - 1], colsum=grads_b[nl - 1])
             for i in range(nl - 1, -1, -1):
+                if fused_bwd:
+                    dz = dzs[nl - 1 - i]
                 if fused and i > 0 and i - 1 == skip:
                     # the skip layer's input was never concatenated: embedding columns, then the hidden ones
                     _wgrad(lib, dz, skipbuf, grads_w[i][:, :E])
@@ -169,7 +185,7 @@ class _DeformMLP(torch.autograd.Function):
                 else:
                     inp = skipbuf[:, :E] if i == 0 else (skipbuf if i - 1 == skip else acts[i - 1])
                     _wgrad(lib, dz, inp, grads_w[i])
-                if i > 0:
+                if i > 0 and not fused_bwd:
                     dz_prev = torch.empty((M, W), **f32)
                     _gemm(lib, dz, WrT[i], dz_prev, mask_in=masks[i - 1], colsum=grads_b[i - 1])
                     dz = dz_prev

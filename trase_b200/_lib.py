@@ -71,6 +71,7 @@ EXPORTS = [
     "trase_b200_l1_ssim_forward", "trase_b200_l1_ssim_backward", "trase_b200_feature_norm_scratch_bytes",
     "trase_b200_feature_norm_reg_forward", "trase_b200_feature_norm_reg_backward",
     "trase_b200_mlp_fused_pack_floats", "trase_b200_mlp_pack_fused", "trase_b200_mlp_forward_fused",
+    "trase_b200_mlp_fused_pack_bwd_floats", "trase_b200_mlp_pack_fused_bwd", "trase_b200_mlp_backward_fused",
 ]
 
 _lib = None
@@ -153,6 +154,12 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_fused_pack_floats.argtypes = [C.c_int] * 3
     lib.trase_b200_mlp_pack_fused.restype = C.c_int
     lib.trase_b200_mlp_pack_fused.argtypes = [C.c_int] * 3 + [C.POINTER(C.c_void_p)] + [C.c_void_p] * 3
+    lib.trase_b200_mlp_fused_pack_bwd_floats.restype = C.c_size_t
+    lib.trase_b200_mlp_fused_pack_bwd_floats.argtypes = [C.c_int]
+    lib.trase_b200_mlp_pack_fused_bwd.restype = C.c_int
+    lib.trase_b200_mlp_pack_fused_bwd.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]
+    lib.trase_b200_mlp_backward_fused.restype = C.c_int
+    lib.trase_b200_mlp_backward_fused.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 6
     lib.trase_b200_mlp_forward_fused.restype = C.c_int
     lib.trase_b200_mlp_forward_fused.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 6
     lib.trase_b200_l1_ssim_backward.restype = C.c_int

@@ -43,7 +43,9 @@ constexpr int FU_W = 256;                 // hidden width
 constexpr int FU_CHUNK = FU_BM * 128;     // 128 rows x 32 fp32 = 16 KB: one A chunk, or half a weight k-block
 constexpr int FU_HCH = FU_W / 32;         // 8 chunks of hidden activations
 constexpr int FU_ECH = 3;                 // up to 96 embedding columns
-constexpr int FU_STAGES = 6;               // 16 KB each: this CTA's half of a weight k-block, or an embedding chunk
+// ring stages of 16 KB (this CTA's half of a weight k-block, or a chunk of the first operand);
+// the backward chain gives one stage up for its bias-gradient accumulators
+template <bool BWD> struct FuCfg { static constexpr int STAGES = BWD ? 5 : 6; };
 constexpr int FU_EPI_WARPS = 8;
 constexpr int FU_THREADS = 128 + 32 * FU_EPI_WARPS;
 constexpr int FU_MAX_LAYERS = 12;
@@ -51,7 +53,8 @@ constexpr int FU_CLUSTER = 2;             // CTA pair: one tcgen05.mma.cta_group
 
 constexpr int FU_OFF_H = 0;
 constexpr int FU_OFF_W = FU_OFF_H + FU_HCH * FU_CHUNK;
-constexpr int FU_OFF_BAR = FU_OFF_W + FU_STAGES * FU_CHUNK;
+constexpr int FU_OFF_BAR = FU_OFF_W + 6 * FU_CHUNK;
+constexpr int FU_OFF_COL = FU_OFF_W + 5 * FU_CHUNK;   // backward: [layers][256] bias-gradient partial sums (<= 16 KB)
 constexpr int FU_SMEM = FU_OFF_BAR + 512;   // 33 mbarriers + the TMEM slot
 
 struct FusedParams {
@@ -60,17 +63,37 @@ struct FusedParams {
   const float* bias;                 // [nl][256], then the 16 head biases
   uint32_t* masks;                   // [nl][M][8]  ReLU bit masks
   float* out16;                      // [M][16]
-  float* acts;                       // [nl][M][256]
+  float* acts;                       // [nl][M][256]  (backward: dZ of every layer, in backward order)
+  float* colsum;                     // backward: [nl][256] bias gradients, forward layer order (+=)
   unsigned long long* prof;          // optional [grid][8] stall-cycle counters (tools/check_fused_mlp.py)
 };
 
 __device__ __forceinline__ int fu_emb_blocks(const FusedParams& p, int L) {
   return (L == 0 || (L < p.nl && L - 1 == p.skip)) ? p.eb : 0;
 }
+// Column sums over the warp's 32 rows: lane l returns the total of v[l] (31 shuffles).
+__device__ __forceinline__ float fu_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int w = 16; w >= 1; w >>= 1) {
+    const bool hi = lane & w;
+#pragma unroll
+    for (int i = 0; i < w; i++) {
+      const float send = hi ? v[i] : v[i + w];
+      const float keep = hi ? v[i + w] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+    }
+  }
+  return v[0];
+}
 __device__ __forceinline__ int fu_h_blocks(int L) { return L == 0 ? 0 : FU_HCH; }
 
+// BWD = false: forward (bias + ReLU epilogue, heads pseudo-layer).
+// BWD = true : the data-gradient chain dZ_{l-1} = (dZ_l W_l) * relu'(h_{l-1}): the same pipeline with the packed
+// upstream gradient [M][16] as first operand, transposed weights, an epilogue that applies the stored ReLU
+// bit mask and accumulates the bias gradients (column sums), and a final drain pseudo-layer without MMAs.
+template <bool BWD>
 __global__ void __launch_bounds__(FU_THREADS, 1)
-mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constant__ CUtensorMap tmW,
+mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constant__ CUtensorMap tmW,
                          const __grid_constant__ CUtensorMap tmWh, const __grid_constant__ CUtensorMap tmActs,
                          const FusedParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -78,6 +101,8 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
   if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
   uint8_t* sH = smem + FU_OFF_H;
   uint8_t* sW = smem + FU_OFF_W;
+  float* sCol = reinterpret_cast<float*>(smem + FU_OFF_COL);
+  constexpr int FU_STAGES = FuCfg<BWD>::STAGES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FU_OFF_BAR);
   uint64_t* full = bars;                        // [STAGES] ring stage landed (leader: in both CTAs)
   uint64_t* empty = full + FU_STAGES;           // [STAGES] ring stage consumed by the pair's MMAs
@@ -106,6 +131,7 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
     fence_barrier_init();
   }
   if (warp == 2) { tmem_alloc_2cta(tmem_slot, 512); tmem_relinquish_2cta(); }
+  if (BWD) for (int i = threadIdx.x; i < p.nl * FU_W; i += FU_THREADS) sCol[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   cluster_sync();            // the peer's barriers exist before anything is signalled on them
@@ -121,7 +147,7 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
-        for (int L = 0; L <= p.nl; L++) {
+        for (int L = 0; L < (BWD ? p.nl : p.nl + 1); L++) {
           const int ne = fu_emb_blocks(p, L), nkb = ne + fu_h_blocks(L);
           for (int kb = 0; kb < nkb; kb++) {
             if (kb < ne) {
@@ -131,7 +157,7 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
               if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
             }
             mbar_wait(&empty[stage], phase ^ 1);
-            if (L < p.nl) {
+            if (BWD || L < p.nl) {
               // output features [128 crank, 128 crank + 128) of this k-block
               mbar_expect_tx(&full[stage], FU_CHUNK);
               tma_load_2d(sW + stage * FU_CHUNK, &tmW, &full[stage], 0, (p.blk_base[L] + kb) * FU_W + crank * 128);
@@ -156,9 +182,10 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
 #define FU_T0() (t0 = clock64())
 #define FU_ADD(x) ((x) += clock64() - t0)
       for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
-        for (int L = 0; L <= p.nl; L++, lc++) {
+        for (int L = 0; L <= p.nl; L++) {
+          const bool mma_layer = !BWD || L < p.nl;         // backward: layer nl only drains the last chunks to HBM
           const uint32_t acc = lc & 1, acc_phase = (lc >> 1) & 1;
-          if (leader) {
+          if (leader && mma_layer) {
             FU_T0();
             mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
             FU_ADD(w_acc);
@@ -188,6 +215,7 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
               a_addr = smem_u32(sH + j * FU_CHUNK);
               tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
             }
+            if (!mma_layer) continue;
             if (leader) {
               FU_T0();
               mbar_wait(&full[stage], phase);
@@ -198,7 +226,7 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
               for (int k = 0; k < 4; k++) {
                 const uint64_t da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
                 const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-                mma_tf32_ss_2cta(tmem_d, da, db, L < p.nl ? idesc_h : idesc_o, (kb | k) != 0);
+                mma_tf32_ss_2cta(tmem_d, da, db, (BWD || L < p.nl) ? idesc_h : idesc_o, (kb | k) != 0);
               }
               mma_commit_2cta(&empty[stage], CMASK);
               if (a_stage >= 0) mma_commit_2cta(&empty[a_stage], CMASK);   // the embedding chunks' stages
@@ -206,7 +234,8 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
             if (++stage == FU_STAGES) { stage = 0; phase ^= 1; }
           }
           if (L > 0) a_phase ^= 1;
-          if (leader) mma_commit_2cta(&tmem_full[acc], CMASK);
+          if (leader && mma_layer) mma_commit_2cta(&tmem_full[acc], CMASK);
+          if (mma_layer) lc++;
           // the epilogue of this layer overwrites the chunks in place: the stores above must have read them first
           // (the epilogue waits for h_free only before its first shared-memory write)
           tma_store_commit();
@@ -227,7 +256,7 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
     if (lane == 0 && !leader) {
       uint32_t stage = 0, phase = 0;
       for (int it = 0; it < iters; it++)
-        for (int L = 0; L <= p.nl; L++) {
+        for (int L = 0; L < (BWD ? p.nl : p.nl + 1); L++) {
           const int n = 2 * fu_emb_blocks(p, L) + fu_h_blocks(L);     // ring entries of this layer
           for (int e = 0; e < n; e++) {
             mbar_wait(&full[stage], phase);
@@ -245,25 +274,33 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
     long long e_full = 0, e_free = 0, t0;
     for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
       const int grow = tile * FU_BM + r;
-      for (int L = 0; L <= p.nl; L++, lc++) {
+      for (int L = 0; L < (BWD ? p.nl : p.nl + 1); L++, lc++) {
         const uint32_t acc = lc & 1, acc_phase = (lc >> 1) & 1;
+        const uint32_t hfree_parity = (uint32_t)(it * (p.nl + 1) + L) & 1u;   // warp 1 signals h_free nl + 1 times per tile
         FU_T0();
         mbar_wait(&tmem_full[acc], acc_phase);
         FU_ADD(e_full);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc * FU_W;
-        if (L < p.nl) {
-          const float* bias = p.bias + L * FU_W;
-          uint32_t* mask = p.masks + ((size_t)L * p.M + (grow < p.M ? grow : 0)) * (FU_W / 32);
+        if (BWD || L < p.nl) {
+          // forward layer this step belongs to: its bias (forward) or its ReLU mask and bias gradient (backward)
+          const int fl = BWD ? p.nl - 1 - L : L;
+          const float* bias = p.bias + fl * FU_W;
+          uint32_t* mask = p.masks + ((size_t)fl * p.M + (grow < p.M ? grow : 0)) * (FU_W / 32);
 #pragma unroll 1
           for (int s = eh; s < FU_HCH; s += 2) {
             uint32_t v[32];
             tmem_ld_32x32(t_addr + s * 32, v);
             float4 bq[8];
+            uint32_t keep = 0;
+            if (BWD) {
+              keep = grow < p.M ? __ldg(mask + s) : 0u;
+            } else {
 #pragma unroll
-            for (int c = 0; c < 8; c++) bq[c] = __ldg(reinterpret_cast<const float4*>(bias + s * 32) + c);
+              for (int c = 0; c < 8; c++) bq[c] = __ldg(reinterpret_cast<const float4*>(bias + s * 32) + c);
+            }
             tmem_ld_wait();
-            if (s == eh) { FU_T0(); mbar_wait(h_free, lc & 1); FU_ADD(e_free); }
+            if (s == eh) { FU_T0(); mbar_wait(h_free, hfree_parity); FU_ADD(e_free); }
             uint8_t* dst = sH + s * FU_CHUNK + r * 128;
             uint32_t pos = 0;
 #pragma unroll
@@ -273,21 +310,33 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
               float* of = reinterpret_cast<float*>(&o);
 #pragma unroll
               for (int j = 0; j < 4; j++) {
-                // ReLU, then round to TF32 (nearest, ties away: + half ulp, truncate — what cvt.rna.tf32
-                // computes for finite values, on the integer pipe instead of the quarter-rate converter)
-                const float x = fmaxf(__uint_as_float(v[c * 4 + j]) + bb[j], 0.f);
+                // forward: bias + ReLU; backward: ReLU derivative from the stored bit mask.  Then round to
+                // TF32 (nearest, ties away: + half ulp, truncate — what cvt.rna.tf32 computes for finite
+                // values, on the integer pipe instead of the quarter-rate converter)
+                float x = __uint_as_float(v[c * 4 + j]);
+                if (BWD) x = ((keep >> (c * 4 + j)) & 1u) ? x : 0.f;
+                else x = fmaxf(x + bb[j], 0.f);
                 const uint32_t u = (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u;
                 pos |= (u != 0u ? 1u : 0u) << (c * 4 + j);
                 of[j] = __uint_as_float(u);
+                if (BWD) v[c * 4 + j] = u;
               }
               *reinterpret_cast<float4*>(dst + ((c ^ (r & 7)) << 4)) = o;
             }
-            if (grow < p.M) mask[s] = pos;
+            if (!BWD && grow < p.M) mask[s] = pos;
             fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
             __syncwarp();
             if (lane == 0) {
               mbar_arrive(&a_local[s]);
               if (leader) mbar_arrive(&a_ready[s]); else mbar_arrive_cluster(&a_ready[s], 0);
+            }
+            if (BWD) {
+              // bias gradient of forward layer fl: column sums of the values just written (rows past M are 0)
+              float cv[32];
+#pragma unroll
+              for (int i = 0; i < 32; i++) cv[i] = __uint_as_float(v[i]);
+              const float tot = fu_transpose_reduce32(cv, lane);
+              atomicAdd(sCol + fl * FU_W + s * 32 + lane, tot);
             }
           }
         } else if (eh == 0) {
@@ -315,6 +364,7 @@ mlp_forward_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid
   }
   tc_fence_before();
   __syncthreads();
+  if (BWD) for (int i = threadIdx.x; i < p.nl * FU_W; i += FU_THREADS) atomicAdd(p.colsum + i, sCol[i]);
   cluster_sync();            // no CTA leaves while its peer may still signal its barriers or read its shared memory
   if (warp == 2) tmem_dealloc_2cta(tmem_base, 512);
 }
@@ -433,6 +483,44 @@ extern "C" TRASE_API int trase_b200_mlp_pack_fused(int nl, int skip, int E, cons
   return 0;
 }
 
+namespace tb {
+namespace mlp {
+template <bool BWD>
+static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMap& tW, const CUtensorMap& tWh,
+                        const CUtensorMap& tA, const FusedParams& p, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp_fused_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, FU_SMEM);
+    if (e != cudaSuccess) { set_error("%s: %s", who, cudaGetErrorString(e)); return 2; }
+    attr_set = true;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int tiles = (p.M + FU_BM - 1) / FU_BM;
+  int grid = tiles < sms ? tiles : sms;
+  grid = (grid + FU_CLUSTER - 1) / FU_CLUSTER * FU_CLUSTER;
+  if (grid > sms) grid -= FU_CLUSTER;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(FU_THREADS);
+  cfg.dynamicSmemBytes = FU_SMEM;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = FU_CLUSTER;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, mlp_fused_kernel<BWD>, tE, tW, tWh, tA, p);
+  if (le != cudaSuccess) { set_error("%s: launch failed: %s", who, cudaGetErrorString(le)); return 2; }
+  count_launches(1);
+  return 0;
+}
+}  // namespace mlp
+}  // namespace tb
+
 // emb: [M][ld_emb] (first E columns used, ld_emb multiple of 4), bias: nl*256 + 16 floats,
 // acts: [nl][M][256] (written), masks: [nl][M][8] (written), out16: [M][16] (written).
 extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const float* emb, int ld_emb,
@@ -450,7 +538,7 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
   int base[mlp::FU_MAX_LAYERS + 2];
   const int total = mlp::fu_layout(nl, skip, E, base);
   for (int L = 0; L <= nl; L++) p.blk_base[L] = base[L];
-  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.prof = mlp::g_fused_prof;
+  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.colsum = nullptr; p.prof = mlp::g_fused_prof;
   CUtensorMap tE, tW, tWh, tA;
   if (!mlp::make_tmap_2d(&tE, emb, M, E, ld_emb, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
@@ -459,38 +547,68 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
     set_error("trase_b200_mlp_forward_fused: cuTensorMapEncodeTiled failed");
     return 2;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp::mlp_forward_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         mlp::FU_SMEM);
-    if (e != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: %s", cudaGetErrorString(e)); return 2; }
-    attr_set = true;
+  return mlp::launch_fused<false>("trase_b200_mlp_forward_fused", tE, tW, tWh, tA, p,
+                                  reinterpret_cast<cudaStream_t>(stream));
+}
+
+// ---- backward data-gradient chain -----------------------------------------------------------------------
+// packed operand of the chain: one k-block from whT [256][16] (head weights transposed), then eight k-blocks
+// per hidden layer nl-1 .. 1 from wT[l-1] = W_l^T restricted to its hidden input columns, [256][256]
+extern "C" TRASE_API size_t trase_b200_mlp_fused_pack_bwd_floats(int nl) {
+  if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS) return 0;
+  return (size_t)(1 + mlp::FU_HCH * (nl - 1)) * mlp::FU_W * 32;
+}
+
+extern "C" TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, const float* whT, const float* const* wT, float* wpack,
+                                                       void* stream) {
+  if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !whT || !wT || !wpack) {
+    set_error("trase_b200_mlp_pack_fused_bwd: bad arguments");
+    return 1;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int tiles = (M + mlp::FU_BM - 1) / mlp::FU_BM;
-  int grid = tiles < sms ? tiles : sms;
-  grid = (grid + mlp::FU_CLUSTER - 1) / mlp::FU_CLUSTER * mlp::FU_CLUSTER;
-  if (grid > sms) grid -= mlp::FU_CLUSTER;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(mlp::FU_THREADS);
-  cfg.dynamicSmemBytes = mlp::FU_SMEM;
-  cfg.stream = reinterpret_cast<cudaStream_t>(stream);
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = mlp::FU_CLUSTER;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, mlp::mlp_forward_fused_kernel, tE, tW, tWh, tA, p);
-  if (le != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: launch failed: %s", cudaGetErrorString(le)); return 2; }
+  mlp::PackTable t;
+  t.nseg = 0;
+  t.seg[t.nseg++] = {whT, mlp::FU_W, 16, 0, 16, 0, 1};
+  for (int L = 1; L < nl; L++) {
+    const float* src = wT[nl - L - 1];          // backward step L differentiates forward layer nl - L
+    if (!src) { set_error("trase_b200_mlp_pack_fused_bwd: null weight pointer"); return 1; }
+    t.seg[t.nseg++] = {src, mlp::FU_W, mlp::FU_W, 0, mlp::FU_W, 1 + (L - 1) * mlp::FU_HCH, mlp::FU_HCH};
+  }
+  const int total = 1 + mlp::FU_HCH * (nl - 1);
+  mlp::mlp_pack_fused_kernel<<<total, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(t, wpack);
   cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) { set_error("trase_b200_mlp_forward_fused: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_fused_bwd: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
   return 0;
+}
+
+// dout: [M][16] packed upstream gradient of the heads; masks: [nl][M][8] from the forward pass;
+// dzs: [nl][M][256] (written): dzs[L] = dZ of forward layer nl-1-L; colsum: [nl][256], forward layer order,
+// receives += the bias gradients.
+extern "C" TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, const float* wpack,
+                                                       const uint32_t* masks, float* dzs, float* colsum,
+                                                       void* stream) {
+  if (M <= 0) return 0;
+  if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !dout || !wpack || !masks || !dzs || !colsum ||
+      ((uintptr_t)dout & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)dzs & 15)) {
+    set_error("trase_b200_mlp_backward_fused: bad arguments (M=%d nl=%d)", M, nl);
+    return 1;
+  }
+  mlp::FusedParams p;
+  p.M = M; p.nl = nl; p.skip = -1; p.eb = 1;
+  p.blk_base[0] = 0;
+  for (int L = 1; L <= nl; L++) p.blk_base[L] = 1 + (L - 1) * mlp::FU_HCH;
+  p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs; p.colsum = colsum;
+  p.prof = mlp::g_fused_prof;
+  const int total = 1 + mlp::FU_HCH * (nl - 1);
+  CUtensorMap tE, tW, tA;
+  if (!mlp::make_tmap_2d(&tE, dout, M, 16, 16, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
+      !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
+      !mlp::make_tmap_acts(&tA, dzs, M, nl)) {
+    set_error("trase_b200_mlp_backward_fused: cuTensorMapEncodeTiled failed");
+    return 2;
+  }
+  return mlp::launch_fused<true>("trase_b200_mlp_backward_fused", tE, tW, tW, tA, p,
+                                 reinterpret_cast<cudaStream_t>(stream));
 }
 
 // debug: device buffer of [grid][8] cycle counters filled by the fused kernel (NULL = off)
