@@ -139,6 +139,12 @@ typedef struct trase_b200_fwd_args {
   int64_t capacity;             /* instances the binning/scratch buffers hold     */
   int* num_rendered_host;       /* pinned host int or NULL (async D2H of R)       */
   void* stream;                 /* cudaStream_t                                   */
+  void* readback_event;         /* cudaEvent_t or NULL: recorded right after the   */
+                                /* D2H of R is queued, i.e. BEFORE the sort and    */
+                                /* the compositing kernel - a host that waits on   */
+                                /* it instead of the stream learns R (and whether  */
+                                /* the workspace overflowed) while the rest of the */
+                                /* forward pass is still running                   */
 } trase_b200_fwd_args;
 
 TRASE_API int trase_b200_rasterize_forward(const trase_b200_fwd_args* args);

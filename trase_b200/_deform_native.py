@@ -52,6 +52,34 @@ def _wgrad(lib, P, Q, D):
                                              M, D[:, j0:].data_ptr(), D.stride(0), s))
 
 
+def _round_transpose(lib, Ws, sizes, skip, E, want_rounded, f32, s):
+    """Wr[i] = TF32-rounded weight (only if want_rounded), WrT[i] = its transpose for i > 0, restricted to the hidden
+    input columns for the layer behind the skip; all in one flat buffer, one small kernel per layer."""
+    nl = len(sizes)
+    n_r = sum(r * c for r, c in sizes) if want_rounded else 0
+    n_t = sum(r * (c - E if i - 1 == skip else c) for i, (r, c) in enumerate(sizes) if i > 0)
+    wbuf = torch.empty(n_r + n_t, **f32)
+    Wr, WrT, off = [], [None] * nl, 0
+    for i, (r, c) in enumerate(sizes):
+        wr = None
+        if want_rounded:
+            wr = wbuf[off:off + r * c].view(r, c)
+            off += r * c
+        wt = None
+        if i > 0:
+            c0 = E if i - 1 == skip else 0
+            wt = wbuf[off:off + r * (c - c0)].view(c - c0, r)
+            off += r * (c - c0)
+            WrT[i] = wt
+        if wr is not None or wt is not None:
+            _lib.check(lib.trase_b200_mlp_round_transpose(
+                Ws[i].detach().contiguous().data_ptr(), r, c, E if (i > 0 and i - 1 == skip) else 0,
+                (c - E) if (i > 0 and i - 1 == skip) else (c if i > 0 else 0),
+                wr.data_ptr() if wr is not None else None, wt.data_ptr() if wt is not None else None, s))
+        Wr.append(wr)
+    return Wr, WrT
+
+
 class _DeformMLP(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, t, Lx, Lt, skip, *params):
@@ -69,34 +97,18 @@ class _DeformMLP(torch.autograd.Function):
             t_stride = 0 if (t.numel() == 1 or t.stride(0) == 0) else 1
             t_c = t if t_stride == 0 else t.contiguous()
             f32 = dict(dtype=torch.float32, device=dev)
-            # TF32-rounded weights (forward operand) and their transposes (backward operand), one small
-            # kernel per layer; the layer after the skip only back-propagates through its hidden columns
             sizes = [(w.shape[0], w.shape[1]) for w in Ws]
-            wbuf = torch.empty(sum(r * c for r, c in sizes) + sum(r * (c - E if i - 1 == skip else c)
-                                                                  for i, (r, c) in enumerate(sizes) if i > 0), **f32)
-            Wr, WrT, off = [], [None] * nl, 0
-            for i, (r, c) in enumerate(sizes):
-                wr = wbuf[off:off + r * c].view(r, c)
-                off += r * c
-                wt = None
-                if i > 0:
-                    c0 = E if i - 1 == skip else 0
-                    wt = wbuf[off:off + r * (c - c0)].view(c - c0, r)
-                    off += r * (c - c0)
-                    WrT[i] = wt
-                _lib.check(lib.trase_b200_mlp_round_transpose(
-                    Ws[i].detach().contiguous().data_ptr(), r, c, E if (i > 0 and i - 1 == skip) else 0,
-                    (c - E) if (i > 0 and i - 1 == skip) else (c if i > 0 else 0), wr.data_ptr(),
-                    wt.data_ptr() if wt is not None else None, s))
-                Wr.append(wr)
+            fused = FUSED_FORWARD and lib.trase_b200_mlp_fused_pack_floats(nl, skip, E) > 0 and \
+                all(r == W for r, _ in sizes)
+            # TF32-rounded weights (forward operand of the layer chain) and their transposes (backward operand);
+            # the fused forward packs its own operand, so there the transposes are left to backward()
+            Wr, WrT = (None, [None] * nl) if fused else _round_transpose(lib, Ws, sizes, skip, E, True, f32, s)
             hb = torch.empty(16 * W * 2 + 16, **f32)
             wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
             _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
                                                      wh.data_ptr(), whT.data_ptr(), bh.data_ptr(), s))
             masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
             out16 = torch.empty((M, 16), **f32)
-            fused = FUSED_FORWARD and lib.trase_b200_mlp_fused_pack_floats(nl, skip, E) > 0 and \
-                all(r == W for r, _ in sizes)
             if fused:
                 # one persistent kernel carries each 128-row tile through all layers (csrc/mlp_fused.cu)
                 emb = torch.empty((M, E), **f32)
@@ -125,7 +137,7 @@ class _DeformMLP(torch.autograd.Function):
                     acts.append(out)
                     inp = skipbuf if i == skip else out
                 _gemm(lib, acts[-1], wh, out16, bias=bh, round_tf32=False)
-        ctx.save_for_backward(skipbuf, whT, masks, *acts, *[w for w in WrT if w is not None])
+        ctx.save_for_backward(skipbuf, whT, masks, *acts, *(Ws if fused else [w for w in WrT if w is not None]))
         ctx.meta = (nl, skip, E, M, sizes, fused)
         return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
 
@@ -136,11 +148,14 @@ class _DeformMLP(torch.autograd.Function):
         saved = ctx.saved_tensors
         skipbuf, whT, masks = saved[0], saved[1], saved[2]
         acts = saved[3:3 + nl]
-        WrT = [None] + list(saved[3 + nl:])
         dev = skipbuf.device
         f32 = dict(dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             s = _stream(dev)
+            if fused:       # the forward kept the raw weights: build the transposed operands now
+                WrT = _round_transpose(lib, saved[3 + nl:], sizes, skip, E, False, f32, s)[1]
+            else:
+                WrT = [None] + list(saved[3 + nl:])
             # every weight / bias gradient lives in one zero-initialised buffer (one memset)
             n_w = sum(r * c for r, c in sizes)
             gbuf = torch.zeros(n_w + nl * W + W * 16 + 16, **f32)

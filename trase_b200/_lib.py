@@ -31,6 +31,7 @@ class FwdArgs(C.Structure):
         ("capacity", C.c_int64),
         ("num_rendered_host", C.c_void_p),
         ("stream", C.c_void_p),
+        ("readback_event", C.c_void_p),
     ]
 
 

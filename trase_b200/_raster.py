@@ -9,6 +9,7 @@ every buffer; the native side only sees raw pointers.
 from __future__ import annotations
 
 import ctypes as C
+import math
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -117,6 +118,8 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
         a.img, a.img_bytes = res.img.data_ptr(), res.img.numel()
         a.num_rendered_host = pinned.data_ptr()
         a.stream = stream.cuda_stream
+        readback = _readback_event(dev, stream)
+        a.readback_event = readback.cuda_event
 
         first = True
         while True:
@@ -127,9 +130,11 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
             a.capacity = capacity
             fn = lib.trase_b200_rasterize_forward if first else lib.trase_b200_rasterize_forward_rebin
             _lib.check(fn(C.byref(a)))
-            # One host wait at the END of the pass (the GPU pipeline itself never
-            # stalls): R must reach Python as an int for ctx (…/__init__.py:103).
-            stream.synchronize()
+            # One host wait per pass, on the event recorded right after the 4-byte readback of R was
+            # queued (the GPU pipeline itself never stalls): R must reach Python as an int for ctx
+            # (…/__init__.py:103).  The sort and the compositing kernel are still running when this
+            # returns, so the caller's Python (loss, autograd start-up, backward launches) overlaps them.
+            readback.synchronize()
             R = int(pinned[0].item()) if P > 0 else 0
             if R <= capacity:
                 break
@@ -140,6 +145,19 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
         res.num_rendered = R
         res.capacity = capacity
         return res
+
+
+_events: Dict = {}
+
+
+def _readback_event(dev, stream):
+    """One reusable CUDA event per device (created by a first record, re-recorded by the library)."""
+    ev = _events.get(dev)
+    if ev is None:
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        _events[dev] = ev
+    return ev
 
 
 def rasterize_backward(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3D_precomp,
@@ -165,17 +183,20 @@ def rasterize_backward(bg, means3D, radii, colors_precomp, scales, rotations, sc
         dL_dout_objects = _f32c(dL_dout_objects, dev)
         M = int(sh.shape[1]) if sh.numel() != 0 else 0
 
-        z = dict(dtype=torch.float32, device=dev)
-        dL_dmeans3D = torch.zeros((P, 3), **z)
-        dL_dmeans2D = torch.zeros((P, 3), **z)
-        dL_dcolors = torch.zeros((P, NUM_CHANNELS), **z)
-        dL_dobjects = torch.zeros((P, NUM_OBJECTS), **z)
-        dL_dconic = torch.zeros((P, 2, 2), **z)
-        dL_dopacity = torch.zeros((P, 1), **z)
-        dL_dcov3D = torch.zeros((P, 6), **z)
-        dL_dsh = torch.zeros((P, M, 3), **z)
-        dL_dscales = torch.zeros((P, 3), **z)
-        dL_drotations = torch.zeros((P, 4), **z)
+        # all gradient buffers carved out of ONE zero-filled allocation (one memset instead of ten);
+        # every sub-buffer starts on a 256-byte boundary (the compositing kernel adds float4s)
+        shapes = [(P, 3), (P, 3), (P, NUM_CHANNELS), (P, NUM_OBJECTS), (P, 2, 2), (P, 1), (P, 6), (P, M, 3), (P, 3),
+                  (P, 4)]
+        offs, n = [], 0
+        for shp in shapes:
+            offs.append(n)
+            cnt = 1
+            for d in shp:
+                cnt *= d
+            n += (cnt + 63) // 64 * 64
+        flat = torch.zeros((n,), dtype=torch.float32, device=dev)
+        (dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dconic, dL_dopacity, dL_dcov3D, dL_dsh, dL_dscales,
+         dL_drotations) = [flat[o:o + math.prod(shp)].view(shp) for o, shp in zip(offs, shapes)]
         if P != 0:
             if capacity is None:
                 capacity = (binning.numel() // 12) if binning.numel() else 0

@@ -168,6 +168,7 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
     TB_STEP("memset", cudaMemsetAsync(a->out_objects, 0, NUM_OBJECTS * HW * 4, stream));
     TB_STEP("memset", cudaMemsetAsync(a->out_depth, 0, HW * 4, stream));
     if (a->num_rendered_host) *a->num_rendered_host = 0;
+    if (a->readback_event) TB_STEP("record readback event", cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->readback_event), stream));
     return 0;
   }
   FwdPointers p = carve(a->geom, a->P, a->img, a->W, a->H, a->binning, a->capacity, a->scratch);
@@ -189,6 +190,7 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
   if (a->num_rendered_host)
     TB_STEP("copy num_rendered",
             cudaMemcpyAsync(a->num_rendered_host, p.counters, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  if (a->readback_event) TB_STEP("record readback event", cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->readback_event), stream));
   if (a->capacity > 0)
     TB_STEP_ST(ST_SORT, "sort_pairs", launch_sort_pingpong(keys_a, vals_a, keys_b, vals_b, p.counters, a->capacity, end_bit,
                                                p.sort_scratch, p.sort_scratch_bytes, stream));
