@@ -46,7 +46,7 @@ constexpr int FU_ECH = 3;                 // up to 96 embedding columns
 // ring stages of 16 KB (this CTA's half of a weight k-block, or a chunk of the first operand);
 // the backward chain gives one stage up for its bias-gradient accumulators
 template <bool BWD> struct FuCfg { static constexpr int STAGES = BWD ? 5 : 6; };
-constexpr int FU_EPI_WARPS = 8;
+constexpr int FU_EPI_WARPS = 8;            // two per TMEM lane quarter, alternating 32-column slabs (12 warps: no gain, the MMA side is the bound)
 constexpr int FU_THREADS = 128 + 32 * FU_EPI_WARPS;
 constexpr int FU_MAX_LAYERS = 12;
 constexpr int FU_CLUSTER = 2;             // CTA pair: one tcgen05.mma.cta_group::2 spans both         // hidden layers + the head pseudo-layer
@@ -288,7 +288,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
           const float* bias = p.bias + fl * FU_W;
           uint32_t* mask = p.masks + ((size_t)fl * p.M + (grow < p.M ? grow : 0)) * (FU_W / 32);
 #pragma unroll 1
-          for (int s = eh; s < FU_HCH; s += 2) {
+          for (int s = eh; s < FU_HCH; s += FU_EPI_WARPS / 4) {
             uint32_t v[32];
             tmem_ld_32x32(t_addr + s * 32, v);
             float4 bq[8];
