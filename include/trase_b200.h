@@ -413,16 +413,16 @@ TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const
  * again one persistent kernel: the gradient tile stays on chip between layers and is
  * written to HBM once per layer (the weight-gradient GEMMs read it from there).
  *   trase_b200_mlp_pack_fused_bwd: whT = packed head matrix transposed [256][16]
- *     (trase_b200_mlp_pack_heads), wT[i] = W_{i+1}^T restricted to its hidden input
- *     columns, [256][256] (trase_b200_mlp_round_transpose), i = 0 .. nl-2.
+ *     (trase_b200_mlp_pack_heads), weights = the same host array of nl raw weight
+ *     pointers as trase_b200_mlp_pack_fused (read transposed, hidden columns only).
  *   trase_b200_mlp_backward_fused: dout [M][16] (trase_b200_mlp_pack_dout), masks from the
  *     forward; writes dzs [nl][M][256] with dzs[L] = dZ of layer nl-1-L, and adds the bias
- *     gradients to colsum [nl][256] (forward layer order). */
+ *     gradient of layer l to colsum[l] (host array of nl device pointers, 256 floats each). */
 TRASE_API size_t trase_b200_mlp_fused_pack_bwd_floats(int nl);
-TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, const float* whT, const float* const* wT, float* wpack,
-                                            void* stream);
+TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, int skip, int E, const float* whT, const float* const* weights,
+                                            float* wpack, void* stream);
 TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, const float* wpack,
-                                            const uint32_t* masks, float* dzs, float* colsum, void* stream);
+                                            const uint32_t* masks, float* dzs, float* const* colsum, void* stream);
 
 /* ref: getHigherMsb (DGR/cuda_rasterizer/rasterizer_impl.cu:38-53). */
 TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);

@@ -164,3 +164,36 @@ def test_fused_forward_matches_layer_chain(M):
     # away from an fp32 evaluation (tests/test_deform_golden.py), so the two paths agree to that level
     for a, b in zip(res[False][1], res[True][1]):
         assert (a - b).abs().max() <= 3e-2 * a.abs().max() + 1e-7
+
+
+@pytest.mark.gpu
+def test_direct_gradient_accumulation_matches_autograd():
+    """With `.grad` tensors already in place (a flat arena), the hidden layers' weight/bias gradient kernels add
+    straight into them; the result must equal autograd's own `grad += new` (same kernels, same order of partial
+    sums up to the final add), including accumulation on top of existing contents."""
+    import torch
+    from trase_b200 import _deform_native as dn
+    from trase_b200.deform import DeformNetwork
+    from trase_b200.distributed import GradArena
+    torch.manual_seed(5)
+    net = DeformNetwork(backend="native").cuda()
+    M = 5000
+    g = torch.Generator(device="cuda").manual_seed(9)
+    x = (torch.rand(M, 3, device="cuda", generator=g) - 0.5) * 3
+    t = torch.full((M, 1), 0.3, device="cuda")
+    go = [torch.randn(M, k, device="cuda", generator=g) for k in (3, 4, 3)]
+    arena = GradArena(net.parameters())
+    res = {}
+    saved = dn.DIRECT_GRAD_ACCUM
+    try:
+        for direct in (False, True):
+            dn.DIRECT_GRAD_ACCUM = direct
+            arena.flat.fill_(0.25)                       # pre-existing gradient content must be kept
+            for _ in range(2):                           # two backward passes accumulate
+                torch.autograd.backward(list(net(x, t)), go)
+            res[direct] = arena.flat.clone()
+    finally:
+        dn.DIRECT_GRAD_ACCUM = saved
+    scale = (res[False] - 0.25).abs().max()
+    assert scale > 0
+    assert (res[False] - res[True]).abs().max() <= 1e-5 * scale

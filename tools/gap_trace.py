@@ -32,3 +32,9 @@ small = sum(max(0, b.time_range.start - a.time_range.end) for a, b in zip(ev[:-1
 print(f"gaps <= 3 us: {small/4:.1f} us/step in total; gaps > 3 us: {sum(g[0] for g in gaps)/4:.1f} us/step")
 for g in sorted(gaps, key=lambda g: -g[0])[:40]:
     print(f"{g[0]:8.1f} us at t={g[3]:9.1f}  after {g[1]:50s} before {g[2]}")
+
+if len(sys.argv) > 2:
+    # kernel sequence of the third step
+    n = len(ev) // 4
+    for e in ev[2 * n:3 * n]:
+        print(f"{e.time_range.start - t0:10.1f} {e.time_range.end - e.time_range.start:8.1f} us  {e.name[:90]}")

@@ -19,7 +19,11 @@ from . import _lib
 
 W = 256
 FUSED_FORWARD = True   # module switch: False runs the layer-by-layer GEMM chain (csrc/mlp_gemm.cu)
-FUSED_BACKWARD = True  # same for the data-gradient chain of the backward pass
+FUSED_BACKWARD = True  # same for the data-gradient chain of the backward pass (needs FUSED_FORWARD)
+# When every hidden-layer parameter already has a contiguous fp32 `.grad` (e.g. views of a flat gradient arena),
+# the weight- and bias-gradient kernels add straight into it (they accumulate anyway) and backward() returns None
+# for those inputs: same result as autograd's `grad += new` without 16 tiny add kernels and a zero-filled buffer.
+DIRECT_GRAD_ACCUM = True
 
 
 def tf32_round(w: torch.Tensor) -> torch.Tensor:
@@ -139,6 +143,9 @@ class _DeformMLP(torch.autograd.Function):
                 _gemm(lib, acts[-1], wh, out16, bias=bh, round_tf32=False)
         ctx.save_for_backward(skipbuf, whT, masks, *acts, *(Ws if fused else [w for w in WrT if w is not None]))
         ctx.meta = (nl, skip, E, M, sizes, fused)
+        # the parameter objects themselves: backward looks their .grad up (DIRECT_GRAD_ACCUM)
+        hp = list(params[:2 * nl])
+        ctx.hidden_params = hp if all(isinstance(p, torch.nn.Parameter) for p in hp) else None
         return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
 
     @staticmethod
@@ -152,20 +159,32 @@ class _DeformMLP(torch.autograd.Function):
         f32 = dict(dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             s = _stream(dev)
-            if fused:       # the forward kept the raw weights: build the transposed operands now
-                WrT = _round_transpose(lib, saved[3 + nl:], sizes, skip, E, False, f32, s)[1]
+            # the fused chain packs its operand from the raw weights the fused forward kept
+            fused_bwd = FUSED_BACKWARD and fused and lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
+            raw_w = list(saved[3 + nl:]) if fused else None
+            if fused_bwd:
+                WrT = None
+            elif fused:
+                WrT = _round_transpose(lib, raw_w, sizes, skip, E, False, f32, s)[1]
             else:
                 WrT = [None] + list(saved[3 + nl:])
-            # every weight / bias gradient lives in one zero-initialised buffer (one memset)
-            n_w = sum(r * c for r, c in sizes)
-            gbuf = torch.zeros(n_w + nl * W + W * 16 + 16, **f32)
-            grads_w, grads_b, off = [], [], 0
-            for r, c in sizes:
-                grads_w.append(gbuf[off:off + r * c].view(r, c))
-                off += r * c
-            for _ in range(nl):
-                grads_b.append(gbuf[off:off + W])
-                off += W
+            # gradient targets: the parameters' own .grad where possible (DIRECT_GRAD_ACCUM), else one zeroed buffer
+            hidden = ctx.hidden_params
+            direct = DIRECT_GRAD_ACCUM and hidden is not None and all(
+                p.grad is not None and p.grad.is_contiguous() and p.grad.dtype == torch.float32 and
+                p.grad.device == dev and p.grad.data_ptr() % 16 == 0 and p.grad.shape == p.shape for p in hidden)
+            gbuf = torch.zeros((0 if direct else sum(r * c for r, c in sizes) + nl * W) + W * 16 + 16, **f32)
+            off = 0
+            if direct:
+                grads_w, grads_b = [p.grad for p in hidden[0::2]], [p.grad for p in hidden[1::2]]
+            else:
+                grads_w, grads_b = [], []
+                for r, c in sizes:
+                    grads_w.append(gbuf[off:off + r * c].view(r, c))
+                    off += r * c
+                for _ in range(nl):
+                    grads_b.append(gbuf[off:off + W])
+                    off += W
             dwhT = gbuf[off:off + W * 16].view(W, 16)
             dbh = gbuf[off + W * 16:off + W * 16 + 16]
             dout = torch.empty((M, 16), **f32)
@@ -174,18 +193,16 @@ class _DeformMLP(torch.autograd.Function):
                                                     dout.data_ptr(), dbh.data_ptr(), s))
             # heads: dWh^T = h_last^T dout
             _wgrad(lib, acts[-1], dout, dwhT)
-            fused_bwd = FUSED_BACKWARD and all(r == W for r, _ in sizes) and \
-                lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
             if fused_bwd:
                 # the whole data-gradient chain in one persistent kernel (csrc/mlp_fused.cu): dzs[L] = dZ of
-                # layer nl-1-L, bias gradients straight into the gradient buffer
+                # layer nl-1-L, bias gradients straight into their targets
                 wpack_b = torch.empty(lib.trase_b200_mlp_fused_pack_bwd_floats(nl), **f32)
-                wT = (ctypes.c_void_p * (nl - 1))(*[WrT[i].data_ptr() for i in range(1, nl)])
-                _lib.check(lib.trase_b200_mlp_pack_fused_bwd(nl, whT.data_ptr(), wT, wpack_b.data_ptr(), s))
+                wptrs = (ctypes.c_void_p * nl)(*[w.detach().contiguous().data_ptr() for w in raw_w])
+                _lib.check(lib.trase_b200_mlp_pack_fused_bwd(nl, skip, E, whT.data_ptr(), wptrs, wpack_b.data_ptr(), s))
                 dzs = torch.empty((nl, M, W), **f32)
+                bptrs = (ctypes.c_void_p * nl)(*[g.data_ptr() for g in grads_b])
                 _lib.check(lib.trase_b200_mlp_backward_fused(M, nl, dout.data_ptr(), wpack_b.data_ptr(),
-                                                             masks.data_ptr(), dzs.data_ptr(),
-                                                             grads_b[0].data_ptr(), s))
+                                                             masks.data_ptr(), dzs.data_ptr(), bptrs, s))
             else:
                 # dZ_{nl-1} = (dout Wh) * relu'(h_last); its column sums are the bias gradient of layer nl-1
                 dz = torch.empty((M, W), **f32)
@@ -207,7 +224,7 @@ class _DeformMLP(torch.autograd.Function):
             dwh = dwhT.t()
             out = [None, None, None, None, None]
             for i in range(nl):
-                out += [grads_w[i], grads_b[i]]
+                out += [None, None] if direct else [grads_w[i], grads_b[i]]
             out += [dwh[0:3], dbh[0:3], dwh[3:7], dbh[3:7], dwh[7:10], dbh[7:10]]
         return tuple(out)
 

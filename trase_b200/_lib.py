@@ -158,9 +158,9 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_fused_pack_bwd_floats.restype = C.c_size_t
     lib.trase_b200_mlp_fused_pack_bwd_floats.argtypes = [C.c_int]
     lib.trase_b200_mlp_pack_fused_bwd.restype = C.c_int
-    lib.trase_b200_mlp_pack_fused_bwd.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]
+    lib.trase_b200_mlp_pack_fused_bwd.argtypes = [C.c_int] * 3 + [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]
     lib.trase_b200_mlp_backward_fused.restype = C.c_int
-    lib.trase_b200_mlp_backward_fused.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 6
+    lib.trase_b200_mlp_backward_fused.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.POINTER(C.c_void_p), C.c_void_p]
     lib.trase_b200_mlp_forward_fused.restype = C.c_int
     lib.trase_b200_mlp_forward_fused.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 6
     lib.trase_b200_l1_ssim_backward.restype = C.c_int

@@ -64,7 +64,7 @@ struct FusedParams {
   uint32_t* masks;                   // [nl][M][8]  ReLU bit masks
   float* out16;                      // [M][16]
   float* acts;                       // [nl][M][256]  (backward: dZ of every layer, in backward order)
-  float* colsum;                     // backward: [nl][256] bias gradients, forward layer order (+=)
+  float* colsum[FU_MAX_LAYERS];      // backward: bias gradient [256] of every forward layer (+=)
   unsigned long long* prof;          // optional [grid][8] stall-cycle counters (tools/check_fused_mlp.py)
 };
 
@@ -364,7 +364,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
   }
   tc_fence_before();
   __syncthreads();
-  if (BWD) for (int i = threadIdx.x; i < p.nl * FU_W; i += FU_THREADS) atomicAdd(p.colsum + i, sCol[i]);
+  if (BWD) for (int i = threadIdx.x; i < p.nl * FU_W; i += FU_THREADS) atomicAdd(p.colsum[i / FU_W] + (i % FU_W), sCol[i]);
   cluster_sync();            // no CTA leaves while its peer may still signal its barriers or read its shared memory
   if (warp == 2) tmem_dealloc_2cta(tmem_base, 512);
 }
@@ -374,8 +374,8 @@ unsigned long long* g_fused_prof = nullptr;   // set through trase_b200_set_tuni
 // ---- weight packing: [k-block][256 rows][32] fp32, TF32-rounded, zero-padded ---------------------------
 constexpr int FU_MAX_SEGS = 16;
 struct PackSeg {
-  const float* src;   // [rows][ld]
-  int rows, ld, k0, kcount, blk0, nblk;
+  const float* src;   // tr == 0: element (n, k) = src[n * ld + k0 + k];  tr == 1: src[(k0 + k) * ld + n0 + n]
+  int rows, ld, k0, kcount, blk0, nblk, tr, n0;
 };
 struct PackTable {
   PackSeg seg[FU_MAX_SEGS];
@@ -394,7 +394,8 @@ __global__ void __launch_bounds__(256) mlp_pack_fused_kernel(const PackTable t, 
     float v = 0.f;
     if (n < sg.rows && k < sg.kcount) {
       uint32_t u;
-      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(sg.src[(size_t)n * sg.ld + sg.k0 + k]));
+      const size_t at = sg.tr ? (size_t)(sg.k0 + k) * sg.ld + sg.n0 + n : (size_t)n * sg.ld + sg.k0 + k;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(sg.src[at]));
       v = __uint_as_float(u);
     }
     out[(size_t)blk * FU_W * 32 + e] = v;
@@ -468,12 +469,12 @@ extern "C" TRASE_API int trase_b200_mlp_pack_fused(int nl, int skip, int E, cons
     if (!src) { set_error("trase_b200_mlp_pack_fused: null weight pointer"); return 1; }
     const int rows = L < nl ? mlp::FU_W : 16;
     if (L == 0) {
-      t.seg[t.nseg++] = {src, rows, E, 0, E, base[L], eb};
+      t.seg[t.nseg++] = {src, rows, E, 0, E, base[L], eb, 0, 0};
     } else if (L < nl && L - 1 == skip) {
-      t.seg[t.nseg++] = {src, rows, E + mlp::FU_W, 0, E, base[L], eb};
-      t.seg[t.nseg++] = {src, rows, E + mlp::FU_W, E, mlp::FU_W, base[L] + eb, mlp::FU_HCH};
+      t.seg[t.nseg++] = {src, rows, E + mlp::FU_W, 0, E, base[L], eb, 0, 0};
+      t.seg[t.nseg++] = {src, rows, E + mlp::FU_W, E, mlp::FU_W, base[L] + eb, mlp::FU_HCH, 0, 0};
     } else {
-      t.seg[t.nseg++] = {src, rows, mlp::FU_W, 0, mlp::FU_W, base[L], mlp::FU_HCH};
+      t.seg[t.nseg++] = {src, rows, mlp::FU_W, 0, mlp::FU_W, base[L], mlp::FU_HCH, 0, 0};
     }
   }
   mlp::mlp_pack_fused_kernel<<<total, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(t, wpack);
@@ -538,7 +539,7 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
   int base[mlp::FU_MAX_LAYERS + 2];
   const int total = mlp::fu_layout(nl, skip, E, base);
   for (int L = 0; L <= nl; L++) p.blk_base[L] = base[L];
-  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.colsum = nullptr; p.prof = mlp::g_fused_prof;
+  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; for (int i = 0; i < mlp::FU_MAX_LAYERS; i++) p.colsum[i] = nullptr; p.prof = mlp::g_fused_prof;
   CUtensorMap tE, tW, tWh, tA;
   if (!mlp::make_tmap_2d(&tE, emb, M, E, ld_emb, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
@@ -553,25 +554,28 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
 
 // ---- backward data-gradient chain -----------------------------------------------------------------------
 // packed operand of the chain: one k-block from whT [256][16] (head weights transposed), then eight k-blocks
-// per hidden layer nl-1 .. 1 from wT[l-1] = W_l^T restricted to its hidden input columns, [256][256]
+// per hidden layer nl-1 .. 1: B[n][k] = W_l[k][off_l + n], read (transposed) straight from the raw nn.Linear
+// weights; off_l = E for the layer behind the skip (its first E input columns are the embedding), else 0
 extern "C" TRASE_API size_t trase_b200_mlp_fused_pack_bwd_floats(int nl) {
   if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS) return 0;
   return (size_t)(1 + mlp::FU_HCH * (nl - 1)) * mlp::FU_W * 32;
 }
 
-extern "C" TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, const float* whT, const float* const* wT, float* wpack,
-                                                       void* stream) {
-  if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !whT || !wT || !wpack) {
+extern "C" TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, int skip, int E, const float* whT,
+                                                       const float* const* weights, float* wpack, void* stream) {
+  if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !whT || !weights || !wpack || E < 0) {
     set_error("trase_b200_mlp_pack_fused_bwd: bad arguments");
     return 1;
   }
   mlp::PackTable t;
   t.nseg = 0;
-  t.seg[t.nseg++] = {whT, mlp::FU_W, 16, 0, 16, 0, 1};
+  t.seg[t.nseg++] = {whT, mlp::FU_W, 16, 0, 16, 0, 1, 0, 0};
   for (int L = 1; L < nl; L++) {
-    const float* src = wT[nl - L - 1];          // backward step L differentiates forward layer nl - L
+    const int fl = nl - L;                      // backward step L differentiates forward layer nl - L
+    const float* src = weights[fl];
     if (!src) { set_error("trase_b200_mlp_pack_fused_bwd: null weight pointer"); return 1; }
-    t.seg[t.nseg++] = {src, mlp::FU_W, mlp::FU_W, 0, mlp::FU_W, 1 + (L - 1) * mlp::FU_HCH, mlp::FU_HCH};
+    const int off = (fl - 1 == skip) ? E : 0;
+    t.seg[t.nseg++] = {src, mlp::FU_W, off + mlp::FU_W, 0, mlp::FU_W, 1 + (L - 1) * mlp::FU_HCH, mlp::FU_HCH, 1, off};
   }
   const int total = 1 + mlp::FU_HCH * (nl - 1);
   mlp::mlp_pack_fused_kernel<<<total, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(t, wpack);
@@ -582,10 +586,10 @@ extern "C" TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, const float* whT,
 }
 
 // dout: [M][16] packed upstream gradient of the heads; masks: [nl][M][8] from the forward pass;
-// dzs: [nl][M][256] (written): dzs[L] = dZ of forward layer nl-1-L; colsum: [nl][256], forward layer order,
-// receives += the bias gradients.
+// dzs: [nl][M][256] (written): dzs[L] = dZ of forward layer nl-1-L; colsum: host array of nl device pointers,
+// colsum[l] = 256 floats that receive += the bias gradient of forward layer l.
 extern "C" TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, const float* wpack,
-                                                       const uint32_t* masks, float* dzs, float* colsum,
+                                                       const uint32_t* masks, float* dzs, float* const* colsum,
                                                        void* stream) {
   if (M <= 0) return 0;
   if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !dout || !wpack || !masks || !dzs || !colsum ||
@@ -597,7 +601,11 @@ extern "C" TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const floa
   p.M = M; p.nl = nl; p.skip = -1; p.eb = 1;
   p.blk_base[0] = 0;
   for (int L = 1; L <= nl; L++) p.blk_base[L] = 1 + (L - 1) * mlp::FU_HCH;
-  p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs; p.colsum = colsum;
+  p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs;
+  for (int i = 0; i < nl; i++) {
+    if (!colsum[i]) { set_error("trase_b200_mlp_backward_fused: null bias-gradient pointer"); return 1; }
+    p.colsum[i] = colsum[i];
+  }
   p.prof = mlp::g_fused_prof;
   const int total = 1 + mlp::FU_HCH * (nl - 1);
   CUtensorMap tE, tW, tA;
