@@ -325,7 +325,7 @@ TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, const float*
  * cap, a frame loop that may not take the driver's allocator lock (cudaMalloc
  * and cudaFree can stall every stream), or a plug-in running inside another
  * runtime's no-allocation callback.  The histogram workspace lives inside the
- * library in a fixed ~1 MiB device array that every GPU loading the library
+ * library in a fixed ~2 MiB device array that every GPU loading the library
  * holds until the process exits; the caller passes only its own key/value
  * buffers and the device count.
  *

@@ -107,6 +107,13 @@ class _DeformMLP(torch.autograd.Function):
             # TF32-rounded weights (forward operand of the layer chain) and their transposes (backward operand);
             # the fused forward packs its own operand, so there the transposes are left to backward()
             Wr, WrT = (None, [None] * nl) if fused else _round_transpose(lib, Ws, sizes, skip, E, True, f32, s)
+            emb = None
+            if fused:
+                # the positional encoding is the longest of the small preparatory kernels: launched first, it
+                # covers the host time needed to launch the others
+                emb = torch.empty((M, E), **f32)
+                _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt, emb.data_ptr(),
+                                                       emb.stride(0), s))
             hb = torch.empty(16 * W * 2 + 16, **f32)
             wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
             _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
@@ -115,9 +122,6 @@ class _DeformMLP(torch.autograd.Function):
             out16 = torch.empty((M, 16), **f32)
             if fused:
                 # one persistent kernel carries each 128-row tile through all layers (csrc/mlp_fused.cu)
-                emb = torch.empty((M, E), **f32)
-                _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt, emb.data_ptr(),
-                                                       emb.stride(0), s))
                 wpack = torch.empty(lib.trase_b200_mlp_fused_pack_floats(nl, skip, E), **f32)
                 wptrs = (ctypes.c_void_p * nl)(*[w.detach().contiguous().data_ptr() for w in Ws])
                 _lib.check(lib.trase_b200_mlp_pack_fused(nl, skip, E, wptrs, wh.data_ptr(), wpack.data_ptr(), s))

@@ -154,7 +154,7 @@ cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPoi
 }
 
 // ---------------------------------------------------------------------------
-// LSD radix sort, 8-bit digits, three kernels per pass:
+// LSD radix sort, 9-bit digits (SORT_RADIX_BITS), three kernels per pass:
 //   upsweep  : per-block digit histogram  → hist[digit][block], digit totals
 //   scan     : one block per digit: exclusive scan along blocks + digit base
 //   downsweep: stable in-block ranking (warp match-any) and scatter
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_upsweep_kernel(const uint6
   const uint32_t block_start = blockIdx.x * SORT_TILE;
   if (block_start >= R) return;
   __shared__ uint32_t s_hist[SORT_RADIX];
-  s_hist[threadIdx.x] = 0;
+  for (int d = threadIdx.x; d < SORT_RADIX; d += SORT_THREADS) s_hist[d] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t warp_base = block_start + warp * (32 * SORT_ITEMS);
@@ -189,9 +189,11 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_upsweep_kernel(const uint6
     }
   }
   __syncthreads();
-  uint32_t c = s_hist[threadIdx.x];
-  hist[(size_t)threadIdx.x * nblk_stride + blockIdx.x] = c;
-  if (c) atomicAdd(&digit_total[threadIdx.x], c);
+  for (int d = threadIdx.x; d < SORT_RADIX; d += SORT_THREADS) {
+    const uint32_t c = s_hist[d];
+    hist[(size_t)d * nblk_stride + blockIdx.x] = c;
+    if (c) atomicAdd(&digit_total[d], c);
+  }
 }
 
 __global__ void __launch_bounds__(SORT_THREADS) radix_scan_kernel(uint32_t* __restrict__ hist, int nblk_stride,
@@ -205,7 +207,8 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scan_kernel(uint32_t* __re
   __shared__ uint32_t s_carry;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // digit base = number of keys with a smaller digit
-  uint32_t v = (threadIdx.x < d) ? digit_total[threadIdx.x] : 0u;
+  uint32_t v = 0;
+  for (int x = threadIdx.x; x < d; x += SORT_THREADS) v += digit_total[x];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   if (lane == 0) s_warp[warp] = v;
@@ -251,8 +254,7 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
   if (block_start >= R) return;
   constexpr int NW = SORT_THREADS / 32;
   __shared__ uint32_t s_cnt[NW][SORT_RADIX];
-#pragma unroll
-  for (int w = 0; w < NW; w++) s_cnt[w][threadIdx.x] = 0;
+  for (int d = threadIdx.x; d < NW * SORT_RADIX; d += SORT_THREADS) (&s_cnt[0][0])[d] = 0;
   __syncthreads();
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -280,9 +282,8 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
     __syncwarp();
   }
   __syncthreads();
-  {
+  for (int d = threadIdx.x; d < SORT_RADIX; d += SORT_THREADS) {
     // per-digit exclusive offsets across warps, plus this block's global base
-    const int d = threadIdx.x;
     uint32_t run = hist[(size_t)d * nblk_stride + blockIdx.x];
 #pragma unroll
     for (int w = 0; w < NW; w++) {

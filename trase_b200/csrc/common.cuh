@@ -83,7 +83,7 @@ inline BinLayout bin_layout(int64_t capacity) {
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;                       // keys per thread
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS; // keys per block
-constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX_BITS = 9;   // 13 tile bits + 32 depth bits = 45 = 5 passes of 9 (8-bit digits needed 6)
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 8;
 

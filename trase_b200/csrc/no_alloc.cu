@@ -19,7 +19,7 @@
 // Limits and rules (also in include/trase_b200.h):
 //   * at most TRASE_B200_STATIC_SORT_MAX pairs per call; larger requests are
 //     refused with an error, nothing is launched;
-//   * the workspace costs about 1 MiB on every GPU that loads the library;
+//   * the workspace costs about 2 MiB on every GPU that loads the library;
 //   * every call on a GPU uses the same array and finds the previous call's
 //     numbers in it.  The part that has to start from zero (the per-digit
 //     totals) is cleared on the caller's stream at the start of each call; the
