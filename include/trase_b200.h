@@ -424,6 +424,24 @@ TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, int skip, int E, const float
 TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, const float* wpack,
                                             const uint32_t* masks, float* dzs, float* const* colsum, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Fused Adam over flat arenas and the densification statistics (SURVEY.md
+ * §8(f) rank 4).  ref: torch.optim.Adam(groups, lr=0.0, eps=1e-15) as set up in
+ * scene/gaussian_model.py:259-289 and scene/deform_model.py:38-43 (torch's
+ * single-tensor update, op for op), and GaussianModel.add_densification_stats
+ * (scene/gaussian_model.py:637-639).
+ * params / grads / exp_avg / exp_avg_sq: n fp32 each.  Segments (host arrays of
+ * nseg <= 64 entries): seg_end[i] = exclusive end offset, step_size[i] =
+ * lr_i / (1 - beta1^t_i), bc2_sqrt[i] = sqrt(1 - beta2^t_i); a segment with
+ * step_size == 0 and bc2_sqrt == 0 is left untouched.
+ * densification_stats: grad_accum[i] += ||viewspace_grad[i][0:2]||, denom[i] += 1
+ * where filter[i] (bool bytes). */
+TRASE_API int trase_b200_adam_step(int64_t n, float* params, const float* grads, float* exp_avg, float* exp_avg_sq,
+                                   int nseg, const int64_t* seg_end, const float* step_size, const float* bc2_sqrt,
+                                   float beta1, float beta2, float eps, void* stream);
+TRASE_API int trase_b200_densification_stats(int P, const float* viewspace_grad, const unsigned char* filter,
+                                             float* grad_accum, float* denom, void* stream);
+
 /* ref: getHigherMsb (DGR/cuda_rasterizer/rasterizer_impl.cu:38-53). */
 TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);
 

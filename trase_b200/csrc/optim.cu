@@ -1,0 +1,102 @@
+// Fused Adam over the flat parameter / gradient arenas and the densification statistics
+// (first part).
+// ref: torch.optim.Adam(groups, lr=0.0, eps=1e-15) as TRASE configures it — one optimizer with a group per
+// Gaussian attribute (scene/gaussian_model.py:259-289) and one for the DeformNetwork (scene/deform_model.py:38-43),
+// each stepping ~10-20 tensors with a handful of elementwise kernels per tensor — and
+// GaussianModel.add_densification_stats (scene/gaussian_model.py:637-639).
+// Here: parameters, gradients and both moments live in flat fp32 buffers (the gradient buffer is the
+// all-reduced arena of trase_b200/distributed.py), segments carry their own step size, one kernel per step.
+#include "common.cuh"
+
+namespace tb {
+
+constexpr int ADAM_MAX_SEGS = 64;
+struct AdamTable {
+  long long end[ADAM_MAX_SEGS];     // exclusive end offset of each segment (ascending)
+  float step_size[ADAM_MAX_SEGS];   // lr / (1 - beta1^t)
+  float bc2_sqrt[ADAM_MAX_SEGS];    // sqrt(1 - beta2^t)
+  int nseg;
+};
+
+// torch's single-tensor Adam, op for op (torch/optim/adam.py _single_tensor_adam):
+//   m.lerp_(g, 1 - b1);  v.mul_(b2).addcmul_(g, g, value = 1 - b2);
+//   denom = v.sqrt() / sqrt(1 - b2^t) + eps;  p.addcdiv_(m, denom, value = -lr / (1 - b1^t))
+__global__ void __launch_bounds__(256) adam_step_kernel(long long n, float* __restrict__ p, const float* __restrict__ g,
+                                                        float* __restrict__ m, float* __restrict__ v,
+                                                        const AdamTable t, float beta1, float beta2, float eps) {
+  const float w1 = 1.f - beta1, w2 = 1.f - beta2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    int lo = 0, hi = t.nseg - 1;            // first segment whose end is > i
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (t.end[mid] > i) hi = mid; else lo = mid + 1;
+    }
+    const float step = t.step_size[lo];
+    if (step == 0.f && t.bc2_sqrt[lo] == 0.f) continue;      // frozen segment (not stepped this call)
+    const float gi = g[i];
+    const float mi = fmaf(w1, gi - m[i], m[i]);
+    const float vi = fmaf(w2 * gi, gi, v[i] * beta2);
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / t.bc2_sqrt[lo] + eps;
+    p[i] = fmaf(-step, mi / denom, p[i]);
+  }
+}
+
+__global__ void __launch_bounds__(256) densification_stats_kernel(int P, const float* __restrict__ grad3,
+                                                                  const bool* __restrict__ filter,
+                                                                  float* __restrict__ accum, float* __restrict__ denom) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < P && filter[i]) {
+    const float x = grad3[3 * i], y = grad3[3 * i + 1];
+    accum[i] += sqrtf(x * x + y * y);
+    denom[i] += 1.f;
+  }
+}
+
+}  // namespace tb
+
+using namespace tb;
+
+extern "C" TRASE_API int trase_b200_adam_step(int64_t n, float* params, const float* grads, float* exp_avg,
+                                              float* exp_avg_sq, int nseg, const int64_t* seg_end,
+                                              const float* step_size, const float* bc2_sqrt, float beta1, float beta2,
+                                              float eps, void* stream) {
+  if (n <= 0) return 0;
+  if (!params || !grads || !exp_avg || !exp_avg_sq || !seg_end || !step_size || !bc2_sqrt || nseg <= 0 ||
+      nseg > ADAM_MAX_SEGS) {
+    set_error("trase_b200_adam_step: bad arguments (n=%lld nseg=%d, at most %d segments)", (long long)n, nseg,
+              ADAM_MAX_SEGS);
+    return 1;
+  }
+  AdamTable t;
+  t.nseg = nseg;
+  long long prev = 0;
+  for (int i = 0; i < nseg; i++) {
+    if (seg_end[i] < prev) { set_error("trase_b200_adam_step: segment ends must ascend"); return 1; }
+    prev = t.end[i] = seg_end[i];
+    t.step_size[i] = step_size[i];
+    t.bc2_sqrt[i] = bc2_sqrt[i];
+  }
+  if (prev != n) { set_error("trase_b200_adam_step: segments must cover the buffer"); return 1; }
+  long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  adam_step_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(n, params, grads, exp_avg, exp_avg_sq,
+                                                                                  t, beta1, beta2, eps);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_adam_step: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+extern "C" TRASE_API int trase_b200_densification_stats(int P, const float* viewspace_grad, const unsigned char* filter,
+                                                        float* grad_accum, float* denom, void* stream) {
+  if (P <= 0) return 0;
+  if (!viewspace_grad || !filter || !grad_accum || !denom) { set_error("trase_b200_densification_stats: null pointer"); return 1; }
+  densification_stats_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, viewspace_grad, reinterpret_cast<const bool*>(filter), grad_accum, denom);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_densification_stats: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
