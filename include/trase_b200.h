@@ -398,7 +398,8 @@ TRASE_API int trase_b200_feature_norm_reg_backward(int C, int64_t N, const float
  *   trase_b200_mlp_forward_fused: emb [M][ld_emb] (E columns used), bias =
  *     nl*256 hidden biases then 16 head biases; writes acts [nl][M][256]
  *     (TF32-rounded post-ReLU activations), masks [nl][M][8] (bit = output > 0)
- *     and out16 [M][16] (heads: 3 warp, 4 rotation, 3 scaling, 6 zero).
+ *     and out16 [M][16] (heads: 3 warp, 4 rotation, 3 scaling, 6 zero).  acts and masks
+ *     both NULL = inference: nothing is kept for a backward pass.
  * Restrictions: width 256, 2 <= nl <= 11, E <= 96 and a multiple of 4,
  * skip < nl - 1 (or -1 for none).
  * ---------------------------------------------------------------------- */

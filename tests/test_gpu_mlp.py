@@ -197,3 +197,21 @@ def test_direct_gradient_accumulation_matches_autograd():
     scale = (res[False] - 0.25).abs().max()
     assert scale > 0
     assert (res[False] - res[True]).abs().max() <= 1e-5 * scale
+
+
+@pytest.mark.gpu
+def test_inference_forward_matches_training_forward():
+    """Under torch.no_grad the fused forward keeps nothing for backward (no activation / mask stores); the three
+    outputs must be bit-identical to the training-mode forward."""
+    import torch
+    from trase_b200.deform import DeformNetwork
+    torch.manual_seed(8)
+    net = DeformNetwork(backend="native").cuda()
+    M = 70001
+    x = (torch.rand(M, 3, device="cuda") - 0.5) * 3
+    t = torch.full((M, 1), 0.6, device="cuda")
+    train = [o.detach() for o in net(x, t)]
+    with torch.no_grad():
+        infer = net(x, t)
+    for a, b in zip(train, infer):
+        assert torch.equal(a, b)

@@ -86,7 +86,7 @@ def _round_transpose(lib, Ws, sizes, skip, E, want_rounded, f32, s):
 
 class _DeformMLP(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, t, Lx, Lt, skip, *params):
+    def forward(ctx, x, t, Lx, Lt, skip, keep, *params):
         lib = _lib.load()
         nl = (len(params) - 6) // 2
         Ws, bs = params[0:2 * nl:2], params[1:2 * nl:2]
@@ -118,7 +118,6 @@ class _DeformMLP(torch.autograd.Function):
             wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
             _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
                                                      wh.data_ptr(), whT.data_ptr(), bh.data_ptr(), s))
-            masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
             out16 = torch.empty((M, 16), **f32)
             if fused:
                 # one persistent kernel carries each 128-row tile through all layers (csrc/mlp_fused.cu)
@@ -126,6 +125,13 @@ class _DeformMLP(torch.autograd.Function):
                 wptrs = (ctypes.c_void_p * nl)(*[w.detach().contiguous().data_ptr() for w in Ws])
                 _lib.check(lib.trase_b200_mlp_pack_fused(nl, skip, E, wptrs, wh.data_ptr(), wpack.data_ptr(), s))
                 ball = torch.cat([b.detach().reshape(-1) for b in bs] + [bh])
+                if not keep:
+                    # inference (torch.no_grad / frozen network): no activations or masks leave the chip
+                    _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
+                                                                wpack.data_ptr(), ball.data_ptr(), None, None,
+                                                                out16.data_ptr(), s))
+                    return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
+                masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
                 acts_all = torch.empty((nl, M, W), **f32)
                 _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
                                                             wpack.data_ptr(), ball.data_ptr(), acts_all.data_ptr(),
@@ -133,6 +139,7 @@ class _DeformMLP(torch.autograd.Function):
                 acts = list(acts_all.unbind(0))
                 skipbuf = emb
             else:
+                masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
                 # skip buffer [M, E + W]: embedding in [:, :E], output of layer `skip` in [:, E:]
                 skipbuf = torch.empty((M, E + W), **f32)
                 _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt,
@@ -226,7 +233,7 @@ class _DeformMLP(torch.autograd.Function):
                     _gemm(lib, dz, WrT[i], dz_prev, mask_in=masks[i - 1], colsum=grads_b[i - 1])
                     dz = dz_prev
             dwh = dwhT.t()
-            out = [None, None, None, None, None]
+            out = [None, None, None, None, None, None]
             for i in range(nl):
                 out += [None, None] if direct else [grads_w[i], grads_b[i]]
             out += [dwh[0:3], dbh[0:3], dwh[3:7], dbh[3:7], dwh[7:10], dbh[7:10]]
@@ -243,4 +250,6 @@ def deform_forward(net, x, t):
         params += [lin.weight, lin.bias]
     for head in (net.gaussian_warp, net.gaussian_rotation, net.gaussian_scaling):
         params += [head.weight, head.bias]
-    return _DeformMLP.apply(x, t, net.multires, net.t_multires, net.skips[0], *params)
+    # grad mode is always off inside Function.forward, so decide here whether anything must be kept for backward
+    keep = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+    return _DeformMLP.apply(x, t, net.multires, net.t_multires, net.skips[0], keep, *params)

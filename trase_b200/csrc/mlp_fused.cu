@@ -213,7 +213,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
               FU_ADD(w_a);
               tc_fence_after();
               a_addr = smem_u32(sH + j * FU_CHUNK);
-              tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
+              if (p.acts) tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
             }
             if (!mma_layer) continue;
             if (leader) {
@@ -323,7 +323,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
               }
               *reinterpret_cast<float4*>(dst + ((c ^ (r & 7)) << 4)) = o;
             }
-            if (!BWD && grow < p.M) mask[s] = pos;
+            if (!BWD && p.masks && grow < p.M) mask[s] = pos;
             fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
             __syncwarp();
             if (lane == 0) {
@@ -524,11 +524,13 @@ static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMa
 
 // emb: [M][ld_emb] (first E columns used, ld_emb multiple of 4), bias: nl*256 + 16 floats,
 // acts: [nl][M][256] (written), masks: [nl][M][8] (written), out16: [M][16] (written).
+// acts == masks == NULL: inference, nothing is kept for a backward pass (no activation traffic to HBM at all).
 extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const float* emb, int ld_emb,
                                                       const float* wpack, const float* bias, float* acts,
                                                       uint32_t* masks, float* out16, void* stream) {
   if (M <= 0) return 0;
-  if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || !acts || !masks || !out16 || (ld_emb & 3) ||
+  if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || !out16 || ((acts == nullptr) != (masks == nullptr)) ||
+      (ld_emb & 3) ||
       ld_emb < E || ((uintptr_t)emb & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)acts & 15) ||
       ((uintptr_t)bias & 15) || ((uintptr_t)out16 & 15)) {
     set_error("trase_b200_mlp_forward_fused: bad arguments (M=%d nl=%d skip=%d E=%d)", M, nl, skip, E);
@@ -544,7 +546,7 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
   if (!mlp::make_tmap_2d(&tE, emb, M, E, ld_emb, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tWh, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 16, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
-      !mlp::make_tmap_acts(&tA, acts, M, nl)) {
+      !mlp::make_tmap_acts(&tA, acts ? acts : out16, M, acts ? nl : 1)) {   // inference: map unused, must still be valid
     set_error("trase_b200_mlp_forward_fused: cuTensorMapEncodeTiled failed");
     return 2;
   }
