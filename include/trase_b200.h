@@ -245,6 +245,10 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
  *   shs = cat(f_dc[P,1,3], f_rest[P,Mrest,3]);  sh_objs = feat / (||feat|| + 1e-9).
  * Backward takes the six upstream gradients (NULL = zero) and writes the
  * gradients of the ten inputs.  rotation / feature buffers 16-byte aligned.
+ * shs == NULL (forward) / g_fdc == NULL (backward): the caller's f_dc and f_rest
+ * are views of one [P][Mrest+1][3] block already, so the SH copy and its
+ * backward split are skipped (the caller passes that block to the rasterizer and
+ * slices its gradient).
  * ---------------------------------------------------------------------- */
 TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const float* xyz, const float* d_xyz, const float* scaling,
                                           const float* d_scaling, const float* rotation, const float* d_rotation,

@@ -308,6 +308,32 @@ def test_fused_assembly_matches_torch_glue(native_lib):
         assert rel_err(_np(a), _np(b)) <= 1e-3
 
 
+def test_aliased_sh_parameters_match_separate_storage(native_lib):
+    """GaussianParams keeps f_dc / f_rest as adjacent views of one SH block so that render() skips the cat copy
+    and the gradient split; a model whose two SH parameters were re-allocated separately (what Module.to or a
+    re-homing optimizer does) takes the copying path.  Same images, same gradients."""
+    from trase_b200 import synth, render as R
+    from trase_b200._assemble import sh_block_of
+    sc = synth.make_scene(6000, 80, 64, 43)
+    view = R.make_view(sc["cam"], DEV)
+    up = {k: v.to(DEV) for k, v in synth.make_upstream_grads(80, 64, 43).items()}
+    bg = torch.zeros(3, device=DEV)
+    res = {}
+    for aliased in (True, False):
+        pc = R.GaussianParams.from_activated(sc, DEV)
+        if not aliased:
+            pc._features_dc = torch.nn.Parameter(pc._features_dc.detach().clone().contiguous())
+            pc._features_rest = torch.nn.Parameter(pc._features_rest.detach().clone().contiguous())
+        assert (sh_block_of(pc._features_dc, pc._features_rest) is not None) == aliased
+        z = [torch.zeros(6000, k, device=DEV) for k in (3, 4, 3)]
+        out = R.render(view, pc, R.PIPE_DEFAULT, bg, z[0], z[1], z[2])
+        torch.autograd.backward([out["render"], out["render_gaussian_features"]], [up["dL_dcolor"], up["dL_dobjects"]])
+        res[aliased] = (out["render"].detach().clone(), [p.grad.detach().clone().contiguous() for p in pc.parameters()])
+    assert torch.equal(res[True][0], res[False][0])
+    for a, b in zip(res[True][1], res[False][1]):
+        assert a.shape == b.shape and rel_err(_np(a), _np(b)) <= 1e-6
+
+
 def test_config4_inference_shape_against_compiled_reference(native_lib):
     """BASELINE.json configs[3]: 2 M Gaussians, 1920x1080, forward only (feature-field inference)."""
     ref_loader = _ref_or_skip()

@@ -17,6 +17,23 @@ def _c(t):
     return t if t.data_ptr() % 16 == 0 else t.clone()
 
 
+def sh_block_of(f_dc, f_rest):
+    """If f_dc [P,1,3] and f_rest [P,Mrest,3] are adjacent views of ONE contiguous [P,Mrest+1,3] block (as
+    GaussianParams lays them out), return that block as a tensor (no copy); else None."""
+    if f_dc.dim() != 3 or f_rest.dim() != 3 or f_dc.dtype != torch.float32 or f_rest.dtype != torch.float32:
+        return None
+    P, Mrest = f_rest.shape[0], f_rest.shape[1]
+    row = 3 * (Mrest + 1)
+    if P == 0 or tuple(f_dc.shape) != (P, 1, 3) or f_rest.shape[2] != 3 or f_dc.device != f_rest.device:
+        return None
+    if f_dc.stride(0) != row or f_dc.stride(2) != 1 or tuple(f_rest.stride()) != (row, 3, 1):
+        return None
+    if f_rest.data_ptr() != f_dc.data_ptr() + 12 or \
+            f_dc.untyped_storage().data_ptr() != f_rest.untyped_storage().data_ptr():
+        return None
+    return torch.as_strided(f_dc.detach(), (P, Mrest + 1, 3), (row, 3, 1))
+
+
 class _Assemble(torch.autograd.Function):
     @staticmethod
     def forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat):
@@ -25,19 +42,23 @@ class _Assemble(torch.autograd.Function):
         P = xyz.shape[0]
         Mrest = f_rest.shape[1]
         with torch.cuda.device(dev):
-            ins = [_c(t) for t in (xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat)]
+            block = sh_block_of(f_dc, f_rest)        # parameters already laid out as the rasterizer's SH input?
+            ins = [_c(t) for t in (xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity)] + \
+                ([None, None] if block is not None else [_c(f_dc), _c(f_rest)]) + [_c(feat)]
             f32 = dict(dtype=torch.float32, device=dev)
             means3D = torch.empty((P, 3), **f32)
             scales = torch.empty((P, 3), **f32)
             rotations = torch.empty((P, 4), **f32)
             opac = torch.empty((P, 1), **f32)
-            shs = torch.empty((P, Mrest + 1, 3), **f32)
+            shs = block if block is not None else torch.empty((P, Mrest + 1, 3), **f32)
             sh_objs = torch.empty((P, 1, 32), **f32)
             _lib.check(lib.trase_b200_assemble_forward(
-                P, Mrest, *[t.data_ptr() for t in ins], means3D.data_ptr(), scales.data_ptr(), rotations.data_ptr(),
-                opac.data_ptr(), shs.data_ptr(), sh_objs.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+                P, Mrest, *[None if t is None else t.data_ptr() for t in ins], means3D.data_ptr(), scales.data_ptr(),
+                rotations.data_ptr(), opac.data_ptr(), None if block is not None else shs.data_ptr(), sh_objs.data_ptr(),
+                torch.cuda.current_stream(dev).cuda_stream))
         ctx.save_for_backward(ins[2], ins[4], ins[6], ins[9])
         ctx.Mrest = Mrest
+        ctx.sh_aliased = block is not None
         return means3D, scales, rotations, opac, shs, sh_objs
 
     @staticmethod
@@ -49,14 +70,19 @@ class _Assemble(torch.autograd.Function):
         with torch.cuda.device(dev):
             ups = [None if g is None else _c(g) for g in (g_means3D, g_scales, g_rotations, g_opac, g_shs, g_objs)]
             f32 = dict(dtype=torch.float32, device=dev)
+            alias = ctx.sh_aliased
             outs = [torch.empty((P, 3), **f32), torch.empty((P, 3), **f32), torch.empty((P, 3), **f32),
                     torch.empty((P, 3), **f32), torch.empty((P, 4), **f32), torch.empty((P, 4), **f32),
-                    torch.empty((P, 1), **f32), torch.empty((P, 1, 3), **f32), torch.empty((P, Mrest, 3), **f32),
-                    torch.empty((P, 1, 32), **f32)]
+                    torch.empty((P, 1), **f32), None if alias else torch.empty((P, 1, 3), **f32),
+                    None if alias else torch.empty((P, Mrest, 3), **f32), torch.empty((P, 1, 32), **f32)]
             _lib.check(lib.trase_b200_assemble_backward(
                 P, Mrest, scaling.data_ptr(), rotation.data_ptr(), opacity.data_ptr(), feat.data_ptr(),
-                *[None if u is None else u.data_ptr() for u in ups], *[o.data_ptr() for o in outs],
+                *[None if u is None else u.data_ptr() for u in ups], *[None if o is None else o.data_ptr() for o in outs],
                 torch.cuda.current_stream(dev).cuda_stream))
+            if alias:
+                # the SH gradient block is already laid out like the parameters: hand out its two slices
+                g = ups[4] if ups[4] is not None else torch.zeros((P, Mrest + 1, 3), **f32)
+                outs[7], outs[8] = g[:, :1], g[:, 1:]
         return tuple(outs)
 
 

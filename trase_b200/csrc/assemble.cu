@@ -147,8 +147,10 @@ extern "C" TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const flo
                                                      float* rotations, float* opac_out, float* shs, float* sh_objs,
                                                      void* stream) {
   if (P <= 0) return 0;
-  if (!xyz || !d_xyz || !scaling || !d_scaling || !rotation || !d_rotation || !opacity || !f_dc || !feat ||
-      !means3D || !scales || !rotations || !opac_out || !shs || !sh_objs || (Mrest > 0 && !f_rest) || Mrest < 0) {
+  // shs == NULL: the caller's f_dc / f_rest already alias one [P][Mrest+1][3] block, no SH copy is made
+  if (!xyz || !d_xyz || !scaling || !d_scaling || !rotation || !d_rotation || !opacity || !feat ||
+      !means3D || !scales || !rotations || !opac_out || !sh_objs || Mrest < 0 ||
+      (shs && (!f_dc || (Mrest > 0 && !f_rest)))) {
     set_error("trase_b200_assemble_forward: null pointer");
     return 1;
   }
@@ -162,12 +164,13 @@ extern "C" TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const flo
   assemble_fwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
   const size_t tot = (size_t)P * (Mrest + 1) * 3;
   int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
-  assemble_sh_kernel<<<g, 256, 0, s>>>(P, Mrest, f_dc, f_rest, shs);
+  if (shs) assemble_sh_kernel<<<g, 256, 0, s>>>(P, Mrest, f_dc, f_rest, shs);
+  const int n_launched_f = shs ? 3 : 2;
   assemble_feat_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(P, reinterpret_cast<const float4*>(feat),
                                                                        reinterpret_cast<float4*>(sh_objs));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_assemble_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
-  count_launches(3);
+  count_launches(n_launched_f);
   return 0;
 }
 
@@ -180,7 +183,7 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
                                                       float* g_fdc, float* g_frest, float* g_feat, void* stream) {
   if (P <= 0) return 0;
   if (!scaling || !rotation || !opacity || !feat || !g_xyz || !g_dxyz || !g_scaling || !g_dscaling || !g_rotation ||
-      !g_drotation || !g_opacity || !g_fdc || !g_feat || (Mrest > 0 && !g_frest)) {
+      !g_drotation || !g_opacity || !g_feat || (g_fdc && Mrest > 0 && !g_frest)) {
     set_error("trase_b200_assemble_backward: null pointer");
     return 1;
   }
@@ -190,12 +193,12 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
   assemble_bwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
   const size_t tot = (size_t)P * (Mrest + 1) * 3;
   int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
-  assemble_sh_bwd_kernel<<<g, 256, 0, s>>>(P, Mrest, g_shs, g_fdc, g_frest);
+  if (g_fdc) assemble_sh_bwd_kernel<<<g, 256, 0, s>>>(P, Mrest, g_shs, g_fdc, g_frest);   // NULL: caller slices g_shs itself
   assemble_feat_bwd_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(
       P, reinterpret_cast<const float4*>(feat), reinterpret_cast<const float4*>(g_objs),
       reinterpret_cast<float4*>(g_feat));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_assemble_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
-  count_launches(3);
+  count_launches(g_fdc ? 3 : 2);
   return 0;
 }

@@ -23,8 +23,14 @@ class GaussianParams(torch.nn.Module):
         super().__init__()
         P = torch.nn.Parameter
         self._xyz = P(xyz)
-        self._features_dc = P(features_dc)          # [P,1,3]
-        self._features_rest = P(features_rest)      # [P,15,3]
+        # The two SH parameters are adjacent views of ONE [P,16,3] block, i.e. already the rasterizer's `shs`
+        # input: render() then needs no torch.cat copy per view and no split of dL/dSH on the way back
+        # (trase_b200/_assemble.py sh_block_of).  Shapes, names and state_dict entries are the reference's;
+        # if anything re-allocates them separately (Module.to, an optimizer that re-homes .data) the copying
+        # path is used again automatically.
+        block = torch.cat((features_dc, features_rest), dim=1).contiguous()
+        self._features_dc = P(block[:, :1])         # [P,1,3]
+        self._features_rest = P(block[:, 1:])       # [P,15,3]
         self._scaling = P(scaling)                  # log-scale
         self._rotation = P(rotation)
         self._opacity = P(opacity)                  # logit
