@@ -605,11 +605,22 @@ __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* _
   const int nx = 3 + 6 * Lx;           // columns of the xyz part
   const int ncol = nx + 1 + 2 * Lt;
   float* row = s_row[w];
+  // one time stamp for every row (the usual case: one view = one t): its encoding is evaluated once per warp
+  // instead of once per row (the second sincosf call of a row costs as much as the 30-lane one for xyz)
+  if (t_stride == 0) {
+    const float tv = t[0];
+    if (lane == 0) row[nx] = tv;
+    for (int k = lane; k < Lt; k += 32) {
+      float sv, cv;
+      sincosf(tv * exp2f((float)k), &sv, &cv);
+      row[nx + 1 + 2 * k] = sv;
+      row[nx + 2 + 2 * k] = cv;
+    }
+    __syncwarp();
+  }
   for (int m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < M; m += warps_per_grid) {
     const float x0 = xyz[3 * m], x1 = xyz[3 * m + 1], x2 = xyz[3 * m + 2];
-    const float tv = t[(size_t)m * t_stride];
     if (lane < 3) row[lane] = lane == 0 ? x0 : (lane == 1 ? x1 : x2);
-    if (lane == 3) row[nx] = tv;
     for (int e = lane; e < 3 * Lx; e += 32) {       // (k, comp) pairs of the xyz part
       const int k = e / 3, comp = e - 3 * k;
       float sv, cv;
@@ -617,11 +628,15 @@ __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* _
       row[3 + 6 * k + comp] = sv;
       row[3 + 6 * k + 3 + comp] = cv;
     }
-    for (int k = lane; k < Lt; k += 32) {
-      float sv, cv;
-      sincosf(tv * exp2f((float)k), &sv, &cv);
-      row[nx + 1 + 2 * k] = sv;
-      row[nx + 2 + 2 * k] = cv;
+    if (t_stride != 0) {
+      const float tv = t[(size_t)m * t_stride];
+      if (lane == 3) row[nx] = tv;
+      for (int k = lane; k < Lt; k += 32) {
+        float sv, cv;
+        sincosf(tv * exp2f((float)k), &sv, &cv);
+        row[nx + 1 + 2 * k] = sv;
+        row[nx + 2 + 2 * k] = cv;
+      }
     }
     __syncwarp();
     float* o = out + (size_t)m * ld;
