@@ -23,7 +23,7 @@ def timeit(fn, n=reps):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
 
-_lib.set_tuning("gemm_resident", int(os.environ.get("GEMM_RES", "0"))); _lib.set_tuning("gemm_prefetch", int(os.environ.get("GEMM_PF", "0")))
+
 t = timeit(lambda i: _gemm(lib, A if i & 1 else A2, B, D, bias=bias, relu=True, mask_out=mk))
 print("gemm fwd   (bias,relu)      %7.1f us  %6.0f GB/s  %6.1f TFLOP/s" % (t, 2*M*256*4/t/1e3, 2*M*256*256/t/1e6))
 t = timeit(lambda i: _gemm(lib, A if i & 1 else A2, B, D, mask_in=mk, colsum=cs))

@@ -38,36 +38,31 @@ struct GemmEpilogue {
   uint32_t* mask_out;        // [M][N/32] written as (output > 0), or null
   float* colsum;      // [N] or null: += column sums of the written values (bias gradient)
   float* D; int ldd;  // output, row pitch in floats
-  int reverse;        // walk the row tiles from the last to the first (see trase_b200_set_tuning "gemm_snake")
-  int prefetch_tiles; // L2 prefetch distance of the activation stream, in tiles per CTA
   int round_tf32;     // round outputs to TF32 (nearest) so the next GEMM's operand truncation is exact
   int M, N, K;
 };
 
-constexpr int RES_MAX_KB = 8;     // resident-B variant: whole K (<= 256) of the weight half stays in smem
-
-// RES = true: the CTA owns one 128-column half of the output, keeps that half of the weight matrix
-// resident in shared memory for its whole lifetime and streams only activation tiles — the weight
-// re-fetch from L2 (twice the activation traffic in the streaming variant) disappears.
-template <int BN, bool RES>
+// (A variant that kept the weights resident in shared memory, an L2 prefetch of the activation stream and a
+// serpentine tile order were measured and dropped: 154 us vs 120 us per layer, no gain, no gain.)
+template <int BN>
 struct GemmSmem {
   static constexpr int A_BYTES = BM * BK * 4;       // 16 KB
   static constexpr int B_BYTES = BN * BK * 4;       // one k-block of B: 32 KB (BN = 256), 16 KB (BN = 128)
   static constexpr int OUT_BYTES = BM * SLAB * 4;   // 16 KB
   static constexpr int OFF_A = 0;
   static constexpr int OFF_B = OFF_A + STAGES * A_BYTES;
-  static constexpr int OFF_OUT = OFF_B + (RES ? RES_MAX_KB : STAGES) * B_BYTES;
+  static constexpr int OFF_OUT = OFF_B + STAGES * B_BYTES;
   static constexpr int OFF_BIAS = OFF_OUT + EPI_WARPS * 4096;   // per epilogue warp: 32 rows x 128 B staging
   static constexpr int OFF_COL = OFF_BIAS + (BN < 32 ? 32 : BN) * 4;   // [4 warps][BN] bias-gradient partial sums
   static constexpr int OFF_BAR = OFF_COL + 4 * (BN < 32 ? 32 : BN) * 4;
   static constexpr int TOTAL = OFF_BAR + 256 + 1024;  // barriers + slack for 1024-byte alignment
 };
 
-template <int BN, bool RES>
+template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmEpilogue ep) {
-  using L = GemmSmem<BN, RES>;
+  using L = GemmSmem<BN>;
   // 1024-byte alignment (128-byte swizzle atoms) comes from the declaration: aligning the pointer
   // by integer arithmetic would hide the shared address space from the compiler and turn every
   // LDS/STS of the epilogue into a generic LD/ST.
@@ -84,27 +79,22 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* empty = bars + STAGES;         // [STAGES]  MMA -> TMA
   uint64_t* tmem_full = bars + 2 * STAGES; // [2]       MMA -> epilogue
   uint64_t* tmem_empty = tmem_full + 2;    // [2]       epilogue -> MMA
-  uint64_t* bfull = tmem_empty + 2;        // [1]       resident B landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = (ep.M + BM - 1) / BM;
   const int num_kb = (ep.K + BK - 1) / BK;
-  // RES: even CTAs own output columns [0,128), odd CTAs [128,256); both walk the same row tiles
-  const int n_off = RES ? (int)(blockIdx.x & 1) * BN : 0;
-  const int tile0 = RES ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-  const int tile_step = RES ? (int)(gridDim.x >> 1) : (int)gridDim.x;
-  // consecutive layers walk the rows in opposite directions so that the rows the previous kernel wrote last
-  // (still in the 126 MB L2) are the ones this kernel reads first
-#define TB_TILE(t) (ep.reverse ? (num_tiles - 1 - (t)) : (t))
+  constexpr int n_off = 0;
+  const int tile0 = (int)blockIdx.x;
+  const int tile_step = (int)gridDim.x;
+#define TB_TILE(t) (t)
   constexpr uint32_t TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // power of two >= 32 (BN = 16 -> 32, 256 -> 512)
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA); prefetch_tmap(&tmB);
     for (int i = 0; i < STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], EPI_WARPS); }
-    mbar_init(bfull, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -122,26 +112,12 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ===== TMA producer =====
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      if (RES) {
-        mbar_expect_tx(bfull, num_kb * L::B_BYTES);
-        for (int kb = 0; kb < num_kb; kb++) tma_load_2d(sB + kb * L::B_BYTES, &tmB, bfull, kb * BK, n_off);
-      }
-      // The smem ring only holds ~1 us of activations; HBM latency under load is longer than that, so
-      // the tiles this CTA will need `pf` iterations from now are pulled into L2 first (TMA prefetch).
-      const int pf = ep.prefetch_tiles;
-      for (int i = 0; i < pf; i++) {
-        const int t = tile0 + i * tile_step;
-        if (t < num_tiles)
-          for (int kb = 0; kb < num_kb; kb++) tma_prefetch_l2_2d(&tmA, kb * BK, TB_TILE(t) * BM);
-      }
       for (int tile = tile0; tile < num_tiles; tile += tile_step) {
-        const int tpf = tile + pf * tile_step;
         for (int kb = 0; kb < num_kb; kb++) {
-          if (pf && tpf < num_tiles) tma_prefetch_l2_2d(&tmA, kb * BK, TB_TILE(tpf) * BM);
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], RES ? L::A_BYTES : L::A_BYTES + L::B_BYTES);
+          mbar_expect_tx(&full[stage], L::A_BYTES + L::B_BYTES);
           tma_load_2d(sA + stage * L::A_BYTES, &tmA, &full[stage], kb * BK, TB_TILE(tile) * BM);
-          if (!RES) tma_load_2d(sB + stage * L::B_BYTES, &tmB, &full[stage], kb * BK, 0);
+          tma_load_2d(sB + stage * L::B_BYTES, &tmB, &full[stage], kb * BK, 0);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -152,7 +128,6 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       constexpr uint32_t idesc = make_idesc_tf32(BM, BN, 0, 0);
       uint32_t stage = 0, phase = 0;
       uint32_t acc = 0, acc_phase = 0;
-      if (RES) mbar_wait(bfull, 0);
       for (int tile = tile0; tile < num_tiles; tile += tile_step) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
@@ -161,7 +136,7 @@ gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(sA + stage * L::A_BYTES);
-          const uint32_t b_addr = smem_u32(sB + (RES ? kb : (int)stage) * L::B_BYTES);
+          const uint32_t b_addr = smem_u32(sB + stage * L::B_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; k++) {
             // K-major, 128-byte swizzle: rows are 128 B apart, 8-row groups 1024 B apart;
@@ -324,10 +299,6 @@ bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t col
   return r == CUDA_SUCCESS;
 }
 
-int g_prefetch_tiles = 0;
-int g_snake = 0;              // alternate the row-tile direction between consecutive GEMM launches
-int g_snake_phase = 0;    // tuning switch ("gemm_prefetch")
-int g_allow_resident = 0;   // tuning switch (trase_b200_set_tuning "gemm_resident")
 static int g_num_sms = 0;
 static int num_sms() {
   if (!g_num_sms) {
@@ -339,25 +310,20 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int BN, bool RES>
+template <int BN>
 static cudaError_t launch_gemm_tn(const CUtensorMap& tA, const CUtensorMap& tB, const GemmEpilogue& ep,
                                   cudaStream_t s) {
   static bool attr_set = false;
-  const int smem = GemmSmem<BN, RES>::TOTAL;
+  const int smem = GemmSmem<BN>::TOTAL;
   if (!attr_set) {
     cudaError_t e =
-        cudaFuncSetAttribute(gemm_tn_tf32_kernel<BN, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(gemm_tn_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   const int tiles = (ep.M + BM - 1) / BM;
-  int grid;
-  if (RES) {
-    grid = 2 * tiles < num_sms() ? 2 * tiles : (num_sms() & ~1);   // CTA pairs: (row tile walker, column half)
-  } else {
-    grid = tiles < num_sms() ? tiles : num_sms();
-  }
-  gemm_tn_tf32_kernel<BN, RES><<<grid, GEMM_THREADS, smem, s>>>(tA, tB, ep);
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_tn_tf32_kernel<BN><<<grid, GEMM_THREADS, smem, s>>>(tA, tB, ep);
   return cudaGetLastError();
 }
 
@@ -381,21 +347,18 @@ extern "C" TRASE_API int trase_b200_gemm_tf32(const float* A, int lda, const flo
     return 1;
   }
   const bool small = N <= 16;
-  const bool resident = !small && N == 256 && K <= mlp::RES_MAX_KB * mlp::BK && mlp::g_allow_resident;
   CUtensorMap tA, tB;
   const bool ok = mlp::make_tmap_2d(&tA, A, M, K, lda, mlp::BM, mlp::BK) &&
-                  mlp::make_tmap_2d(&tB, B, N, K, ldb, small ? 16 : (resident ? 128 : 256), mlp::BK);
+                  mlp::make_tmap_2d(&tB, B, N, K, ldb, small ? 16 : 256, mlp::BK);
   if (!ok) {
     set_error("trase_b200_gemm_tf32: cuTensorMapEncodeTiled failed");
     return 2;
   }
   mlp::GemmEpilogue ep;
   ep.bias = bias; ep.relu = relu; ep.mask_in = mask_in; ep.mask_out = mask_out; ep.colsum = colsum;
-  ep.round_tf32 = round_tf32; ep.prefetch_tiles = mlp::g_prefetch_tiles; ep.reverse = mlp::g_snake ? (mlp::g_snake_phase++ & 1) : 0; ep.D = D; ep.ldd = ldd; ep.M = M; ep.N = N; ep.K = K;
+  ep.round_tf32 = round_tf32; ep.D = D; ep.ldd = ldd; ep.M = M; ep.N = N; ep.K = K;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  cudaError_t e = small ? mlp::launch_gemm_tn<16, false>(tA, tB, ep, st)
-                        : (resident ? mlp::launch_gemm_tn<128, true>(tA, tB, ep, st)
-                                    : mlp::launch_gemm_tn<256, false>(tA, tB, ep, st));
+  cudaError_t e = small ? mlp::launch_gemm_tn<16>(tA, tB, ep, st) : mlp::launch_gemm_tn<256>(tA, tB, ep, st);
   if (e != cudaSuccess) {
     set_error("trase_b200_gemm_tf32: CUDA error: %s", cudaGetErrorString(e));
     return 2;
@@ -422,7 +385,6 @@ constexpr int WG_BOX_BYTES = WG_ROWS * 128;  // one 32-row x 32-col fp32 box
 struct WgradParams {
   int M, I, J;      // reduction length, output rows (<= 256), output cols (<= 256)
   float* D; int ldd;
-  int reverse;
 };
 
 constexpr int WG_THREADS = 256;
@@ -453,9 +415,7 @@ wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
   const int per = (nblk + gridDim.x - 1) / gridDim.x;
   const int blk0 = blockIdx.x * per;
   const int blk1 = min(nblk, blk0 + per);
-  // CTA c owns row blocks [blk0, blk1); with `reverse` the ownership is mirrored so that the CTAs which start
-  // first take the rows written last by the producer kernel
-#define WG_BLK(b) (p.reverse ? (nblk - 1 - (b)) : (b))
+#define WG_BLK(b) (b)
   constexpr uint32_t TMEM_COLS = 512;
 
   if (warp == 0 && lane == 0) {
@@ -569,7 +529,6 @@ extern "C" TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, c
   }
   mlp::WgradParams wp;
   wp.M = M; wp.I = I; wp.J = J; wp.D = D; wp.ldd = ldd;
-  wp.reverse = 0;
   const int nblk = (M + mlp::WG_ROWS - 1) / mlp::WG_ROWS;
   const int grid = nblk < mlp::num_sms() ? nblk : mlp::num_sms();
   mlp::wgrad_tf32_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);

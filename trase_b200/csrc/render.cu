@@ -31,7 +31,6 @@
 #include "common.cuh"
 
 namespace tb {
-namespace mlp { extern int g_allow_resident; extern int g_prefetch_tiles; extern int g_snake; }
 
 struct Tuning {
   int fwd_ppt = 2;
@@ -572,9 +571,6 @@ void set_tuning(const char* key, int value) {
   };
   if (eq(key, "fwd_ppt")) g_tuning.fwd_ppt = value;
   if (eq(key, "bwd_ppt")) g_tuning.bwd_ppt = value;
-  if (eq(key, "gemm_resident")) mlp::g_allow_resident = value;
-  if (eq(key, "gemm_prefetch")) mlp::g_prefetch_tiles = value;
-  if (eq(key, "gemm_snake")) mlp::g_snake = value;
 }
 
 }  // namespace tb
