@@ -447,6 +447,21 @@ TRASE_API int trase_b200_adam_step(int64_t n, float* params, const float* grads,
 TRASE_API int trase_b200_densification_stats(int P, const float* viewspace_grad, const unsigned char* filter,
                                              float* grad_accum, float* denom, void* stream);
 
+/* Feature-loss front end (second part): bilinear resize of the
+ * rendered feature image to the mask resolution, gather of the sampled pixels and L2
+ * normalisation, without materialising the resized image.
+ * ref: train.py:283 (F.interpolate(..., mode='bilinear'), align_corners=False) and
+ * utils/feature_utils.py:50-53 (rendered_features[:, sampled_pixel] -> normalize).
+ * feat [C][H][W] (C <= 64); idx: N flat indices (row-major, int64) into the Hm x Wm
+ * mask grid; out [N][C]; inv_norm [N] kept for backward (may be NULL when
+ * normalize == 0).  backward ADDS into d_feat [C][H][W] (zero it first). */
+TRASE_API int trase_b200_sample_features_forward(int C, int H, int W, int Hm, int Wm, int N, const float* feat,
+                                                 const int64_t* idx, int normalize, float* out, float* inv_norm,
+                                                 void* stream);
+TRASE_API int trase_b200_sample_features_backward(int C, int H, int W, int Hm, int Wm, int N, const int64_t* idx,
+                                                  int normalize, const float* out, const float* inv_norm,
+                                                  const float* g_out, float* d_feat, void* stream);
+
 /* ref: getHigherMsb (DGR/cuda_rasterizer/rasterizer_impl.cu:38-53). */
 TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);
 

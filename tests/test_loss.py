@@ -114,3 +114,27 @@ def test_feature_norm_regulariser_matches_torch(shape):
     assert abs(reg.item() - r.item()) < 1e-6 and abs(mean_norm.item() - m.item()) < 1e-6
     assert torch.isfinite(x.grad).all()
     assert (x.grad.cpu().double() - xr.grad).abs().max() <= GRAD_TOL * xr.grad.abs().max()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,mask_hw", [((32, 101, 135), (64, 80)), ((32, 64, 64), (64, 64)), ((8, 40, 50), (90, 77))])
+def test_sampled_feature_front_end_matches_reference_formulation(shape, mask_hw):
+    """train.py:283 + utils/feature_utils.py:50-55 in torch (interpolate the whole image, boolean-index, normalize,
+    einsum) against the fused sampler: correspondence matrix 1e-5 abs, image gradient 1e-3 of its max."""
+    import torch.nn.functional as F
+    from trase_b200 import feature_utils
+    g = torch.Generator().manual_seed(shape[1])
+    feat = torch.randn(*shape, generator=g)
+    sampled = torch.rand(*mask_hw, generator=g) < 0.05
+    up = torch.randn(int(sampled.sum()), int(sampled.sum()), generator=g)
+    x = feat.cuda().requires_grad_(True)
+    cf = feature_utils.get_features_correspondence_matrix(x, sampled.cuda(), mask_hw)
+    (cf * up.cuda()).sum().backward()
+    xr = feat.double().requires_grad_(True)
+    r = F.interpolate(xr.unsqueeze(0), mask_hw, mode="bilinear").squeeze(0)
+    s = F.normalize(r[:, sampled].permute(1, 0), dim=-1, p=2)
+    cr = torch.einsum("hc,jc->hj", s, s)
+    (cr * up.double()).sum().backward()
+    assert cf.shape == cr.shape
+    assert (cf.cpu().double() - cr).abs().max() <= 1e-5
+    assert (x.grad.cpu().double() - xr.grad).abs().max() <= GRAD_TOL * xr.grad.abs().max()

@@ -73,7 +73,8 @@ EXPORTS = [
     "trase_b200_feature_norm_reg_forward", "trase_b200_feature_norm_reg_backward",
     "trase_b200_mlp_fused_pack_floats", "trase_b200_mlp_pack_fused", "trase_b200_mlp_forward_fused",
     "trase_b200_mlp_fused_pack_bwd_floats", "trase_b200_mlp_pack_fused_bwd", "trase_b200_mlp_backward_fused",
-    "trase_b200_adam_step", "trase_b200_densification_stats",
+    "trase_b200_adam_step", "trase_b200_densification_stats", "trase_b200_sample_features_forward",
+    "trase_b200_sample_features_backward",
 ]
 
 _lib = None
@@ -162,6 +163,10 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_pack_fused_bwd.argtypes = [C.c_int] * 3 + [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]
     lib.trase_b200_mlp_backward_fused.restype = C.c_int
     lib.trase_b200_mlp_backward_fused.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.POINTER(C.c_void_p), C.c_void_p]
+    lib.trase_b200_sample_features_forward.restype = C.c_int
+    lib.trase_b200_sample_features_forward.argtypes = [C.c_int] * 6 + [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 3
+    lib.trase_b200_sample_features_backward.restype = C.c_int
+    lib.trase_b200_sample_features_backward.argtypes = [C.c_int] * 6 + [C.c_void_p, C.c_int] + [C.c_void_p] * 5
     lib.trase_b200_adam_step.restype = C.c_int
     lib.trase_b200_adam_step.argtypes = [C.c_int64] + [C.c_void_p] * 4 + [C.c_int, C.POINTER(C.c_int64),
                                                                           C.POINTER(C.c_float), C.POINTER(C.c_float),

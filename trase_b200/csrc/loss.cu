@@ -365,3 +365,143 @@ extern "C" TRASE_API int trase_b200_feature_norm_reg_backward(int C, int64_t N, 
   count_launches(1);
   return 0;
 }
+
+// ---- feature-loss front end: bilinear resize + sampled-pixel gather + L2 normalise ----
+// ref: train.py:283  rendered_features = F.interpolate(rendered_features[None], sam_masks.shape[-2:], mode='bilinear')[0]
+//      utils/feature_utils.py:50-53  f = normalize(rendered_features[:, sampled_pixel].permute(1, 0), dim=-1)
+// The reference resizes all C x H x W planes to the mask resolution and then keeps ~5000 pixels; its backward
+// writes full gradient planes several times.  Here one warp per SAMPLED pixel evaluates the four bilinear taps
+// for all channels (lane = channel), normalises, and the backward scatters to the 4 x C touched entries only.
+namespace tb {
+
+// torch's area_pixel_compute_source_index (align_corners = False): src = scale * (dst + 0.5) - 0.5, clamped at 0
+__device__ __forceinline__ void bilinear_taps(int dst, int in_size, float scale, int& i0, int& i1, float& l1) {
+  float src = scale * ((float)dst + 0.5f) - 0.5f;
+  src = src < 0.f ? 0.f : src;
+  i0 = (int)src;
+  if (i0 > in_size - 1) i0 = in_size - 1;
+  i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+  l1 = src - (float)i0;
+}
+
+constexpr int SF_MAX_C = 64;   // channels per sample: two per lane at most
+
+__global__ void __launch_bounds__(256) sample_features_fwd_kernel(int C, int H, int W, int Hm, int Wm, int N,
+                                                                  const float* __restrict__ feat,
+                                                                  const long long* __restrict__ idx, int normalize,
+                                                                  float* __restrict__ out, float* __restrict__ inv_norm) {
+  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (n >= N) return;
+  const long long p = idx[n];
+  const int ym = (int)(p / Wm), xm = (int)(p - (long long)ym * Wm);
+  int y0, y1, x0, x1;
+  float ly, lx;
+  bilinear_taps(ym, H, (float)H / (float)Hm, y0, y1, ly);
+  bilinear_taps(xm, W, (float)W / (float)Wm, x0, x1, lx);
+  const float hy = 1.f - ly, hx = 1.f - lx;
+  const size_t plane = (size_t)H * W;
+  float v[2] = {0.f, 0.f};
+  float ss = 0.f;
+#pragma unroll
+  for (int r = 0; r < 2; r++) {
+    const int c = lane + 32 * r;
+    if (c < C) {
+      const float* f = feat + c * plane;
+      // same association as torch's upsample_bilinear2d: h0 * (w0 * a + w1 * b) + h1 * (w0 * c + w1 * d)
+      v[r] = hy * (hx * f[(size_t)y0 * W + x0] + lx * f[(size_t)y0 * W + x1]) +
+             ly * (hx * f[(size_t)y1 * W + x0] + lx * f[(size_t)y1 * W + x1]);
+      ss += v[r] * v[r];
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  // F.normalize: v / max(||v||, 1e-12)
+  const float inv = normalize ? 1.f / fmaxf(sqrtf(ss), 1e-12f) : 1.f;
+  if (lane == 0 && inv_norm) inv_norm[n] = inv;
+#pragma unroll
+  for (int r = 0; r < 2; r++) {
+    const int c = lane + 32 * r;
+    if (c < C) out[(size_t)n * C + c] = v[r] * inv;
+  }
+}
+
+__global__ void __launch_bounds__(256) sample_features_bwd_kernel(int C, int H, int W, int Hm, int Wm, int N,
+                                                                  const long long* __restrict__ idx, int normalize,
+                                                                  const float* __restrict__ out,
+                                                                  const float* __restrict__ inv_norm,
+                                                                  const float* __restrict__ g_out,
+                                                                  float* __restrict__ d_feat) {
+  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (n >= N) return;
+  const long long p = idx[n];
+  const int ym = (int)(p / Wm), xm = (int)(p - (long long)ym * Wm);
+  int y0, y1, x0, x1;
+  float ly, lx;
+  bilinear_taps(ym, H, (float)H / (float)Hm, y0, y1, ly);
+  bilinear_taps(xm, W, (float)W / (float)Wm, x0, x1, lx);
+  const float hy = 1.f - ly, hx = 1.f - lx;
+  const size_t plane = (size_t)H * W;
+  float g[2] = {0.f, 0.f}, o[2] = {0.f, 0.f};
+  float dot = 0.f;
+#pragma unroll
+  for (int r = 0; r < 2; r++) {
+    const int c = lane + 32 * r;
+    if (c < C) {
+      g[r] = g_out[(size_t)n * C + c];
+      o[r] = out[(size_t)n * C + c];
+      dot += g[r] * o[r];
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, s);
+  const float inv = normalize ? inv_norm[n] : 1.f;
+#pragma unroll
+  for (int r = 0; r < 2; r++) {
+    const int c = lane + 32 * r;
+    if (c < C) {
+      // d/dv of v / ||v||: (g - o (o . g)) / ||v||     (o = normalised output)
+      const float gv = normalize ? (g[r] - o[r] * dot) * inv : g[r];
+      float* d = d_feat + c * plane;
+      atomicAdd(d + (size_t)y0 * W + x0, hy * hx * gv);
+      atomicAdd(d + (size_t)y0 * W + x1, hy * lx * gv);
+      atomicAdd(d + (size_t)y1 * W + x0, ly * hx * gv);
+      atomicAdd(d + (size_t)y1 * W + x1, ly * lx * gv);
+    }
+  }
+}
+
+}  // namespace tb
+
+extern "C" TRASE_API int trase_b200_sample_features_forward(int C, int H, int W, int Hm, int Wm, int N,
+                                                            const float* feat, const int64_t* idx, int normalize,
+                                                            float* out, float* inv_norm, void* stream) {
+  if (N <= 0) return 0;
+  if (C <= 0 || C > SF_MAX_C || H <= 0 || W <= 0 || Hm <= 0 || Wm <= 0 || !feat || !idx || !out) {
+    set_error("trase_b200_sample_features_forward: bad arguments (C=%d, at most %d channels)", C, SF_MAX_C);
+    return 1;
+  }
+  sample_features_fwd_kernel<<<(N + 7) / 8, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      C, H, W, Hm, Wm, N, feat, reinterpret_cast<const long long*>(idx), normalize, out, inv_norm);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_sample_features_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+// d_feat ([C][H][W]) must be zero-initialised (or hold a gradient to accumulate into).
+extern "C" TRASE_API int trase_b200_sample_features_backward(int C, int H, int W, int Hm, int Wm, int N,
+                                                             const int64_t* idx, int normalize, const float* out,
+                                                             const float* inv_norm, const float* g_out,
+                                                             float* d_feat, void* stream) {
+  if (N <= 0) return 0;
+  if (C <= 0 || C > SF_MAX_C || !idx || !out || !g_out || !d_feat || (normalize && !inv_norm)) {
+    set_error("trase_b200_sample_features_backward: bad arguments");
+    return 1;
+  }
+  sample_features_bwd_kernel<<<(N + 7) / 8, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      C, H, W, Hm, Wm, N, reinterpret_cast<const long long*>(idx), normalize, out, inv_norm, g_out, d_feat);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_sample_features_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
