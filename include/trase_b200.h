@@ -136,7 +136,8 @@ typedef struct trase_b200_fwd_args {
   void* img;     size_t img_bytes;
   void* binning; size_t binning_bytes;
   void* scratch; size_t scratch_bytes;
-  int64_t capacity;             /* instances the binning/scratch buffers hold     */
+  int64_t capacity;             /* instances the binning/scratch buffers hold;    */
+                                /* at least P (the P-sized depth sort borrows them) */
   int* num_rendered_host;       /* pinned host int or NULL (async D2H of R)       */
   void* stream;                 /* cudaStream_t                                   */
   void* readback_event;         /* cudaEvent_t or NULL: recorded right after the   */

@@ -99,6 +99,7 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
         key = (dev.index or 0, P, W, H)
         hint = _capacity_hint.get(key)
         capacity = _initial_capacity(P, W, H) if hint is None else int(hint * 1.25) + 4096
+        capacity = max(capacity, P)      # the depth sort of the P Gaussians borrows the instance buffers
         if P == 0:
             capacity = 0
         pinned = _pinned_int(dev)
@@ -138,7 +139,7 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
             R = int(pinned[0].item()) if P > 0 else 0
             if R <= capacity:
                 break
-            capacity = int(R * 1.25) + 4096  # workspace was too small: re-bin only
+            capacity = max(int(R * 1.25) + 4096, P)  # workspace was too small: re-bin only
             first = False
         del scratch
         _capacity_hint[key] = R

@@ -153,6 +153,11 @@ static int check_fwd_args(const trase_b200_fwd_args* a) {
     return 1;
   }
   if (a->capacity > 0xFFFFFFF0ll) { set_error("trase_b200: capacity exceeds 32-bit instance indices"); return 1; }
+  if (a->P > 0 && a->capacity < a->P) {
+    set_error("trase_b200: capacity (%lld) must be at least P (%d): the depth sort of the Gaussians borrows the "
+              "instance buffers", (long long)a->capacity, a->P);
+    return 1;
+  }
   return 0;
 }
 
@@ -174,9 +179,10 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
   FwdPointers p = carve(a->geom, a->P, a->img, a->W, a->H, a->binning, a->capacity, a->scratch);
   const int grid_x = (a->W + TILE - 1) / TILE, grid_y = (a->H + TILE - 1) / TILE;
   const int end_bit = 32 + (int)higher_msb((uint32_t)(grid_x * grid_y));
-  // Sort ping-pongs between the binning buffers and the scratch buffers; start
-  // on the side that makes the last pass land in the binning buffers.
-  const bool even = (sort_num_passes(end_bit) & 1) == 0;
+  // Instances are sorted on their tile bits only (the Gaussians were put in depth order before emission, see
+  // binning.cu).  The sort ping-pongs between the binning buffers and the scratch buffers; start on the side
+  // that makes the last pass land in the binning buffers.
+  const bool even = (sort_num_passes(32, end_bit) & 1) == 0;
   uint64_t* keys_a = even ? p.point_list_keys : p.keys_unsorted;
   uint32_t* vals_a = even ? p.point_list : p.vals_unsorted;
   uint64_t* keys_b = even ? p.keys_unsorted : p.point_list_keys;
@@ -186,18 +192,22 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
   pd.vals_unsorted = vals_a;
 
   if (with_preprocess) TB_STEP_ST(ST_PREPROCESS_FWD, "preprocess_forward", launch_preprocess_forward(*a, p, stream));
-  TB_STEP_ST(ST_SCAN_DUP, "scan_and_duplicate", launch_scan_and_duplicate(*a, pd, stream));
+  // depth order of the Gaussians (P-sized sort on the other ping-pong side), block scan, key emission
+  TB_STEP_ST(ST_SCAN_DUP, "scan_and_duplicate", launch_scan_and_duplicate(*a, pd, keys_b, vals_b, stream));
   if (a->num_rendered_host)
     TB_STEP("copy num_rendered",
             cudaMemcpyAsync(a->num_rendered_host, p.counters, sizeof(int), cudaMemcpyDeviceToHost, stream));
   if (a->readback_event) TB_STEP("record readback event", cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->readback_event), stream));
   if (a->capacity > 0)
-    TB_STEP_ST(ST_SORT, "sort_pairs", launch_sort_pingpong(keys_a, vals_a, keys_b, vals_b, p.counters, a->capacity, end_bit,
-                                               p.sort_scratch, p.sort_scratch_bytes, stream));
+    TB_STEP_ST(ST_SORT, "sort_pairs", launch_sort_pingpong(keys_a, vals_a, keys_b, vals_b, p.counters, a->capacity, 32,
+                                               end_bit, p.sort_scratch, p.sort_scratch_bytes, stream));
   TB_STEP_ST(ST_RANGES, "identify_ranges", launch_identify_ranges(*a, p, stream));
   TB_STEP_ST(ST_RENDER_FWD, "render_forward", launch_render_forward(*a, p, stream));
   // preprocess, block-sum scan, key duplication, 3 kernels per radix pass, ranges, compositing
-  count_launches((with_preprocess ? 1 : 0) + 2 + (a->capacity > 0 ? 3 * sort_num_passes(end_bit) + 1 : 0) + 1);
+  // preprocess; depth keys + P-sized sort + ordered block sums + block scan + key emission; tile-bit sort;
+  // ranges; compositing
+  count_launches((with_preprocess ? 1 : 0) + 1 + 3 * sort_num_passes(0, 32) + 3 +
+                 (a->capacity > 0 ? 3 * sort_num_passes(32, end_bit) : 0) + 1 + 1);
   return 0;
 }
 

@@ -7,6 +7,13 @@
 //   cub::DeviceRadixSort::SortPairs    DGR/cuda_rasterizer/rasterizer_impl.cu:310-316
 //   identifyTileRanges                 DGR/cuda_rasterizer/rasterizer_impl.cu:119-141
 //
+// Sort strategy: the reference sorts all R tile instances on the 32 depth bits AND the tile bits (45 bits at
+// config 2).  Depth is a property of the Gaussian, not of the instance, so here the P Gaussians are sorted by
+// depth first (stable, 4 cheap passes over P keys), instances are emitted in that order, and the R instances
+// only need a stable sort on the tile bits (2 passes instead of 5 over 12 bytes x R).  Within a tile the
+// result is ordered by (depth, Gaussian index) — exactly what the reference's stable 45-bit sort of the
+// index-ordered emission yields.
+//
 // Design differences: the instance count R never goes to the host between
 // kernels (the reference blocks on a 4-byte D2H at rasterizer_impl.cu:288);
 // every kernel reads R from device memory and grids are sized for the
@@ -67,17 +74,53 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums_kernel(const uin
 }
 
 // ---------------------------------------------------------------------------
-// Key duplication.  One thread per Gaussian computes its offset (block scan +
+// Depth keys of the Gaussians (input of the P-sized sort): visible ones by their view-space depth bits,
+// the rest behind everything (they emit no instance, their place does not matter).
+__global__ void __launch_bounds__(PRE_BLOCK) gaussian_depth_keys_kernel(int P, const float* __restrict__ depths,
+                                                                         const uint32_t* __restrict__ tiles_touched,
+                                                                         uint64_t* __restrict__ keys,
+                                                                         uint32_t* __restrict__ vals,
+                                                                         uint32_t* __restrict__ counters) {
+  const int i = blockIdx.x * PRE_BLOCK + threadIdx.x;
+  if (i < P) {
+    keys[i] = tiles_touched[i] ? (uint64_t)__float_as_uint(depths[i]) : 0xffffffffull;
+    vals[i] = (uint32_t)i;
+  }
+  if (i == 0) counters[2] = (uint32_t)P;      // element count of the P-sized sort, read from device memory like R
+}
+
+// Tile counts summed per block of PRE_BLOCK Gaussians taken in depth order.
+__global__ void __launch_bounds__(PRE_BLOCK) ordered_block_sums_kernel(int P, const uint32_t* __restrict__ order,
+                                                                        const uint32_t* __restrict__ tiles_touched,
+                                                                        uint32_t* __restrict__ block_sums) {
+  __shared__ uint32_t s_warp[PRE_BLOCK / 32];
+  const int pos = blockIdx.x * PRE_BLOCK + threadIdx.x;
+  uint32_t v = (pos < P) ? tiles_touched[order[pos]] : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < PRE_BLOCK / 32; w++) t += s_warp[w];
+    block_sums[blockIdx.x] = t;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Key duplication.  One thread per Gaussian, taken in depth order (`order`), computes its offset (block scan +
 // scanned block offset); Gaussians touching more than DUP_COOP tiles are
 // emitted by the whole warp so that one large splat does not serialise a lane.
 constexpr int DUP_COOP = 16;
 __global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
-    int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+    int P, const uint32_t* __restrict__ order, const float2* __restrict__ means2D, const float* __restrict__ depths,
     const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_offsets,
     uint32_t* __restrict__ point_offsets, const uint32_t* __restrict__ counters, uint64_t* __restrict__ keys,
     uint32_t* __restrict__ vals, const int* __restrict__ radii, int grid_x, int grid_y) {
   __shared__ uint32_t s_warp[PRE_BLOCK / 32];
-  const int idx = blockIdx.x * PRE_BLOCK + threadIdx.x;
+  const int pos = blockIdx.x * PRE_BLOCK + threadIdx.x;
+  const int idx = (pos < P) ? (int)order[pos] : P;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t cnt = (idx < P) ? tiles_touched[idx] : 0u;
   uint32_t incl = cnt;
@@ -128,7 +171,7 @@ __global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
     const uint32_t b_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
     const uint32_t b_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
     const uint32_t b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
-    const uint32_t b_idx = (uint32_t)(blockIdx.x * PRE_BLOCK + (warp << 5) + src);
+    const uint32_t b_idx = (uint32_t)__shfl_sync(0xffffffffu, idx, src);
     for (uint32_t k = lane; k < b_cnt; k += 32) {
       const uint32_t y = b_y0 + k / b_w, x = b_x0 + k % b_w;
       uint64_t key = (uint64_t)(y * (uint32_t)grid_x + x);
@@ -140,14 +183,29 @@ __global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
   }
 }
 
-cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s) {
+// Depth order of the Gaussians -> block sums in that order -> R and block offsets -> instance keys.
+// `p.keys_unsorted / p.vals_unsorted` is where the instances go (the side the R-sized sort starts from);
+// (ok_keys, ok_vals) is the OTHER ping-pong side: the P-sized sort starts and (4 passes) ends there, so the
+// order array is not overwritten while the instances are being written.
+cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, uint64_t* ok_keys,
+                                      uint32_t* ok_vals, cudaStream_t s) {
   const int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
-  scan_block_sums_kernel<<<1, SCAN_THREADS, 0, s>>>(p.block_sums, p.block_offsets, nblk, p.counters,
-                                                   (unsigned long long)a.capacity);
+  gaussian_depth_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, p.depths, p.tiles_touched, ok_keys, ok_vals, p.counters);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
+  e = launch_sort_pingpong(ok_keys, ok_vals, p.keys_unsorted, p.vals_unsorted, p.counters + 2, a.P, 0, 32,
+                           p.sort_scratch, p.sort_scratch_bytes, s);
+  if (e != cudaSuccess) return e;
+  static_assert(((32 + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS) % 2 == 0,
+                "the depth sort must take an even number of passes so that it ends on the side it started from");
+  const uint32_t* order = ok_vals;
+  ordered_block_sums_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, order, p.tiles_touched, p.block_sums);
+  scan_block_sums_kernel<<<1, SCAN_THREADS, 0, s>>>(p.block_sums, p.block_offsets, nblk, p.counters,
+                                                   (unsigned long long)a.capacity);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
   const int grid_x = (a.W + TILE - 1) / TILE, grid_y = (a.H + TILE - 1) / TILE;
-  duplicate_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, p.means2D, p.depths, p.tiles_touched, p.block_offsets,
+  duplicate_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, order, p.means2D, p.depths, p.tiles_touched, p.block_offsets,
                                                    p.point_offsets, p.counters, p.keys_unsorted, p.vals_unsorted,
                                                    a.radii, grid_x, grid_y);
   return cudaGetLastError();
@@ -317,29 +375,29 @@ __global__ void copy_pairs_kernel(const uint64_t* __restrict__ keys_in, const ui
 
 // Ping-pong sort.  Data starts in (keys_a, vals_a); after `passes` passes it is
 // in A again when `passes` is even, in B when odd (see sort_result_in_b).
-int sort_num_passes(int end_bit) {
-  int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+int sort_num_passes(int begin_bit, int end_bit) {
+  int passes = (end_bit - begin_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
   if (passes < 1) passes = 1;
   if (passes > SORT_MAX_PASSES) passes = SORT_MAX_PASSES;
   return passes;
 }
 cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b,
-                                 const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
-                                 size_t scratch_bytes, cudaStream_t s) {
+                                 const uint32_t* count_dev, int64_t capacity, int begin_bit, int end_bit,
+                                 void* scratch, size_t scratch_bytes, cudaStream_t s) {
   if (capacity <= 0) return cudaSuccess;
   if (scratch_bytes < sort_scratch_bytes(capacity)) return cudaErrorInvalidValue;
   const int nblk = (int)sort_num_blocks(capacity);
   uint32_t* hist = reinterpret_cast<uint32_t*>(scratch);
   uint32_t* digit_total =
       reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(scratch) + align_up((size_t)nblk * SORT_RADIX * 4, WS_ALIGN));
-  const int passes = sort_num_passes(end_bit);
+  const int passes = sort_num_passes(begin_bit, end_bit);
   cudaError_t e = cudaMemsetAsync(digit_total, 0, (size_t)SORT_MAX_PASSES * SORT_RADIX * 4, s);
   if (e != cudaSuccess) return e;
   uint64_t* kin = keys_a; uint32_t* vin = vals_a;
   uint64_t* kout = keys_b; uint32_t* vout = vals_b;
   const unsigned long long cap = (unsigned long long)capacity;
   for (int pass = 0; pass < passes; pass++) {
-    const int shift = pass * SORT_RADIX_BITS;
+    const int shift = begin_bit + pass * SORT_RADIX_BITS;
     uint32_t* tot = digit_total + pass * SORT_RADIX;
     radix_upsweep_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
     radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap);
@@ -356,10 +414,10 @@ cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* ke
                               const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
                               size_t scratch_bytes, cudaStream_t s) {
   if (capacity <= 0) return cudaSuccess;
-  cudaError_t e = launch_sort_pingpong(keys_in, vals_in, keys_out, vals_out, count_dev, capacity, end_bit, scratch,
+  cudaError_t e = launch_sort_pingpong(keys_in, vals_in, keys_out, vals_out, count_dev, capacity, 0, end_bit, scratch,
                                        scratch_bytes, s);
   if (e != cudaSuccess) return e;
-  if ((sort_num_passes(end_bit) & 1) == 0) {  // result sits in the input buffers
+  if ((sort_num_passes(0, end_bit) & 1) == 0) {  // result sits in the input buffers
     int g = (int)sort_num_blocks(capacity) * (SORT_ITEMS / 4);
     if (g < 1) g = 1;
     copy_pairs_kernel<<<g, SORT_THREADS, 0, s>>>(keys_in, vals_in, keys_out, vals_out, count_dev,

@@ -133,14 +133,15 @@ struct FwdPointers {
 };
 
 cudaError_t launch_preprocess_forward(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
-cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
+cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, uint64_t* ok_keys,
+                                      uint32_t* ok_vals, cudaStream_t s);
 cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                               const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
                               size_t scratch_bytes, cudaStream_t s);
-int sort_num_passes(int end_bit);
+int sort_num_passes(int begin_bit, int end_bit);
 cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b,
-                                 const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
-                                 size_t scratch_bytes, cudaStream_t s);
+                                 const uint32_t* count_dev, int64_t capacity, int begin_bit, int end_bit,
+                                 void* scratch, size_t scratch_bytes, cudaStream_t s);
 cudaError_t launch_identify_ranges(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
 cudaError_t launch_render_forward(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
 cudaError_t launch_render_backward(const trase_b200_bwd_args& a, const FwdPointers& p, cudaStream_t s);
