@@ -333,7 +333,8 @@ def run_ours(args, rank, world, device):
         R = _raster._capacity_hint.get((device.index or 0, cfg["P"], cfg["W"], cfg["H"]), 0)
         P, N = cfg["P"], cfg["W"] * cfg["H"]
         T = ((cfg["W"] + 15) // 16) * ((cfg["H"] + 15) // 16)
-        n_pass = (32 + max(1, T.bit_length()) + 8) // 9      # 9-bit digits (csrc/common.cuh SORT_RADIX_BITS)
+        # SURVEY §8(d).2 counts the reference's sort: 8-bit passes over all 32 + tile bits, whatever we launch
+        n_pass = (32 + max(1, T.bit_length()) + 7) // 8
         stages = {}
         for k, (tot, cnt) in prof.items():
             if cnt:
