@@ -204,10 +204,7 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
   TB_STEP_ST(ST_RANGES, "identify_ranges", launch_identify_ranges(*a, p, stream));
   TB_STEP_ST(ST_RENDER_FWD, "render_forward", launch_render_forward(*a, p, stream));
   // preprocess, block-sum scan, key duplication, 3 kernels per radix pass, ranges, compositing
-  // preprocess; depth keys + P-sized sort + ordered block sums + block scan + key emission; tile-bit sort;
-  // ranges; compositing
-  count_launches((with_preprocess ? 1 : 0) + 1 + 3 * sort_num_passes(0, 32) + 3 +
-                 (a->capacity > 0 ? 3 * sort_num_passes(32, end_bit) : 0) + 1 + 1);
+  count_launches((with_preprocess ? 1 : 0) + 2);   // preprocess, ranges, compositing (binning counts its own)
   return 0;
 }
 

@@ -208,6 +208,7 @@ cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPoi
   duplicate_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, order, p.means2D, p.depths, p.tiles_touched, p.block_offsets,
                                                    p.point_offsets, p.counters, p.keys_unsorted, p.vals_unsorted,
                                                    a.radii, grid_x, grid_y);
+  count_launches(4);      // depth keys, ordered block sums, block-sum scan, key emission (the sort counts its own)
   return cudaGetLastError();
 }
 
@@ -396,6 +397,9 @@ cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* k
   uint64_t* kin = keys_a; uint32_t* vin = vals_a;
   uint64_t* kout = keys_b; uint32_t* vout = vals_b;
   const unsigned long long cap = (unsigned long long)capacity;
+  // (A one-launch-per-pass variant for small sorts — histogram, grid-wide barrier, prefix, scatter in one resident
+  // kernel — was measured for the P-sized depth sort: same 27 us per pass as these three launches, both are bound
+  // by memory latency at 74 blocks, so the simpler form stays.)
   for (int pass = 0; pass < passes; pass++) {
     const int shift = begin_bit + pass * SORT_RADIX_BITS;
     uint32_t* tot = digit_total + pass * SORT_RADIX;
@@ -407,6 +411,7 @@ cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* k
     uint64_t* tk = kin; kin = kout; kout = tk;
     uint32_t* tv = vin; vin = vout; vout = tv;
   }
+  count_launches(3 * passes);
   return cudaSuccess;
 }
 
