@@ -226,21 +226,22 @@ __device__ __forceinline__ uint32_t sort_count(const uint32_t* count_dev, unsign
   return (uint32_t)(r < capacity ? r : capacity);
 }
 
+template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS) radix_upsweep_kernel(const uint64_t* __restrict__ keys,
                                                                      const uint32_t* __restrict__ count_dev,
                                                                      unsigned long long capacity, int shift,
                                                                      uint32_t* __restrict__ hist, int nblk_stride,
                                                                      uint32_t* __restrict__ digit_total) {
   const uint32_t R = sort_count(count_dev, capacity);
-  const uint32_t block_start = blockIdx.x * SORT_TILE;
+  const uint32_t block_start = blockIdx.x * (SORT_THREADS * ITEMS);
   if (block_start >= R) return;
   __shared__ uint32_t s_hist[SORT_RADIX];
   for (int d = threadIdx.x; d < SORT_RADIX; d += SORT_THREADS) s_hist[d] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t warp_base = block_start + warp * (32 * SORT_ITEMS);
+  const uint32_t warp_base = block_start + warp * (32 * ITEMS);
 #pragma unroll
-  for (int j = 0; j < SORT_ITEMS; j++) {
+  for (int j = 0; j < ITEMS; j++) {
     uint32_t i = warp_base + j * 32 + lane;
     if (i < R) {
       uint32_t d = (uint32_t)(keys[i] >> shift) & (SORT_RADIX - 1);
@@ -258,9 +259,9 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_upsweep_kernel(const uint6
 __global__ void __launch_bounds__(SORT_THREADS) radix_scan_kernel(uint32_t* __restrict__ hist, int nblk_stride,
                                                                   const uint32_t* __restrict__ digit_total,
                                                                   const uint32_t* __restrict__ count_dev,
-                                                                  unsigned long long capacity) {
+                                                                  unsigned long long capacity, int tile_keys) {
   const uint32_t R = sort_count(count_dev, capacity);
-  const int nblk = (int)((R + SORT_TILE - 1) / SORT_TILE);
+  const int nblk = (int)((R + tile_keys - 1) / tile_keys);
   const int d = blockIdx.x;
   __shared__ uint32_t s_warp[SORT_THREADS / 32];
   __shared__ uint32_t s_carry;
@@ -304,12 +305,13 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scan_kernel(uint32_t* __re
   }
 }
 
+template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
     const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, uint64_t* __restrict__ keys_out,
     uint32_t* __restrict__ vals_out, const uint32_t* __restrict__ count_dev, unsigned long long capacity, int shift,
     const uint32_t* __restrict__ hist, int nblk_stride) {
   const uint32_t R = sort_count(count_dev, capacity);
-  const uint32_t block_start = blockIdx.x * SORT_TILE;
+  const uint32_t block_start = blockIdx.x * (SORT_THREADS * ITEMS);
   if (block_start >= R) return;
   constexpr int NW = SORT_THREADS / 32;
   __shared__ uint32_t s_cnt[NW][SORT_RADIX];
@@ -318,16 +320,16 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t lane_lt = (1u << lane) - 1u;
-  const uint32_t warp_base = block_start + warp * (32 * SORT_ITEMS);
-  uint64_t key[SORT_ITEMS];
-  uint32_t rank[SORT_ITEMS];
+  const uint32_t warp_base = block_start + warp * (32 * ITEMS);
+  uint64_t key[ITEMS];
+  uint32_t rank[ITEMS];
 #pragma unroll
-  for (int j = 0; j < SORT_ITEMS; j++) {
+  for (int j = 0; j < ITEMS; j++) {
     const uint32_t i = warp_base + j * 32 + lane;
     key[j] = (i < R) ? keys_in[i] : ~0ull;
   }
 #pragma unroll
-  for (int j = 0; j < SORT_ITEMS; j++) {
+  for (int j = 0; j < ITEMS; j++) {
     const uint32_t i = warp_base + j * 32 + lane;
     const bool valid = i < R;
     const uint32_t d = (uint32_t)(key[j] >> shift) & (SORT_RADIX - 1);
@@ -353,7 +355,7 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
   }
   __syncthreads();
 #pragma unroll
-  for (int j = 0; j < SORT_ITEMS; j++) {
+  for (int j = 0; j < ITEMS; j++) {
     const uint32_t i = warp_base + j * 32 + lane;
     if (i < R) {
       const uint32_t d = (uint32_t)(key[j] >> shift) & (SORT_RADIX - 1);
@@ -403,9 +405,17 @@ cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* k
   for (int pass = 0; pass < passes; pass++) {
     const int shift = begin_bit + pass * SORT_RADIX_BITS;
     uint32_t* tot = digit_total + pass * SORT_RADIX;
-    radix_upsweep_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
-    radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap);
-    radix_downsweep_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift, hist, nblk);
+    if (sort_is_small(capacity)) {
+      radix_upsweep_kernel<SORT_ITEMS_SMALL><<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
+      radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap, SORT_TILE_SMALL);
+      radix_downsweep_kernel<SORT_ITEMS_SMALL><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift,
+                                                                            hist, nblk);
+    } else {
+      radix_upsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
+      radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap, SORT_TILE);
+      radix_downsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift, hist,
+                                                                      nblk);
+    }
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     uint64_t* tk = kin; kin = kout; kout = tk;
@@ -423,7 +433,7 @@ cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* ke
                                        scratch_bytes, s);
   if (e != cudaSuccess) return e;
   if ((sort_num_passes(0, end_bit) & 1) == 0) {  // result sits in the input buffers
-    int g = (int)sort_num_blocks(capacity) * (SORT_ITEMS / 4);
+    int g = (int)((capacity + 1023) / 1024);
     if (g < 1) g = 1;
     copy_pairs_kernel<<<g, SORT_THREADS, 0, s>>>(keys_in, vals_in, keys_out, vals_out, count_dev,
                                                  (unsigned long long)capacity);

@@ -38,7 +38,11 @@
 namespace tb {
 
 constexpr int64_t kStaticSortMax = TRASE_B200_STATIC_SORT_MAX;
-constexpr size_t kStaticBlocks = (size_t)((kStaticSortMax + SORT_TILE - 1) / SORT_TILE);
+// the largest block count any admissible capacity needs: big sorts use 4096-key tiles, sorts up to
+// SORT_SMALL_MAX keys 1024-key tiles
+constexpr size_t kStaticBlocksBig = (size_t)((kStaticSortMax + SORT_TILE - 1) / SORT_TILE);
+constexpr size_t kStaticBlocksSmall = (size_t)((SORT_SMALL_MAX + SORT_TILE_SMALL - 1) / SORT_TILE_SMALL);
+constexpr size_t kStaticBlocks = kStaticBlocksBig > kStaticBlocksSmall ? kStaticBlocksBig : kStaticBlocksSmall;
 // same layout as sort_scratch_bytes(kStaticSortMax): block histograms, then digit totals
 constexpr size_t kStaticBytes =
     ((kStaticBlocks * SORT_RADIX * 4 + WS_ALIGN - 1) / WS_ALIGN) * WS_ALIGN +
