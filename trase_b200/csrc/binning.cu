@@ -366,6 +366,129 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
   }
 }
 
+// Downsweep with a local reorder: the block's keys are first placed in shared memory in digit order, then
+// written out, so that each digit's run leaves as one contiguous piece instead of 8-byte stores scattered
+// over up to 32 sectors per request (the tile-bit passes of depth-ordered instances are fully scattered).
+// Same ranks, same stable order as radix_downsweep_kernel.  Dynamic shared memory: keys (aliasing the
+// per-warp counters once every thread holds its local position), values, three digit tables.
+template <int ITEMS>
+__global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_staged_kernel(
+    const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, uint64_t* __restrict__ keys_out,
+    uint32_t* __restrict__ vals_out, const uint32_t* __restrict__ count_dev, unsigned long long capacity, int shift,
+    const uint32_t* __restrict__ hist, int nblk_stride) {
+  const uint32_t R = sort_count(count_dev, capacity);
+  constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
+  const uint32_t block_start = blockIdx.x * TILE_KEYS;
+  if (block_start >= R) return;
+  constexpr int NW = SORT_THREADS / 32;
+  constexpr int DPT = SORT_RADIX / SORT_THREADS;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  uint64_t* s_keys = reinterpret_cast<uint64_t*>(s_raw);                       // [TILE_KEYS]  (>= NW*RADIX*4 bytes)
+  uint32_t (*s_cnt)[SORT_RADIX] = reinterpret_cast<uint32_t (*)[SORT_RADIX]>(s_raw);   // aliases s_keys
+  uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_raw + (size_t)TILE_KEYS * 8);        // [TILE_KEYS]
+  uint32_t* s_lbase = s_vals + TILE_KEYS;                                      // [RADIX] local exclusive base
+  uint32_t* s_gdelta = s_lbase + SORT_RADIX;                                   // [RADIX] global base - local base
+  __shared__ uint32_t s_warp[NW];
+  static_assert((size_t)TILE_KEYS * 8 >= (size_t)NW * SORT_RADIX * 4, "key staging must cover the counters");
+  for (int d = threadIdx.x; d < NW * SORT_RADIX; d += SORT_THREADS) (&s_cnt[0][0])[d] = 0;
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t lane_lt = (1u << lane) - 1u;
+  const uint32_t warp_base = block_start + warp * (32 * ITEMS);
+  uint64_t key[ITEMS];
+  uint32_t rank[ITEMS];
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const uint32_t i = warp_base + j * 32 + lane;
+    key[j] = (i < R) ? keys_in[i] : ~0ull;
+  }
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const uint32_t i = warp_base + j * 32 + lane;
+    const bool valid = i < R;
+    const uint32_t d = (uint32_t)(key[j] >> shift) & (SORT_RADIX - 1);
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : 0xffffffffu);
+    const int leader = __ffs(peers) - 1;
+    uint32_t c = 0;
+    if (valid && lane == leader) c = s_cnt[warp][d];
+    c = __shfl_sync(0xffffffffu, c, leader);
+    rank[j] = c + __popc(peers & lane_lt);
+    if (valid && lane == leader) s_cnt[warp][d] = c + __popc(peers);
+    __syncwarp();
+  }
+  __syncthreads();
+  // per-warp exclusive offsets inside each digit (local), block totals, global bases
+  uint32_t tot[DPT], gbase[DPT];
+#pragma unroll
+  for (int q = 0; q < DPT; q++) {
+    const int d = threadIdx.x + q * SORT_THREADS;
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+      const uint32_t t = s_cnt[w][d];
+      s_cnt[w][d] = run;
+      run += t;
+    }
+    tot[q] = run;
+    gbase[q] = hist[(size_t)d * nblk_stride + blockIdx.x];
+  }
+  // exclusive scan of the block's digit totals in digit order (thread t holds digits t, t + 256)
+  uint32_t carry = 0;
+#pragma unroll
+  for (int q = 0; q < DPT; q++) {
+    uint32_t incl = tot[q];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t woff = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+      if (w < warp) woff += s_warp[w];
+      all += s_warp[w];
+    }
+    const uint32_t lb = carry + woff + incl - tot[q];
+    s_lbase[threadIdx.x + q * SORT_THREADS] = lb;
+    s_gdelta[threadIdx.x + q * SORT_THREADS] = gbase[q] - lb;
+    carry += all;
+    __syncthreads();
+  }
+  // local positions (registers), then the counters' memory becomes the key staging area
+  uint32_t lp[ITEMS];
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const uint32_t d = (uint32_t)(key[j] >> shift) & (SORT_RADIX - 1);
+    lp[j] = s_lbase[d] + s_cnt[warp][d] + rank[j];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const uint32_t i = warp_base + j * 32 + lane;
+    if (i < R) {
+      s_keys[lp[j]] = key[j];
+      s_vals[lp[j]] = vals_in[i];
+    }
+  }
+  __syncthreads();
+  const uint32_t n_valid = min((uint32_t)TILE_KEYS, R - block_start);
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    const uint32_t i = j * SORT_THREADS + threadIdx.x;
+    if (i < n_valid) {
+      const uint64_t k = s_keys[i];
+      const uint32_t d = (uint32_t)(k >> shift) & (SORT_RADIX - 1);
+      const uint32_t pos = s_gdelta[d] + i;
+      keys_out[pos] = k;
+      vals_out[pos] = s_vals[i];
+    }
+  }
+}
+constexpr int SORT_STAGED_SMEM = SORT_TILE * 12 + 2 * SORT_RADIX * 4;
+
 __global__ void copy_pairs_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                   uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                   const uint32_t* __restrict__ count_dev, unsigned long long capacity) {
@@ -375,6 +498,8 @@ __global__ void copy_pairs_kernel(const uint64_t* __restrict__ keys_in, const ui
     vals_out[i] = vals_in[i];
   }
 }
+
+int g_sort_staged = 1;   // trase_b200_set_tuning("sort_staged", 0|1)
 
 // Ping-pong sort.  Data starts in (keys_a, vals_a); after `passes` passes it is
 // in A again when `passes` is even, in B when odd (see sort_result_in_b).
@@ -413,8 +538,20 @@ cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* k
     } else {
       radix_upsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
       radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap, SORT_TILE);
-      radix_downsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift, hist,
-                                                                      nblk);
+      if (g_sort_staged) {
+        static bool attr_set = false;
+        if (!attr_set) {
+          e = cudaFuncSetAttribute(radix_downsweep_staged_kernel<SORT_ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   SORT_STAGED_SMEM);
+          if (e != cudaSuccess) return e;
+          attr_set = true;
+        }
+        radix_downsweep_staged_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, SORT_STAGED_SMEM, s>>>(
+            kin, vin, kout, vout, count_dev, cap, shift, hist, nblk);
+      } else {
+        radix_downsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift, hist,
+                                                                        nblk);
+      }
     }
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;

@@ -38,6 +38,7 @@ struct Tuning {
 };
 static Tuning g_tuning;
 void set_tuning(const char* key, int value);
+extern int g_sort_staged;
 
 constexpr int FWD_BATCH = 128;
 constexpr int BWD_BATCH = 256;
@@ -571,6 +572,7 @@ void set_tuning(const char* key, int value) {
   };
   if (eq(key, "fwd_ppt")) g_tuning.fwd_ppt = value;
   if (eq(key, "bwd_ppt")) g_tuning.bwd_ppt = value;
+  if (eq(key, "sort_staged")) g_sort_staged = value;
 }
 
 }  // namespace tb
