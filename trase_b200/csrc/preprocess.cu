@@ -442,8 +442,18 @@ __device__ __forceinline__ float3 dnormvdv3(float3 v, float3 dv) {
 
 __global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdParams q) {
   const int idx = blockIdx.x * PRE_BLOCK + threadIdx.x;
-  if (idx >= q.P || !(q.radii[idx] > 0)) return;
-
+  // dL/dSH of a Gaussian is (basis value i) x (dL/dRGB): 16 + 3 numbers.  They are staged per warp and written
+  // by the whole warp as one contiguous block (a thread writing its own 192 bytes with 4-byte stores at a
+  // 192-byte stride kept the L2 at 64 % of its peak on partial sectors).
+  __shared__ float s_shw[PRE_BLOCK / 32][32][17];
+  __shared__ float s_shrgb[PRE_BLOCK / 32][32][3];
+  __shared__ unsigned char s_shact[PRE_BLOCK / 32][32];
+  float shw[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) shw[i] = 0.f;
+  float3 sh_rgb = {0.f, 0.f, 0.f};
+  const bool active = idx < q.P && q.radii[idx] > 0;
+  if (active) {
   const float3 mean = {q.means3D[3 * idx], q.means3D[3 * idx + 1], q.means3D[3 * idx + 2]};
   const float* view = q.view;
 
@@ -558,10 +568,8 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdP
     dL_dRGB.z *= (cb & 4) ? 0 : 1;
 
     float3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
-    float* dsh = q.dL_dsh + (size_t)idx * q.M * 3;
-    auto put = [&](int i, float w) {
-      dsh[3 * i] = w * dL_dRGB.x; dsh[3 * i + 1] = w * dL_dRGB.y; dsh[3 * i + 2] = w * dL_dRGB.z;
-    };
+    sh_rgb = dL_dRGB;
+    auto put = [&](int i, float w) { shw[i] = w; };
     auto axpy = [](float3& acc, float w, const float3& v) {
       acc.x += w * v.x; acc.y += w * v.y; acc.z += w * v.z;
     };
@@ -665,6 +673,25 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdP
     dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
            2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
     reinterpret_cast<float4*>(q.dL_drot)[idx] = dq;
+  }
+  }  // active
+
+  if (q.shs) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < 16; i++) s_shw[warp][lane][i] = shw[i];
+    s_shrgb[warp][lane][0] = sh_rgb.x; s_shrgb[warp][lane][1] = sh_rgb.y; s_shrgb[warp][lane][2] = sh_rgb.z;
+    s_shact[warp][lane] = active ? 1 : 0;
+    __syncwarp();
+    const int M3 = q.M * 3;
+    const int ncoef = min((q.D + 1) * (q.D + 1), 16);
+    float* dst = q.dL_dsh + (size_t)(blockIdx.x * PRE_BLOCK + warp * 32) * M3;
+    for (int f = lane; f < 32 * M3; f += 32) {
+      const int g = f / M3, e = f - g * M3;
+      const int i = e / 3, c = e - 3 * i;
+      // coefficients beyond the active degree are not written (the buffer arrives zero-initialised), as in the reference
+      if (s_shact[warp][g] && i < ncoef) dst[f] = s_shw[warp][g][i] * s_shrgb[warp][g][c];
+    }
   }
 }
 
