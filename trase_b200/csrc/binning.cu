@@ -110,9 +110,7 @@ __global__ void __launch_bounds__(PRE_BLOCK) ordered_block_sums_kernel(int P, co
 
 // ---------------------------------------------------------------------------
 // Key duplication.  One thread per Gaussian, taken in depth order (`order`), computes its offset (block scan +
-// scanned block offset); Gaussians touching more than DUP_COOP tiles are
-// emitted by the whole warp so that one large splat does not serialise a lane.
-constexpr int DUP_COOP = 16;
+// scanned block offset); the instances of a warp's 32 Gaussians are then written by the whole warp.
 __global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
     int P, const uint32_t* __restrict__ order, const float2* __restrict__ means2D, const float* __restrict__ depths,
     const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_offsets,
@@ -139,47 +137,40 @@ __global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
   if (idx < P) point_offsets[idx] = off_incl;
   if (counters[1]) return;  // capacity overflow: emit nothing (host retries)
 
-  uint32_t off = off_incl - cnt;
+  const uint32_t off = off_incl - cnt;
   uint2 rmin = {0, 0}, rmax = {0, 0};
   uint32_t depth_bits = 0;
   if (cnt > 0) {
     tile_rect_dev(means2D[idx], radii[idx], grid_x, grid_y, rmin, rmax);
     depth_bits = __float_as_uint(depths[idx]);
   }
-  const uint32_t w = rmax.x - rmin.x;
-
-  // small splats: the owning lane writes its own instances, row-major (y outer, x inner)
-  if (cnt > 0 && cnt <= DUP_COOP) {
-    for (uint32_t y = rmin.y; y < rmax.y; y++)
-      for (uint32_t x = rmin.x; x < rmax.x; x++) {
-        uint64_t key = (uint64_t)(y * (uint32_t)grid_x + x);
-        key <<= 32;
-        key |= depth_bits;
-        keys[off] = key;
-        vals[off] = (uint32_t)idx;
-        off++;
-      }
-  }
-  // large splats: warp-cooperative
-  unsigned big = __ballot_sync(0xffffffffu, cnt > DUP_COOP);
-  while (big) {
-    const int src = __ffs(big) - 1;
-    big &= big - 1;
-    const uint32_t b_cnt = __shfl_sync(0xffffffffu, cnt, src);
-    const uint32_t b_off = __shfl_sync(0xffffffffu, off, src);
-    const uint32_t b_w = __shfl_sync(0xffffffffu, w, src);
-    const uint32_t b_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
-    const uint32_t b_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
-    const uint32_t b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
-    const uint32_t b_idx = (uint32_t)__shfl_sync(0xffffffffu, idx, src);
-    for (uint32_t k = lane; k < b_cnt; k += 32) {
-      const uint32_t y = b_y0 + k / b_w, x = b_x0 + k % b_w;
-      uint64_t key = (uint64_t)(y * (uint32_t)grid_x + x);
-      key <<= 32;
-      key |= b_depth;
-      keys[b_off + k] = key;
-      vals[b_off + k] = b_idx;
-    }
+  // Emission by the whole warp: the warp's instances form one contiguous output range (the offsets are a prefix
+  // sum), lane l writes instances l, l+32, ... of that range and finds the owning Gaussian by a binary search
+  // over the warp's 32 offsets — consecutive lanes write consecutive keys (a lane writing its own run of ~12
+  // keys scattered every store over partial sectors).
+  __shared__ uint32_t s_start[PRE_BLOCK / 32][33];
+  __shared__ uint4 s_rec[PRE_BLOCK / 32][32];      // x0, y0, width, depth bits
+  __shared__ uint32_t s_gid[PRE_BLOCK / 32][32];
+  const uint32_t warp_first = __shfl_sync(0xffffffffu, off, 0);
+  s_start[warp][lane] = off - warp_first;
+  if (lane == 31) s_start[warp][32] = off + cnt - warp_first;
+  s_rec[warp][lane] = make_uint4(rmin.x, rmin.y, rmax.x - rmin.x, depth_bits);
+  s_gid[warp][lane] = (uint32_t)idx;
+  __syncwarp();
+  const uint32_t total = s_start[warp][32];
+  for (uint32_t t = lane; t < total; t += 32) {
+    int lo = 0;                                   // last lane whose start is <= t (empty Gaussians share a start:
+#pragma unroll                                    //  the search lands on the last of them, i.e. the non-empty one)
+    for (int step = 16; step > 0; step >>= 1)
+      if (s_start[warp][lo + step] <= t) lo += step;
+    const uint4 rec = s_rec[warp][lo];
+    const uint32_t k = t - s_start[warp][lo];
+    const uint32_t y = rec.y + k / rec.z, x = rec.x + k % rec.z;
+    uint64_t key = (uint64_t)(y * (uint32_t)grid_x + x);
+    key <<= 32;
+    key |= rec.w;
+    keys[warp_first + t] = key;
+    vals[warp_first + t] = s_gid[warp][lo];
   }
 }
 
