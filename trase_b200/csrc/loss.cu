@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(LOSS_THREADS)
 l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, const LossWindow win,
                    int do_ssim, float* __restrict__ maps, float* __restrict__ partials) {
   __shared__ float sx[LHY][LHX + 1], sy[LHY][LHX + 1];
-  __shared__ float sh[5][LHY][LTX];
+  __shared__ __align__(16) float sh[5][LHY][LTX];
   __shared__ float s_red[LOSS_THREADS / 32];
   const int tx0 = blockIdx.x * LTX, ty0 = blockIdx.y * LTY;
   const size_t plane = (size_t)H * W;
@@ -74,42 +74,63 @@ l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
   }
   __syncthreads();
   if (do_ssim) {
-    for (int i = threadIdx.x; i < LHY * LTX; i += LOSS_THREADS) {
-      const int r = i / LTX, c = i - r * LTX;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+    // horizontal pass, four adjacent outputs per work item: 14 + 14 loads feed 4 x 11 taps of all five moments
+    // (same tap order per output as a one-output loop, so the sums are unchanged)
+    for (int i = threadIdx.x; i < LHY * (LTX / 4); i += LOSS_THREADS) {
+      const int r = i / (LTX / 4), c0 = (i - r * (LTX / 4)) * 4;
+      float xs[LW + 3], ys[LW + 3];
 #pragma unroll
-      for (int k = 0; k < LW; k++) {
-        const float g = win.g[k], xv = sx[r][c + k], yv = sy[r][c + k];
-        a0 = fmaf(g, xv, a0);
-        a1 = fmaf(g, yv, a1);
-        a2 = fmaf(g, xv * xv, a2);
-        a3 = fmaf(g, yv * yv, a3);
-        a4 = fmaf(g, xv * yv, a4);
+      for (int k = 0; k < LW + 3; k++) { xs[k] = sx[r][c0 + k]; ys[k] = sy[r][c0 + k]; }
+      float a[5][4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        a[0][j] = a[1][j] = a[2][j] = a[3][j] = a[4][j] = 0.f;
+#pragma unroll
+        for (int k = 0; k < LW; k++) {
+          const float g = win.g[k], xv = xs[j + k], yv = ys[j + k];
+          a[0][j] = fmaf(g, xv, a[0][j]);
+          a[1][j] = fmaf(g, yv, a[1][j]);
+          a[2][j] = fmaf(g, xv * xv, a[2][j]);
+          a[3][j] = fmaf(g, yv * yv, a[3][j]);
+          a[4][j] = fmaf(g, xv * yv, a[4][j]);
+        }
       }
-      sh[0][r][c] = a0; sh[1][r][c] = a1; sh[2][r][c] = a2; sh[3][r][c] = a3; sh[4][r][c] = a4;
+#pragma unroll
+      for (int m = 0; m < 5; m++)
+        *reinterpret_cast<float4*>(&sh[m][r][c0]) = make_float4(a[m][0], a[m][1], a[m][2], a[m][3]);
     }
     __syncthreads();
   }
   float l1 = 0.f, ss = 0.f;
   const int c = threadIdx.x & 31;
+  constexpr int RPT = LTY / (LOSS_THREADS / 32);          // 4 vertically adjacent outputs per thread
+  const int r0 = (threadIdx.x >> 5) * RPT;
+  // vertical pass: 14 loads per moment feed the 4 x 11 taps of this thread's four rows
+  float mom[5][RPT];
+  if (do_ssim) {
 #pragma unroll
-  for (int j = 0; j < LTY / (LOSS_THREADS / 32); j++) {
-    const int r = (threadIdx.x >> 5) + j * (LOSS_THREADS / 32);
+    for (int m = 0; m < 5; m++) {
+      float col[LW + RPT - 1];
+#pragma unroll
+      for (int k = 0; k < LW + RPT - 1; k++) col[k] = sh[m][r0 + k][c];
+#pragma unroll
+      for (int j = 0; j < RPT; j++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < LW; k++) acc = fmaf(win.g[k], col[j + k], acc);
+        mom[m][j] = acc;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < RPT; j++) {
+    const int r = r0 + j;
     const int gy = ty0 + r, gx = tx0 + c;
     if (gy >= H || gx >= W) continue;
     const float xv = sx[r + LR][c + LR], yv = sy[r + LR][c + LR];
     l1 += fabsf(xv - yv);
     if (!do_ssim) continue;
-    float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
-#pragma unroll
-    for (int k = 0; k < LW; k++) {
-      const float g = win.g[k];
-      mu1 = fmaf(g, sh[0][r + k][c], mu1);
-      mu2 = fmaf(g, sh[1][r + k][c], mu2);
-      e11 = fmaf(g, sh[2][r + k][c], e11);
-      e22 = fmaf(g, sh[3][r + k][c], e22);
-      e12 = fmaf(g, sh[4][r + k][c], e12);
-    }
+    const float mu1 = mom[0][j], mu2 = mom[1][j], e11 = mom[2][j], e22 = mom[3][j], e12 = mom[4][j];
     const float mu1sq = mu1 * mu1, mu2sq = mu2 * mu2, mu12 = mu1 * mu2;
     const float s1 = e11 - mu1sq, s2 = e22 - mu2sq, s12 = e12 - mu12;
     const float A1 = 2.f * mu12 + SSIM_C1, A2 = 2.f * s12 + SSIM_C2;
@@ -168,7 +189,7 @@ l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
                    const float* __restrict__ maps, const LossWindow win, float w_l1, float w_ssim, float inv_n,
                    const float* __restrict__ grad_out3, float* __restrict__ d_img) {
   __shared__ float sm[3][LHY][LHX + 1];
-  __shared__ float sh[3][LHY][LTX];
+  __shared__ __align__(16) float sh[3][LHY][LTX];
   const int tx0 = blockIdx.x * LTX, ty0 = blockIdx.y * LTY;
   const size_t plane = (size_t)H * W;
   const size_t n = (size_t)gridDim.z * plane;
@@ -189,41 +210,54 @@ l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
       sm[2][r][c] = in ? maps[2 * n + o] : 0.f;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < LHY * LTX; i += LOSS_THREADS) {
-      const int r = i / LTX, c = i - r * LTX;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+    for (int i = threadIdx.x; i < LHY * (LTX / 4); i += LOSS_THREADS) {
+      const int r = i / (LTX / 4), c0 = (i - r * (LTX / 4)) * 4;
 #pragma unroll
-      for (int k = 0; k < LW; k++) {
-        const float g = win.g[k];
-        a0 = fmaf(g, sm[0][r][c + k], a0);
-        a1 = fmaf(g, sm[1][r][c + k], a1);
-        a2 = fmaf(g, sm[2][r][c + k], a2);
+      for (int m = 0; m < 3; m++) {
+        float v[LW + 3];
+#pragma unroll
+        for (int k = 0; k < LW + 3; k++) v[k] = sm[m][r][c0 + k];
+        float a[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          a[j] = 0.f;
+#pragma unroll
+          for (int k = 0; k < LW; k++) a[j] = fmaf(win.g[k], v[j + k], a[j]);
+        }
+        *reinterpret_cast<float4*>(&sh[m][r][c0]) = make_float4(a[0], a[1], a[2], a[3]);
       }
-      sh[0][r][c] = a0; sh[1][r][c] = a1; sh[2][r][c] = a2;
     }
     __syncthreads();
   }
   const int c = threadIdx.x & 31;
+  constexpr int RPT = LTY / (LOSS_THREADS / 32);
+  const int r0 = (threadIdx.x >> 5) * RPT;
+  float cv[3][RPT];
+  if (do_ssim) {
 #pragma unroll
-  for (int j = 0; j < LTY / (LOSS_THREADS / 32); j++) {
-    const int r = (threadIdx.x >> 5) + j * (LOSS_THREADS / 32);
+    for (int m = 0; m < 3; m++) {
+      float col[LW + RPT - 1];
+#pragma unroll
+      for (int k = 0; k < LW + RPT - 1; k++) col[k] = sh[m][r0 + k][c];
+#pragma unroll
+      for (int j = 0; j < RPT; j++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < LW; k++) acc = fmaf(win.g[k], col[j + k], acc);
+        cv[m][j] = acc;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < RPT; j++) {
+    const int r = r0 + j;
     const int gy = ty0 + r, gx = tx0 + c;
     if (gy >= H || gx >= W) continue;
     const size_t o = base + (size_t)gy * W + gx;
     const float xv = img[o], yv = gt[o];
     const float d = xv - yv;
     float g = k_l1 * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));
-    if (do_ssim) {
-      float cm = 0.f, c11 = 0.f, c12 = 0.f;
-#pragma unroll
-      for (int k = 0; k < LW; k++) {
-        const float w = win.g[k];
-        cm = fmaf(w, sh[0][r + k][c], cm);
-        c11 = fmaf(w, sh[1][r + k][c], c11);
-        c12 = fmaf(w, sh[2][r + k][c], c12);
-      }
-      g += k_ssim * (cm + 2.f * xv * c11 + yv * c12);
-    }
+    if (do_ssim) g += k_ssim * (cv[0][j] + 2.f * xv * cv[1][j] + yv * cv[2][j]);
     d_img[o] = g;
   }
 }
