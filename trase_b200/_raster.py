@@ -45,12 +45,13 @@ def _f32c(t: torch.Tensor, device: torch.device) -> torch.Tensor:
     return t
 
 
-def _pinned_int(device: torch.device) -> torch.Tensor:
+def _pinned_int(device: torch.device, stream=None) -> torch.Tensor:
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    t = _pinned.get(idx)
+    key = (idx, stream.cuda_stream if stream is not None else 0)     # per stream, like the readback event
+    t = _pinned.get(key)
     if t is None:
         t = torch.zeros(2, dtype=torch.int32).pin_memory()
-        _pinned[idx] = t
+        _pinned[key] = t
     return t
 
 
@@ -102,8 +103,8 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
         capacity = max(capacity, P)      # the depth sort of the P Gaussians borrows the instance buffers
         if P == 0:
             capacity = 0
-        pinned = _pinned_int(dev)
         stream = torch.cuda.current_stream(dev)
+        pinned = _pinned_int(dev, stream)
 
         a = _lib.FwdArgs()
         a.P, a.sh_degree, a.M, a.W, a.H = P, int(degree), M, W, H
@@ -152,12 +153,13 @@ _events: Dict = {}
 
 
 def _readback_event(dev, stream):
-    """One reusable CUDA event per device (created by a first record, re-recorded by the library)."""
-    ev = _events.get(dev)
+    """One reusable CUDA event per (device, stream), created by a first record, re-recorded by the library."""
+    key = (dev, stream.cuda_stream)          # one event per stream: forwards on different streams may overlap
+    ev = _events.get(key)
     if ev is None:
         ev = torch.cuda.Event()
         ev.record(stream)
-        _events[dev] = ev
+        _events[key] = ev
     return ev
 
 
