@@ -40,6 +40,20 @@ static Tuning g_tuning;
 void set_tuning(const char* key, int value);
 extern int g_sort_staged;
 
+// Blackwell packed FP32: one FFMA2 performs two independent IEEE fp32 FMAs on register pairs (same results as two
+// FFMAs, half the issue slots — the compositing kernels are bound by instruction issue, not by the FMA pipe).
+__device__ __forceinline__ void ffma2(float2& acc, const float2 a, const unsigned long long bb) {
+  unsigned long long c = *reinterpret_cast<unsigned long long*>(&acc);
+  const unsigned long long av = *reinterpret_cast<const unsigned long long*>(&a);
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(c) : "l"(av), "l"(bb));
+  acc = *reinterpret_cast<float2*>(&c);
+}
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+
 constexpr int FWD_BATCH = 128;
 constexpr int BWD_BATCH = 256;
 constexpr unsigned FULL = 0xffffffffu;
@@ -132,7 +146,8 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
   const float wx0 = (float)(blockIdx.x * TILE + wbx), wx1 = wx0 + 7.f;
   const float wy0 = (float)(blockIdx.y * TILE + wby), wy1 = wy0 + (float)(4 * PPT - 1);
 
-  float pyf[PPT], T[PPT], C[PPT][3], D[PPT], O[PPT][NUM_OBJECTS];
+  float pyf[PPT], T[PPT], C[PPT][3], D[PPT];
+  float2 O[PPT][NUM_OBJECTS / 2];      // feature accumulators as channel pairs (FFMA2)
   bool done[PPT], inside[PPT];
   uint32_t last[PPT];
 #pragma unroll
@@ -143,7 +158,7 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
     T[p] = 1.0f; D[p] = 0.f; last[p] = 0;
     C[p][0] = C[p][1] = C[p][2] = 0.f;
 #pragma unroll
-    for (int ch = 0; ch < NUM_OBJECTS; ch++) O[p][ch] = 0.f;
+    for (int ch = 0; ch < NUM_OBJECTS / 2; ch++) O[p][ch] = make_float2(0.f, 0.f);
   }
 
   for (uint32_t base = range.x; base < range.y; base += FWD_BATCH) {
@@ -177,12 +192,35 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
         bool cand = false;
         if (jj < n) cand = splat_may_touch(s_xy[jj], s_co[jj], s_reach[jj], wx0, wx1, wy0, wy1);
         unsigned cmask = __ballot_sync(0xffffffffu, cand);
-        while (cmask) {
-          const int j = sub + __ffs(cmask) - 1;
+        if (!cmask) continue;
+        // software pipeline over the survivors: the exponent chain of the NEXT survivor (loads, quadratic form,
+        // expf) is issued before the blend of the current one, so its latency hides under the 72 FMAs
+        auto stage_a = [&](int jx, float (&ex)[PPT], float (&pw)[PPT], float& opac, float& thr) {
+          const float2 xy = s_xy[jx];
+          const float4 co = s_co[jx];
+          opac = co.w;
+          thr = s_reach[jx].z;
+#pragma unroll
+          for (int p = 0; p < PPT; p++) {
+            float dx, dy;
+            pw[p] = splat_power(xy, co, pxf, pyf[p], dx, dy);
+            ex[p] = expf(pw[p]);
+          }
+        };
+        int j = sub + __ffs(cmask) - 1;
+        float ex[PPT], pw[PPT], opac, thr;
+        stage_a(j, ex, pw, opac, thr);
+        while (true) {
           cmask &= cmask - 1;
-        const float2 xy = s_xy[j];
-        const float3 reach = s_reach[j];
-        const float4 co = s_co[j];
+          const bool has_next = cmask != 0;
+          int jn = j;
+          float exn[PPT], pwn[PPT], opacn = 0.f, thrn = 0.f;
+#pragma unroll
+          for (int p = 0; p < PPT; p++) { exn[p] = 0.f; pwn[p] = 0.f; }
+          if (has_next) {
+            jn = sub + __ffs(cmask) - 1;
+            stage_a(jn, exn, pwn, opacn, thrn);
+          }
         float w[PPT];
         bool any = false;
         still = false;
@@ -190,10 +228,8 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
         for (int p = 0; p < PPT; p++) {
           w[p] = 0.f;
           if (!done[p]) {
-            float dx, dy;
-            const float power = splat_power(xy, co, pxf, pyf[p], dx, dy);
-            if (!(power > 0.0f) && !(power < reach.z)) {
-              const float alpha = fminf(0.99f, co.w * expf(power));
+            if (!(pw[p] > 0.0f) && !(pw[p] < thr)) {
+              const float alpha = fminf(0.99f, opac * ex[p]);
               if (!(alpha < 1.0f / 255.0f)) {
                 const float test_T = T[p] * (1 - alpha);
                 if (test_T < 0.0001f) {
@@ -218,21 +254,25 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
             C[p][2] = fmaf(cd.z, w[p], C[p][2]);
             D[p] = fmaf(cd.w, w[p], D[p]);
           }
+          unsigned long long ww[PPT];
+#pragma unroll
+          for (int p = 0; p < PPT; p++) ww[p] = pack2(w[p], w[p]);
 #pragma unroll
           for (int c4 = 0; c4 < 8; c4++) {
             const float4 f = s_feat[j * 8 + c4];
 #pragma unroll
             for (int p = 0; p < PPT; p++) {
-              O[p][4 * c4 + 0] = fmaf(f.x, w[p], O[p][4 * c4 + 0]);
-              O[p][4 * c4 + 1] = fmaf(f.y, w[p], O[p][4 * c4 + 1]);
-              O[p][4 * c4 + 2] = fmaf(f.z, w[p], O[p][4 * c4 + 2]);
-              O[p][4 * c4 + 3] = fmaf(f.w, w[p], O[p][4 * c4 + 3]);
+              ffma2(O[p][2 * c4 + 0], make_float2(f.x, f.y), ww[p]);
+              ffma2(O[p][2 * c4 + 1], make_float2(f.z, f.w), ww[p]);
             }
           }
         }
         // the candidate loop is warp-uniform (ballots): leave it only when the whole warp is finished
         still = __any_sync(0xffffffffu, still);
-        if (!still) break;
+        if (!still || !has_next) break;
+        j = jn; opac = opacn; thr = thrn;
+#pragma unroll
+        for (int p = 0; p < PPT; p++) { ex[p] = exn[p]; pw[p] = pwn[p]; }
         }
       }
     }
@@ -250,7 +290,10 @@ __global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdPa
       q.out_color[HW + pix] = C[p][1] + T[p] * bg1;
       q.out_color[2 * HW + pix] = C[p][2] + T[p] * bg2;
 #pragma unroll
-      for (int ch = 0; ch < NUM_OBJECTS; ch++) q.out_objects[ch * HW + pix] = O[p][ch];
+      for (int ch = 0; ch < NUM_OBJECTS / 2; ch++) {
+        q.out_objects[(2 * ch) * HW + pix] = O[p][ch].x;
+        q.out_objects[(2 * ch + 1) * HW + pix] = O[p][ch].y;
+      }
       q.out_depth[pix] = D[p];
     }
   }
