@@ -425,7 +425,8 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
   const float wy0 = (float)(blockIdx.y * TILE + wby), wy1 = wy0 + (float)(4 * PPT - 1);
 
   float pyf[PPT], T[PPT], T_final[PPT], S[PPT], last_alpha[PPT], last_dot[PPT], bg_dot[PPT];
-  float dLc[PPT][3], dLo[PPT][NUM_OBJECTS];
+  float dLc[PPT][3];
+  float2 dLo[PPT][NUM_OBJECTS / 2];     // upstream feature gradients as channel pairs (FFMA2 operands)
   uint32_t last[PPT];
   uint32_t my_max = 0;
 #pragma unroll
@@ -441,7 +442,9 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
 #pragma unroll
     for (int c = 0; c < 3; c++) dLc[p][c] = inside ? q.dL_dpix[c * HW + pix] : 0.f;
 #pragma unroll
-    for (int ch = 0; ch < NUM_OBJECTS; ch++) dLo[p][ch] = inside ? q.dL_dpix_obj[ch * HW + pix] : 0.f;
+    for (int ch = 0; ch < NUM_OBJECTS / 2; ch++)
+      dLo[p][ch] = inside ? make_float2(q.dL_dpix_obj[(2 * ch) * HW + pix], q.dL_dpix_obj[(2 * ch + 1) * HW + pix])
+                          : make_float2(0.f, 0.f);
     bg_dot[p] = q.bg[0] * dLc[p][0] + q.bg[1] * dLc[p][1] + q.bg[2] * dLc[p][2];
   }
   // largest contributor count of the tile: nothing behind it received any weight
@@ -517,10 +520,10 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
       }
       if (!__any_sync(FULL, any)) continue;
 
-      float vobj[32];
+      float2 vobj2[16];
       float vs[16];
 #pragma unroll
-      for (int i = 0; i < 32; i++) vobj[i] = 0.f;
+      for (int i = 0; i < 16; i++) vobj2[i] = make_float2(0.f, 0.f);
 #pragma unroll
       for (int i = 0; i < 16; i++) vs[i] = 0.f;
 
@@ -533,17 +536,20 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
           dot[p] = fmaf(cd.y, dLc[p][1], dot[p]);
           dot[p] = fmaf(cd.z, dLc[p][2], dot[p]);
         }
+        float2 dot2[PPT];
+#pragma unroll
+        for (int p = 0; p < PPT; p++) dot2[p] = make_float2(0.f, 0.f);
 #pragma unroll
         for (int c4 = 0; c4 < 8; c4++) {
           const float4 f = s_feat[k * 8 + c4];
 #pragma unroll
           for (int p = 0; p < PPT; p++) {
-            dot[p] = fmaf(f.x, dLo[p][4 * c4 + 0], dot[p]);
-            dot[p] = fmaf(f.y, dLo[p][4 * c4 + 1], dot[p]);
-            dot[p] = fmaf(f.z, dLo[p][4 * c4 + 2], dot[p]);
-            dot[p] = fmaf(f.w, dLo[p][4 * c4 + 3], dot[p]);
+            ffma2(dot2[p], make_float2(f.x, f.y), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 0]));
+            ffma2(dot2[p], make_float2(f.z, f.w), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 1]));
           }
         }
+#pragma unroll
+        for (int p = 0; p < PPT; p++) dot[p] += dot2[p].x + dot2[p].y;
 #pragma unroll
         for (int p = 0; p < PPT; p++) {
           if (act[p]) {
@@ -568,11 +574,15 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
             vs[6] += -0.5f * gdx * dy[p] * dL_dG;
             vs[7] += -0.5f * gdy * dy[p] * dL_dG;
             vs[8] += G[p] * dL_dalpha;
+            const unsigned long long ww = pack2(w[p], w[p]);
 #pragma unroll
-            for (int ch = 0; ch < NUM_OBJECTS; ch++) vobj[ch] = fmaf(w[p], dLo[p][ch], vobj[ch]);
+            for (int ch = 0; ch < NUM_OBJECTS / 2; ch++) ffma2(vobj2[ch], dLo[p][ch], ww);
           }
         }
       }
+      float vobj[32];
+#pragma unroll
+      for (int i = 0; i < 16; i++) { vobj[2 * i] = vobj2[i].x; vobj[2 * i + 1] = vobj2[i].y; }
       const float tot_obj = warp_transpose_reduce32(vobj, lane);
       const float tot_s = warp_transpose_reduce16(vs, lane);
       const uint32_t id = s_id[k];
