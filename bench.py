@@ -116,7 +116,11 @@ class Workload:
             wv[3, :3] = centre - centre @ Rm.T
         self.cam = synth.make_camera(W, H, wv)
         self.view = make_view(self.cam, device)
+        # training: a materialised [P,1] tensor (train.py:202 adds per-iteration noise to the expanded time stamp);
+        # inference: the reference's own broadcast view, fid.unsqueeze(0).expand(N, -1) (render.py / train.py:450)
         self.time = torch.full((P, 1), 0.37 + 0.1 * rank, device=device)
+        if name.startswith("inference"):
+            self.time = torch.full((1, 1), 0.37 + 0.1 * rank, device=device).expand(P, 1)
         up = synth.make_upstream_grads(W, H, cfg["seed"] + rank)
         self.dL_dcolor, self.dL_dobjects = up["dL_dcolor"].to(device), up["dL_dobjects"].to(device)
         self.bg = torch.zeros(3, device=device)
