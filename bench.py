@@ -250,6 +250,10 @@ class _Null:
         return False
 
 
+# SMs the persistent MLP kernels leave free when a gradient all-reduce runs under the MLP backward (N > 1)
+RESERVE_SMS_MULTI = 0
+
+
 def algorithmic_bytes(stage, P, R, N, K=16, n_pass=6):
     """SURVEY.md §8(d).2 per-stage compulsory traffic (bytes per launch group)."""
     return {
@@ -447,6 +451,9 @@ def main():
     ap.add_argument("--workload", default="neu3d", choices=list(WORKLOADS))
     ap.add_argument("--mlp", default=os.environ.get("TRASE_B200_MLP", "native"), choices=["torch", "torch-tf32", "native"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reserve-sms", type=int, default=None,
+                    help="SMs the persistent MLP kernels leave to the concurrent NCCL all-reduce (default: 0 at N=1, "
+                         "RESERVE_SMS_MULTI at N>1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -468,8 +475,14 @@ def main():
             if not have_gpu:
                 raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
                                  "(use --impl reference for the CPU port)")
+            from trase_b200 import _lib
+            reserve = args.reserve_sms if args.reserve_sms is not None else (RESERVE_SMS_MULTI if world > 1 else 0)
+            if args.workload != "inference2m":        # inference has no collective
+                _lib.set_tuning("reserve_sms", reserve)
             line = run_inference(args, rank, world, device) if args.workload == "inference2m" else \
                 run_ours(args, rank, world, device)
+            if line is not None and args.workload != "inference2m":
+                line["config"]["reserve_sms"] = reserve
         if rank == 0 and line is not None:
             print(json.dumps(line), flush=True)
     finally:

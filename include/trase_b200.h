@@ -469,7 +469,8 @@ TRASE_API uint32_t trase_b200_higher_msb(uint32_t n);
 /* Kernel-variant selection for benchmarking (no reference counterpart; the
  * reference fixes its launch shapes at compile time, DGR/cuda_rasterizer/config.h).
  * Keys: "fwd_ppt", "bwd_ppt" (pixels per thread: 1 or 2), "sort_staged" (0 | 1:
- * shared-memory reorder in the radix downsweep). Results do not depend
+ * shared-memory reorder in the radix downsweep), "reserve_sms" (SMs the persistent MLP
+ * kernels leave free for a concurrent collective). Results do not depend
  * on the variant beyond floating-point summation order. */
 TRASE_API void trase_b200_set_tuning(const char* key, int value);
 

@@ -37,6 +37,7 @@ using namespace ptx;
 
 bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
                   uint32_t box_cols, CUtensorMapSwizzle swz);
+int num_sms();
 
 constexpr int FU_BM = 128;
 constexpr int FU_W = 256;                 // hidden width
@@ -495,9 +496,7 @@ static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMa
     if (e != cudaSuccess) { set_error("%s: %s", who, cudaGetErrorString(e)); return 2; }
     attr_set = true;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = num_sms() & ~1;          // SMs available to the persistent MLP kernels (see "reserve_sms"), whole pairs
   const int tiles = (p.M + FU_BM - 1) / FU_BM;
   int grid = tiles < sms ? tiles : sms;
   grid = (grid + FU_CLUSTER - 1) / FU_CLUSTER * FU_CLUSTER;

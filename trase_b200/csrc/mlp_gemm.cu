@@ -300,14 +300,19 @@ bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t col
 }
 
 static int g_num_sms = 0;
-static int num_sms() {
+// SMs the persistent MLP kernels leave free (trase_b200_set_tuning "reserve_sms").  With view-parallel training the
+// NCCL all-reduce of the Gaussians' gradients runs under the MLP backward; a persistent kernel that wants every
+// SM would find some taken by NCCL's CTAs and run its last CTAs as a second wave.
+int g_reserve_sms = 0;
+int num_sms() {
   if (!g_num_sms) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
     if (g_num_sms <= 0) g_num_sms = 148;
   }
-  return g_num_sms;
+  const int n = g_num_sms - g_reserve_sms;
+  return n > 2 ? n : 2;
 }
 
 template <int BN>

@@ -39,6 +39,7 @@ struct Tuning {
 static Tuning g_tuning;
 void set_tuning(const char* key, int value);
 extern int g_sort_staged;
+namespace mlp { extern int g_reserve_sms; }
 
 // Blackwell packed FP32: one FFMA2 performs two independent IEEE fp32 FMAs on register pairs (same results as two
 // FFMAs, half the issue slots — the compositing kernels are bound by instruction issue, not by the FMA pipe).
@@ -626,6 +627,7 @@ void set_tuning(const char* key, int value) {
   if (eq(key, "fwd_ppt")) g_tuning.fwd_ppt = value;
   if (eq(key, "bwd_ppt")) g_tuning.bwd_ppt = value;
   if (eq(key, "sort_staged")) g_sort_staged = value;
+  if (eq(key, "reserve_sms")) mlp::g_reserve_sms = value < 0 ? 0 : value;
 }
 
 }  // namespace tb
