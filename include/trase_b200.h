@@ -429,6 +429,9 @@ TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, int skip, int E, const float
                                             float* wpack, void* stream);
 TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, const float* wpack,
                                             const uint32_t* masks, float* dzs, float* const* colsum, void* stream);
+/* Debug only (no reference counterpart): device buffer of [grid][8] uint64 stall-cycle counters that the
+ * whole-network kernels fill when set (NULL = off); read by tools/check_fused_mlp.py. */
+TRASE_API void trase_b200_mlp_fused_set_prof(unsigned long long* dev_buf);
 
 /* ------------------------------------------------------------------------
  * Fused Adam over flat arenas and the densification statistics (SURVEY.md

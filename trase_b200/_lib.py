@@ -74,7 +74,7 @@ EXPORTS = [
     "trase_b200_mlp_fused_pack_floats", "trase_b200_mlp_pack_fused", "trase_b200_mlp_forward_fused",
     "trase_b200_mlp_fused_pack_bwd_floats", "trase_b200_mlp_pack_fused_bwd", "trase_b200_mlp_backward_fused",
     "trase_b200_adam_step", "trase_b200_densification_stats", "trase_b200_sample_features_forward",
-    "trase_b200_sample_features_backward",
+    "trase_b200_sample_features_backward", "trase_b200_mlp_fused_set_prof",
 ]
 
 _lib = None
