@@ -81,3 +81,14 @@ def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/libtrase_b200.so")
     with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
         _lib.load()
+
+
+def test_sort_scratch_is_monotone_in_capacity(native_lib):
+    """A workspace sized for `capacity` must serve every smaller sort (the depth sort of the P Gaussians borrows the
+    one sized for the instance capacity), across the switch from 1024- to 4096-key tiles at 2^20 keys."""
+    f = native_lib.trase_b200_sort_scratch_bytes
+    caps = [1, 1000, 262_144, 300_000, 1 << 20, (1 << 20) + 1, 1_054_096, 2_000_000, 4_000_000, 1 << 22, 10_000_000]
+    sizes = [f(c) for c in caps]
+    assert sizes == sorted(sizes)
+    assert native_lib.trase_b200_scratch_bytes(1_000_000, 1_054_096) >= f(1_000_000)
+    assert native_lib.trase_b200_scratch_bytes(2_000_000, 1_500_000) >= native_lib.trase_b200_scratch_bytes(0, 2_000_000)

@@ -10,6 +10,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import threading
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -22,6 +23,9 @@ NUM_OBJECTS = 32
 # last instance count seen per (device, P, W, H): sizes the next call's binning workspace
 _capacity_hint: Dict[Tuple[int, int, int, int], int] = {}
 _pinned: Dict[int, torch.Tensor] = {}
+# the tables below are shared by every host thread that renders; each entry is keyed per (device, stream), so two
+# threads on two streams never share an entry — the lock only protects the dictionaries themselves
+_state_lock = threading.Lock()
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -48,10 +52,11 @@ def _f32c(t: torch.Tensor, device: torch.device) -> torch.Tensor:
 def _pinned_int(device: torch.device, stream=None) -> torch.Tensor:
     idx = device.index if device.index is not None else torch.cuda.current_device()
     key = (idx, stream.cuda_stream if stream is not None else 0)     # per stream, like the readback event
-    t = _pinned.get(key)
-    if t is None:
-        t = torch.zeros(2, dtype=torch.int32).pin_memory()
-        _pinned[key] = t
+    with _state_lock:
+        t = _pinned.get(key)
+        if t is None:
+            t = torch.zeros(2, dtype=torch.int32).pin_memory()
+            _pinned[key] = t
     return t
 
 
@@ -98,7 +103,8 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
         res.img = torch.empty((lib.trase_b200_img_bytes(W, H),), **u8)
 
         key = (dev.index or 0, P, W, H)
-        hint = _capacity_hint.get(key)
+        with _state_lock:
+            hint = _capacity_hint.get(key)
         capacity = _initial_capacity(P, W, H) if hint is None else int(hint * 1.25) + 4096
         capacity = max(capacity, P)      # the depth sort of the P Gaussians borrows the instance buffers
         if P == 0:
@@ -143,7 +149,8 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
             capacity = max(int(R * 1.25) + 4096, P)  # workspace was too small: re-bin only
             first = False
         del scratch
-        _capacity_hint[key] = R
+        with _state_lock:
+            _capacity_hint[key] = R
         res.num_rendered = R
         res.capacity = capacity
         return res
@@ -155,11 +162,12 @@ _events: Dict = {}
 def _readback_event(dev, stream):
     """One reusable CUDA event per (device, stream), created by a first record, re-recorded by the library."""
     key = (dev, stream.cuda_stream)          # one event per stream: forwards on different streams may overlap
-    ev = _events.get(key)
-    if ev is None:
-        ev = torch.cuda.Event()
-        ev.record(stream)
-        _events[key] = ev
+    with _state_lock:
+        ev = _events.get(key)
+        if ev is None:
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            _events[key] = ev
     return ev
 
 

@@ -12,7 +12,7 @@
 namespace tb {
 
 static thread_local char g_err[512] = {0};
-unsigned long long g_launch_count = 0;
+std::atomic<unsigned long long> g_launch_count{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -20,6 +20,8 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+
+void clear_error() { g_err[0] = 0; }
 
 static int fail_cuda(const char* where, cudaError_t e) {
   set_error("trase_b200: CUDA error in %s: %s", where, cudaGetErrorString(e));
@@ -220,7 +222,10 @@ const char* trase_b200_last_error(void) { return g_err; }
 size_t trase_b200_geom_bytes(int P) { return geom_layout(P).total; }
 size_t trase_b200_img_bytes(int W, int H) { return img_layout(W, H).total; }
 size_t trase_b200_binning_bytes(int64_t capacity) { return bin_layout(capacity).total; }
-size_t trase_b200_scratch_bytes(int P, int64_t capacity) { (void)P; return scratch_layout(capacity).total; }
+size_t trase_b200_scratch_bytes(int P, int64_t capacity) {
+  // the P-sized depth sort borrows this workspace: size it for whichever is larger
+  return scratch_layout(capacity > (int64_t)P ? capacity : (int64_t)P).total;
+}
 
 void trase_b200_geom_offsets(int P, size_t* out) {
   GeomLayout L = geom_layout(P);
@@ -272,7 +277,7 @@ static int backward_impl(const trase_b200_bwd_args* a, int stages) {
 int trase_b200_rasterize_backward(const trase_b200_bwd_args* a) { return backward_impl(a, 3); }
 int trase_b200_rasterize_backward_stages(const trase_b200_bwd_args* a, int stages) { return backward_impl(a, stages); }
 
-unsigned long long trase_b200_launch_count(void) { return g_launch_count; }
+unsigned long long trase_b200_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
 
 void trase_b200_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(g_prof_mu);

@@ -530,13 +530,9 @@ cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* k
       radix_upsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
       radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap, SORT_TILE);
       if (g_sort_staged) {
-        static bool attr_set = false;
-        if (!attr_set) {
-          e = cudaFuncSetAttribute(radix_downsweep_staged_kernel<SORT_ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   SORT_STAGED_SMEM);
-          if (e != cudaSuccess) return e;
-          attr_set = true;
-        }
+        static PerDeviceOnce attr_once;
+        e = ensure_max_dyn_smem(attr_once, radix_downsweep_staged_kernel<SORT_ITEMS>, SORT_STAGED_SMEM);
+        if (e != cudaSuccess) return e;
         radix_downsweep_staged_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, SORT_STAGED_SMEM, s>>>(
             kin, vin, kout, vout, count_dev, cap, shift, hist, nblk);
       } else {

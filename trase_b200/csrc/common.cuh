@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <atomic>
 #include "../../include/trase_b200.h"
 
 namespace tb {
@@ -98,8 +99,14 @@ inline size_t sort_num_blocks(int64_t capacity) {
   return (size_t)((capacity + tile - 1) / tile);
 }
 // scratch: [block_hist: RADIX * nblocks u32][digit_totals: MAX_PASSES * RADIX u32]
+// Monotone in `capacity`: a workspace sized for `capacity` serves every sort of n <= capacity keys, whichever tile
+// size n selects (the P-sized depth sort borrows the workspace sized for the instance capacity, and a capacity just
+// above SORT_SMALL_MAX needs fewer 4096-key blocks than a smaller sort needs 1024-key blocks).
 inline size_t sort_scratch_bytes(int64_t capacity) {
-  size_t nb = sort_num_blocks(capacity);
+  const int64_t small_part = capacity < SORT_SMALL_MAX ? capacity : SORT_SMALL_MAX;
+  const size_t nb_small = (size_t)((small_part + SORT_TILE_SMALL - 1) / SORT_TILE_SMALL);
+  const size_t nb_big = capacity > SORT_SMALL_MAX ? (size_t)((capacity + SORT_TILE - 1) / SORT_TILE) : 0;
+  size_t nb = nb_small > nb_big ? nb_small : nb_big;
   if (nb == 0) nb = 1;
   return align_up(nb * SORT_RADIX * 4, WS_ALIGN) + align_up(SORT_MAX_PASSES * SORT_RADIX * 4, WS_ALIGN);
 }
@@ -119,11 +126,30 @@ inline ScratchLayout scratch_layout(int64_t capacity) {
 }
 
 // number of kernels this library has launched (bench.py's gpu_launches)
-extern unsigned long long g_launch_count;
-inline void count_launches(int n) { g_launch_count += (unsigned long long)n; }
+extern std::atomic<unsigned long long> g_launch_count;
+inline void count_launches(int n) { g_launch_count.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
-// host-side error recording (api.cu)
+// host-side error recording (api.cu); the message is per host thread
 void set_error(const char* fmt, ...);
+void clear_error();
+
+// Function attributes (the opt-in to more than 48 KB of dynamic shared memory) belong to the (function, device)
+// pair, not to the process: one process driving several GPUs has to set them on each.  One flag per device.
+constexpr int TB_MAX_DEVICES = 64;
+struct PerDeviceOnce {
+  std::atomic<unsigned char> done[TB_MAX_DEVICES];
+};
+template <typename K>
+inline cudaError_t ensure_max_dyn_smem(PerDeviceOnce& once, K kernel, int bytes) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const bool tracked = dev >= 0 && dev < TB_MAX_DEVICES;
+  if (tracked && once.done[dev].load(std::memory_order_acquire)) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess && tracked) once.done[dev].store(1, std::memory_order_release);
+  return e;
+}
 
 // launchers (one per .cu)
 struct FwdPointers {

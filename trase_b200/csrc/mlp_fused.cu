@@ -490,11 +490,10 @@ namespace mlp {
 template <bool BWD>
 static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMap& tW, const CUtensorMap& tWh,
                         const CUtensorMap& tA, const FusedParams& p, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_fused_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, FU_SMEM);
+  static PerDeviceOnce attr_once;
+  {
+    cudaError_t e = ensure_max_dyn_smem(attr_once, mlp_fused_kernel<BWD>, FU_SMEM);
     if (e != cudaSuccess) { set_error("%s: %s", who, cudaGetErrorString(e)); return 2; }
-    attr_set = true;
   }
   const int sms = num_sms() & ~1;          // SMs available to the persistent MLP kernels (see "reserve_sms"), whole pairs
   const int tiles = (p.M + FU_BM - 1) / FU_BM;

@@ -318,13 +318,11 @@ int num_sms() {
 template <int BN>
 static cudaError_t launch_gemm_tn(const CUtensorMap& tA, const CUtensorMap& tB, const GemmEpilogue& ep,
                                   cudaStream_t s) {
-  static bool attr_set = false;
+  static PerDeviceOnce attr_once;
   const int smem = GemmSmem<BN>::TOTAL;
-  if (!attr_set) {
-    cudaError_t e =
-        cudaFuncSetAttribute(gemm_tn_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  {
+    cudaError_t e = ensure_max_dyn_smem(attr_once, gemm_tn_tf32_kernel<BN>, smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   const int tiles = (ep.M + BM - 1) / BM;
   const int grid = tiles < num_sms() ? tiles : num_sms();
@@ -525,12 +523,11 @@ extern "C" TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, c
     set_error("trase_b200_wgrad_tf32: cuTensorMapEncodeTiled failed");
     return 2;
   }
-  static bool attr_set = false;
+  static PerDeviceOnce attr_once;
   const int smem = 2 * mlp::WG_STAGES * 8 * mlp::WG_BOX_BYTES + 256 + 1024;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp::wgrad_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  {
+    cudaError_t e = ensure_max_dyn_smem(attr_once, mlp::wgrad_tf32_kernel, smem);
     if (e != cudaSuccess) { set_error("trase_b200_wgrad_tf32: %s", cudaGetErrorString(e)); return 2; }
-    attr_set = true;
   }
   mlp::WgradParams wp;
   wp.M = M; wp.I = I; wp.J = J; wp.D = D; wp.ldd = ldd;

@@ -81,6 +81,7 @@ using namespace tb;
 extern "C" TRASE_API int trase_b200_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
                                                       uint32_t* vals_out, const uint32_t* count_dev,
                                                       int64_t capacity, int end_bit, void* stream) {
+  clear_error();
   if (capacity < 0 || end_bit < 1 || end_bit > 64) {
     set_error("trase_b200_sort_pairs_static: bad arguments (capacity=%lld, end_bit=%d)", (long long)capacity, end_bit);
     return 1;

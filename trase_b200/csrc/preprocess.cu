@@ -25,37 +25,6 @@ __device__ __constant__ float kSH_C3[7] = {-0.5900435899266435f, 2.8906114426405
                                            0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
                                            -0.5900435899266435f};
 
-// ---- tiny column-major 3x3 (m[c][r]), products written term by term in the
-// order k = 0,1,2 so that rounding matches a column-major library product.
-struct Mat3 {
-  float m[3][3];
-};
-__device__ __forceinline__ Mat3 mat3_cols(float a0, float a1, float a2, float b0, float b1, float b2, float c0,
-                                          float c1, float c2) {
-  Mat3 r;
-  r.m[0][0] = a0; r.m[0][1] = a1; r.m[0][2] = a2;
-  r.m[1][0] = b0; r.m[1][1] = b1; r.m[1][2] = b2;
-  r.m[2][0] = c0; r.m[2][1] = c1; r.m[2][2] = c2;
-  return r;
-}
-__device__ __forceinline__ Mat3 mul(const Mat3& A, const Mat3& B) {
-  Mat3 R;
-#pragma unroll
-  for (int c = 0; c < 3; c++)
-#pragma unroll
-    for (int r = 0; r < 3; r++)
-      R.m[c][r] = A.m[0][r] * B.m[c][0] + A.m[1][r] * B.m[c][1] + A.m[2][r] * B.m[c][2];
-  return R;
-}
-__device__ __forceinline__ Mat3 transpose(const Mat3& A) {
-  Mat3 R;
-#pragma unroll
-  for (int c = 0; c < 3; c++)
-#pragma unroll
-    for (int r = 0; r < 3; r++) R.m[c][r] = A.m[r][c];
-  return R;
-}
-
 // ---- pinned fp32 sequences -------------------------------------------------
 // ptxas is free to re-fuse un-annotated mul/add pairs, and does so differently
 // in differently shaped kernels.  Everything that decides an integer output of
@@ -143,8 +112,9 @@ struct PreFwdParams {
 };
 
 // SH → RGB (forward.cu:23-74).  `sh` points at this Gaussian's [M][3] block.
+// `avail` = floats readable from shp to the end of the SH tensor (bounds the rounded-up vector loads).
 __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3 pos, const float3 campos,
-                                            const float* __restrict__ shp, uint8_t& clamp_bits) {
+                                            const float* __restrict__ shp, long long avail, uint8_t& clamp_bits) {
   float3 dir = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
   // glm::length = sqrt(dot(v,v)); dot is x*x + y*y + z*z evaluated left to right
   float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
@@ -154,9 +124,9 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3 pos, const flo
   // is 16-byte aligned (M = 4 or 16 on an aligned tensor), scalar loads otherwise.
   float shv[48];
   const int nfl = (deg + 1) * (deg + 1) * 3;
-  if ((((uintptr_t)shp) & 15) == 0) {
+  const int nvec = (nfl + 3) >> 2;
+  if ((((uintptr_t)shp) & 15) == 0 && 4ll * nvec <= avail) {
     const float4* s4 = reinterpret_cast<const float4*>(shp);
-    const int nvec = (nfl + 3) >> 2;
 #pragma unroll
     for (int i = 0; i < 12; i++) {
       if (i < nvec) {
@@ -349,7 +319,7 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreFwdP
       if (q.colors_precomp == nullptr) {
         uint8_t cb;
         const float3 cam = {q.campos[0], q.campos[1], q.campos[2]};
-        rgb = sh_to_rgb(q.D, p_orig, cam, q.shs + (size_t)idx * q.M * 3, cb);
+        rgb = sh_to_rgb(q.D, p_orig, cam, q.shs + (size_t)idx * q.M * 3, (long long)(q.P - idx) * q.M * 3, cb);
         q.clamped[idx] = cb;
       } else {
         rgb = {__ldg(q.colors_precomp + (size_t)idx * 3), __ldg(q.colors_precomp + (size_t)idx * 3 + 1),
@@ -430,14 +400,110 @@ struct PreBwdParams {
   float* dL_dmeans3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;
 };
 
-__device__ __forceinline__ float3 dnormvdv3(float3 v, float3 dv) {
-  float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
-  float invsum32 = 1.0f / sqrt(sum2 * sum2 * sum2);
-  float3 o;
-  o.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
-  o.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
-  o.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
-  return o;
+// Gradient through v -> v/|v|:  J^T g = (g |v|^2 - v (v.g)) / |v|^3.
+__device__ __forceinline__ float3 unit_vector_grad(const float3 v, const float3 g) {
+  const float n2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  const float vg = v.x * g.x + v.y * g.y + v.z * g.z;
+  const float inv_n3 = 1.0f / (n2 * sqrtf(n2));
+  return float3{(g.x * n2 - v.x * vg) * inv_n3, (g.y * n2 - v.y * vg) * inv_n3, (g.z * n2 - v.z * vg) * inv_n3};
+}
+
+__device__ __forceinline__ float dot3(const float3 a, const float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float3 axpby(float a, const float3 x, float b, const float3 y) {
+  return float3{a * x.x + b * y.x, a * x.y + b * y.y, a * x.z + b * y.z};
+}
+// symmetric 3x3 (xx, xy, xz, yy, yz, zz) times vector
+__device__ __forceinline__ float3 sym3_mul(const float* s, const float3 v) {
+  return float3{s[0] * v.x + s[1] * v.y + s[2] * v.z, s[1] * v.x + s[3] * v.y + s[4] * v.z,
+                s[2] * v.x + s[4] * v.y + s[5] * v.z};
+}
+
+// Backward of the EWA projection, in the kernel's own terms.  The forward pass is
+//   cov2D = A Sigma A^T + 0.3 I,   A = J Wr  (2x3),   conic = cov2D^-1,
+// with Wr the rotation rows w0,w1,w2 of the view matrix and J's two rows (j00,0,j02), (0,j11,j12).  With the rows
+// a0 = j00 w0 + j02 w2 and a1 = j11 w1 + j12 w2 of A and u_i = Sigma a_i:
+//   cov2D = [[a0.u0 + .3, a0.u1], [a0.u1, a1.u1 + .3]]
+//   dL/dcov2D = -adj G adj / (det^2 + 1e-7)      (G = the symmetric conic gradient, adj = adjugate of cov2D;
+//                                                 the 1e-7 is the reference's guard, backward.cu:196-198)
+//   dL/dSigma = A^T D A  (returned with doubled off-diagonals: one parameter stands for both entries)
+//   dL/da0 = 2 Daa u0 + 2 Dab u1,  dL/da1 = 2 Dcc u1 + 2 Dab u0
+//   dL/dj** = the w rows dotted with those, and from there to the view-space mean t and back through Wr^T.
+// Same mathematics as computeCov2DCUDA (DGR/cuda_rasterizer/backward.cu:139-269); gradients only have to agree
+// to 1e-3, so the evaluation order is this kernel's own.
+__device__ __forceinline__ float3 ewa_projection_backward(const float3 mean, const float* __restrict__ view,
+                                                          float focal_x, float focal_y, float tan_fovx, float tan_fovy,
+                                                          const float* sigma, const float3 g_conic, float* dsigma) {
+  const float3 w0 = {view[0], view[4], view[8]}, w1 = {view[1], view[5], view[9]}, w2 = {view[2], view[6], view[10]};
+  float tx = dot3(w0, mean) + view[12], ty = dot3(w1, mean) + view[13];
+  const float tz = dot3(w2, mean) + view[14];
+  const float iz = 1.0f / tz;
+  const float limx = 1.3f * tan_fovx, limy = 1.3f * tan_fovy;
+  const float rx = tx * iz, ry = ty * iz;
+  const bool x_inside = !(rx < -limx || rx > limx), y_inside = !(ry < -limy || ry > limy);
+  const float cx = fminf(limx, fmaxf(-limx, rx)), cy = fminf(limy, fmaxf(-limy, ry));   // clamped t.x/t.z, t.y/t.z
+  const float j00 = focal_x * iz, j11 = focal_y * iz;
+  const float j02 = -j00 * cx, j12 = -j11 * cy;                                        // -f t.x / t.z^2
+
+  const float3 a0 = axpby(j00, w0, j02, w2), a1 = axpby(j11, w1, j12, w2);
+  const float3 u0 = sym3_mul(sigma, a0), u1 = sym3_mul(sigma, a1);
+  const float a = dot3(a0, u0) + 0.3f, b = dot3(a0, u1), c = dot3(a1, u1) + 0.3f;
+
+  const float det = a * c - b * b;
+  const float k = 1.0f / (det * det + 0.0000001f);
+  float Daa = 0.f, Dab = 0.f, Dcc = 0.f;          // dL/dcov2D as a symmetric matrix
+  if (k != 0.f) {
+    // adj = [[c,-b],[-b,a]];  Q = adj G adj
+    const float p0 = c * g_conic.x - b * g_conic.y, p1 = c * g_conic.y - b * g_conic.z;   // first row of adj G
+    const float q0 = a * g_conic.y - b * g_conic.x, q1 = a * g_conic.z - b * g_conic.y;   // second row of adj G
+    Daa = -k * (p0 * c - p1 * b);
+    Dab = -k * (p1 * a - p0 * b);
+    Dcc = -k * (q1 * a - q0 * b);
+  }
+  // dL/dSigma = Daa a0 a0^T + Dab (a0 a1^T + a1 a0^T) + Dcc a1 a1^T
+  const float3 e0 = axpby(Daa, a0, Dab, a1), e1 = axpby(Dab, a0, Dcc, a1);    // dSigma = a0 e0^T + a1 e1^T
+  dsigma[0] = a0.x * e0.x + a1.x * e1.x;
+  dsigma[3] = a0.y * e0.y + a1.y * e1.y;
+  dsigma[5] = a0.z * e0.z + a1.z * e1.z;
+  dsigma[1] = (a0.x * e0.y + a1.x * e1.y) + (a0.y * e0.x + a1.y * e1.x);
+  dsigma[2] = (a0.x * e0.z + a1.x * e1.z) + (a0.z * e0.x + a1.z * e1.x);
+  dsigma[4] = (a0.y * e0.z + a1.y * e1.z) + (a0.z * e0.y + a1.z * e1.y);
+
+  const float3 g0 = axpby(2.f * Daa, u0, 2.f * Dab, u1), g1 = axpby(2.f * Dcc, u1, 2.f * Dab, u0);  // dL/da0, dL/da1
+  const float dj00 = dot3(w0, g0), dj02 = dot3(w2, g0), dj11 = dot3(w1, g1), dj12 = dot3(w2, g1);
+  // j00 = fx/tz, j02 = -fx tx/tz^2 (tx clamped: no gradient through x when the clamp is active), same for y
+  const float dtx = x_inside ? -j00 * iz * dj02 : 0.f;
+  const float dty = y_inside ? -j11 * iz * dj12 : 0.f;
+  const float dtz = -iz * (j00 * dj00 + j11 * dj11 + 2.f * (j02 * dj02 + j12 * dj12));
+  return float3{w0.x * dtx + w1.x * dty + w2.x * dtz, w0.y * dtx + w1.y * dty + w2.y * dtz,
+                w0.z * dtx + w1.z * dty + w2.z * dtz};
+}
+
+// Backward of Sigma = sum_k s_k^2 r_k r_k^T (r_k = columns of the rotation built from the UN-normalised quaternion
+// (r,x,y,z), s = scale_modifier * scale).  With G = dL/dSigma as a symmetric matrix:
+//   dL/ds_k = 2 s_k r_k^T G r_k              (the reference does not apply the scale_modifier chain factor; kept)
+//   h_k = dL/dr_k = 2 s_k^2 G r_k, and the quaternion gradient collects the symmetric and antisymmetric parts of
+//   H = [h_0 h_1 h_2].  Same mathematics as computeCov3D's backward (backward.cu:273-334), own evaluation order.
+__device__ __forceinline__ void scale_rotation_backward(const float3 scale, float mod, const float4 q,
+                                                        const float* dsigma, float3& dscale, float4& dquat) {
+  const float r = q.x, x = q.y, y = q.z, z = q.w;
+  const float3 r0 = {1.f - 2.f * (y * y + z * z), 2.f * (x * y + r * z), 2.f * (x * z - r * y)};
+  const float3 r1 = {2.f * (x * y - r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z + r * x)};
+  const float3 r2 = {2.f * (x * z + r * y), 2.f * (y * z - r * x), 1.f - 2.f * (x * x + y * y)};
+  // symmetric-matrix form of the stored gradient (off-diagonals were doubled)
+  const float G[6] = {dsigma[0], 0.5f * dsigma[1], 0.5f * dsigma[2], dsigma[3], 0.5f * dsigma[4], dsigma[5]};
+  const float3 s = {mod * scale.x, mod * scale.y, mod * scale.z};
+  const float3 t0 = sym3_mul(G, r0), t1 = sym3_mul(G, r1), t2 = sym3_mul(G, r2);
+  dscale = float3{2.f * s.x * dot3(r0, t0), 2.f * s.y * dot3(r1, t1), 2.f * s.z * dot3(r2, t2)};
+  const float k0 = 2.f * s.x * s.x, k1 = 2.f * s.y * s.y, k2 = 2.f * s.z * s.z;
+  const float3 h0 = {k0 * t0.x, k0 * t0.y, k0 * t0.z}, h1 = {k1 * t1.x, k1 * t1.y, k1 * t1.z},
+               h2 = {k2 * t2.x, k2 * t2.y, k2 * t2.z};
+  // H[j][k] = h_k[j]: axial vector of H - H^T and the symmetric sums
+  const float ax = h1.z - h2.y, ay = h2.x - h0.z, az = h0.y - h1.x;
+  const float sxy = h0.y + h1.x, sxz = h0.z + h2.x, syz = h1.z + h2.y;
+  dquat.x = 2.f * (x * ax + y * ay + z * az);
+  dquat.y = 2.f * (r * ax + y * sxy + z * sxz) - 4.f * x * (h1.y + h2.z);
+  dquat.z = 2.f * (r * ay + x * sxy + z * syz) - 4.f * y * (h0.x + h2.z);
+  dquat.w = 2.f * (r * az + x * sxz + y * syz) - 4.f * z * (h0.x + h1.y);
 }
 
 __global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdParams q) {
@@ -455,101 +521,28 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdP
   const bool active = idx < q.P && q.radii[idx] > 0;
   if (active) {
   const float3 mean = {q.means3D[3 * idx], q.means3D[3 * idx + 1], q.means3D[3 * idx + 2]};
-  const float* view = q.view;
 
-  // ---- conic → cov2D → cov3D and the Jacobian part of dL/dmean (backward.cu:139-269)
-  float cov3D[6];
+  // ---- conic -> cov2D -> Sigma, and the Jacobian's share of dL/dmean
+  float sigma[6], dcov[6];
 #pragma unroll
-  for (int i = 0; i < 6; i++) cov3D[i] = q.cov3Ds[(size_t)idx * 6 + i];
-  const float4 dLc4 = reinterpret_cast<const float4*>(q.dL_dconic)[idx];
-  const float3 dL_dconic = {dLc4.x, dLc4.y, dLc4.w};
-  float3 t = xform4x3(mean, view);
-  const float h_x = q.focal_x, h_y = q.focal_y;
-  const float limx = 1.3f * q.tan_fovx;
-  const float limy = 1.3f * q.tan_fovy;
-  const float txtz = t.x / t.z;
-  const float tytz = t.y / t.z;
-  t.x = min(limx, max(-limx, txtz)) * t.z;
-  t.y = min(limy, max(-limy, tytz)) * t.z;
-  const float x_grad_mul = txtz < -limx || txtz > limx ? 0 : 1;
-  const float y_grad_mul = tytz < -limy || tytz > limy ? 0 : 1;
-
-  Mat3 J = mat3_cols(h_x / t.z, 0.0f, -(h_x * t.x) / (t.z * t.z), 0.0f, h_y / t.z, -(h_y * t.y) / (t.z * t.z), 0, 0, 0);
-  Mat3 Wm = mat3_cols(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
-  Mat3 Vrk = mat3_cols(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
-  Mat3 T = mul(Wm, J);
-  Mat3 cov2D = mul(mul(transpose(T), transpose(Vrk)), T);
-
-  float a = cov2D.m[0][0] += 0.3f;
-  float b = cov2D.m[0][1];
-  float c = cov2D.m[1][1] += 0.3f;
-
-  float denom = a * c - b * b;
-  float dL_da = 0, dL_db = 0, dL_dc = 0;
-  float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-  float dcov[6];
-  if (denom2inv != 0) {
-    dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
-    dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
-    dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
-
-    dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
-    dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
-    dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
-    dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
-              2 * T.m[1][0] * T.m[1][1] * dL_dc;
-    dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
-              2 * T.m[1][0] * T.m[1][2] * dL_dc;
-    dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
-              2 * T.m[1][1] * T.m[1][2] * dL_dc;
-  } else {
-#pragma unroll
-    for (int i = 0; i < 6; i++) dcov[i] = 0;
-  }
+  for (int i = 0; i < 6; i++) sigma[i] = q.cov3Ds[(size_t)idx * 6 + i];
+  const float4 dLc4 = reinterpret_cast<const float4*>(q.dL_dconic)[idx];   // (x, y, unused, w)
+  float3 dL_dmean_acc = ewa_projection_backward(mean, q.view, q.focal_x, q.focal_y, q.tan_fovx, q.tan_fovy, sigma,
+                                                float3{dLc4.x, dLc4.y, dLc4.w}, dcov);
 #pragma unroll
   for (int i = 0; i < 6; i++) q.dL_dcov3D[(size_t)idx * 6 + i] = dcov[i];
 
-  float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
-                  (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
-  float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
-                  (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
-  float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
-                  (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
-  float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
-                  (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
-  float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
-                  (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
-  float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
-                  (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
-
-  float dL_dJ00 = Wm.m[0][0] * dL_dT00 + Wm.m[0][1] * dL_dT01 + Wm.m[0][2] * dL_dT02;
-  float dL_dJ02 = Wm.m[2][0] * dL_dT00 + Wm.m[2][1] * dL_dT01 + Wm.m[2][2] * dL_dT02;
-  float dL_dJ11 = Wm.m[1][0] * dL_dT10 + Wm.m[1][1] * dL_dT11 + Wm.m[1][2] * dL_dT12;
-  float dL_dJ12 = Wm.m[2][0] * dL_dT10 + Wm.m[2][1] * dL_dT11 + Wm.m[2][2] * dL_dT12;
-
-  float tz = 1.f / t.z;
-  float tz2 = tz * tz;
-  float tz3 = tz2 * tz;
-
-  float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
-  float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
-  float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
-                 (2 * h_y * t.y) * tz3 * dL_dJ12;
-
-  float3 dL_dmean_acc = xform_vec4x3_T({dL_dtx, dL_dty, dL_dtz}, view);
-
-  // ---- projection part (backward.cu:361-377)
-  const float* proj = q.proj;
-  float4 m_hom = xform4x4(mean, proj);
-  float m_w = 1.0f / (m_hom.w + 0.0000001f);
-  const float3 g2 = {q.dL_dmean2D[3 * idx], q.dL_dmean2D[3 * idx + 1], 0.f};
-  float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
-  float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
-  float3 dL_dmean;
-  dL_dmean.x = (proj[0] * m_w - proj[3] * mul1) * g2.x + (proj[1] * m_w - proj[3] * mul2) * g2.y;
-  dL_dmean.y = (proj[4] * m_w - proj[7] * mul1) * g2.x + (proj[5] * m_w - proj[7] * mul2) * g2.y;
-  dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * g2.x + (proj[9] * m_w - proj[11] * mul2) * g2.y;
-  dL_dmean_acc.x += dL_dmean.x; dL_dmean_acc.y += dL_dmean.y; dL_dmean_acc.z += dL_dmean.z;
+  // ---- screen-space mean: ndc = h.xy / (h.w + 1e-7), h = proj p  =>  d ndc_x / d p_k = (P[k][0] - ndc_x P[k][3]) / w
+  {
+    const float* pm = q.proj;
+    const float4 h = xform4x4(mean, pm);
+    const float iw = 1.0f / (h.w + 0.0000001f);
+    const float nx = h.x * iw, ny = h.y * iw;
+    const float gx = q.dL_dmean2D[3 * idx] * iw, gy = q.dL_dmean2D[3 * idx + 1] * iw;
+    dL_dmean_acc.x += (pm[0] - nx * pm[3]) * gx + (pm[1] - ny * pm[3]) * gy;
+    dL_dmean_acc.y += (pm[4] - nx * pm[7]) * gx + (pm[5] - ny * pm[7]) * gy;
+    dL_dmean_acc.z += (pm[8] - nx * pm[11]) * gx + (pm[9] - ny * pm[11]) * gy;
+  }
 
   // ---- SH backward (backward.cu:18-134)
   if (q.shs) {
@@ -623,55 +616,21 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdP
     float3 dL_ddir = {dRGBdx.x * dL_dRGB.x + dRGBdx.y * dL_dRGB.y + dRGBdx.z * dL_dRGB.z,
                       dRGBdy.x * dL_dRGB.x + dRGBdy.y * dL_dRGB.y + dRGBdy.z * dL_dRGB.z,
                       dRGBdz.x * dL_dRGB.x + dRGBdz.y * dL_dRGB.y + dRGBdz.z * dL_dRGB.z};
-    float3 dm = dnormvdv3(dir_orig, dL_ddir);
+    float3 dm = unit_vector_grad(dir_orig, dL_ddir);
     dL_dmean_acc.x += dm.x; dL_dmean_acc.y += dm.y; dL_dmean_acc.z += dm.z;
   }
   q.dL_dmeans3D[3 * idx] = dL_dmean_acc.x;
   q.dL_dmeans3D[3 * idx + 1] = dL_dmean_acc.y;
   q.dL_dmeans3D[3 * idx + 2] = dL_dmean_acc.z;
 
-  // ---- cov3D → scale / rotation (backward.cu:273-334)
+  // ---- Sigma -> scale / rotation
   if (q.scales) {
     const float3 scale = {q.scales[3 * idx], q.scales[3 * idx + 1], q.scales[3 * idx + 2]};
     const float4 rot = reinterpret_cast<const float4*>(q.rotations)[idx];
-    float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
-    Mat3 R = mat3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                       2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                       2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-    const float3 s = {q.scale_modifier * scale.x, q.scale_modifier * scale.y, q.scale_modifier * scale.z};
-    Mat3 S = mat3_cols(s.x, 0.0f, 0.0f, 0.0f, s.y, 0.0f, 0.0f, 0.0f, s.z);
-    Mat3 M = mul(S, R);
-    Mat3 dL_dSigma = mat3_cols(dcov[0], 0.5f * dcov[1], 0.5f * dcov[2], 0.5f * dcov[1], dcov[3], 0.5f * dcov[4],
-                               0.5f * dcov[2], 0.5f * dcov[4], dcov[5]);
-    // dL_dM = 2 * M * dL_dSigma  (scalar * matrix scales every column first)
-    Mat3 M2;
-#pragma unroll
-    for (int cc = 0; cc < 3; cc++)
-#pragma unroll
-      for (int rr = 0; rr < 3; rr++) M2.m[cc][rr] = M.m[cc][rr] * 2.0f;
-    Mat3 dL_dM = mul(M2, dL_dSigma);
-    Mat3 Rt = transpose(R);
-    Mat3 dL_dMt = transpose(dL_dM);
-
     float3 dscale;
-    dscale.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
-    dscale.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
-    dscale.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
-    q.dL_dscale[3 * idx] = dscale.x; q.dL_dscale[3 * idx + 1] = dscale.y; q.dL_dscale[3 * idx + 2] = dscale.z;
-
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-      dL_dMt.m[0][k] *= s.x; dL_dMt.m[1][k] *= s.y; dL_dMt.m[2][k] *= s.z;
-    }
     float4 dq;
-    dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
-           2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
-    dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
-           2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
-    dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
-           2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
-    dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
-           2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
+    scale_rotation_backward(scale, q.scale_modifier, rot, dcov, dscale, dq);
+    q.dL_dscale[3 * idx] = dscale.x; q.dL_dscale[3 * idx + 1] = dscale.y; q.dL_dscale[3 * idx + 2] = dscale.z;
     reinterpret_cast<float4*>(q.dL_drot)[idx] = dq;
   }
   }  // active
