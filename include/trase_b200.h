@@ -264,6 +264,20 @@ TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const float* scalin
                                            float* g_opacity, float* g_fdc, float* g_frest, float* g_feat,
                                            void* stream);
 
+/* kNN-smoothed per-Gaussian features.  ref: GaussianModel.get_smoothed_gaussian_features
+ * (scene/gaussian_model.py:79-104), the FEATURE state's default input to render()
+ * (train.py:274-275 with smooth_K = 16, gaussian_renderer/__init__.py:116-119):
+ *   out[p] = mean over the selected neighbours j of normalize(feat[j])     (F.normalize, eps 1e-12)
+ * knn_idx [P][K] int64 is the caller's neighbour map (the reference gets it from pytorch3d.ops.knn_points and caches
+ * it; the search is not part of this library); sel_cols (HOST array of n_sel <= 32 column numbers in [0, K)) are the
+ * neighbours that take part in this call — the reference draws int(K*dropout) of them with torch.randperm.
+ * feat, out, g_out, g_feat: [P][32] fp32 on the device.  backward overwrites g_feat. */
+TRASE_API int trase_b200_smooth_features_forward(int P, int K, const int* sel_cols, int n_sel, const float* feat,
+                                                 const long long* knn_idx, float* out, void* stream);
+TRASE_API int trase_b200_smooth_features_backward(int P, int K, const int* sel_cols, int n_sel, const float* feat,
+                                                  const long long* knn_idx, const float* g_out, float* g_feat,
+                                                  void* stream);
+
 /* ------------------------------------------------------------------------
  * DeformNetwork MLP building block.  ref: the eleven nn.Linear layers of
  * DeformNetwork.forward (utils/time_utils.py:106-131), which the reference runs

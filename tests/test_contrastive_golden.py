@@ -1,0 +1,97 @@
+"""FEATURE-state loss front end against golden vectors produced by the reference's own functions
+(tests/golden/make_golden_contrastive.py imports utils/feature_utils.py and utils/loss_utils.py from /root/reference).
+
+CPU: the torch restatements (mask-correspondence matrix, pixel weights, the two soft-mined losses, loss_nnfm_style).
+GPU: the whole FEATURE-state loss through the fused front end (feature-norm kernel + sampled bilinear resize kernel)
+with its gradient w.r.t. the rendered feature image."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from trase_b200 import feature_utils as FU
+from trase_b200 import loss_utils as LU
+
+CASES = ["mixed", "no_negative"]
+
+
+def _case(g, tag, dev="cpu"):
+    t = lambda k: torch.from_numpy(g[tag + "_" + k]).to(dev)
+    return t("masks").long(), t("feat"), t("sampled_pixel"), t("sampled_mask")
+
+
+@pytest.mark.parametrize("tag", CASES)
+def test_mask_matrix_and_weights_match_the_reference(tag):
+    g = load_golden("contrastive")
+    masks, _, sp, sm = _case(g, tag)
+    C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
+    assert np.array_equal(C.numpy(), g[tag + "_C"])
+    w = FU.get_pixel_weights(masks, sp)
+    assert np.allclose(w.numpy(), g[tag + "_weights"], rtol=1e-6, atol=1e-6, equal_nan=True)
+
+
+@pytest.mark.parametrize("tag", CASES)
+def test_soft_mined_losses_match_the_reference(tag):
+    g = load_golden("contrastive")
+    C, w = torch.from_numpy(g[tag + "_C"]), torch.from_numpy(g[tag + "_weights"])
+    C_F = torch.from_numpy(g[tag + "_C_F"]).requires_grad_(True)
+    pos = LU.pixel_mask_correspondence_loss_soft_hard_positive(C=C, C_F=C_F, positive_th=0.75, weights=w)
+    neg = LU.pixel_mask_correspondence_loss_soft_negative(C=C, C_F=C_F, negative_th=0.5, weights=w)
+    assert abs(float(pos) - g[tag + "_vals"][0]) <= 1e-6 * max(1.0, abs(g[tag + "_vals"][0]))
+    assert abs(float(neg) - g[tag + "_vals"][1]) <= 1e-6 * max(1.0, abs(g[tag + "_vals"][1]))
+    (pos + neg).backward()                       # differentiable, and finite when nothing was mined
+    assert torch.isfinite(C_F.grad).all()
+
+
+def test_sample_pixel_and_mask_rates_and_coverage():
+    g = torch.Generator().manual_seed(3)
+    masks = torch.zeros(50, 60, 80, dtype=torch.int64)
+    for i in range(50):
+        masks[i, i:i + 10, 2 * (i % 30):2 * (i % 30) + 20] = 1
+    sp, sm = FU.get_sample_pixel_and_mask(masks, 1500, 25, generator=g)
+    assert sp.shape == (60, 80) and sm.shape == (50,)
+    assert not (sp & (masks.sum(0) == 0)).any()              # uncovered pixels are never sampled
+    assert 10 <= int(sm.sum()) <= 40
+    covered = float((masks.sum(0) != 0).float().mean())
+    assert abs(int(sp.sum()) - 1500 * covered) < 200
+
+
+def test_nnfm_style_loss_matches_the_reference():
+    g = load_golden("contrastive")
+    f1 = torch.from_numpy(g["nnfm_f1"]).requires_grad_(True)
+    l = LU.loss_nnfm_style(f1, torch.from_numpy(g["nnfm_f2"]))
+    l.backward()
+    assert abs(float(l) - g["nnfm_val"][0]) <= 1e-6
+    assert np.abs(f1.grad.numpy() - g["nnfm_grad"]).max() <= 1e-6 * max(1.0, np.abs(g["nnfm_grad"]).max())
+
+
+def test_smooth_map_helper_returns_self_first():
+    xyz = torch.randn(200, 3, generator=torch.Generator().manual_seed(1))
+    idx = FU.build_feature_smooth_map(xyz, K=4)
+    assert idx.shape == (200, 4) and torch.equal(idx[:, 0], torch.arange(200))
+    d = (xyz[:, None] - xyz[None]).norm(dim=-1)
+    assert torch.equal(idx.sort(1).values, d.topk(4, largest=False).indices.sort(1).values)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", CASES)
+def test_feature_state_loss_and_gradient_on_gpu(native_lib, tag):
+    """train.py:280-296 end to end on the GPU: fused feature-norm regulariser + fused sampled resize + the losses."""
+    g = load_golden("contrastive")
+    dev = torch.device("cuda:0")
+    masks, feat, sp, sm = _case(g, tag, dev)
+    feat.requires_grad_(True)
+    C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
+    w = FU.get_pixel_weights(masks, sp)
+    reg = LU.feature_norm_reg(feat)
+    C_F = FU.get_features_correspondence_matrix(feat, sp)          # resize folded in
+    assert np.abs(C_F.detach().cpu().numpy() - g[tag + "_C_F"]).max() <= 2e-6
+    pos = LU.pixel_mask_correspondence_loss_soft_hard_positive(C=C, C_F=C_F, positive_th=0.75, weights=w)
+    neg = LU.pixel_mask_correspondence_loss_soft_negative(C=C, C_F=C_F, negative_th=0.5, weights=w)
+    loss = pos + neg + 1.0 * reg
+    loss.backward()
+    vals = g[tag + "_vals"]
+    for got, ref in zip((pos, neg, reg, loss), vals):
+        assert abs(float(got) - ref) <= 2e-5 * max(1.0, abs(ref))
+    gref = g[tag + "_grad"]
+    assert np.abs(feat.grad.cpu().numpy() - gref).max() <= 1e-4 * np.abs(gref).max()

@@ -129,6 +129,74 @@ def test_native_deform_network_matches_torch(native_lib):
         assert err <= 2.0 * y + 2e-3, (n, err, y)
 
 
+def test_native_blender_deform_network_matches_torch(native_lib):
+    """is_blender variant (utils/time_utils.py:78-80, 108-109: timenet 13 -> 256 -> 30, 93-wide input, 349-wide skip
+    layer) on the native path: outputs and the gradients of EVERY parameter, timenet included, against the torch
+    fp32 backend, with torch's own TF32 path as the yardstick like the default model above."""
+    from trase_b200.deform import DeformNetwork
+    torch.manual_seed(4)
+    M = 20011
+    ref = DeformNetwork(is_blender=True, backend="torch").to(DEV)
+    nat = DeformNetwork(is_blender=True, backend="native").to(DEV)
+    nat.load_state_dict(ref.state_dict())
+    assert ref.linear[0].weight.shape == (256, 93) and ref.linear[5].weight.shape == (256, 349)
+    x = (torch.rand(M, 3, device=DEV) - 0.5) * 4
+    t = torch.full((1, 1), 0.37, device=DEV).expand(M, 1)          # as train.py / render.py pass it
+    go = [torch.randn(M, k, device=DEV) for k in (3, 4, 3)]
+    torch.backends.cuda.matmul.allow_tf32 = False
+    outs_r = ref(x, t)
+    torch.autograd.backward(list(outs_r), go)
+    base = [p.grad.clone() for p in ref.parameters()]
+    ref.zero_grad()
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        torch.autograd.backward(list(ref(x, t)), go)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = False
+    yard = [((p.grad - b).norm() / b.norm()).item() for p, b in zip(ref.parameters(), base)]
+    outs_n = nat(x, t)
+    torch.autograd.backward(list(outs_n), go)
+    for a, b in zip(outs_r, outs_n):
+        assert (a - b).abs().max().item() <= 5e-3 * max(1.0, a.abs().max().item())
+    for (n, q), b, y in zip(nat.named_parameters(), base, yard):
+        assert q.grad is not None, n
+        err = ((q.grad - b).norm() / b.norm()).item()
+        assert err <= 2.0 * y + 2e-3, (n, err, y)
+    # a materialised (non-broadcast) but uniform time column is accepted too; differing rows are refused
+    with torch.no_grad():
+        again = nat(x, t.contiguous())
+        assert torch.equal(again[0], outs_n[0].detach())
+        with pytest.raises(NotImplementedError):
+            nat(x, torch.rand(M, 1, device=DEV))
+
+
+def test_direct_gradient_path_is_opt_in(native_lib):
+    """Without a GradArena the weight gradients come back through autograd (so torch.autograd.grad works and leaves
+    .grad alone); with hooks on an arena parameter the ordinary path is taken for the whole network."""
+    from trase_b200.deform import DeformNetwork
+    from trase_b200.distributed import GradArena
+    torch.manual_seed(6)
+    net = DeformNetwork(backend="native").to(DEV)
+    M = 3000
+    x = (torch.rand(M, 3, device=DEV) - 0.5) * 3
+    t = torch.full((M, 1), 0.2, device=DEV)
+    for p in net.parameters():
+        p.grad = torch.zeros_like(p)               # plain .grad tensors, no arena: must NOT be written directly
+    outs = net(x, t)
+    loss = sum(o.sum() for o in outs)
+    grads = torch.autograd.grad(loss, list(net.parameters()))
+    assert all(g is not None and torch.isfinite(g).all() for g in grads)
+    assert all(not p.grad.any() for p in net.parameters())
+    arena = GradArena(net.parameters())
+    seen = []
+    net.linear[2].weight.register_post_accumulate_grad_hook(lambda p: seen.append(p.grad.abs().sum().item()))
+    sum(o.sum() for o in net(x, t)).backward()
+    assert len(seen) == 1 and seen[0] > 0          # the hook ran and saw the accumulated gradient
+    ref = torch.cat([g.reshape(-1) for g in grads])
+    got = torch.cat([arena.view_of(p).reshape(-1) for p in net.parameters()])
+    assert (ref - got).abs().max() <= 1e-4 * ref.abs().max() + 1e-6
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("M", [1, 127, 129, 1000, 128 * 148 + 5, 128 * 149 * 2 + 77])
 def test_fused_forward_matches_layer_chain(M):

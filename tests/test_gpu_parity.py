@@ -181,7 +181,7 @@ def test_depth_sort_fits_a_capacity_just_above_the_small_sort_limit(native_lib):
     workspace must cover both (it used to be rejected with 'invalid argument')."""
     from trase_b200 import synth, _raster
     P, W, H = 300_000, 320, 240
-    sc = synth.make_scene(P, W, H, 11)
+    sc = synth.make_scene(P, W, H, 11, target_radius_px=1.5)      # small splats: 1-2 tiles each, R < 2^20
     a = scene_args(sc, 0.0, DEV)
     full = cuda_forward(a)
     assert full.num_rendered < (1 << 20)
@@ -330,6 +330,46 @@ def test_fused_assembly_matches_torch_glue(native_lib):
     assert (o0["render_gaussian_features"] - o1["render_gaussian_features"]).abs().max() <= 1e-5
     for a, b in zip(g0, g1):
         assert rel_err(_np(a), _np(b)) <= 1e-3
+
+
+def test_smoothed_feature_render_matches_torch_glue(native_lib):
+    """FEATURE state's default call (train.py:274-275): render(..., is_smooth_gaussian_features=True, smooth_K=16).
+    The fused gather-normalise-mean kernels (csrc/assemble.cu) against the reference's torch formulation
+    (scene/gaussian_model.py:94-103), with the same neighbour subset: feature image and the gradient of the raw
+    per-Gaussian features; also the standalone pc.get_smoothed_gaussian_features values."""
+    from trase_b200 import synth, render as R
+    from trase_b200.feature_utils import build_feature_smooth_map
+    P = 6000
+    sc = synth.make_scene(P, 96, 80, 45)
+    view = R.make_view(sc["cam"], DEV)
+    up = {k: v.to(DEV) for k, v in synth.make_upstream_grads(96, 80, 45).items()}
+    bg = torch.zeros(3, device=DEV)
+    knn = build_feature_smooth_map(sc["means3D"], K=16)
+    assert torch.equal(knn[:, 0], torch.arange(P))
+    z = [torch.zeros(P, k, device=DEV) for k in (3, 4, 3)]
+    res = {}
+    for fused in (False, True):
+        R.FUSED_GLUE = fused
+        try:
+            pc = R.GaussianParams.from_activated(sc, DEV)
+            with torch.no_grad():      # un-normalised raw features, one exactly zero row (the clamped normalize branch)
+                pc._gaussian_features.mul_(torch.rand(P, 1, 1, generator=torch.Generator().manual_seed(2)).to(DEV) * 3 + 0.1)
+                pc._gaussian_features[17] = 0
+            pc.set_feature_smooth_map(knn)
+            torch.manual_seed(11)                      # render() draws the neighbour subset with torch.randperm
+            out = R.render(view, pc, R.PIPE_DEFAULT, bg, z[0], z[1], z[2], is_smooth_gaussian_features=True,
+                           smooth_K=16)
+            out["render_gaussian_features"].backward(up["dL_dobjects"])
+            sm = pc.get_smoothed_gaussian_features(K=16, dropout=0.5, select_point=[3, 0, 9, 12, 5, 1, 7, 15]).detach()
+            res[fused] = (out["render_gaussian_features"].detach().clone(), pc._gaussian_features.grad.clone(), sm)
+        finally:
+            R.FUSED_GLUE = True
+    assert res[True][2].shape == (P, 1, 32)
+    assert (res[False][2] - res[True][2]).abs().max() <= 1e-6
+    assert (res[False][0] - res[True][0]).abs().max() <= 1e-5
+    assert rel_err(_np(res[False][1]), _np(res[True][1])) <= 1e-3
+    # K <= 1 returns the raw parameter itself, as the reference does
+    assert pc.get_smoothed_gaussian_features(K=1) is pc._gaussian_features
 
 
 def test_aliased_sh_parameters_match_separate_storage(native_lib):

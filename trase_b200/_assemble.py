@@ -4,6 +4,8 @@ reference's render() (gaussian_renderer/__init__.py:82-121) with
 scene/gaussian_model.py's activations, in one forward and one backward launch group."""
 from __future__ import annotations
 
+import ctypes as C
+
 import torch
 
 from . import _lib
@@ -89,3 +91,44 @@ class _Assemble(torch.autograd.Function):
 def assemble_inputs(xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat):
     """-> (means3D, scales, rotations, opacity, shs, sh_objs); all arguments CUDA fp32 tensors."""
     return _Assemble.apply(xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat)
+
+
+class _SmoothFeatures(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, feat, knn_idx, sel_cols):
+        lib = _lib.load()
+        if not feat.is_cuda:
+            raise RuntimeError("trase_b200: smoothed features run on CUDA tensors only")
+        dev = feat.device
+        P, K = knn_idx.shape
+        f = _c(feat).view(P, 32)
+        idx = knn_idx.to(device=dev, dtype=torch.int64).contiguous()
+        sel = (C.c_int * len(sel_cols))(*[int(c) for c in sel_cols])
+        with torch.cuda.device(dev):
+            out = torch.empty((P, 1, 32), dtype=torch.float32, device=dev)
+            _lib.check(lib.trase_b200_smooth_features_forward(P, K, sel, len(sel_cols), f.data_ptr(), idx.data_ptr(),
+                                                              out.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+        ctx.save_for_backward(f, idx)
+        ctx.sel = sel
+        ctx.shape = feat.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        lib = _lib.load()
+        f, idx = ctx.saved_tensors
+        P, K = idx.shape
+        dev = f.device
+        with torch.cuda.device(dev):
+            g = _c(g_out)
+            g_feat = torch.empty((P, 32), dtype=torch.float32, device=dev)
+            _lib.check(lib.trase_b200_smooth_features_backward(P, K, ctx.sel, len(ctx.sel), f.data_ptr(), idx.data_ptr(),
+                                                               g.data_ptr(), g_feat.data_ptr(),
+                                                               torch.cuda.current_stream(dev).cuda_stream))
+        return g_feat.view(ctx.shape), None, None
+
+
+def smooth_features(feat, knn_idx, sel_cols):
+    """mean over the selected columns of knn_idx of normalize(feat[neighbour]) -> [P,1,32]; one gather kernel per
+    direction (scene/gaussian_model.py:94-103 runs normalize + index + mean + their autograd)."""
+    return _SmoothFeatures.apply(feat, knn_idx, tuple(int(c) for c in sel_cols))

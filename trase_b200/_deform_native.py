@@ -20,10 +20,23 @@ from . import _lib
 W = 256
 FUSED_FORWARD = True   # module switch: False runs the layer-by-layer GEMM chain (csrc/mlp_gemm.cu)
 FUSED_BACKWARD = True  # same for the data-gradient chain of the backward pass (needs FUSED_FORWARD)
-# When every hidden-layer parameter already has a contiguous fp32 `.grad` (e.g. views of a flat gradient arena),
-# the weight- and bias-gradient kernels add straight into it (they accumulate anyway) and backward() returns None
-# for those inputs: same result as autograd's `grad += new` without 16 tiny add kernels and a zero-filled buffer.
+# When every hidden-layer parameter's `.grad` is a view of a flat gradient arena that opted in
+# (trase_b200.distributed.GradArena marks its parameters), the weight- and bias-gradient kernels add straight into
+# it (they accumulate anyway) and backward() returns None for those inputs: same result as autograd's
+# `grad += new` without 16 tiny add kernels and a zero-filled buffer.  This bypasses autograd's own accumulation, so
+# it is OPT-IN per parameter (only GradArena parameters) and never taken when a parameter carries gradient hooks or
+# when `.grad` was replaced since the arena was built; everything else gets the gradients returned the normal way.
+# Restriction that comes with the opt-in: drive an arena-backed network with `.backward()`, not with
+# torch.autograd.grad (which must not touch `.grad`).  Module switch: False disables it everywhere.
 DIRECT_GRAD_ACCUM = True
+
+
+def _direct_ok(p, dev) -> bool:
+    g = p.grad
+    return (getattr(p, "_trase_arena_grad_ptr", None) is not None and g is not None and
+            g.data_ptr() == p._trase_arena_grad_ptr and g.is_contiguous() and g.dtype == torch.float32 and
+            g.device == dev and g.data_ptr() % 16 == 0 and g.shape == p.shape and
+            not getattr(p, "_post_accumulate_grad_hooks", None) and not getattr(p, "_backward_hooks", None))
 
 
 def tf32_round(w: torch.Tensor) -> torch.Tensor:
@@ -181,9 +194,7 @@ class _DeformMLP(torch.autograd.Function):
                 WrT = [None] + list(saved[3 + nl:])
             # gradient targets: the parameters' own .grad where possible (DIRECT_GRAD_ACCUM), else one zeroed buffer
             hidden = ctx.hidden_params
-            direct = DIRECT_GRAD_ACCUM and hidden is not None and all(
-                p.grad is not None and p.grad.is_contiguous() and p.grad.dtype == torch.float32 and
-                p.grad.device == dev and p.grad.data_ptr() % 16 == 0 and p.grad.shape == p.shape for p in hidden)
+            direct = DIRECT_GRAD_ACCUM and hidden is not None and all(_direct_ok(p, dev) for p in hidden)
             gbuf = torch.zeros((0 if direct else sum(r * c for r, c in sizes) + nl * W) + W * 16 + 16, **f32)
             off = 0
             if direct:
@@ -240,11 +251,45 @@ class _DeformMLP(torch.autograd.Function):
         return tuple(out)
 
 
+def _blender_params(net, t):
+    """is_blender variant (utils/time_utils.py:78-80, 108-109): the time embedding goes through `timenet`
+    (13 -> 256 -> 30) before it joins the 63 position columns.  One view has ONE time stamp, so that 30-vector tau is
+    the same for every row and its share of the two layers that read the embedding is a constant:
+        W[:, 63:93] @ tau   added to that layer's bias.
+    The kernels then run the ordinary network on a 64-column embedding (63 position columns + one zero column, zero
+    weight column to match); timenet itself and the bias folding are two tiny torch ops whose autograd carries the
+    gradients back to timenet and to the weight columns that were folded away."""
+    from .deform import positional_encoding
+    if not (t.numel() == 1 or t.stride(0) == 0 or t.shape[0] == 1):
+        if not bool((t == t[:1]).all()):
+            raise NotImplementedError("native is_blender DeformNetwork: one time stamp per call (the reference always "
+                                      "passes fid.unsqueeze(0).expand(N, -1), train.py:196, render.py)")
+    tau = net.timenet(positional_encoding(t[:1].reshape(1, 1), net.t_multires))[0]          # [30]
+    nx = 3 + 6 * net.multires
+    nt = tau.shape[0]
+    params = []
+    for i, lin in enumerate(net.linear):
+        Wt, b = lin.weight, lin.bias
+        if i == 0 or (i - 1) in net.skips:
+            zero_col = Wt.new_zeros(Wt.shape[0], 1)
+            b = b + Wt[:, nx:nx + nt] @ tau
+            Wt = torch.cat([Wt[:, :nx], zero_col, Wt[:, nx + nt:]], dim=1)
+        params += [Wt, b]
+    return params
+
+
 def deform_forward(net, x, t):
-    if net.is_blender or net.is_6dof:
-        raise NotImplementedError("native DeformNetwork path covers the default (non-blender, non-6DoF) model")
+    if net.is_6dof:
+        raise NotImplementedError("native DeformNetwork path covers the non-6DoF models")
     if not x.is_cuda:
         raise RuntimeError("trase_b200: the native DeformNetwork path runs on CUDA tensors only")
+    if net.is_blender:
+        params = _blender_params(net, t)
+        for head in (net.gaussian_warp, net.gaussian_rotation, net.gaussian_scaling):
+            params += [head.weight, head.bias]
+        keep = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        # Lt = 0: the embedding kernel writes the 63 position columns and the raw "t" column, which is fed a zero
+        return _DeformMLP.apply(x, x.new_zeros(1, 1), net.multires, 0, net.skips[0], keep, *params)
     params = []
     for lin in net.linear:
         params += [lin.weight, lin.bias]

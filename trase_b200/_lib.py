@@ -75,6 +75,7 @@ EXPORTS = [
     "trase_b200_mlp_fused_pack_bwd_floats", "trase_b200_mlp_pack_fused_bwd", "trase_b200_mlp_backward_fused",
     "trase_b200_adam_step", "trase_b200_densification_stats", "trase_b200_sample_features_forward",
     "trase_b200_sample_features_backward", "trase_b200_mlp_fused_set_prof",
+    "trase_b200_smooth_features_forward", "trase_b200_smooth_features_backward",
 ]
 
 _lib = None
@@ -123,6 +124,12 @@ def load() -> C.CDLL:
     lib.trase_b200_sort_pairs_static.restype = C.c_int
     lib.trase_b200_sort_pairs_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                                  C.c_int64, C.c_int, C.c_void_p]
+    lib.trase_b200_smooth_features_forward.restype = C.c_int
+    lib.trase_b200_smooth_features_forward.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p,
+                                                       C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.trase_b200_smooth_features_backward.restype = C.c_int
+    lib.trase_b200_smooth_features_backward.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p,
+                                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.trase_b200_gemm_tf32.restype = C.c_int
     lib.trase_b200_gemm_tf32.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                          C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]

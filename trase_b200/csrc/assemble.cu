@@ -135,9 +135,117 @@ __global__ void __launch_bounds__(256) assemble_feat_bwd_kernel(int P, const flo
   if (valid) g_feat[e] = make_float4(g.x * inv - f.x * k, g.y * inv - f.y * k, g.z * inv - f.z * k, g.w * inv - f.w * k);
 }
 
+
+// ---------------------------------------------------------------------------
+// kNN-smoothed features (scene/gaussian_model.py:79-104): mean over a subset of each Gaussian's K nearest
+// neighbours of their L2-normalised (F.normalize, eps 1e-12) feature rows.  One warp per Gaussian, lane = channel;
+// a neighbour row is one coalesced 128-byte read.  The neighbour index map is the caller's (the search itself is
+// outside this path); `sel` lists which of the map's K columns take part (the reference draws int(K*dropout) of
+// them per call with torch.randperm).
+constexpr int SMOOTH_MAX_SEL = 32;
+struct SmoothSel { int n; unsigned char col[SMOOTH_MAX_SEL]; };
+
+__global__ void __launch_bounds__(256) smooth_feat_fwd_kernel(int P, int K, SmoothSel sel,
+                                                              const float* __restrict__ feat,
+                                                              const long long* __restrict__ idx, float* __restrict__ out) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= P) return;
+  float acc = 0.f;
+  for (int k = 0; k < sel.n; k++) {
+    const long long j = __ldg(idx + (size_t)p * K + sel.col[k]);
+    const float v = __ldg(feat + (size_t)j * NUM_OBJECTS + lane);
+    float n2 = v * v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+    acc += v / fmaxf(sqrtf(n2), 1e-12f);
+  }
+  out[(size_t)p * NUM_OBJECTS + lane] = acc / (float)sel.n;
+}
+
+// Scatter of the mean's gradient back through each neighbour's normalisation: d/dv (v/|v|) = (g - u (u.g)) / |v|.
+__global__ void __launch_bounds__(256) smooth_feat_bwd_kernel(int P, int K, SmoothSel sel,
+                                                              const float* __restrict__ feat,
+                                                              const long long* __restrict__ idx,
+                                                              const float* __restrict__ g_out, float* __restrict__ g_feat) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= P) return;
+  const float g = g_out[(size_t)p * NUM_OBJECTS + lane] / (float)sel.n;
+  for (int k = 0; k < sel.n; k++) {
+    const long long j = __ldg(idx + (size_t)p * K + sel.col[k]);
+    const float v = __ldg(feat + (size_t)j * NUM_OBJECTS + lane);
+    float n2 = v * v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+    const float n = sqrtf(n2);
+    float gv;
+    if (n > 1e-12f) {
+      const float u = v / n;
+      float ug = u * g;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) ug += __shfl_xor_sync(0xffffffffu, ug, o);
+      gv = (g - u * ug) / n;
+    } else {
+      gv = g * 1e12f;                       // clamped branch of F.normalize
+    }
+    atomicAdd(g_feat + (size_t)j * NUM_OBJECTS + lane, gv);
+  }
+}
+
+static bool smooth_args_ok(const char* who, int P, int K, const int* sel_cols, int n_sel, const void* a, const void* b,
+                           const void* c, SmoothSel& sel) {
+  if (!a || !b || !c || !sel_cols || K <= 0 || n_sel <= 0 || n_sel > SMOOTH_MAX_SEL || K > 255) {
+    set_error("%s: bad arguments (K=%d, n_sel=%d; at most %d selected columns)", who, K, n_sel, SMOOTH_MAX_SEL);
+    return false;
+  }
+  sel.n = n_sel;
+  for (int i = 0; i < n_sel; i++) {
+    if (sel_cols[i] < 0 || sel_cols[i] >= K) { set_error("%s: selected column %d outside [0, %d)", who, sel_cols[i], K); return false; }
+    sel.col[i] = (unsigned char)sel_cols[i];
+  }
+  (void)P;
+  return true;
+}
+
 }  // namespace tb
 
 using namespace tb;
+
+extern "C" TRASE_API int trase_b200_smooth_features_forward(int P, int K, const int* sel_cols, int n_sel,
+                                                            const float* feat, const long long* knn_idx, float* out,
+                                                            void* stream) {
+  clear_error();
+  if (P <= 0) return 0;
+  SmoothSel sel;
+  if (!smooth_args_ok("trase_b200_smooth_features_forward", P, K, sel_cols, n_sel, feat, knn_idx, out, sel)) return 1;
+  smooth_feat_fwd_kernel<<<(int)(((size_t)P * 32 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, K, sel, feat, knn_idx, out);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_smooth_features_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+extern "C" TRASE_API int trase_b200_smooth_features_backward(int P, int K, const int* sel_cols, int n_sel,
+                                                             const float* feat, const long long* knn_idx,
+                                                             const float* g_out, float* g_feat, void* stream) {
+  clear_error();
+  if (P <= 0) return 0;
+  SmoothSel sel;
+  if (!g_out || !smooth_args_ok("trase_b200_smooth_features_backward", P, K, sel_cols, n_sel, feat, knn_idx, g_feat, sel)) {
+    if (!g_out) set_error("trase_b200_smooth_features_backward: null pointer");
+    return 1;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(g_feat, 0, (size_t)P * NUM_OBJECTS * 4, s);      // accumulated into below
+  if (e == cudaSuccess) {
+    smooth_feat_bwd_kernel<<<(int)(((size_t)P * 32 + 255) / 256), 256, 0, s>>>(P, K, sel, feat, knn_idx, g_out, g_feat);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) { set_error("trase_b200_smooth_features_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
 
 extern "C" TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const float* xyz, const float* d_xyz,
                                                      const float* scaling, const float* d_scaling,

@@ -25,7 +25,12 @@ import torch.distributed as dist
 
 
 class GradArena:
-    """Flat gradient buffer shared by a list of parameters."""
+    """Flat gradient buffer shared by a list of parameters.
+
+    Every `.grad` becomes a view into `flat`.  Parameters of an arena are marked so that the native DeformNetwork
+    backward may add weight/bias gradients straight into their slots instead of returning them to autograd; drive
+    such a network with `.backward()` (not torch.autograd.grad), and do not hang gradient hooks on those parameters
+    if the direct path is wanted (parameters with hooks are handled the ordinary way)."""
 
     def __init__(self, params: Iterable[torch.nn.Parameter], early: Iterable[torch.nn.Parameter] = ()):
         params = [p for p in params if p.requires_grad]
@@ -48,6 +53,9 @@ class GradArena:
         self.flat = torch.zeros(n, device=dev, dtype=dt)
         for p, off in zip(self.params, self.offsets):
             p.grad = self.flat[off:off + p.numel()].view_as(p)
+            # opt-in mark for kernels that can add a gradient straight into its arena slot (the native DeformNetwork
+            # backward, trase_b200/_deform_native.py DIRECT_GRAD_ACCUM): records WHICH buffer was agreed on
+            p._trase_arena_grad_ptr = p.grad.data_ptr()
         for p in first:
             p.register_post_accumulate_grad_hook(self._early_hook)
 

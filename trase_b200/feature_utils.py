@@ -67,3 +67,59 @@ def get_features_correspondence_matrix(rendered_features, sampled_pixel, out_hw=
     out_hw = tuple(sampled_pixel.shape[-2:]) if out_hw is None else out_hw
     f = sample_resized_features(rendered_features, out_hw, sampled_pixel, normalize=True)
     return f @ f.t()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# No-grad front end of the FEATURE state (utils/feature_utils.py:17-48): which pixels and masks take part in
+# this step's contrastive loss, the pixel-pair weights and the mask-correspondence matrix.  Plain torch on the
+# caller's device (the reference hard-codes .cuda(); these follow the masks' device and take an optional
+# generator so that tests are reproducible).
+
+@torch.no_grad()
+def get_sample_pixel_and_mask(sam_masks, num_sampled_pixels, num_sampled_masks, generator=None):
+    """utils/feature_utils.py:17-26: Bernoulli samples of the masks (rate num_sampled_masks / N) and of the pixels
+    (rate num_sampled_pixels / (H*W)); pixels that no mask covers are dropped."""
+    dev = sam_masks.device
+    n_masks, Hm, Wm = sam_masks.shape[0], sam_masks.shape[-2], sam_masks.shape[-1]
+    u_mask = torch.rand(n_masks, generator=generator, device=dev if generator is None else generator.device).to(dev)
+    u_pix = torch.rand(Hm, Wm, generator=generator, device=dev if generator is None else generator.device).to(dev)
+    sampled_mask = u_mask < num_sampled_masks / n_masks
+    covered = sam_masks.sum(dim=0) != 0
+    sampled_pixel = (u_pix < num_sampled_pixels / (Hm * Wm)) & covered
+    return sampled_pixel, sampled_mask
+
+
+@torch.no_grad()
+def get_pixel_weights(sam_masks, sampled_pixel):
+    """utils/feature_utils.py:28-38: pairs of pixels that lie in small masks weigh more.  Per pixel the mean area of
+    the masks covering it; per pair the product of the two; weight = max product / product clamped to >= 1, then
+    mapped affinely onto [1, 10]."""
+    area = sam_masks.sum(dim=(-2, -1))                                        # [n_masks]
+    cover = sam_masks.sum(dim=0)                                              # masks per pixel
+    mean_area = (sam_masks * area[:, None, None]).sum(dim=0) / (cover + 1e-9)
+    a = mean_area[sampled_pixel]                                              # [N]
+    prod = a[:, None] * a[None, :]
+    top = prod.max()
+    prod = torch.where(prod == 0, torch.full_like(prod, 1e10), prod)
+    w = (top / prod).clamp_min(1.0)
+    lo, hi = w.min(), w.max()
+    return (w - lo) / (hi - lo) * 9.0 + 1.0
+
+
+@torch.no_grad()
+def get_pixel_mask_correspondence_matrix(sam_masks, sampled_pixel, sampled_mask):
+    """utils/feature_utils.py:40-48: C[h, j] = 1 when sampled pixels h and j share at least one sampled mask."""
+    member = sam_masks[:, sampled_pixel][sampled_mask, :].float()             # [masks, N]
+    shared = member.t() @ member
+    return (shared != 0).to(shared.dtype)
+
+
+def build_feature_smooth_map(xyz, K=16):
+    """Index map of the K nearest Gaussians of every Gaussian (self included), [P, K] int64 — what
+    scene/gaussian_model.py:86-92 obtains from pytorch3d.ops.knn_points.  The kNN search itself is outside the
+    accelerated path; this helper uses scipy's k-d tree on the host so that callers without pytorch3d can still
+    fill `GaussianParams.feature_smooth_map`."""
+    from scipy.spatial import cKDTree
+    pts = xyz.detach().cpu().double().numpy()
+    _, idx = cKDTree(pts).query(pts, k=K)
+    return torch.from_numpy(idx.reshape(len(pts), K)).to(device=xyz.device, dtype=torch.int64)

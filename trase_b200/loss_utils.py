@@ -120,3 +120,49 @@ def feature_norm_reg(rendered_features, return_norm=False):
     """train.py:280-281: (1 - rendered_features.norm(dim=0, p=2).mean()) ** 2, one kernel per direction."""
     out2 = _FeatureNormReg.apply(rendered_features)
     return (out2[1], out2[0]) if return_norm else out2[1]
+
+
+# ---------------------------------------------------------------------------------------------------------
+# FEATURE-state contrastive losses in their default "soft" mining mode (utils/loss_utils.py:304-349) and the
+# style-transfer loop's nearest-neighbour feature loss (:223-228).  These sit outside the rasterizer path and
+# work on the N x N similarity matrix of the ~5000 sampled pixels: plain torch, written with masked sums so that
+# no boolean-index gather and no host synchronisation is needed (the reference syncs twice per loss).
+
+def _soft_mined_pair_loss(C, C_F, mined, same_mask, weights, per_pair):
+    """Shared form of the two losses.  `mined[i, j]`: pair (i, j) triggers mining; a column j is kept when any row
+    mined it; kept pairs are the strictly-upper-triangle entries of kept columns; the loss sums `per_pair` over
+    the kept pairs whose mask relation is `same_mask` and divides by the number of kept pairs."""
+    n = C_F.shape[0]
+    col_kept = mined.any(dim=0)                                               # [n]
+    upper = torch.ones(n, n, dtype=torch.bool, device=C_F.device).triu(1)     # i < j (the diagonal is excluded)
+    kept = upper & col_kept[None, :]
+    n_kept = kept.sum()
+    sel = kept & same_mask
+    # the weights are masked first (not the products): an unselected pair must not see its weight at all, in
+    # either direction — degenerate inputs give NaN weights (0/0 in the reference's min-max mapping)
+    w_sel = sel.to(per_pair.dtype) if weights is None else torch.where(sel, weights, torch.zeros_like(weights))
+    total = (w_sel * per_pair).sum()
+    # no selected pair: the reference returns the Python float 0.0 (and prints a warning)
+    return torch.where(sel.any(), total / n_kept.clamp_min(1).to(total.dtype), torch.zeros_like(total))
+
+
+def pixel_mask_correspondence_loss_soft_hard_positive(C, C_F, positive_th=0.75, weights=None, **_unused):
+    """utils/loss_utils.py:304-325: pull together pixel pairs of the same mask, mined by 'some same-mask pair in
+    this column is still below positive_th'."""
+    same = C == 1
+    return _soft_mined_pair_loss(C, C_F, (C_F < positive_th) & same, same, weights, -C_F)
+
+
+def pixel_mask_correspondence_loss_soft_negative(C, C_F, negative_th=0.5, weights=None, **_unused):
+    """utils/loss_utils.py:327-349: push apart pixel pairs of different masks (hinge at 0), mined by 'some
+    different-mask pair in this column is still above negative_th'."""
+    diff = C == 0
+    return _soft_mined_pair_loss(C, C_F, (C_F > negative_th) & diff, diff, weights, torch.relu(C_F))
+
+
+def loss_nnfm_style(feat1, feats2):
+    """utils/loss_utils.py:223-228: mean over the columns of feat1 [C, N1] of the cosine distance to the nearest
+    column of feats2 [C, N2]."""
+    a = feat1 / torch.linalg.norm(feat1, dim=0)
+    b = feats2 / torch.linalg.norm(feats2, dim=0)
+    return (1.0 - a.t() @ b).amin(dim=1).mean()

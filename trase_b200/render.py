@@ -37,6 +37,7 @@ class GaussianParams(torch.nn.Module):
         self._gaussian_features = P(gaussian_features)  # [P,1,32]
         self.active_sh_degree = active_sh_degree
         self.max_sh_degree = max_sh_degree
+        self.feature_smooth_map = None              # {"K": K, "m": [P,K] int64 neighbour map}, as in the reference
 
     @classmethod
     def from_activated(cls, scene: dict, device) -> "GaussianParams":
@@ -72,6 +73,34 @@ class GaussianParams(torch.nn.Module):
         return self._gaussian_features
 
 
+    def set_feature_smooth_map(self, knn_idx):
+        """Install a precomputed [P,K] nearest-neighbour index map (the reference fills the same cache from
+        pytorch3d.ops.knn_points on first use, scene/gaussian_model.py:85-92)."""
+        self.feature_smooth_map = {"K": int(knn_idx.shape[1]), "m": knn_idx.to(self._xyz.device, torch.int64)}
+
+    def get_smoothed_gaussian_features(self, K=16, dropout=0.5, select_point=None):
+        """scene/gaussian_model.py:79-104.  Same arguments and result; `select_point` (optional) fixes the neighbour
+        subset the reference draws with torch.randperm(K)[:int(K*dropout)], for reproducible tests.  The neighbour
+        map is taken from `feature_smooth_map` (set_feature_smooth_map) or built once with a host k-d tree; the
+        gather-normalise-mean runs as one CUDA kernel per direction on CUDA tensors."""
+        if K <= 1:
+            return self._gaussian_features
+        assert dropout < 0 or int(K * dropout) >= 1
+        if self.feature_smooth_map is None or self.feature_smooth_map["K"] != K:
+            from .feature_utils import build_feature_smooth_map
+            with torch.no_grad():
+                self.set_feature_smooth_map(build_feature_smooth_map(self.get_xyz, K))
+        m = self.feature_smooth_map["m"]
+        if select_point is None:
+            select_point = torch.randperm(K)[:int(K * dropout)] if 0 < dropout < 1 else torch.arange(K)
+        cols = [int(c) for c in select_point]
+        if self._gaussian_features.is_cuda and FUSED_GLUE:
+            from ._assemble import smooth_features
+            return smooth_features(self._gaussian_features, m, cols)
+        normed = torch.nn.functional.normalize(self._gaussian_features, dim=-1, p=2)
+        return normed[m[:, cols], 0, :].mean(dim=1).unsqueeze(1)
+
+
 def make_view(cam: dict, device) -> SimpleNamespace:
     """Camera object with the attributes `render()` reads (scene/cameras.py:27-79)."""
     return SimpleNamespace(FoVx=2 * math.atan(cam["tanfovx"]), FoVy=2 * math.atan(cam["tanfovy"]),
@@ -89,10 +118,9 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
            override_color=None, mask=None, norm_gaussian_features=True, is_smooth_gaussian_features=False,
            smooth_K=16):
     """gaussian_renderer/__init__.py:37-155.  Background tensor must be on the GPU."""
-    if is_6dof or is_smooth_gaussian_features or getattr(pipe, "convert_SHs_python", False) or \
-            getattr(pipe, "compute_cov3D_python", False):
-        raise NotImplementedError("6-DoF deformation, kNN-smoothed features and the *_python pipeline switches "
-                                  "are outside the accelerated path")
+    if is_6dof or getattr(pipe, "convert_SHs_python", False) or getattr(pipe, "compute_cov3D_python", False):
+        raise NotImplementedError("6-DoF deformation and the *_python pipeline switches are outside the "
+                                  "accelerated path")
     screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True) + 0
     try:
         screenspace_points.retain_grad()
@@ -112,9 +140,12 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
     if fused:
         # one fused kernel group instead of ~20 elementwise torch kernels (and as many in autograd)
         from ._assemble import assemble_inputs
+        # FEATURE state (train.py:274-275): the kNN-smoothed features take the place of the raw ones
+        feats = pc.get_smoothed_gaussian_features(K=smooth_K, dropout=0.5) if is_smooth_gaussian_features \
+            else pc._gaussian_features
         means3D, scales, rotations, opacity, shs, sh_objs = assemble_inputs(
             pc._xyz, d_xyz, pc._scaling, d_scaling, pc._rotation, d_rotation, pc._opacity, pc._features_dc,
-            pc._features_rest, pc._gaussian_features)
+            pc._features_rest, feats)
         colors_precomp = None
     else:
         means3D = pc.get_xyz + d_xyz
@@ -122,7 +153,8 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
         scales = pc.get_scaling + d_scaling
         rotations = pc.get_rotation + d_rotation
         shs, colors_precomp = (pc.get_features, None) if override_color is None else (None, override_color)
-        sh_objs = pc.get_gaussian_features
+        sh_objs = pc.get_smoothed_gaussian_features(K=smooth_K, dropout=0.5) if is_smooth_gaussian_features \
+            else pc.get_gaussian_features
         if norm_gaussian_features:
             sh_objs = sh_objs / (sh_objs.norm(dim=2, keepdim=True) + 1e-9)
     if mask is not None:
