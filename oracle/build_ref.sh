@@ -13,7 +13,7 @@
 # cuda_rasterizer/rasterizer_impl.h:27 uses std::uintptr_t without <cstdint>
 # (gcc 13).
 #
-# Result: oracle/_ref/diff_gaussian_rasterization/{__init__.py,_C.so}
+# Result: oracle/_ref/diff_gaussian_rasterization/{__init__.py,_C.so}, oracle/_ref/trase_ref/utils/*.py
 #   - _C.so exposes rasterize_gaussians / rasterize_gaussians_backward /
 #     mark_visible (ext.cpp:15-19)
 #   - __init__.py is the reference's own wrapper, installed (like
@@ -60,4 +60,14 @@ g++ -shared -o "$OUT/_C.so" "$OBJ"/*.o -L"$TORCH_LIB" -L/usr/local/cuda/lib64 \
     -lc10 -ltorch_cpu -ltorch -ltorch_python -lc10_cuda -ltorch_cuda -lcudart \
     -Wl,-rpath,"$TORCH_LIB"
 install -m 0644 "$REF/diff_gaussian_rasterization/__init__.py" "$OUT/__init__.py"
+# The reference's own Python for the pieces either side of the rasterizer that the reference arm of bench.py and the
+# golden-vector scripts drive: DeformNetwork (utils/time_utils.py + rigid_utils.py) and the FEATURE-state / style
+# losses (utils/loss_utils.py, utils/feature_utils.py).  Installed unmodified, as package `utils` under
+# oracle/_ref/trase_ref/ (oracle/ref_loader.py:load_utils puts that directory on sys.path).
+TOP="$(cd "$REF/../.." && pwd)"
+mkdir -p "$HERE/_ref/trase_ref/utils"
+: > "$HERE/_ref/trase_ref/utils/__init__.py"
+for f in time_utils.py rigid_utils.py loss_utils.py feature_utils.py; do
+  install -m 0644 "$TOP/utils/$f" "$HERE/_ref/trase_ref/utils/$f"
+done
 echo "build_ref: built $OUT/_C.so"

@@ -42,6 +42,49 @@ def load():
     return mod
 
 
+_utils = None
+
+
+def utils_available() -> bool:
+    return os.path.exists(os.path.join(REF_DIR, "trase_ref", "utils", "time_utils.py"))
+
+
+def load_utils():
+    """The reference's own `utils` package (time_utils.DeformNetwork, loss_utils, feature_utils), installed
+    unmodified by oracle/build_ref.sh.  loss_utils.py imports pytorch3d and torchvision at module level for helpers
+    this path never calls; neither ships in this image, so empty stand-in modules are registered for exactly those
+    imports.  Returns a namespace with .time_utils, .loss_utils, .feature_utils."""
+    global _utils
+    if _utils is not None:
+        return _utils
+    if not utils_available():
+        raise RuntimeError("oracle/_ref/trase_ref is not installed; run oracle/build_ref.sh where /root/reference exists")
+    import importlib
+    import types
+    for name in ("pytorch3d", "pytorch3d.ops", "torchvision", "torchvision.utils"):
+        if name not in sys.modules:
+            try:
+                importlib.import_module(name)
+            except Exception:
+                m = types.ModuleType(name)
+                m.save_image = None
+                sys.modules[name] = m
+    if not hasattr(sys.modules["pytorch3d"], "ops"):
+        sys.modules["pytorch3d"].ops = sys.modules["pytorch3d.ops"]
+    root = os.path.join(REF_DIR, "trase_ref")
+    if "utils" in sys.modules and not getattr(sys.modules["utils"], "__file__", "").startswith(root):
+        raise RuntimeError("another top-level `utils` package is already imported")
+    sys.path.insert(0, root)
+    try:
+        ns = types.SimpleNamespace(time_utils=importlib.import_module("utils.time_utils"),
+                                   loss_utils=importlib.import_module("utils.loss_utils"),
+                                   feature_utils=importlib.import_module("utils.feature_utils"))
+    finally:
+        sys.path.remove(root)
+    _utils = ns
+    return ns
+
+
 def _align(x: int, a: int = 128) -> int:
     return (x + a - 1) // a * a
 

@@ -1,0 +1,149 @@
+"""GPU, 2 ranks over NCCL: the parity definition of the view-parallel path (SURVEY.md §8e, §4 last row).
+
+    gradient arena after GradArena.all_reduce()  ==  sum over the V views of the SINGLE-GPU backward
+                                                     through the compiled reference rasterizer (oracle/_ref)
+
+One view per rank, real NCCL all-reduce (the early segment overlapped under the MLP backward exactly as bench.py
+runs it), checked on rank 0 at <= 1e-3 for every per-Gaussian parameter; the DeformNetwork's own gradients (outside
+the rasterizer's parity boundary: TF32 products) are checked against the sum of the same native backward run view by
+view on one GPU.  `reduce_densification_stats` is checked the same way.  Skips below 2 GPUs.
+"""
+import os
+import socket
+import tempfile
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+P, W, H, SEED = 40_000, 320, 240, 21
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _setup(device, backend):
+    from trase_b200 import synth
+    from trase_b200.deform import DeformNetwork
+    from trase_b200.render import GaussianParams
+    sc = synth.make_scene(P, W, H, SEED)
+    pc = GaussianParams.from_activated(sc, device)
+    torch.manual_seed(1234)
+    net = DeformNetwork(backend=backend).to(device)
+    with torch.no_grad():
+        for head in (net.gaussian_warp, net.gaussian_rotation, net.gaussian_scaling):
+            head.weight.mul_(1e-2)
+            head.bias.mul_(1e-2)
+    return sc, pc, net
+
+
+def _view(v, device):
+    from trase_b200 import synth
+    from trase_b200.render import make_view
+    cam = synth.make_camera(W, H, synth.orbit_world_view(0.05 * v, -0.03 * v) if v else None)
+    up = synth.make_upstream_grads(W, H, SEED + v)
+    t = torch.full((P, 1), 0.3 + 0.2 * v, device=device)
+    return make_view(cam, device), t, up["dL_dcolor"].to(device), up["dL_dobjects"].to(device)
+
+
+def _backward_one_view(pc, net, v, device, rasterizer_cls=None, deltas=None):
+    """fwd+bwd of view v into whatever .grad the parameters have; returns the render package."""
+    from trase_b200 import render as R
+    view, t, gc, go = _view(v, device)
+    d = net(pc.get_xyz.detach(), t) if deltas is None else deltas
+    saved = R.GaussianRasterizer, R.GaussianRasterizationSettings, R.FUSED_GLUE
+    if rasterizer_cls is not None:
+        R.GaussianRasterizer, R.GaussianRasterizationSettings = rasterizer_cls
+        R.FUSED_GLUE = False
+    try:
+        out = R.render(view, pc, R.PIPE_DEFAULT, torch.zeros(3, device=device), d[0], d[1], d[2])
+    finally:
+        R.GaussianRasterizer, R.GaussianRasterizationSettings, R.FUSED_GLUE = saved
+    torch.autograd.backward([out["render"], out["render_gaussian_features"]], [gc, go])
+    return out
+
+
+def _worker(rank, world, port, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    device = torch.device("cuda", rank)
+    torch.cuda.set_device(device)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+    try:
+        from trase_b200.distributed import GradArena, reduce_densification_stats
+        from trase_b200.optim import add_densification_stats
+        sc, pc, net = _setup(device, "native")
+        params = list(pc.parameters()) + list(net.parameters())
+        arena = GradArena(params, early=list(pc.parameters()))
+        arena.zero()
+        arena.arm()
+        out = _backward_one_view(pc, net, rank, device)
+        assert arena._work is not None, "the early segment's all-reduce was not started under the MLP backward"
+        arena.all_reduce()
+        # densification statistics of this rank's view, then the cross-rank reduction
+        accum = torch.zeros(P, 1, device=device)
+        denom = torch.zeros(P, 1, device=device)
+        max_r = torch.zeros(P, dtype=torch.int32, device=device)
+        vis = out["visibility_filter"]
+        add_densification_stats(accum, denom, out["viewspace_points"], vis)
+        max_r[vis] = torch.max(max_r[vis], out["radii"][vis])
+        mine = (accum.clone(), denom.clone(), max_r.clone())
+        reduce_densification_stats(accum, denom, max_r)
+        gathered = [[torch.empty_like(t) for _ in range(world)] for t in mine]
+        for lst, t in zip(gathered, mine):
+            dist.all_gather(lst, t)
+        torch.cuda.synchronize(device)
+        if rank == 0:
+            assert torch.allclose(accum, sum(gathered[0]), rtol=1e-6, atol=0)
+            assert torch.equal(denom, sum(gathered[1]))
+            assert torch.equal(max_r, torch.stack(gathered[2]).max(0).values)
+            torch.save({"names": [n for n, _ in pc.named_parameters()] + ["mlp." + n for n, _ in net.named_parameters()],
+                        "grads": [arena.view_of(p).detach().cpu() for p in params]}, out_path)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_allreduced_arena_equals_sum_of_reference_single_gpu_backwards(native_lib):
+    from oracle import ref_loader
+    if not ref_loader.available():
+        pytest.skip("oracle/_ref not built")
+    world = 2
+    with tempfile.TemporaryDirectory() as d:
+        out_path = os.path.join(d, "arena.pt")
+        mp.spawn(_worker, args=(world, _free_port(), out_path), nprocs=world, join=True)
+        got = torch.load(out_path)
+    device = torch.device("cuda:0")
+    ref = ref_loader.load()
+    cls = (ref.GaussianRasterizer, ref.GaussianRasterizationSettings)
+    # (1) per-Gaussian parameters: sum over views of the reference rasterizer's backward (its own torch glue), fed
+    # with the same deformation the ranks used
+    sc, pc, net = _setup(device, "native")
+    for v in range(world):
+        with torch.no_grad():
+            deltas = net(pc.get_xyz.detach(), _view(v, device)[1])
+        _backward_one_view(pc, net, v, device, rasterizer_cls=cls, deltas=[x.clone() for x in deltas])
+    want = {n: p.grad.detach().cpu() for n, p in pc.named_parameters()}
+    # (2) DeformNetwork parameters: sum over views of the single-GPU native backward
+    sc2, pc2, net2 = _setup(device, "native")
+    for v in range(world):
+        _backward_one_view(pc2, net2, v, device)
+    want.update({"mlp." + n: p.grad.detach().cpu() for n, p in net2.named_parameters()})
+    report = []
+    for name, g in zip(got["names"], got["grads"]):
+        w = want[name]
+        err = float((g.double() - w.double()).abs().max() / max(float(w.double().abs().max()), 1e-30))
+        report.append((name, err))
+    print("all-reduced arena vs sum of single-GPU backwards (max-norm relative error):")
+    for name, err in report:
+        print("  %-28s %.2e" % (name, err))
+    for name, err in report:
+        assert err <= 1e-3, (name, err)

@@ -39,6 +39,46 @@ def _direct_ok(p, dev) -> bool:
             not getattr(p, "_post_accumulate_grad_hooks", None) and not getattr(p, "_backward_hooks", None))
 
 
+# ---- optional per-stage timing (bench.py's `stages`): CUDA event pairs on the launching stream around the forward
+# kernel, the backward data-gradient chain and the weight-gradient launches; off by default
+_prof_on = False
+_prof_live = []          # (stage, start_event, end_event)
+
+
+def profile_enable(on: bool) -> None:
+    global _prof_on
+    _prof_on = bool(on)
+
+
+class _Span:
+    def __init__(self, stage):
+        self.stage = stage
+
+    def __enter__(self):
+        if _prof_on:
+            self.a = torch.cuda.Event(enable_timing=True)
+            self.a.record()
+        return self
+
+    def __exit__(self, *exc):
+        if _prof_on:
+            b = torch.cuda.Event(enable_timing=True)
+            b.record()
+            _prof_live.append((self.stage, self.a, b))
+        return False
+
+
+def profile_read() -> dict:
+    """{stage: (total ms, spans)} for mlp_fwd / mlp_bwd_chain / mlp_wgrad since the last read."""
+    out = {}
+    for stage, a, b in _prof_live:
+        b.synchronize()
+        tot, cnt = out.get(stage, (0.0, 0))
+        out[stage] = (tot + a.elapsed_time(b), cnt + 1)
+    _prof_live.clear()
+    return out
+
+
 def tf32_round(w: torch.Tensor) -> torch.Tensor:
     """Round-to-nearest to TF32 (10 mantissa bits), like cvt.rna.tf32.f32."""
     return ((w.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
@@ -140,15 +180,17 @@ class _DeformMLP(torch.autograd.Function):
                 ball = torch.cat([b.detach().reshape(-1) for b in bs] + [bh])
                 if not keep:
                     # inference (torch.no_grad / frozen network): no activations or masks leave the chip
-                    _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
-                                                                wpack.data_ptr(), ball.data_ptr(), None, None,
-                                                                out16.data_ptr(), s))
+                    with _Span("mlp_fwd"):
+                        _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
+                                                                    wpack.data_ptr(), ball.data_ptr(), None, None,
+                                                                    out16.data_ptr(), s))
                     return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
                 masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
                 acts_all = torch.empty((nl, M, W), **f32)
-                _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
-                                                            wpack.data_ptr(), ball.data_ptr(), acts_all.data_ptr(),
-                                                            masks.data_ptr(), out16.data_ptr(), s))
+                with _Span("mlp_fwd"):
+                    _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
+                                                                wpack.data_ptr(), ball.data_ptr(), acts_all.data_ptr(),
+                                                                masks.data_ptr(), out16.data_ptr(), s))
                 acts = list(acts_all.unbind(0))
                 skipbuf = emb
             else:
@@ -214,7 +256,8 @@ class _DeformMLP(torch.autograd.Function):
             _lib.check(lib.trase_b200_mlp_pack_dout(M, *[None if g is None else g.data_ptr() for g in gs],
                                                     dout.data_ptr(), dbh.data_ptr(), s))
             # heads: dWh^T = h_last^T dout
-            _wgrad(lib, acts[-1], dout, dwhT)
+            with _Span("mlp_wgrad"):
+                _wgrad(lib, acts[-1], dout, dwhT)
             if fused_bwd:
                 # the whole data-gradient chain in one persistent kernel (csrc/mlp_fused.cu): dzs[L] = dZ of
                 # layer nl-1-L, bias gradients straight into their targets
@@ -223,12 +266,15 @@ class _DeformMLP(torch.autograd.Function):
                 _lib.check(lib.trase_b200_mlp_pack_fused_bwd(nl, skip, E, whT.data_ptr(), wptrs, wpack_b.data_ptr(), s))
                 dzs = torch.empty((nl, M, W), **f32)
                 bptrs = (ctypes.c_void_p * nl)(*[g.data_ptr() for g in grads_b])
-                _lib.check(lib.trase_b200_mlp_backward_fused(M, nl, dout.data_ptr(), wpack_b.data_ptr(),
-                                                             masks.data_ptr(), dzs.data_ptr(), bptrs, s))
+                with _Span("mlp_bwd_chain"):
+                    _lib.check(lib.trase_b200_mlp_backward_fused(M, nl, dout.data_ptr(), wpack_b.data_ptr(),
+                                                                 masks.data_ptr(), dzs.data_ptr(), bptrs, s))
             else:
                 # dZ_{nl-1} = (dout Wh) * relu'(h_last); its column sums are the bias gradient of layer nl-1
                 dz = torch.empty((M, W), **f32)
                 _gemm(lib, dout, whT, dz, mask_in=masks[nl - 1], colsum=grads_b[nl - 1])
+            span = _Span("mlp_wgrad" if fused_bwd else "mlp_bwd_unfused")   # fused chain: this loop is wgrad only
+            span.__enter__()
             for i in range(nl - 1, -1, -1):
                 if fused_bwd:
                     dz = dzs[nl - 1 - i]
@@ -243,6 +289,7 @@ class _DeformMLP(torch.autograd.Function):
                     dz_prev = torch.empty((M, W), **f32)
                     _gemm(lib, dz, WrT[i], dz_prev, mask_in=masks[i - 1], colsum=grads_b[i - 1])
                     dz = dz_prev
+            span.__exit__()
             dwh = dwhT.t()
             out = [None, None, None, None, None, None]
             for i in range(nl):

@@ -47,6 +47,19 @@ def make_camera(W: int, H: int, world_view: torch.Tensor | None = None) -> Dict[
                 projmatrix=full.contiguous(), campos=campos, focal=f)
 
 
+def orbit_world_view(yaw, pitch, centre=(0.0, 0.0, 4.75)):
+    """World->view in the row-vector convention: the camera orbits the scene centre by (yaw, pitch) radians."""
+    cy, sy, cp, sp = math.cos(yaw), math.sin(yaw), math.cos(pitch), math.sin(pitch)
+    Ry = torch.tensor([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rx = torch.tensor([[1, 0, 0], [0, cp, -sp], [0, sp, cp]])
+    Rm = (Rx @ Ry).float()
+    c = torch.tensor(centre)
+    wv = torch.eye(4)
+    wv[:3, :3] = Rm.T
+    wv[3, :3] = c - c @ Rm.T
+    return wv
+
+
 def make_scene(P: int, W: int, H: int, seed: int = 1, sh_degree: int = 3, target_radius_px: float = 10.0
                ) -> Dict[str, object]:
     g = torch.Generator().manual_seed(seed)
