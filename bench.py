@@ -370,7 +370,8 @@ class Workload:
             sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks,
                                                   generator=self.sample_gen)
             C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
-            out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16)
+            out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16,
+                              want_viewspace_grad=False)   # past densify_until_iter nobody reads viewspace_points.grad
             feats = out["render_gaussian_features"]
             reg = LU.feature_norm_reg(feats)
             C_F = FU.get_features_correspondence_matrix(feats, sp)        # bilinear resize folded into the gather
@@ -384,7 +385,8 @@ class Workload:
         FU, LU = ru.feature_utils, ru.loss_utils
         sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks)
         C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
-        out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16)
+        out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16,
+                              want_viewspace_grad=False)   # past densify_until_iter nobody reads viewspace_points.grad
         feats = out["render_gaussian_features"]
         reg = (1 - feats.norm(dim=0, p=2).mean()) ** 2
         resized = torch.nn.functional.interpolate(feats.unsqueeze(0), masks.shape[-2:], mode="bilinear").squeeze(0)

@@ -160,6 +160,18 @@ TRASE_API int trase_b200_rasterize_forward_rebin(const trase_b200_fwd_args* args
  * All dL_* outputs must be zero-filled by the caller (the reference does the
  * same with torch::zeros, DGR/rasterize_points.cu:165-174); dL_dconic [P][4]
  * is the internal float4 the reference keeps (DGR/cuda_rasterizer/backward.cu:566-568).
+ *
+ * Partial gradients (the reference always computes all of them): a NULL output
+ * pointer means "not wanted", and the kernels skip the work behind it.
+ *  - dL_dobjects == NULL: the per-Gaussian feature gradient is not accumulated
+ *    (the feature parameter is frozen in TRASE's GAUSSIAN training state,
+ *    scene/gaussian_model.py:303-315).
+ *  - all other dL_d* outputs NULL, dL_dobjects set: feature gradient only (the
+ *    FEATURE state, where nothing else trains): no dL/dalpha chain, no preprocess
+ *    backward.  The others must be given or omitted together.
+ *  - dL_dout_objects == NULL / dL_dout_color == NULL: that upstream gradient is
+ *    zero (the loss did not read that image).  dL_dout_color is required when the
+ *    geometry group is wanted, dL_dout_objects when only dL_dobjects is.
  * ---------------------------------------------------------------------- */
 typedef struct trase_b200_bwd_args {
   int P, sh_degree, M, W, H;

@@ -301,6 +301,84 @@ def test_runs_on_a_side_stream(native_lib):
     assert torch.equal(base.color, side.color)
 
 
+# ------------------------------------------------ partial gradients ----------
+@pytest.mark.parametrize("ppt", [1, 2])
+def test_partial_gradient_variants_equal_the_full_backward(native_lib, ppt):
+    """The backward computes only what the caller will read (NULL output pointer = not wanted).  Every variant must
+    return, for the gradients it does compute, what the full backward returns: without the feature gradient
+    (GAUSSIAN state, frozen feature parameter), the feature gradient alone (FEATURE state), and with an absent
+    (= zero) upstream feature gradient (a loss on the colour image only)."""
+    from trase_b200 import synth, _raster, _lib
+    P, W, H = 30000, 200, 152
+    sc = synth.make_scene(P, W, H, 31)
+    up = {k: v.to(DEV) for k, v in synth.make_upstream_grads(W, H, 31).items()}
+    a = scene_args(sc, 0.5, DEV)
+    _lib.set_tuning("bwd_ppt", ppt)
+    try:
+        res = cuda_forward(a)
+
+        def bwd(dcol, dobj, **kw):
+            out = _raster.rasterize_backward(a["bg"], a["means3D"], res.radii, a["colors_precomp"], a["scales"],
+                                             a["rotations"], 1.0, a["cov3D_precomp"], a["viewmatrix"], a["projmatrix"],
+                                             a["tanfovx"], a["tanfovy"], dcol, a["sh"], dobj, a["sh_objs"], a["degree"],
+                                             a["campos"], res.geom, res.num_rendered, res.binning, res.img, False,
+                                             capacity=res.capacity, **kw)
+            return dict(zip(GRAD_NAMES, out))
+
+        full = bwd(up["dL_dcolor"], up["dL_dobjects"])
+        no_df = bwd(up["dL_dcolor"], up["dL_dobjects"], need_features=False)
+        df_only = bwd(None, up["dL_dobjects"], need_geom=False)
+        zero_obj = bwd(up["dL_dcolor"], torch.zeros_like(up["dL_dobjects"]))
+        col_only = bwd(up["dL_dcolor"], None, need_features=False)
+    finally:
+        _lib.set_tuning("bwd_ppt", 2)
+    assert no_df["objects"] is None and all(df_only[k] is None for k in GRAD_NAMES if k != "objects")
+    for k in GRAD_NAMES:
+        if k != "objects":
+            assert rel_err(_np(full[k]), _np(no_df[k])) <= 1e-5, k        # same arithmetic, other atomic order
+            assert rel_err(_np(zero_obj[k]), _np(col_only[k])) <= 1e-5, k
+    assert rel_err(_np(full["objects"]), _np(df_only["objects"])) <= 1e-5
+    assert float(full["objects"].abs().max()) > 0
+
+
+def test_autograd_skips_what_nobody_needs(native_lib):
+    """Through the public API: with only sh_objs requiring grad (FEATURE state) or only the others (GAUSSIAN state,
+    frozen features), the gradients that are produced equal those of a run where everything requires grad."""
+    from trase_b200 import synth
+    from trase_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    P, W, H = 12000, 120, 96
+    sc = synth.scene_to(synth.make_scene(P, W, H, 33), DEV)
+    up = {k: v.to(DEV) for k, v in synth.make_upstream_grads(W, H, 33).items()}
+    st = synth.settings_from(sc, torch.zeros(3, device=DEV), GaussianRasterizationSettings)
+    names = ("means3D", "shs", "sh_objs", "opacities", "scales", "rotations")
+
+    def run(train, use_color=True, use_objects=True):
+        leaves = {k: sc[k].clone().requires_grad_(k in train) for k in names}
+        color, radii, objects, depth = GaussianRasterizer(st)(
+            means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"]), opacities=leaves["opacities"],
+            shs=leaves["shs"], sh_objs=leaves["sh_objs"], scales=leaves["scales"], rotations=leaves["rotations"])
+        outs, gs = [], []
+        if use_color:
+            outs.append(color); gs.append(up["dL_dcolor"])
+        if use_objects:
+            outs.append(objects); gs.append(up["dL_dobjects"])
+        torch.autograd.backward(outs, gs)
+        return {k: v.grad for k, v in leaves.items()}
+
+    everything = run(names)
+    feature_state = run(("sh_objs",), use_color=False)
+    gaussian_state = run([n for n in names if n != "sh_objs"])
+    colour_loss = run([n for n in names if n != "sh_objs"], use_objects=False)
+    colour_ref = run(names, use_objects=False)
+    assert all(feature_state[k] is None for k in names if k != "sh_objs") and gaussian_state["sh_objs"] is None
+    everything_obj_only = run(names, use_color=False)
+    assert rel_err(_np(everything_obj_only["sh_objs"]), _np(feature_state["sh_objs"])) <= 1e-5
+    for k in names:
+        if k != "sh_objs":
+            assert rel_err(_np(everything[k]), _np(gaussian_state[k])) <= 1e-5, k
+            assert rel_err(_np(colour_ref[k]), _np(colour_loss[k])) <= 1e-5, k
+
+
 # ------------------------------------------ fused activation / assembly -----
 def test_fused_assembly_matches_torch_glue(native_lib):
     """render() with the fused assembly kernels == render() with the reference's torch glue, outputs and

@@ -61,6 +61,13 @@ class _Assemble(torch.autograd.Function):
         ctx.save_for_backward(ins[2], ins[4], ins[6], ins[9])
         ctx.Mrest = Mrest
         ctx.sh_aliased = block is not None
+        # an output whose sources are all frozen is not differentiable: the rasterizer then knows (needs_input_grad)
+        # that nobody wants that gradient and skips the work behind it (FEATURE state: everything but sh_objs)
+        n = ctx.needs_input_grad
+        frozen = [t for t, live in ((means3D, n[0] or n[1]), (scales, n[2] or n[3]), (rotations, n[4] or n[5]),
+                                    (opac, n[6]), (shs, n[7] or n[8]), (sh_objs, n[9])) if not live]
+        if frozen:
+            ctx.mark_non_differentiable(*frozen)
         return means3D, scales, rotations, opac, shs, sh_objs
 
     @staticmethod

@@ -173,13 +173,26 @@ def _readback_event(dev, stream):
 
 def rasterize_backward(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3D_precomp,
                        viewmatrix, projmatrix, tanfovx, tanfovy, dL_dout_color, sh, dL_dout_objects, sh_objs,
-                       degree, campos, geom, R, binning, img, debug, capacity=None):
+                       degree, campos, geom, R, binning, img, debug, capacity=None, need_geom=True,
+                       need_features=True):
     """Same argument order as `_C.rasterize_gaussians_backward` (DGR/ext.cpp:17);
-    returns the same 9 gradients (DGR/rasterize_points.cu:213)."""
+    returns the same 9 gradients (DGR/rasterize_points.cu:213).
+
+    need_geom / need_features say which of them anyone will read (autograd's needs_input_grad): with
+    need_features=False the feature gradient slot is None, with need_geom=False the eight others are None and only
+    the feature gradient is computed (no dL/dalpha chain, no preprocess backward).  dL_dout_objects (or, for the
+    feature-only case, dL_dout_color) may be None = an all-zero upstream gradient."""
     lib = _lib.load()
     dev = means3D.device
     P = int(means3D.shape[0])
-    H, W = int(dL_dout_color.shape[1]), int(dL_dout_color.shape[2])
+    if not need_geom and not need_features:
+        return (None,) * 9
+    some = dL_dout_color if dL_dout_color is not None else dL_dout_objects
+    H, W = int(some.shape[1]), int(some.shape[2])
+    if need_geom and dL_dout_color is None:
+        dL_dout_color = torch.zeros((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+    if not need_geom and dL_dout_objects is None:          # feature gradient of a loss that never read the features
+        return (None, None, torch.zeros((P, NUM_OBJECTS), dtype=torch.float32, device=dev)) + (None,) * 6
     with torch.cuda.device(dev):
         means3D = _f32c(means3D, dev)
         bg = _f32c(bg, dev); viewmatrix = _f32c(viewmatrix, dev); projmatrix = _f32c(projmatrix, dev)
@@ -190,14 +203,16 @@ def rasterize_backward(bg, means3D, radii, colors_precomp, scales, rotations, sc
         cov3D_precomp = _f32c(cov3D_precomp, dev) if cov3D_precomp.numel() else cov3D_precomp
         sh = _f32c(sh, dev) if sh.numel() else sh
         sh_objs = _f32c(sh_objs, dev) if sh_objs.numel() else sh_objs
-        dL_dout_color = _f32c(dL_dout_color, dev)
-        dL_dout_objects = _f32c(dL_dout_objects, dev)
+        dL_dout_color = _f32c(dL_dout_color, dev) if dL_dout_color is not None else None
+        dL_dout_objects = _f32c(dL_dout_objects, dev) if dL_dout_objects is not None else None
         M = int(sh.shape[1]) if sh.numel() != 0 else 0
 
         # all gradient buffers carved out of ONE zero-filled allocation (one memset instead of ten);
         # every sub-buffer starts on a 256-byte boundary (the compositing kernel adds float4s)
         shapes = [(P, 3), (P, 3), (P, NUM_CHANNELS), (P, NUM_OBJECTS), (P, 2, 2), (P, 1), (P, 6), (P, M, 3), (P, 3),
                   (P, 4)]
+        wanted = [need_geom, need_geom, need_geom, need_features] + [need_geom] * 6
+        shapes = [shp if w else (0,) for shp, w in zip(shapes, wanted)]     # unwanted gradients take no memory
         offs, n = [], 0
         for shp in shapes:
             offs.append(n)
@@ -221,15 +236,18 @@ def rasterize_backward(bg, means3D, radii, colors_precomp, scales, rotations, sc
             a.viewmatrix, a.projmatrix, a.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
             a.radii = _ptr(radii)
             a.geom, a.img, a.binning, a.capacity = _ptr(geom), _ptr(img), _ptr(binning), int(capacity)
-            a.dL_dout_color, a.dL_dout_objects = _ptr(dL_dout_color), _ptr(dL_dout_objects)
+            a.dL_dout_color = _ptr(dL_dout_color) if need_geom else None
+            a.dL_dout_objects = _ptr(dL_dout_objects)
             a.dL_dmeans2D, a.dL_dconic, a.dL_dopacity = _ptr(dL_dmeans2D), _ptr(dL_dconic), _ptr(dL_dopacity)
             a.dL_dcolors, a.dL_dobjects, a.dL_dmeans3D = _ptr(dL_dcolors), _ptr(dL_dobjects), _ptr(dL_dmeans3D)
             a.dL_dcov3D, a.dL_dsh = _ptr(dL_dcov3D), _ptr(dL_dsh)
             a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
             a.stream = torch.cuda.current_stream(dev).cuda_stream
             _lib.check(lib.trase_b200_rasterize_backward(C.byref(a)))
-        return (dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
-                dL_drotations)
+        out = (dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+               dL_drotations)
+        keep = [need_geom, need_geom, need_features] + [need_geom] * 6
+        return tuple(g if k else None for g, k in zip(out, keep))
 
 
 def mark_visible(means3D, viewmatrix, projmatrix) -> torch.Tensor:

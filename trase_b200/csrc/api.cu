@@ -249,19 +249,34 @@ static int backward_impl(const trase_b200_bwd_args* a, int stages) {
   if (a->P < 0 || a->W <= 0 || a->H <= 0) { set_error("trase_b200: bad sizes"); return 1; }
   if (a->P == 0) return 0;
   if (!a->means3D || !a->background || !a->viewmatrix || !a->projmatrix || !a->campos || !a->radii || !a->geom ||
-      !a->img || !a->sh_objs || !a->dL_dout_color || !a->dL_dout_objects) {
+      !a->img || !a->sh_objs) {
     set_error("trase_b200: backward is missing a required input");
     return 1;
   }
-  if (!a->dL_dmeans2D || !a->dL_dconic || !a->dL_dopacity || !a->dL_dcolors || !a->dL_dobjects || !a->dL_dmeans3D ||
-      !a->dL_dcov3D) {
-    set_error("trase_b200: backward is missing a required gradient buffer");
+  // Which gradients are wanted: either the whole geometry/colour group (NULL for none of them), and/or dL_dobjects.
+  const bool any_geom = a->dL_dmeans2D || a->dL_dconic || a->dL_dopacity || a->dL_dcolors || a->dL_dmeans3D ||
+                        a->dL_dcov3D || a->dL_dsh || a->dL_dscales || a->dL_drotations;
+  const bool want_geom = a->dL_dmeans2D && a->dL_dconic && a->dL_dopacity && a->dL_dcolors && a->dL_dmeans3D && a->dL_dcov3D;
+  if (any_geom && !want_geom) {
+    set_error("trase_b200: backward needs dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D and dL_dcov3D "
+              "together (pass NULL for all gradient buffers except dL_dobjects to get the feature gradient only)");
     return 1;
   }
-  if (a->shs && !a->colors_precomp && !a->dL_dsh) { set_error("trase_b200: dL_dsh required when SHs are used"); return 1; }
-  if (a->scales && (!a->rotations || !a->dL_dscales || !a->dL_drotations)) {
-    set_error("trase_b200: rotations/dL_dscales/dL_drotations required with scales");
+  if (!want_geom && !a->dL_dobjects) { set_error("trase_b200: backward was asked for no gradient at all"); return 1; }
+  if (want_geom && !a->dL_dout_color) {
+    set_error("trase_b200: dL_dout_color is required when geometry/colour gradients are wanted");
     return 1;
+  }
+  if (!want_geom && !a->dL_dout_objects) {
+    set_error("trase_b200: dL_dout_objects is required when only the feature gradient is wanted");
+    return 1;
+  }
+  if (want_geom) {
+    if (a->shs && !a->colors_precomp && !a->dL_dsh) { set_error("trase_b200: dL_dsh required when SHs are used"); return 1; }
+    if (a->scales && (!a->rotations || !a->dL_dscales || !a->dL_drotations)) {
+      set_error("trase_b200: rotations/dL_dscales/dL_drotations required with scales");
+      return 1;
+    }
   }
   if (a->capacity > 0 && !a->binning) { set_error("trase_b200: binning workspace missing"); return 1; }
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(a->stream);
@@ -269,6 +284,7 @@ static int backward_impl(const trase_b200_bwd_args* a, int stages) {
   FwdPointers p = carve(const_cast<void*>(a->geom), a->P, const_cast<void*>(a->img), a->W, a->H,
                         const_cast<void*>(a->binning), a->capacity, nullptr);
   if (stages & 1) TB_STEP_ST(ST_RENDER_BWD, "render_backward", launch_render_backward(*a, p, stream));
+  if (!want_geom) stages &= 1;                    // feature gradient only: nothing flows into the per-Gaussian geometry
   if (stages & 2) TB_STEP_ST(ST_PREPROCESS_BWD, "preprocess_backward", launch_preprocess_backward(*a, p, stream));
   count_launches(((stages & 1) ? 1 : 0) + ((stages & 2) ? 1 : 0));
   return 0;

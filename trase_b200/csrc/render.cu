@@ -401,14 +401,27 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
   return v[0];
 }
 
-template <int PPT>
+// Which gradients the caller wants decides how much of the per-pair work exists at all (the reference always does
+// all of it, backward.cu:392-574):
+//   GEOM   : gradients of colour, opacity, 2D mean and conic (everything that needs dL/dalpha: the dot products with
+//            the upstream gradient, the scalar recursion, the nine scalar reductions);
+//   DF     : gradient of the per-Gaussian feature row, dF[j][c] += w * dL/dO[p][c] (32 FMAs per pair and the
+//            32-channel cross-lane reduction) — not wanted while the feature parameter is frozen (GAUSSIAN state);
+//   OBJ_UP : an upstream gradient of the feature image exists (false: the loss read the colour image only, the 32
+//            feature channels drop out of dL/dalpha and the feature rows are not even staged).
+// FEATURE state (only the feature parameter trains) is GEOM = false: alpha and T are recomputed and dF accumulated,
+// nothing else.  Every variant evaluates alpha and T with the same pinned sequence, so which pairs blend never
+// depends on the variant.
+template <int PPT, bool GEOM, bool DF, bool OBJ_UP>
 __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel(const RenderBwdParams q) {
   constexpr int NT = 256 / PPT;
+  constexpr bool NEED_FEAT = GEOM && OBJ_UP;        // feature rows are only read for dL/dalpha
+  constexpr bool NEED_DLO = DF || NEED_FEAT;        // upstream feature gradient planes
   __shared__ uint32_t s_id[BWD_BATCH];
   __shared__ float2 s_xy[BWD_BATCH];
   __shared__ float4 s_co[BWD_BATCH];
-  __shared__ float4 s_rgbd[BWD_BATCH];
-  __shared__ float4 s_feat[BWD_BATCH * 8];
+  __shared__ float4 s_rgbd[GEOM ? BWD_BATCH : 1];
+  __shared__ float4 s_feat[NEED_FEAT ? BWD_BATCH * 8 : 1];
   __shared__ float3 s_reach[BWD_BATCH];
   __shared__ uint32_t s_max[NT / 32];
 
@@ -441,12 +454,13 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
     my_max = max(my_max, last[p]);
     S[p] = 0.f; last_alpha[p] = 0.f; last_dot[p] = 0.f;
 #pragma unroll
-    for (int c = 0; c < 3; c++) dLc[p][c] = inside ? q.dL_dpix[c * HW + pix] : 0.f;
+    for (int c = 0; c < 3; c++) dLc[p][c] = (GEOM && inside) ? q.dL_dpix[c * HW + pix] : 0.f;
 #pragma unroll
     for (int ch = 0; ch < NUM_OBJECTS / 2; ch++)
-      dLo[p][ch] = inside ? make_float2(q.dL_dpix_obj[(2 * ch) * HW + pix], q.dL_dpix_obj[(2 * ch + 1) * HW + pix])
-                          : make_float2(0.f, 0.f);
-    bg_dot[p] = q.bg[0] * dLc[p][0] + q.bg[1] * dLc[p][1] + q.bg[2] * dLc[p][2];
+      dLo[p][ch] = (NEED_DLO && inside)
+                       ? make_float2(q.dL_dpix_obj[(2 * ch) * HW + pix], q.dL_dpix_obj[(2 * ch + 1) * HW + pix])
+                       : make_float2(0.f, 0.f);
+    bg_dot[p] = GEOM ? q.bg[0] * dLc[p][0] + q.bg[1] * dLc[p][1] + q.bg[2] * dLc[p][2] : 0.f;
   }
   // largest contributor count of the tile: nothing behind it received any weight
 #pragma unroll
@@ -475,11 +489,13 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
       const float4 co = q.conic_opacity[id];
       s_co[k] = co;
       s_reach[k] = splat_reach(co);
-      s_rgbd[k] = q.rgbd[id];
+      if (GEOM) s_rgbd[k] = q.rgbd[id];
     }
-    for (int e = threadIdx.x; e < n * 8; e += NT) {
-      const uint32_t id = q.point_list[range.x + hi - 1 - (e >> 3)];
-      s_feat[e] = __ldg(q.feat4 + (size_t)id * 8 + (e & 7));
+    if (NEED_FEAT) {
+      for (int e = threadIdx.x; e < n * 8; e += NT) {
+        const uint32_t id = q.point_list[range.x + hi - 1 - (e >> 3)];
+        s_feat[e] = __ldg(q.feat4 + (size_t)id * 8 + (e & 7));
+      }
     }
     __syncthreads();
 
@@ -528,7 +544,18 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
 #pragma unroll
       for (int i = 0; i < 16; i++) vs[i] = 0.f;
 
-      if (any) {
+      if (any && !GEOM) {
+        // feature gradient only: dF[j][c] += w * dL/dO[p][c]
+#pragma unroll
+        for (int p = 0; p < PPT; p++) {
+          if (act[p]) {
+            const unsigned long long ww = pack2(w[p], w[p]);
+#pragma unroll
+            for (int ch = 0; ch < NUM_OBJECTS / 2; ch++) ffma2(vobj2[ch], dLo[p][ch], ww);
+          }
+        }
+      }
+      if (any && GEOM) {
         const float4 cd = s_rgbd[k];
         float dot[PPT];
 #pragma unroll
@@ -537,20 +564,22 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
           dot[p] = fmaf(cd.y, dLc[p][1], dot[p]);
           dot[p] = fmaf(cd.z, dLc[p][2], dot[p]);
         }
-        float2 dot2[PPT];
+        if (NEED_FEAT) {
+          float2 dot2[PPT];
 #pragma unroll
-        for (int p = 0; p < PPT; p++) dot2[p] = make_float2(0.f, 0.f);
+          for (int p = 0; p < PPT; p++) dot2[p] = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int c4 = 0; c4 < 8; c4++) {
-          const float4 f = s_feat[k * 8 + c4];
+          for (int c4 = 0; c4 < 8; c4++) {
+            const float4 f = s_feat[k * 8 + c4];
 #pragma unroll
-          for (int p = 0; p < PPT; p++) {
-            ffma2(dot2[p], make_float2(f.x, f.y), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 0]));
-            ffma2(dot2[p], make_float2(f.z, f.w), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 1]));
+            for (int p = 0; p < PPT; p++) {
+              ffma2(dot2[p], make_float2(f.x, f.y), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 0]));
+              ffma2(dot2[p], make_float2(f.z, f.w), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 1]));
+            }
           }
-        }
 #pragma unroll
-        for (int p = 0; p < PPT; p++) dot[p] += dot2[p].x + dot2[p].y;
+          for (int p = 0; p < PPT; p++) dot[p] += dot2[p].x + dot2[p].y;
+        }
 #pragma unroll
         for (int p = 0; p < PPT; p++) {
           if (act[p]) {
@@ -575,19 +604,24 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
             vs[6] += -0.5f * gdx * dy[p] * dL_dG;
             vs[7] += -0.5f * gdy * dy[p] * dL_dG;
             vs[8] += G[p] * dL_dalpha;
-            const unsigned long long ww = pack2(w[p], w[p]);
+            if (DF) {
+              const unsigned long long ww = pack2(w[p], w[p]);
 #pragma unroll
-            for (int ch = 0; ch < NUM_OBJECTS / 2; ch++) ffma2(vobj2[ch], dLo[p][ch], ww);
+              for (int ch = 0; ch < NUM_OBJECTS / 2; ch++) ffma2(vobj2[ch], dLo[p][ch], ww);
+            }
           }
         }
       }
-      float vobj[32];
-#pragma unroll
-      for (int i = 0; i < 16; i++) { vobj[2 * i] = vobj2[i].x; vobj[2 * i + 1] = vobj2[i].y; }
-      const float tot_obj = warp_transpose_reduce32(vobj, lane);
-      const float tot_s = warp_transpose_reduce16(vs, lane);
       const uint32_t id = s_id[k];
-      atomicAdd(q.dL_dobjects + (size_t)id * NUM_OBJECTS + lane, tot_obj);
+      if (DF) {
+        float vobj[32];
+#pragma unroll
+        for (int i = 0; i < 16; i++) { vobj[2 * i] = vobj2[i].x; vobj[2 * i + 1] = vobj2[i].y; }
+        const float tot_obj = warp_transpose_reduce32(vobj, lane);
+        atomicAdd(q.dL_dobjects + (size_t)id * NUM_OBJECTS + lane, tot_obj);
+      }
+      if (!GEOM) continue;
+      const float tot_s = warp_transpose_reduce16(vs, lane);
       if (lane < 9) {
         float* dst;
         if (lane < 3) dst = q.dL_dcolors + (size_t)id * 3 + lane;
@@ -612,10 +646,20 @@ cudaError_t launch_render_backward(const trase_b200_bwd_args& a, const FwdPointe
   q.dL_dmean2D = a.dL_dmeans2D; q.dL_dconic = a.dL_dconic; q.dL_dopacity = a.dL_dopacity;
   q.dL_dcolors = a.dL_dcolors; q.dL_dobjects = a.dL_dobjects;
   dim3 grid((a.W + TILE - 1) / TILE, (a.H + TILE - 1) / TILE, 1);
-  if (g_tuning.bwd_ppt == 1)
-    render_bwd_kernel<1><<<grid, 256, 0, s>>>(q);
-  else
-    render_bwd_kernel<2><<<grid, 128, 0, s>>>(q);
+  // what the caller asked for (NULL = not wanted / not provided; api.cu has validated the combinations)
+  const bool geom = a.dL_dmeans2D != nullptr, df = a.dL_dobjects != nullptr, obj_up = a.dL_dout_objects != nullptr;
+  if (!geom && (!df || !obj_up)) return cudaSuccess;      // nothing to compute
+  const bool one = g_tuning.bwd_ppt == 1;
+#define TB_BWD(G_, D_, O_)                                                    \
+  do {                                                                        \
+    if (one) render_bwd_kernel<1, G_, D_, O_><<<grid, 256, 0, s>>>(q);        \
+    else render_bwd_kernel<2, G_, D_, O_><<<grid, 128, 0, s>>>(q);            \
+  } while (0)
+  if (!geom) TB_BWD(false, true, true);
+  else if (df && obj_up) TB_BWD(true, true, true);
+  else if (obj_up) TB_BWD(true, false, true);
+  else TB_BWD(true, false, false);        // no upstream feature gradient: dF would be zero as well
+#undef TB_BWD
   return cudaGetLastError();
 }
 

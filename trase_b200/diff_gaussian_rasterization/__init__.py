@@ -47,6 +47,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         else:
             res = _raster.rasterize_forward(*args)
 
+        # outputs the loss never read arrive in backward as None instead of materialised zero images
+        ctx.set_materialize_grads(False)
         ctx.raster_settings = raster_settings
         ctx.num_rendered = res.num_rendered
         ctx.capacity = res.capacity
@@ -61,10 +63,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, sh_objs, geomBuffer, binningBuffer,
          imgBuffer) = ctx.saved_tensors
         H, W = raster_settings.image_height, raster_settings.image_width
-        if grad_out_color is None:
-            grad_out_color = torch.zeros((3, H, W), dtype=torch.float32, device=means3D.device)
-        if grad_out_objects is None:
-            grad_out_objects = torch.zeros((_raster.NUM_OBJECTS, H, W), dtype=torch.float32, device=means3D.device)
+        # Only what autograd will actually use is computed (the reference always computes all nine gradients): the
+        # feature gradient is skipped while the feature parameter is frozen (GAUSSIAN state), and when ONLY the
+        # feature parameter trains (FEATURE state) the dL/dalpha chain and the preprocess backward are skipped.
+        need = ctx.needs_input_grad            # means3D, means2D, sh, sh_objs, colors_precomp, opacities, scales, ...
+        need_features = bool(need[3])
+        need_geom = any(need[i] for i in (0, 1, 2, 4, 5, 6, 7, 8))
+        if grad_out_color is None and grad_out_objects is None:
+            return (None,) * 10
 
         args = (raster_settings.bg, means3D, radii, colors_precomp, scales, rotations,
                 raster_settings.scale_modifier, cov3Ds_precomp, raster_settings.viewmatrix,
@@ -74,19 +80,21 @@ class _RasterizeGaussians(torch.autograd.Function):
         if raster_settings.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:
-                grads9 = _raster.rasterize_backward(*args, capacity=ctx.capacity)
+                grads9 = _raster.rasterize_backward(*args, capacity=ctx.capacity, need_geom=need_geom,
+                                                    need_features=need_features)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            grads9 = _raster.rasterize_backward(*args, capacity=ctx.capacity)
+            grads9 = _raster.rasterize_backward(*args, capacity=ctx.capacity, need_geom=need_geom,
+                                                need_features=need_features)
         (grad_means2D, grad_colors_precomp, grad_objects, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
          grad_scales, grad_rotations) = grads9
 
         # input order of forward (…/__init__.py:151-162)
-        return (grad_means3D, grad_means2D, grad_sh, grad_objects.unsqueeze(1), grad_colors_precomp, grad_opacities,
-                grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
+        return (grad_means3D, grad_means2D, grad_sh, None if grad_objects is None else grad_objects.unsqueeze(1),
+                grad_colors_precomp, grad_opacities, grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
 
 
 class GaussianRasterizationSettings(NamedTuple):

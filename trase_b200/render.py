@@ -116,16 +116,25 @@ PIPE_DEFAULT = SimpleNamespace(convert_SHs_python=False, compute_cov3D_python=Fa
 
 def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, is_6dof=False, scaling_modifier=1.0,
            override_color=None, mask=None, norm_gaussian_features=True, is_smooth_gaussian_features=False,
-           smooth_K=16):
-    """gaussian_renderer/__init__.py:37-155.  Background tensor must be on the GPU."""
+           smooth_K=16, want_viewspace_grad=True):
+    """gaussian_renderer/__init__.py:37-155.  Background tensor must be on the GPU.
+
+    `want_viewspace_grad` (extension, default = the reference's behaviour): the reference always makes
+    `viewspace_points` a gradient leaf so that `.grad` can feed the densification statistics
+    (train.py:362-366).  A caller that will not read it (FEATURE state past `densify_until_iter`, style transfer past
+    it, evaluation) passes False; if then nothing but the feature parameter requires grad, the rasterizer's backward
+    computes the feature gradient only."""
     if is_6dof or getattr(pipe, "convert_SHs_python", False) or getattr(pipe, "compute_cov3D_python", False):
         raise NotImplementedError("6-DoF deformation and the *_python pipeline switches are outside the "
                                   "accelerated path")
-    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True) + 0
-    try:
-        screenspace_points.retain_grad()
-    except Exception:
-        pass
+    if want_viewspace_grad:
+        screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True) + 0
+        try:
+            screenspace_points.retain_grad()
+        except Exception:
+            pass
+    else:
+        screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype)
     raster_settings = GaussianRasterizationSettings(
         image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width),
         tanfovx=math.tan(viewpoint_camera.FoVx * 0.5), tanfovy=math.tan(viewpoint_camera.FoVy * 0.5), bg=bg_color,
