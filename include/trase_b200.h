@@ -455,6 +455,25 @@ TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, int skip, int E, const float
                                             float* wpack, void* stream);
 TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, const float* wpack,
                                             const uint32_t* masks, float* dzs, float* const* colsum, void* stream);
+/* BF16 side outputs for the weight gradients.  ref: the autograd backward of the eleven nn.Linear layers of
+ * utils/time_utils.py:106-131 (dW = dZ^T X, cuBLAS SGEMM in the reference).  The activations X_l and the layer
+ * gradients dZ_l that the two whole-network kernels write to HBM have exactly one reader, the weight-gradient
+ * product, which is bound by streaming them.  These variants write them as BF16 ([nl][M][256], 16-byte aligned)
+ * instead of fp32 — half the bytes written and read; the layer chain itself is unchanged (TF32 operands in shared
+ * memory, fp32 accumulation) — and trase_b200_wgrad_bf16 consumes them (BF16 products, fp32 accumulation in TMEM,
+ * D accumulated into like trase_b200_wgrad_tf32).  trase_b200_f32_to_bf16 converts the two small operands no
+ * fused kernel produces (the positional encoding, the packed head gradient): dst [rows][ld_dst] bf16, columns
+ * >= cols zero-filled. */
+TRASE_API int trase_b200_mlp_forward_fused_bf16(int M, int nl, int skip, int E, const float* emb, int ld_emb,
+                                                const float* wpack, const float* bias, void* acts16,
+                                                uint32_t* masks, float* out16, void* stream);
+TRASE_API int trase_b200_mlp_backward_fused_bf16(int M, int nl, const float* dout, const float* wpack,
+                                                 const uint32_t* masks, void* dzs16, float* const* colsum,
+                                                 void* stream);
+TRASE_API int trase_b200_wgrad_bf16(const void* P, int ldp, int I, const void* Q, int ldq, int J, int M, float* D,
+                                    int ldd, void* stream);
+TRASE_API int trase_b200_f32_to_bf16(int rows, int cols, const float* src, int ld_src, void* dst, int ld_dst,
+                                     void* stream);
 /* Debug only (no reference counterpart): device buffer of [grid][8] uint64 stall-cycle counters that the
  * whole-network kernels fill when set (NULL = off); read by tools/check_fused_mlp.py. */
 TRASE_API void trase_b200_mlp_fused_set_prof(unsigned long long* dev_buf);

@@ -96,6 +96,71 @@ def test_wgrad(native_lib, M, I, J):
     assert err <= 5e-3, err
 
 
+@pytest.mark.parametrize("M,I,J,ldq", [(64, 256, 256, 256), (1000, 256, 256, 256), (4099, 256, 84, 88),
+                                       (3001, 256, 16, 16), (777, 256, 64, 64), (300000, 256, 256, 256)])
+def test_wgrad_bf16(native_lib, M, I, J, ldq):
+    """D += P^T Q with bf16 operands read MN-major straight from the row-major tensors: against the exact product of
+    the same bf16 values (only the fp32 accumulation order differs), accumulating on top of existing contents."""
+    g = torch.Generator(device=DEV).manual_seed(M + I + J)
+    P = torch.randn(M, I, device=DEV, generator=g).to(torch.bfloat16)
+    Q = torch.zeros(M, ldq, device=DEV, dtype=torch.bfloat16)
+    Q[:, :J] = torch.randn(M, J, device=DEV, generator=g).to(torch.bfloat16)
+    D = torch.full((I, ((J + 3) // 4) * 4), 0.5, device=DEV)
+    rc = native_lib.trase_b200_wgrad_bf16(P.data_ptr(), P.stride(0), I, Q.data_ptr(), Q.stride(0), J, M, D.data_ptr(),
+                                          D.stride(0), torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, native_lib.trase_b200_last_error()
+    torch.cuda.synchronize()
+    ref = P.double().T @ Q[:, :J].double() + 0.5
+    scale = ref.abs().max().item()
+    assert torch.isfinite(D).all()
+    assert (D[:, :J].double() - ref).abs().max().item() / scale <= 2e-5
+
+
+def test_bf16_weight_gradient_path_against_fp32_tensors(native_lib):
+    """BF16_WGRAD writes the kept activations / layer gradients as bf16 and multiplies them as bf16.  Same outputs
+    (the layer chain is untouched), bias gradients identical up to atomics, weight gradients within bf16 rounding of
+    the fp32-tensor path; both reported against torch fp32 next to torch's own TF32 path."""
+    from trase_b200 import _deform_native as dn
+    from trase_b200.deform import DeformNetwork
+    torch.manual_seed(3)
+    M = 60011
+    ref = DeformNetwork(backend="torch").to(DEV)
+    nat = DeformNetwork(backend="native").to(DEV)
+    nat.load_state_dict(ref.state_dict())
+    x = (torch.rand(M, 3, device=DEV) - 0.5) * 4
+    t = torch.full((M, 1), 0.37, device=DEV)
+    go = [torch.randn(M, k, device=DEV) for k in (3, 4, 3)]
+    torch.autograd.backward(list(ref(x, t)), go)
+    base = [p.grad.clone() for p in ref.parameters()]
+    ref.zero_grad()
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        torch.autograd.backward(list(ref(x, t)), go)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = False
+    yard = [((p.grad - b).norm() / b.norm()).item() for p, b in zip(ref.parameters(), base)]
+    res = {}
+    saved = dn.BF16_WGRAD
+    try:
+        for mode in (False, True):
+            dn.BF16_WGRAD = mode
+            nat.zero_grad()
+            outs = nat(x, t)
+            torch.autograd.backward(list(outs), go)
+            res[mode] = ([o.detach().clone() for o in outs], [p.grad.detach().clone() for p in nat.parameters()])
+    finally:
+        dn.BF16_WGRAD = saved
+    for a, b in zip(res[False][0], res[True][0]):
+        assert torch.equal(a, b)                       # forward values do not depend on the side-output format
+    print("relative gradient error vs torch fp32: parameter, torch-TF32 yardstick, native fp32 tensors, native bf16 tensors")
+    for (n, _), b, y, g32, g16 in zip(nat.named_parameters(), base, yard, res[False][1], res[True][1]):
+        e32 = ((g32 - b).norm() / b.norm()).item()
+        e16 = ((g16 - b).norm() / b.norm()).item()
+        print("  %-28s %.2e  %.2e  %.2e" % (n, y, e32, e16))
+        assert e16 <= 2.0 * y + 4e-3, (n, e16, y)
+        assert ((g16 - g32).norm() / g32.norm()).item() <= 1e-2, n
+
+
 def test_native_deform_network_matches_torch(native_lib):
     """Outputs within TF32 accuracy of torch fp32; gradients no further from torch
     fp32 than torch's own TF32 (cuBLAS) path is (x2 slack) — the yardstick for what

@@ -29,6 +29,12 @@ FUSED_BACKWARD = True  # same for the data-gradient chain of the backward pass (
 # Restriction that comes with the opt-in: drive an arena-backed network with `.backward()`, not with
 # torch.autograd.grad (which must not touch `.grad`).  Module switch: False disables it everywhere.
 DIRECT_GRAD_ACCUM = True
+# The activations and layer gradients that the two whole-network kernels write to HBM are read by exactly one
+# consumer, the weight-gradient products, which are bound by streaming them.  With this switch they are written
+# (and read) as BF16 — the layer chain itself keeps its TF32 operands — which halves that traffic; weight
+# gradients then carry bf16 rounding noise (8 mantissa bits per factor, averaged over the M rows of the sum;
+# measured against fp32 in tests/test_gpu_mlp.py next to the TF32 yardstick).  False: fp32 tensors, TF32 products.
+BF16_WGRAD = True
 
 
 def _direct_ok(p, dev) -> bool:
@@ -109,6 +115,23 @@ def _wgrad(lib, P, Q, D):
                                              M, D[:, j0:].data_ptr(), D.stride(0), s))
 
 
+def _wgrad16(lib, P16, Q16, D):
+    """D[i, j] += sum_m P16[m, i] Q16[m, j] with bf16 operands (csrc/mlp_gemm.cu wgrad_bf16_kernel)."""
+    M, I = P16.shape
+    J = D.shape[1]
+    _lib.check(lib.trase_b200_wgrad_bf16(P16.data_ptr(), P16.stride(0), I, Q16.data_ptr(), Q16.stride(0), J, M,
+                                         D.data_ptr(), D.stride(0), _stream(P16.device)))
+
+
+def _to_bf16(lib, src, cols, ld_dst):
+    """[M][ld_dst] bf16 copy of the first `cols` columns of the fp32 matrix `src` (padding columns zero)."""
+    M = src.shape[0]
+    dst = torch.empty((M, ld_dst), dtype=torch.bfloat16, device=src.device)
+    _lib.check(lib.trase_b200_f32_to_bf16(M, cols, src.data_ptr(), src.stride(0), dst.data_ptr(), ld_dst,
+                                          _stream(src.device)))
+    return dst
+
+
 def _round_transpose(lib, Ws, sizes, skip, E, want_rounded, f32, s):
     """Wr[i] = TF32-rounded weight (only if want_rounded), WrT[i] = its transpose for i > 0, restricted to the hidden
     input columns for the layer behind the skip; all in one flat buffer, one small kernel per layer."""
@@ -186,13 +209,15 @@ class _DeformMLP(torch.autograd.Function):
                                                                     out16.data_ptr(), s))
                     return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
                 masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
-                acts_all = torch.empty((nl, M, W), **f32)
+                bf16 = BF16_WGRAD and FUSED_BACKWARD and lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
+                acts_all = torch.empty((nl, M, W), dtype=torch.bfloat16 if bf16 else torch.float32, device=dev)
+                fwd = lib.trase_b200_mlp_forward_fused_bf16 if bf16 else lib.trase_b200_mlp_forward_fused
                 with _Span("mlp_fwd"):
-                    _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
-                                                                wpack.data_ptr(), ball.data_ptr(), acts_all.data_ptr(),
-                                                                masks.data_ptr(), out16.data_ptr(), s))
+                    _lib.check(fwd(M, nl, skip, E, emb.data_ptr(), emb.stride(0), wpack.data_ptr(), ball.data_ptr(),
+                                   acts_all.data_ptr(), masks.data_ptr(), out16.data_ptr(), s))
                 acts = list(acts_all.unbind(0))
-                skipbuf = emb
+                # backward reads the embedding only as a weight-gradient operand: keep the bf16 copy in that case
+                skipbuf = _to_bf16(lib, emb, E, (E + 7) // 8 * 8) if bf16 else emb
             else:
                 masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
                 # skip buffer [M, E + W]: embedding in [:, :E], output of layer `skip` in [:, E:]
@@ -209,6 +234,7 @@ class _DeformMLP(torch.autograd.Function):
                 _gemm(lib, acts[-1], wh, out16, bias=bh, round_tf32=False)
         ctx.save_for_backward(skipbuf, whT, masks, *acts, *(Ws if fused else [w for w in WrT if w is not None]))
         ctx.meta = (nl, skip, E, M, sizes, fused)
+        ctx.bf16 = bool(fused and acts[0].dtype == torch.bfloat16)
         # the parameter objects themselves: backward looks their .grad up (DIRECT_GRAD_ACCUM)
         hp = list(params[:2 * nl])
         ctx.hidden_params = hp if all(isinstance(p, torch.nn.Parameter) for p in hp) else None
@@ -226,7 +252,9 @@ class _DeformMLP(torch.autograd.Function):
         with torch.cuda.device(dev):
             s = _stream(dev)
             # the fused chain packs its operand from the raw weights the fused forward kept
-            fused_bwd = FUSED_BACKWARD and fused and lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
+            bf16 = ctx.bf16                 # the forward wrote bf16 activations: the fused chain + bf16 wgrad follow
+            fused_bwd = (bf16 or FUSED_BACKWARD) and fused and lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
+            wgrad = _wgrad16 if bf16 else _wgrad
             raw_w = list(saved[3 + nl:]) if fused else None
             if fused_bwd:
                 WrT = None
@@ -257,18 +285,18 @@ class _DeformMLP(torch.autograd.Function):
                                                     dout.data_ptr(), dbh.data_ptr(), s))
             # heads: dWh^T = h_last^T dout
             with _Span("mlp_wgrad"):
-                _wgrad(lib, acts[-1], dout, dwhT)
+                wgrad(lib, acts[-1], _to_bf16(lib, dout, 16, 16) if bf16 else dout, dwhT)
             if fused_bwd:
                 # the whole data-gradient chain in one persistent kernel (csrc/mlp_fused.cu): dzs[L] = dZ of
                 # layer nl-1-L, bias gradients straight into their targets
                 wpack_b = torch.empty(lib.trase_b200_mlp_fused_pack_bwd_floats(nl), **f32)
                 wptrs = (ctypes.c_void_p * nl)(*[w.detach().contiguous().data_ptr() for w in raw_w])
                 _lib.check(lib.trase_b200_mlp_pack_fused_bwd(nl, skip, E, whT.data_ptr(), wptrs, wpack_b.data_ptr(), s))
-                dzs = torch.empty((nl, M, W), **f32)
+                dzs = torch.empty((nl, M, W), dtype=torch.bfloat16 if bf16 else torch.float32, device=dev)
                 bptrs = (ctypes.c_void_p * nl)(*[g.data_ptr() for g in grads_b])
+                bwd = lib.trase_b200_mlp_backward_fused_bf16 if bf16 else lib.trase_b200_mlp_backward_fused
                 with _Span("mlp_bwd_chain"):
-                    _lib.check(lib.trase_b200_mlp_backward_fused(M, nl, dout.data_ptr(), wpack_b.data_ptr(),
-                                                                 masks.data_ptr(), dzs.data_ptr(), bptrs, s))
+                    _lib.check(bwd(M, nl, dout.data_ptr(), wpack_b.data_ptr(), masks.data_ptr(), dzs.data_ptr(), bptrs, s))
             else:
                 # dZ_{nl-1} = (dout Wh) * relu'(h_last); its column sums are the bias gradient of layer nl-1
                 dz = torch.empty((M, W), **f32)
@@ -280,11 +308,11 @@ class _DeformMLP(torch.autograd.Function):
                     dz = dzs[nl - 1 - i]
                 if fused and i > 0 and i - 1 == skip:
                     # the skip layer's input was never concatenated: embedding columns, then the hidden ones
-                    _wgrad(lib, dz, skipbuf, grads_w[i][:, :E])
-                    _wgrad(lib, dz, acts[i - 1], grads_w[i][:, E:])
+                    wgrad(lib, dz, skipbuf, grads_w[i][:, :E])
+                    wgrad(lib, dz, acts[i - 1], grads_w[i][:, E:])
                 else:
                     inp = skipbuf[:, :E] if i == 0 else (skipbuf if i - 1 == skip else acts[i - 1])
-                    _wgrad(lib, dz, inp, grads_w[i])
+                    wgrad(lib, dz, inp, grads_w[i])
                 if i > 0 and not fused_bwd:
                     dz_prev = torch.empty((M, W), **f32)
                     _gemm(lib, dz, WrT[i], dz_prev, mask_in=masks[i - 1], colsum=grads_b[i - 1])

@@ -76,6 +76,8 @@ EXPORTS = [
     "trase_b200_adam_step", "trase_b200_densification_stats", "trase_b200_sample_features_forward",
     "trase_b200_sample_features_backward", "trase_b200_mlp_fused_set_prof",
     "trase_b200_smooth_features_forward", "trase_b200_smooth_features_backward",
+    "trase_b200_mlp_forward_fused_bf16", "trase_b200_mlp_backward_fused_bf16", "trase_b200_wgrad_bf16",
+    "trase_b200_f32_to_bf16",
 ]
 
 _lib = None
@@ -168,6 +170,16 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_fused_pack_bwd_floats.argtypes = [C.c_int]
     lib.trase_b200_mlp_pack_fused_bwd.restype = C.c_int
     lib.trase_b200_mlp_pack_fused_bwd.argtypes = [C.c_int] * 3 + [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]
+    lib.trase_b200_mlp_forward_fused_bf16.restype = C.c_int
+    lib.trase_b200_mlp_forward_fused_bf16.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 6
+    lib.trase_b200_mlp_backward_fused_bf16.restype = C.c_int
+    lib.trase_b200_mlp_backward_fused_bf16.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.POINTER(C.c_void_p),
+                                                                                             C.c_void_p]
+    lib.trase_b200_wgrad_bf16.restype = C.c_int
+    lib.trase_b200_wgrad_bf16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                          C.c_void_p, C.c_int, C.c_void_p]
+    lib.trase_b200_f32_to_bf16.restype = C.c_int
+    lib.trase_b200_f32_to_bf16.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
     lib.trase_b200_mlp_backward_fused.restype = C.c_int
     lib.trase_b200_mlp_backward_fused.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.POINTER(C.c_void_p), C.c_void_p]
     lib.trase_b200_sample_features_forward.restype = C.c_int

@@ -29,6 +29,7 @@
 // run as a last pseudo-layer with N = 32 whose first 16 output columns go straight to global memory.
 #include "common.cuh"
 #include "ptx.cuh"
+#include <cuda_bf16.h>
 
 namespace tb {
 namespace mlp {
@@ -46,7 +47,8 @@ constexpr int FU_HCH = FU_W / 32;         // 8 chunks of hidden activations
 constexpr int FU_ECH = 3;                 // up to 96 embedding columns
 // ring stages of 16 KB (this CTA's half of a weight k-block, or a chunk of the first operand);
 // the backward chain gives one stage up for its bias-gradient accumulators
-template <bool BWD> struct FuCfg { static constexpr int STAGES = BWD ? 5 : 6; };
+// A16 (bf16 side output, see below) gives one more stage up: 8 epilogue warps x 2 KB of store staging
+template <bool BWD, bool A16> struct FuCfg { static constexpr int STAGES = (BWD ? 5 : 6) - (A16 ? 1 : 0); };
 constexpr int FU_EPI_WARPS = 8;            // two per TMEM lane quarter, alternating 32-column slabs (12 warps: no gain, the MMA side is the bound)
 constexpr int FU_THREADS = 128 + 32 * FU_EPI_WARPS;
 constexpr int FU_MAX_LAYERS = 12;
@@ -65,6 +67,7 @@ struct FusedParams {
   uint32_t* masks;                   // [nl][M][8]  ReLU bit masks
   float* out16;                      // [M][16]
   float* acts;                       // [nl][M][256]  (backward: dZ of every layer, in backward order)
+  int acts16;                        // A16 kernels: the bf16 tensor map (tmActs) is live
   float* colsum[FU_MAX_LAYERS];      // backward: bias gradient [256] of every forward layer (+=)
   unsigned long long* prof;          // optional [grid][8] stall-cycle counters (tools/check_fused_mlp.py)
 };
@@ -92,7 +95,14 @@ __device__ __forceinline__ int fu_h_blocks(int L) { return L == 0 ? 0 : FU_HCH; 
 // BWD = true : the data-gradient chain dZ_{l-1} = (dZ_l W_l) * relu'(h_{l-1}): the same pipeline with the packed
 // upstream gradient [M][16] as first operand, transposed weights, an epilogue that applies the stored ReLU
 // bit mask and accumulates the bias gradients (column sums), and a final drain pseudo-layer without MMAs.
-template <bool BWD>
+//
+// A16 = true: what goes to HBM for the backward pass is a BF16 copy of each layer's output instead of the fp32 one.
+// Nothing in the chain itself reads those tensors back (the next layer's operand stays in shared memory, fp32 rounded
+// to TF32; the data-gradient chain needs only the ReLU bit masks): their only consumer is the weight-gradient
+// product dW = dZ^T X, which streams them once from HBM and is bound by exactly that traffic.  Half the bytes
+// written here, half the bytes read there.  Each epilogue warp converts its 32x32 slab (from the value BEFORE the
+// TF32 rounding), stages it in 2 KB of its own (64-byte-swizzled rows) and TMA-stores it itself; warp 1 stores nothing.
+template <bool BWD, bool A16>
 __global__ void __launch_bounds__(FU_THREADS, 1)
 mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constant__ CUtensorMap tmW,
                          const __grid_constant__ CUtensorMap tmWh, const __grid_constant__ CUtensorMap tmActs,
@@ -103,7 +113,8 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
   uint8_t* sH = smem + FU_OFF_H;
   uint8_t* sW = smem + FU_OFF_W;
   float* sCol = reinterpret_cast<float*>(smem + FU_OFF_COL);
-  constexpr int FU_STAGES = FuCfg<BWD>::STAGES;
+  constexpr int FU_STAGES = FuCfg<BWD, A16>::STAGES;
+  uint8_t* sStore = sW + FU_STAGES * FU_CHUNK;          // A16: per-epilogue-warp bf16 store staging (the stage given up)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FU_OFF_BAR);
   uint64_t* full = bars;                        // [STAGES] ring stage landed (leader: in both CTAs)
   uint64_t* empty = full + FU_STAGES;           // [STAGES] ring stage consumed by the pair's MMAs
@@ -214,7 +225,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
               FU_ADD(w_a);
               tc_fence_after();
               a_addr = smem_u32(sH + j * FU_CHUNK);
-              if (p.acts) tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
+              if (!A16 && p.acts) tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
             }
             if (!mma_layer) continue;
             if (leader) {
@@ -304,6 +315,12 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
             if (s == eh) { FU_T0(); mbar_wait(h_free, hfree_parity); FU_ADD(e_free); }
             uint8_t* dst = sH + s * FU_CHUNK + r * 128;
             uint32_t pos = 0;
+            uint8_t* st16 = sStore + (warp - 4) * 2048;
+            if (A16 && p.acts16) {
+              // this warp's previous slab store must have read its staging before it is overwritten
+              if (lane == 0) tma_store_wait_read<0>();
+              __syncwarp();
+            }
 #pragma unroll
             for (int c = 0; c < 8; c++) {
               const float bb[4] = {bq[c].x, bq[c].y, bq[c].z, bq[c].w};
@@ -321,13 +338,34 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
                 pos |= (u != 0u ? 1u : 0u) << (c * 4 + j);
                 of[j] = __uint_as_float(u);
                 if (BWD) v[c * 4 + j] = u;
+                if (A16 && !BWD) v[c * 4 + j] = __float_as_uint(x);      // unrounded value for the bf16 copy
               }
               *reinterpret_cast<float4*>(dst + ((c ^ (r & 7)) << 4)) = o;
+            }
+            if (A16 && p.acts16) {
+              // 32 values -> 64 bytes of bf16, row `lane` of the warp's staging, 16-byte chunks XOR-swizzled like
+              // CU_TENSOR_MAP_SWIZZLE_64B (chunk ^ bits 7..8 of the address = (row >> 1) & 3): conflict-free STS.128
+#pragma unroll
+              for (int c = 0; c < 4; c++) {
+                uint4 o16;
+                uint32_t* ow = reinterpret_cast<uint32_t*>(&o16);
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                  const __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[c * 8 + 2 * j]),
+                                                                  __uint_as_float(v[c * 8 + 2 * j + 1]));
+                  ow[j] = *reinterpret_cast<const uint32_t*>(&h2);
+                }
+                *reinterpret_cast<uint4*>(st16 + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4)) = o16;
+              }
             }
             if (!BWD && p.masks && grow < p.M) mask[s] = pos;
             fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
             __syncwarp();
             if (lane == 0) {
+              if (A16 && p.acts16) {
+                tma_store_3d(&tmActs, st16, s * 32, tile * FU_BM + ew * 32, L);     // rows past M are clipped
+                tma_store_commit();
+              }
               mbar_arrive(&a_local[s]);
               if (leader) mbar_arrive(&a_ready[s]); else mbar_arrive_cluster(&a_ready[s], 0);
             }
@@ -361,6 +399,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
         if (lane == 0) { if (leader) mbar_arrive(&tmem_empty[acc]); else mbar_arrive_cluster(&tmem_empty[acc], 0); }
       }
     }
+    if (A16 && lane == 0) tma_store_wait<0>();
     if (p.prof && warp == 4 && lane == 0) { p.prof[blockIdx.x * 8 + 5] = e_full; p.prof[blockIdx.x * 8 + 6] = e_free; }
   }
   tc_fence_before();
@@ -439,6 +478,26 @@ static bool make_tmap_acts(CUtensorMap* m, float* base, uint64_t M, uint64_t nl)
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// bf16 [nl][M][256] side output of the A16 kernels: one 32-row x 32-column box per epilogue-warp slab
+static bool make_tmap_acts16(CUtensorMap* m, void* base, uint64_t M, uint64_t nl) {
+  static EncodeTiledFn3 fn = nullptr;
+  if (!fn) {
+    void* q = nullptr;
+    cudaDriverEntryPointQueryResult r;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &q, cudaEnableDefault, &r) != cudaSuccess ||
+        r != cudaDriverEntryPointSuccess)
+      return false;
+    fn = reinterpret_cast<EncodeTiledFn3>(q);
+  }
+  cuuint64_t dims[3] = {(cuuint64_t)FU_W, M, nl};
+  cuuint64_t strides[2] = {(cuuint64_t)FU_W * 2, M * FU_W * 2};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 }  // namespace mlp
 }  // namespace tb
 
@@ -487,12 +546,12 @@ extern "C" TRASE_API int trase_b200_mlp_pack_fused(int nl, int skip, int E, cons
 
 namespace tb {
 namespace mlp {
-template <bool BWD>
+template <bool BWD, bool A16>
 static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMap& tW, const CUtensorMap& tWh,
                         const CUtensorMap& tA, const FusedParams& p, cudaStream_t stream) {
   static PerDeviceOnce attr_once;
   {
-    cudaError_t e = ensure_max_dyn_smem(attr_once, mlp_fused_kernel<BWD>, FU_SMEM);
+    cudaError_t e = ensure_max_dyn_smem(attr_once, mlp_fused_kernel<BWD, A16>, FU_SMEM);
     if (e != cudaSuccess) { set_error("%s: %s", who, cudaGetErrorString(e)); return 2; }
   }
   const int sms = num_sms() & ~1;          // SMs available to the persistent MLP kernels (see "reserve_sms"), whole pairs
@@ -512,7 +571,7 @@ static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMa
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, mlp_fused_kernel<BWD>, tE, tW, tWh, tA, p);
+  cudaError_t le = cudaLaunchKernelEx(&cfg, mlp_fused_kernel<BWD, A16>, tE, tW, tWh, tA, p);
   if (le != cudaSuccess) { set_error("%s: launch failed: %s", who, cudaGetErrorString(le)); return 2; }
   count_launches(1);
   return 0;
@@ -523,12 +582,28 @@ static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMa
 // emb: [M][ld_emb] (first E columns used, ld_emb multiple of 4), bias: nl*256 + 16 floats,
 // acts: [nl][M][256] (written), masks: [nl][M][8] (written), out16: [M][16] (written).
 // acts == masks == NULL: inference, nothing is kept for a backward pass (no activation traffic to HBM at all).
+static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* emb, int ld_emb, const float* wpack,
+                                  const float* bias, float* acts, void* acts16, uint32_t* masks, float* out16,
+                                  void* stream);
 extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const float* emb, int ld_emb,
                                                       const float* wpack, const float* bias, float* acts,
                                                       uint32_t* masks, float* out16, void* stream) {
+  return mlp_forward_fused_impl(M, nl, skip, E, emb, ld_emb, wpack, bias, acts, nullptr, masks, out16, stream);
+}
+// Same network, but the activations kept for the backward pass are written as BF16 (acts16: [nl][M][256] bf16,
+// 16-byte aligned): their only reader is the weight-gradient product (trase_b200_wgrad_bf16).
+extern "C" TRASE_API int trase_b200_mlp_forward_fused_bf16(int M, int nl, int skip, int E, const float* emb,
+                                                           int ld_emb, const float* wpack, const float* bias,
+                                                           void* acts16, uint32_t* masks, float* out16, void* stream) {
+  if (!acts16 || !masks) { set_error("trase_b200_mlp_forward_fused_bf16: acts16 and masks are required"); return 1; }
+  return mlp_forward_fused_impl(M, nl, skip, E, emb, ld_emb, wpack, bias, nullptr, acts16, masks, out16, stream);
+}
+static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* emb, int ld_emb, const float* wpack,
+                                  const float* bias, float* acts, void* acts16, uint32_t* masks, float* out16,
+                                  void* stream) {
   if (M <= 0) return 0;
-  if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || !out16 || ((acts == nullptr) != (masks == nullptr)) ||
-      (ld_emb & 3) ||
+  if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || !out16 ||
+      (((acts == nullptr) && (acts16 == nullptr)) != (masks == nullptr)) || ((uintptr_t)acts16 & 15) || (ld_emb & 3) ||
       ld_emb < E || ((uintptr_t)emb & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)acts & 15) ||
       ((uintptr_t)bias & 15) || ((uintptr_t)out16 & 15)) {
     set_error("trase_b200_mlp_forward_fused: bad arguments (M=%d nl=%d skip=%d E=%d)", M, nl, skip, E);
@@ -539,17 +614,23 @@ extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, i
   int base[mlp::FU_MAX_LAYERS + 2];
   const int total = mlp::fu_layout(nl, skip, E, base);
   for (int L = 0; L <= nl; L++) p.blk_base[L] = base[L];
-  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; for (int i = 0; i < mlp::FU_MAX_LAYERS; i++) p.colsum[i] = nullptr; p.prof = mlp::g_fused_prof;
+  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.acts16 = acts16 ? 1 : 0;
+  for (int i = 0; i < mlp::FU_MAX_LAYERS; i++) p.colsum[i] = nullptr;
+  p.prof = mlp::g_fused_prof;
   CUtensorMap tE, tW, tWh, tA;
   if (!mlp::make_tmap_2d(&tE, emb, M, E, ld_emb, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tWh, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 16, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
-      !mlp::make_tmap_acts(&tA, acts ? acts : out16, M, acts ? nl : 1)) {   // inference: map unused, must still be valid
+      !(acts16 ? mlp::make_tmap_acts16(&tA, acts16, M, nl)
+               : mlp::make_tmap_acts(&tA, acts ? acts : out16, M, acts ? nl : 1))) {   // inference: map unused, must still be valid
     set_error("trase_b200_mlp_forward_fused: cuTensorMapEncodeTiled failed");
     return 2;
   }
-  return mlp::launch_fused<false>("trase_b200_mlp_forward_fused", tE, tW, tWh, tA, p,
-                                  reinterpret_cast<cudaStream_t>(stream));
+  if (acts16)
+    return mlp::launch_fused<false, true>("trase_b200_mlp_forward_fused_bf16", tE, tW, tWh, tA, p,
+                                          reinterpret_cast<cudaStream_t>(stream));
+  return mlp::launch_fused<false, false>("trase_b200_mlp_forward_fused", tE, tW, tWh, tA, p,
+                                         reinterpret_cast<cudaStream_t>(stream));
 }
 
 // ---- backward data-gradient chain -----------------------------------------------------------------------
@@ -588,12 +669,26 @@ extern "C" TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, int skip, int E, 
 // dout: [M][16] packed upstream gradient of the heads; masks: [nl][M][8] from the forward pass;
 // dzs: [nl][M][256] (written): dzs[L] = dZ of forward layer nl-1-L; colsum: host array of nl device pointers,
 // colsum[l] = 256 floats that receive += the bias gradient of forward layer l.
+static int mlp_backward_fused_impl(int M, int nl, const float* dout, const float* wpack, const uint32_t* masks,
+                                   float* dzs, void* dzs16, float* const* colsum, void* stream);
 extern "C" TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, const float* wpack,
                                                        const uint32_t* masks, float* dzs, float* const* colsum,
                                                        void* stream) {
+  if (!dzs) { set_error("trase_b200_mlp_backward_fused: bad arguments (dzs)"); return 1; }
+  return mlp_backward_fused_impl(M, nl, dout, wpack, masks, dzs, nullptr, colsum, stream);
+}
+// Same chain with the layer gradients dZ written as BF16 (dzs16: [nl][M][256] bf16) for trase_b200_wgrad_bf16.
+extern "C" TRASE_API int trase_b200_mlp_backward_fused_bf16(int M, int nl, const float* dout, const float* wpack,
+                                                            const uint32_t* masks, void* dzs16, float* const* colsum,
+                                                            void* stream) {
+  if (!dzs16) { set_error("trase_b200_mlp_backward_fused_bf16: bad arguments (dzs16)"); return 1; }
+  return mlp_backward_fused_impl(M, nl, dout, wpack, masks, nullptr, dzs16, colsum, stream);
+}
+static int mlp_backward_fused_impl(int M, int nl, const float* dout, const float* wpack, const uint32_t* masks,
+                                   float* dzs, void* dzs16, float* const* colsum, void* stream) {
   if (M <= 0) return 0;
-  if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !dout || !wpack || !masks || !dzs || !colsum ||
-      ((uintptr_t)dout & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)dzs & 15)) {
+  if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !dout || !wpack || !masks || !colsum ||
+      ((uintptr_t)dout & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)dzs & 15) || ((uintptr_t)dzs16 & 15)) {
     set_error("trase_b200_mlp_backward_fused: bad arguments (M=%d nl=%d)", M, nl);
     return 1;
   }
@@ -601,7 +696,7 @@ extern "C" TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const floa
   p.M = M; p.nl = nl; p.skip = -1; p.eb = 1;
   p.blk_base[0] = 0;
   for (int L = 1; L <= nl; L++) p.blk_base[L] = 1 + (L - 1) * mlp::FU_HCH;
-  p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs;
+  p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs; p.acts16 = dzs16 ? 1 : 0;
   for (int i = 0; i < nl; i++) {
     if (!colsum[i]) { set_error("trase_b200_mlp_backward_fused: null bias-gradient pointer"); return 1; }
     p.colsum[i] = colsum[i];
@@ -611,12 +706,15 @@ extern "C" TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const floa
   CUtensorMap tE, tW, tA;
   if (!mlp::make_tmap_2d(&tE, dout, M, 16, 16, mlp::FU_BM, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
-      !mlp::make_tmap_acts(&tA, dzs, M, nl)) {
+      !(dzs16 ? mlp::make_tmap_acts16(&tA, dzs16, M, nl) : mlp::make_tmap_acts(&tA, dzs, M, nl))) {
     set_error("trase_b200_mlp_backward_fused: cuTensorMapEncodeTiled failed");
     return 2;
   }
-  return mlp::launch_fused<true>("trase_b200_mlp_backward_fused", tE, tW, tW, tA, p,
-                                 reinterpret_cast<cudaStream_t>(stream));
+  if (dzs16)
+    return mlp::launch_fused<true, true>("trase_b200_mlp_backward_fused_bf16", tE, tW, tW, tA, p,
+                                         reinterpret_cast<cudaStream_t>(stream));
+  return mlp::launch_fused<true, false>("trase_b200_mlp_backward_fused", tE, tW, tW, tA, p,
+                                        reinterpret_cast<cudaStream_t>(stream));
 }
 
 // debug: device buffer of [grid][8] cycle counters filled by the fused kernel (NULL = off)

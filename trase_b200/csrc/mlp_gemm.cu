@@ -17,6 +17,7 @@
 // zero-fill / clipping, so no operand is ever padded in memory.
 #include "common.cuh"
 #include "ptx.cuh"
+#include <cuda_bf16.h>
 
 namespace tb {
 namespace mlp {
@@ -536,6 +537,218 @@ extern "C" TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, c
   mlp::wgrad_tf32_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_wgrad_tf32: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+// ===========================================================================
+// Weight gradient from BF16 operands:  D[i, j] += sum_m P[m, i] * Q[m, j], P and Q row-major bf16 (the side copies
+// the fused forward / backward kernels write, whose only reader this is), D fp32.
+// Same structure as wgrad_tf32_kernel — operands MN-major straight from the row-major tensors, the m range split over
+// persistent CTAs, the whole I x J result in TMEM — with half the bytes per element and K = 16 per MMA:
+//   TMA box = 64 rows (m) x 64 columns, 128-byte swizzle: the canonical MN-major layout of 16-bit operands
+//   (128-byte rows of 64 elements along MN, 8-row swizzle atoms along the reduction: SBO = 1024, next 64 MN elements
+//   one box further: LBO = box size).
+namespace tb {
+namespace mlp {
+
+constexpr int WH_ROWS = 64;                       // m rows per stage (4 MMAs of K = 16)
+constexpr int WH_STAGES = 3;
+constexpr int WH_BOX_BYTES = WH_ROWS * 128;       // one 64-row x 64-col bf16 box
+constexpr int WH_OP_BYTES = 4 * WH_BOX_BYTES;     // up to 256 columns per operand = 32 KB
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+wgrad_bf16_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ, const WgradParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
+  uint8_t* sP = smem;
+  uint8_t* sQ = smem + WH_STAGES * WH_OP_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * WH_STAGES * WH_OP_BYTES);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + WH_STAGES;
+  uint64_t* done = bars + 2 * WH_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_halves = (p.I + 127) / 128;
+  const int i_boxes = n_halves * 2;                      // 64-column boxes of P
+  const int j_boxes = (p.J + 63) / 64;
+  const int jpad = ((p.J + 15) / 16) * 16;               // N of the MMA
+  const int nblk = (p.M + WH_ROWS - 1) / WH_ROWS;
+  const int per = (nblk + gridDim.x - 1) / gridDim.x;
+  const int blk0 = blockIdx.x * per;
+  const int blk1 = min(nblk, blk0 + per);
+  constexpr uint32_t TMEM_COLS = 512;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmP); prefetch_tmap(&tmQ);
+    for (int i = 0; i < WH_STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int b = blk0; b < blk1; b++) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_expect_tx(&full[stage], (i_boxes + j_boxes) * WH_BOX_BYTES);
+        for (int c = 0; c < i_boxes; c++)
+          tma_load_2d(sP + stage * WH_OP_BYTES + c * WH_BOX_BYTES, &tmP, &full[stage], c * 64, b * WH_ROWS);
+        for (int c = 0; c < j_boxes; c++)
+          tma_load_2d(sQ + stage * WH_OP_BYTES + c * WH_BOX_BYTES, &tmQ, &full[stage], c * 64, b * WH_ROWS);
+        if (++stage == WH_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, jpad, 1, 1);
+      uint32_t stage = 0, phase = 0;
+      for (int b = blk0; b < blk1; b++) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        const uint32_t pa = smem_u32(sP + stage * WH_OP_BYTES);
+        const uint32_t qa = smem_u32(sQ + stage * WH_OP_BYTES);
+#pragma unroll
+        for (int kg = 0; kg < WH_ROWS / 16; kg++) {
+          // one MMA (K = 16) = two 8-row swizzle atoms, 2048 bytes into the box
+          const uint64_t db = make_smem_desc_sw128(qa + kg * 2048, WH_BOX_BYTES, 1024, 2);
+          for (int h = 0; h < n_halves; h++) {
+            const uint64_t da = make_smem_desc_sw128(pa + h * 2 * WH_BOX_BYTES + kg * 2048, WH_BOX_BYTES, 1024, 2);
+            mma_bf16_ss(tmem_base + h * 256, da, db, idesc, (b != blk0) || (kg != 0));
+          }
+        }
+        mma_commit(&empty[stage]);
+        if (++stage == WH_STAGES) { stage = 0; phase ^= 1; }
+      }
+      mma_commit(done);
+    }
+  } else if (warp >= 4 && blk0 < blk1) {
+    const int ew = warp & 3;
+    mbar_wait(done, 0);
+    tc_fence_after();
+    for (int h = 0; h < n_halves; h++) {
+      const int i = h * 128 + ew * 32 + lane;
+      for (int c0 = 0; c0 < p.J; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + h * 256 + c0, v);
+        tmem_ld_wait();
+        if (i < p.I) {
+          float* dst = p.D + (size_t)i * p.ldd + c0;
+#pragma unroll
+          for (int q = 0; q < 8; q++) {
+            if (c0 + q * 4 < p.J) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + q * 4),
+                           "f"(__uint_as_float(v[q * 4])), "f"(__uint_as_float(v[q * 4 + 1])),
+                           "f"(__uint_as_float(v[q * 4 + 2])), "f"(__uint_as_float(v[q * 4 + 3]))
+                           : "memory");
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+typedef CUresult (*EncodeTiledFn16)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static bool make_tmap_2d_bf16(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                              uint32_t box_rows, uint32_t box_cols) {
+  static EncodeTiledFn16 fn = nullptr;
+  if (!fn) {
+    void* q = nullptr;
+    cudaDriverEntryPointQueryResult r;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &q, cudaEnableDefault, &r) != cudaSuccess ||
+        r != cudaDriverEntryPointSuccess)
+      return false;
+    fn = reinterpret_cast<EncodeTiledFn16>(q);
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// dst[r][c] = bf16(src[r][c]) for c < cols; columns [cols, ld_dst) of dst are zero-filled
+__global__ void __launch_bounds__(256) f32_to_bf16_kernel(int rows, int cols, const float* __restrict__ src, int ld_src,
+                                                          __nv_bfloat16* __restrict__ dst, int ld_dst) {
+  const size_t total = (size_t)rows * ld_dst;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t r = e / ld_dst;
+    const int c = (int)(e - r * ld_dst);
+    dst[e] = __float2bfloat16_rn(c < cols ? src[r * ld_src + c] : 0.f);
+  }
+}
+
+}  // namespace mlp
+}  // namespace tb
+
+// D[i][j] += sum_m P[m][i] * Q[m][j];  P [M][I], Q [M][J] row-major BF16 (pitches ldp / ldq in elements, multiples
+// of 8; 16-byte aligned bases), D [I][J] fp32 (pitch ldd, multiple of 4).  I <= 256, J <= 256, J a multiple of 4.
+extern "C" TRASE_API int trase_b200_wgrad_bf16(const void* P, int ldp, int I, const void* Q, int ldq, int J, int M,
+                                               float* D, int ldd, void* stream) {
+  using namespace tb;
+  if (M <= 0 || I <= 0 || J <= 0 || I > 256 || J > 256 || (J & 3) || !P || !Q || !D) {
+    set_error("trase_b200_wgrad_bf16: bad arguments (M=%d I=%d J=%d)", M, I, J);
+    return 1;
+  }
+  if ((ldp & 7) || (ldq & 7) || (ldd & 3) || ((uintptr_t)P & 15) || ((uintptr_t)Q & 15) || ((uintptr_t)D & 15)) {
+    set_error("trase_b200_wgrad_bf16: pointers must be 16-byte aligned, bf16 pitches multiples of 8, ldd of 4");
+    return 1;
+  }
+  CUtensorMap tP, tQ;
+  if (!mlp::make_tmap_2d_bf16(&tP, P, M, I, ldp, mlp::WH_ROWS, 64) ||
+      !mlp::make_tmap_2d_bf16(&tQ, Q, M, J, ldq, mlp::WH_ROWS, 64)) {
+    set_error("trase_b200_wgrad_bf16: cuTensorMapEncodeTiled failed");
+    return 2;
+  }
+  static PerDeviceOnce attr_once;
+  const int smem = 2 * mlp::WH_STAGES * mlp::WH_OP_BYTES + 256 + 1024;
+  {
+    cudaError_t e = ensure_max_dyn_smem(attr_once, mlp::wgrad_bf16_kernel, smem);
+    if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16: %s", cudaGetErrorString(e)); return 2; }
+  }
+  mlp::WgradParams wp;
+  wp.M = M; wp.I = I; wp.J = J; wp.D = D; wp.ldd = ldd;
+  const int nblk = (M + mlp::WH_ROWS - 1) / mlp::WH_ROWS;
+  const int grid = nblk < mlp::num_sms() ? nblk : mlp::num_sms();
+  mlp::wgrad_bf16_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+// dst [rows][ld_dst] bf16 <- src [rows][ld_src] fp32 (first `cols` columns; the rest of each dst row is zeroed).
+// Used for the two small wgrad operands no fused kernel produces: the positional encoding and the packed upstream
+// gradient of the heads.
+extern "C" TRASE_API int trase_b200_f32_to_bf16(int rows, int cols, const float* src, int ld_src, void* dst,
+                                                int ld_dst, void* stream) {
+  using namespace tb;
+  if (rows <= 0) return 0;
+  if (!src || !dst || cols <= 0 || ld_src < cols || ld_dst < cols) {
+    set_error("trase_b200_f32_to_bf16: bad arguments");
+    return 1;
+  }
+  const size_t total = (size_t)rows * ld_dst;
+  const int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  mlp::f32_to_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      rows, cols, src, ld_src, reinterpret_cast<__nv_bfloat16*>(dst), ld_dst);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_f32_to_bf16: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
   return 0;
 }

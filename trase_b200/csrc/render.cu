@@ -413,7 +413,8 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 // nothing else.  Every variant evaluates alpha and T with the same pinned sequence, so which pairs blend never
 // depends on the variant.
 template <int PPT, bool GEOM, bool DF, bool OBJ_UP>
-__global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel(const RenderBwdParams q) {
+__global__ void __launch_bounds__(256 / PPT, (GEOM && !OBJ_UP) ? (PPT == 2 ? 6 : 3) : (PPT == 2 ? 3 : 2))
+render_bwd_kernel(const RenderBwdParams q) {      // the colour-only variant needs ~80 registers: twice the resident warps
   constexpr int NT = 256 / PPT;
   constexpr bool NEED_FEAT = GEOM && OBJ_UP;        // feature rows are only read for dL/dalpha
   constexpr bool NEED_DLO = DF || NEED_FEAT;        // upstream feature gradient planes
@@ -565,20 +566,22 @@ __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? 3 : 2) render_bwd_kernel
           dot[p] = fmaf(cd.z, dLc[p][2], dot[p]);
         }
         if (NEED_FEAT) {
-          float2 dot2[PPT];
+          // two independent packed accumulators per pixel: dependent-FMA chains of 8 instead of 16 (the kernel is
+          // bound by fixed-latency dependencies at 12 warps per SM, not by the FMA pipe)
+          float2 dot2[PPT], dot2b[PPT];
 #pragma unroll
-          for (int p = 0; p < PPT; p++) dot2[p] = make_float2(0.f, 0.f);
+          for (int p = 0; p < PPT; p++) { dot2[p] = make_float2(0.f, 0.f); dot2b[p] = make_float2(0.f, 0.f); }
 #pragma unroll
           for (int c4 = 0; c4 < 8; c4++) {
             const float4 f = s_feat[k * 8 + c4];
 #pragma unroll
             for (int p = 0; p < PPT; p++) {
               ffma2(dot2[p], make_float2(f.x, f.y), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 0]));
-              ffma2(dot2[p], make_float2(f.z, f.w), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 1]));
+              ffma2(dot2b[p], make_float2(f.z, f.w), *reinterpret_cast<const unsigned long long*>(&dLo[p][2 * c4 + 1]));
             }
           }
 #pragma unroll
-          for (int p = 0; p < PPT; p++) dot[p] += dot2[p].x + dot2[p].y;
+          for (int p = 0; p < PPT; p++) dot[p] += (dot2[p].x + dot2b[p].x) + (dot2[p].y + dot2b[p].y);
         }
 #pragma unroll
         for (int p = 0; p < PPT; p++) {
