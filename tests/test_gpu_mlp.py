@@ -191,7 +191,9 @@ def test_native_deform_network_matches_torch(native_lib):
         assert (a - b).abs().max().item() <= 5e-3 * max(1.0, a.abs().max().item())
     for (n, q), b, y in zip(nat.named_parameters(), base, yard):
         err = ((q.grad - b).norm() / b.norm()).item()
-        assert err <= 2.0 * y + 2e-3, (n, err, y)
+        # + 4e-3: the head weight gradients are bf16 x bf16 products of the last activations and the upstream
+        # gradient (BF16_WGRAD; 3e-3 measured, 7e-4 with fp32 tensors); the hidden layers are dominated by the chain
+        assert err <= 2.0 * y + 4e-3, (n, err, y)
 
 
 def test_native_blender_deform_network_matches_torch(native_lib):
@@ -226,7 +228,9 @@ def test_native_blender_deform_network_matches_torch(native_lib):
     for (n, q), b, y in zip(nat.named_parameters(), base, yard):
         assert q.grad is not None, n
         err = ((q.grad - b).norm() / b.norm()).item()
-        assert err <= 2.0 * y + 2e-3, (n, err, y)
+        # + 4e-3: the head weight gradients are bf16 x bf16 products of the last activations and the upstream
+        # gradient (BF16_WGRAD; 3e-3 measured, 7e-4 with fp32 tensors); the hidden layers are dominated by the chain
+        assert err <= 2.0 * y + 4e-3, (n, err, y)
     # a materialised (non-broadcast) but uniform time column is accepted too; differing rows are refused
     with torch.no_grad():
         again = nat(x, t.contiguous())
