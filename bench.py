@@ -36,7 +36,7 @@ import torch.distributed as dist  # noqa: E402
 
 METRIC = "fwd+bwd RGB+feature render steps/sec"
 UNIT = "steps/s"
-DTYPE = "f32 rasterizer; DeformNetwork MLP tf32 operands, fp32 accumulate"
+DTYPE = "f32 rasterizer; DeformNetwork MLP tf32 operands / fp32 accumulate, weight gradients from bf16 side copies"
 WORKLOADS = {  # BASELINE.json configs
     "neu3d": dict(P=300_000, W=1352, H=1014, seed=2, views=1, state="GAUSSIAN",
                   desc="configs[1]: Neu3D-shaped 300k Gaussians 1352x1014, DeformNetwork MLP + RGB+feature fwd+bwd"),

@@ -495,6 +495,17 @@ TRASE_API int trase_b200_adam_step(int64_t n, float* params, const float* grads,
                                    float beta1, float beta2, float eps, void* stream);
 TRASE_API int trase_b200_densification_stats(int P, const float* viewspace_grad, const unsigned char* filter,
                                              float* grad_accum, float* denom, void* stream);
+/* Densification / pruning over the flat arenas.  ref: cat_tensors_to_optimizer, _prune_optimizer, prune_points and
+ * densification_postfix (scene/gaussian_model.py:472-561), which re-allocate every parameter tensor and both Adam
+ * moments one by one with torch.cat / boolean indexing.  Here the host builds ONE row map (output row r <- input row
+ * src_rows[r]; fresh[r] = 1 for clones and split children, whose moments start at zero) and one launch gathers all
+ * per-Gaussian segments of the parameter buffer and of both moment buffers.  Segment s is a [P][width[s]] row-major
+ * block at float offset old_off[s] (input) / new_off[s] (output); old_m/old_v/new_m/new_v may all be NULL. */
+TRASE_API int trase_b200_arena_gather_rows(int nseg, const int64_t* old_off, const int64_t* new_off, const int* width,
+                                           int64_t P_new, const int64_t* src_rows, const unsigned char* fresh,
+                                           const float* old_p, const float* old_m, const float* old_v, float* new_p,
+                                           float* new_m, float* new_v, void* stream);
+
 
 /* Feature-loss front end (second part): bilinear resize of the
  * rendered feature image to the mask resolution, gather of the sampled pixels and L2

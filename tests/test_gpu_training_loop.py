@@ -93,3 +93,187 @@ def test_four_training_steps_match_the_reference_path():
     for name in LRS:
         a, b = getattr(pc, name).detach(), getattr(pc_r, name).detach()
         assert (a - b).abs().max().item() <= 2e-3 * b.abs().max().item(), name
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Densification over the flat arenas against the reference's per-tensor procedure, restated here on
+# torch.optim.Adam exactly as scene/gaussian_model.py does it (cat_tensors_to_optimizer :513-534,
+# _prune_optimizer :472-492, densify_and_clone :594-615, densify_and_split :563-592, densify_and_prune :617-635,
+# reset_opacity :378-381 with replace_tensor_to_optimizer :457-470).
+class _RefModel:
+    NAMES = ["_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation", "_gaussian_features"]
+
+    def __init__(self, tensors, lrs):
+        self.p = {k: torch.nn.Parameter(v.clone()) for k, v in tensors.items()}
+        self.opt = torch.optim.Adam([{"params": [self.p[k]], "lr": lrs[k], "name": k} for k in self.NAMES], lr=0.0,
+                                    eps=1e-15)
+        self.percent_dense = 0.01
+
+    def _replace(self, fn_param, fn_state):
+        for group in self.opt.param_groups:
+            old = group["params"][0]
+            st = self.opt.state.get(old, None)
+            new = torch.nn.Parameter(fn_param(group["name"], old).requires_grad_(True))
+            if st is not None:
+                st["exp_avg"] = fn_state(group["name"], st["exp_avg"])
+                st["exp_avg_sq"] = fn_state(group["name"], st["exp_avg_sq"])
+                del self.opt.state[old]
+                self.opt.state[new] = st
+            group["params"][0] = new
+            self.p[group["name"]] = new
+
+    def cat(self, ext):
+        self._replace(lambda n, t: torch.cat((t, ext[n]), dim=0),
+                      lambda n, s: torch.cat((s, torch.zeros_like(ext[n])), dim=0))
+        P = self.p["_xyz"].shape[0]
+        dev = self.p["_xyz"].device
+        self.accum, self.denom = torch.zeros((P, 1), device=dev), torch.zeros((P, 1), device=dev)
+        self.max_radii2D = torch.zeros(P, device=dev)
+
+    def prune(self, mask):
+        keep = ~mask
+        self._replace(lambda n, t: t[keep], lambda n, s: s[keep])
+        self.accum, self.denom, self.max_radii2D = self.accum[keep], self.denom[keep], self.max_radii2D[keep]
+
+    def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, N=2):
+        from trase_b200.densify import build_rotation
+        grads = self.accum / self.denom
+        grads[grads.isnan()] = 0.0
+        scaling = lambda: torch.exp(self.p["_scaling"])
+        sel = (torch.norm(grads, dim=-1) >= max_grad) & (scaling().max(dim=1).values <= self.percent_dense * extent)
+        n_clone = int(sel.sum())
+        self.cat({k: self.p[k][sel] for k in self.NAMES})
+        P = self.p["_xyz"].shape[0]
+        padded = torch.zeros(P, device=grads.device)
+        padded[:grads.shape[0]] = grads.squeeze()
+        sel = (padded >= max_grad) & (scaling().max(dim=1).values > self.percent_dense * extent)
+        n_split = int(sel.sum())
+        stds = scaling()[sel].repeat(N, 1)
+        samples = torch.normal(mean=torch.zeros((stds.size(0), 3), device=stds.device), std=stds)
+        rots = build_rotation(self.p["_rotation"][sel]).repeat(N, 1, 1)
+        ext = {k: self.p[k][sel].repeat(*([N] + [1] * (self.p[k].dim() - 1))) for k in self.NAMES}
+        ext["_xyz"] = torch.bmm(rots, samples.unsqueeze(-1)).squeeze(-1) + self.p["_xyz"][sel].repeat(N, 1)
+        ext["_scaling"] = torch.log(scaling()[sel].repeat(N, 1) / (0.8 * N))
+        self.cat(ext)
+        self.prune(torch.cat((sel, torch.zeros(N * n_split, device=sel.device, dtype=torch.bool))))
+        prune = (torch.sigmoid(self.p["_opacity"]) < min_opacity).squeeze()
+        if max_screen_size:
+            prune = prune | (self.max_radii2D > max_screen_size) | (scaling().max(dim=1).values > 0.1 * extent)
+        self.prune(prune)
+        return n_clone, n_split
+
+    def reset_opacity(self):
+        o = torch.min(torch.sigmoid(self.p["_opacity"]), torch.ones_like(self.p["_opacity"]) * 0.01)
+        new = torch.log(o / (1 - o))
+        for group in self.opt.param_groups:
+            if group["name"] == "_opacity":
+                old = group["params"][0]
+                st = self.opt.state.get(old)
+                st["exp_avg"], st["exp_avg_sq"] = torch.zeros_like(new), torch.zeros_like(new)
+                del self.opt.state[old]
+                group["params"][0] = torch.nn.Parameter(new.detach().requires_grad_(True))
+                self.opt.state[group["params"][0]] = st
+                self.p["_opacity"] = group["params"][0]
+
+
+def test_densify_prune_and_opacity_reset_match_the_per_tensor_procedure(native_lib, tmp_path):
+    """A few training steps, then densify_and_prune and reset_opacity on the flat arenas against the reference's
+    per-tensor procedure started from the SAME state: Gaussian counts, every parameter and both Adam moments must be
+    identical (they are copies and the same torch formulas); training then continues on the resized arenas; the
+    checkpoint tuple round-trips and its optimizer halves load into stock torch.optim.Adam."""
+    from trase_b200 import render as R, loss_utils, densify as D
+    from trase_b200.distributed import GradArena
+    from trase_b200.optim import ArenaAdam
+    dev = torch.device("cuda:0")
+    bg = torch.zeros(3, device=dev)
+    sc, pc, net, view, gt = _build(dev)
+    P0 = pc._xyz.shape[0]
+    arena = GradArena(list(pc.parameters()))
+    opt = ArenaAdam(arena, _groups(pc), eps=1e-15)
+    state = D.DensifyState(P0, dev)
+
+    def step():
+        opt.zero_grad()
+        P = pc._xyz.shape[0]
+        t = torch.full((P, 1), 0.3, device=dev)
+        with torch.no_grad():
+            d = net(pc.get_xyz.detach(), t)
+        out = R.render(view, pc, R.PIPE_DEFAULT, bg, d[0], d[1], d[2])
+        loss = loss_utils.l1_ssim_loss(out["render"], gt, 0.2) + loss_utils.feature_norm_reg(out["render_gaussian_features"])
+        loss.backward()
+        state.update_max_radii(out["radii"], out["visibility_filter"])
+        D.add_densification_stats(state.xyz_gradient_accum, state.denom, out["viewspace_points"], out["visibility_filter"])
+        opt.step()
+        return loss.item()
+
+    for _ in range(5):
+        step()
+    # the reference-style model starts from exactly this state
+    ref = _RefModel({k: getattr(pc, k).detach() for k in _RefModel.NAMES}, LRS)
+    seg = {id(p): (off, p.numel()) for p, off in zip(arena.params, arena.offsets)}
+    for group in ref.opt.param_groups:
+        p = group["params"][0]
+        off, n = seg[id(getattr(pc, group["name"]))]
+        ref.opt.state[p] = {"step": torch.tensor(5.0), "exp_avg": opt.exp_avg[off:off + n].view_as(p).clone(),
+                            "exp_avg_sq": opt.exp_avg_sq[off:off + n].view_as(p).clone()}
+    ref.accum, ref.denom = state.xyz_gradient_accum.clone(), state.denom.clone()
+    ref.max_radii2D = state.max_radii2D.clone()
+    thr = float((state.xyz_gradient_accum / state.denom.clamp_min(1)).quantile(0.9))     # top 10 % densify
+    extent = 2.0
+    with torch.no_grad():                              # make the split branch and the opacity prune fire too
+        big = torch.arange(P0, device=dev) % 7 == 0
+        pc._scaling.data[big] += 2.5
+        ref.p["_scaling"].data[big] += 2.5
+        pc._opacity.data[::11] = -8.0
+        ref.p["_opacity"].data[::11] = -8.0
+    torch.manual_seed(77)
+    n_ref = ref.densify_and_prune(thr, 0.005, extent, 20)
+    torch.manual_seed(77)
+    n_ours = D.densify_and_prune(pc, opt, state, thr, 0.005, extent, 20)
+    assert n_ours == n_ref and n_ours[0] > 0 and n_ours[1] > 0
+    P1 = pc._xyz.shape[0]
+    assert P1 == ref.p["_xyz"].shape[0] and P1 != P0
+    seg = {id(p): (off, p.numel()) for p, off in zip(arena.params, arena.offsets)}
+    for group in ref.opt.param_groups:
+        k = group["name"]
+        mine, theirs = getattr(pc, k), group["params"][0]
+        assert mine.shape == theirs.shape, k
+        assert torch.equal(mine.detach(), theirs.detach()), k
+        off, n = seg[id(mine)]
+        st = ref.opt.state[theirs]
+        assert torch.equal(opt.exp_avg[off:off + n].view_as(mine), st["exp_avg"]), k
+        assert torch.equal(opt.exp_avg_sq[off:off + n].view_as(mine), st["exp_avg_sq"]), k
+        assert mine.grad.shape == mine.shape and mine.grad.data_ptr() == arena.flat.data_ptr() + 4 * off
+    assert state.xyz_gradient_accum.shape == (P1, 1) and not state.max_radii2D.any()
+    # opacity reset
+    ref.reset_opacity()
+    D.reset_opacity(pc, opt)
+    assert torch.equal(pc._opacity.detach(), ref.p["_opacity"].detach())
+    off, n = seg[id(pc._opacity)]
+    assert not opt.exp_avg[off:off + n].any() and not opt.exp_avg_sq[off:off + n].any()
+    # prune_points alone
+    mask = torch.arange(P1, device=dev) % 5 == 0
+    ref.prune(mask)
+    D.prune_points(pc, opt, state, mask)
+    assert torch.equal(pc._rotation.detach(), ref.p["_rotation"].detach())
+    # training goes on over the resized arenas
+    losses = [step() for _ in range(3)]
+    assert all(l == l for l in losses) and pc._xyz.shape[0] == state.denom.shape[0]
+    # checkpoint tuple (train.py:394-396) round trip
+    path = tmp_path / "chkpnt7.pth"
+    torch.save((D.capture(pc, opt, state, 1.5), 7), path)
+    model_args, it = torch.load(path, weights_only=False)
+    assert it == 7 and len(model_args) == 13
+    sc2, pc2, net2, view2, gt2 = _build(dev)
+    arena2 = GradArena(list(pc2.parameters()))
+    opt2 = ArenaAdam(arena2, _groups(pc2), eps=1e-15)
+    state2 = D.DensifyState(pc2._xyz.shape[0], dev)
+    assert D.restore(pc2, opt2, state2, model_args) == 1.5
+    for k in _RefModel.NAMES:
+        assert torch.equal(getattr(pc2, k).detach(), getattr(pc, k).detach()), k
+    assert torch.equal(opt2.exp_avg, opt.exp_avg) and torch.equal(opt2.exp_avg_sq, opt.exp_avg_sq)
+    assert opt2._steps == opt._steps
+    stock = torch.optim.Adam([{"params": [torch.nn.Parameter(getattr(pc, k).detach().clone())], "lr": 0.0, "name": k}
+                              for k in LRS if k != "_gaussian_features"], lr=0.0, eps=1e-15)
+    stock.load_state_dict(model_args[11]["GAUSSIAN"])           # each half is a stock Adam state_dict
+    assert len(stock.state) == 6

@@ -77,7 +77,7 @@ EXPORTS = [
     "trase_b200_sample_features_backward", "trase_b200_mlp_fused_set_prof",
     "trase_b200_smooth_features_forward", "trase_b200_smooth_features_backward",
     "trase_b200_mlp_forward_fused_bf16", "trase_b200_mlp_backward_fused_bf16", "trase_b200_wgrad_bf16",
-    "trase_b200_f32_to_bf16",
+    "trase_b200_f32_to_bf16", "trase_b200_arena_gather_rows",
 ]
 
 _lib = None
@@ -175,6 +175,9 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_backward_fused_bf16.restype = C.c_int
     lib.trase_b200_mlp_backward_fused_bf16.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.POINTER(C.c_void_p),
                                                                                              C.c_void_p]
+    lib.trase_b200_arena_gather_rows.restype = C.c_int
+    lib.trase_b200_arena_gather_rows.argtypes = [C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int),
+                                                 C.c_int64] + [C.c_void_p] * 9
     lib.trase_b200_wgrad_bf16.restype = C.c_int
     lib.trase_b200_wgrad_bf16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                           C.c_void_p, C.c_int, C.c_void_p]

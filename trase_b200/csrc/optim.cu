@@ -54,9 +54,72 @@ __global__ void __launch_bounds__(256) densification_stats_kernel(int P, const f
   }
 }
 
+// Densification / pruning as ONE gather pass over the flat arenas (ref: the per-tensor torch.cat / boolean-index
+// re-allocation of every parameter and both Adam moments in cat_tensors_to_optimizer / _prune_optimizer,
+// scene/gaussian_model.py:472-534).  Every per-Gaussian segment s is a [P][width_s] row-major block; output row r of
+// every segment takes input row src[r]; rows flagged `fresh` (clones, split children) start with zero moments.
+constexpr int GATHER_MAX_SEGS = 16;
+struct GatherTable {
+  long long old_off[GATHER_MAX_SEGS], new_off[GATHER_MAX_SEGS];
+  int width[GATHER_MAX_SEGS];
+  int nseg;
+};
+__global__ void __launch_bounds__(256) arena_gather_rows_kernel(const GatherTable t, long long P_new,
+                                                                const long long* __restrict__ src,
+                                                                const unsigned char* __restrict__ fresh,
+                                                                const float* __restrict__ old_p,
+                                                                const float* __restrict__ old_m,
+                                                                const float* __restrict__ old_v, float* __restrict__ new_p,
+                                                                float* __restrict__ new_m, float* __restrict__ new_v) {
+  const int sgi = blockIdx.y;
+  const int w = t.width[sgi];
+  const long long total = P_new * w;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const long long r = e / w;
+    const int c = (int)(e - r * w);
+    const long long from = t.old_off[sgi] + src[r] * w + c, to = t.new_off[sgi] + e;
+    new_p[to] = old_p[from];
+    if (old_m) {
+      const bool z = fresh[r] != 0;
+      new_m[to] = z ? 0.f : old_m[from];
+      new_v[to] = z ? 0.f : old_v[from];
+    }
+  }
+}
+
 }  // namespace tb
 
 using namespace tb;
+
+extern "C" TRASE_API int trase_b200_arena_gather_rows(int nseg, const int64_t* old_off, const int64_t* new_off,
+                                                      const int* width, int64_t P_new, const int64_t* src_rows,
+                                                      const unsigned char* fresh, const float* old_p,
+                                                      const float* old_m, const float* old_v, float* new_p, float* new_m,
+                                                      float* new_v, void* stream) {
+  clear_error();
+  if (P_new <= 0 || nseg <= 0) return 0;
+  if (nseg > GATHER_MAX_SEGS || !old_off || !new_off || !width || !src_rows || !old_p || !new_p ||
+      ((old_m != nullptr) != (old_v != nullptr)) || (old_m && (!new_m || !new_v || !fresh))) {
+    set_error("trase_b200_arena_gather_rows: bad arguments (nseg=%d, at most %d segments)", nseg, GATHER_MAX_SEGS);
+    return 1;
+  }
+  GatherTable t;
+  t.nseg = nseg;
+  int wmax = 1;
+  for (int i = 0; i < nseg; i++) {
+    if (width[i] <= 0) { set_error("trase_b200_arena_gather_rows: segment width must be positive"); return 1; }
+    t.old_off[i] = old_off[i]; t.new_off[i] = new_off[i]; t.width[i] = width[i];
+    if (width[i] > wmax) wmax = width[i];
+  }
+  long long blocks = (P_new * wmax + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  arena_gather_rows_kernel<<<dim3((unsigned)blocks, (unsigned)nseg), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      t, P_new, reinterpret_cast<const long long*>(src_rows), fresh, old_p, old_m, old_v, new_p, new_m, new_v);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_arena_gather_rows: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
 
 extern "C" TRASE_API int trase_b200_adam_step(int64_t n, float* params, const float* grads, float* exp_avg,
                                               float* exp_avg_sq, int nseg, const int64_t* seg_end,
