@@ -248,6 +248,7 @@ class Workload:
         self.gt_dev = torch.empty(3, H, W, device=self.device)
 
     full_arena = False     # True: keep the round-1 arena (feature gradient included) for comparison runs
+    fused_loss = True      # FEATURE state: the fused contrastive-loss kernels (False: the torch N x N formulation)
 
     def _setup_feature(self):
         """FEATURE state (train.py:244-296): only the per-Gaussian segmentation feature trains."""
@@ -369,11 +370,16 @@ class Workload:
             from trase_b200 import feature_utils as FU, loss_utils as LU
             sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks,
                                                   generator=self.sample_gen)
-            C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
             out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16,
                               want_viewspace_grad=False)   # past densify_until_iter nobody reads viewspace_points.grad
             feats = out["render_gaussian_features"]
             reg = LU.feature_norm_reg(feats)
+            if self.fused_loss:
+                # mask matrix, pair weights, similarities and both losses without any N x N tensor (csrc/contrastive.cu)
+                pos, neg = FU.soft_contrastive_losses(feats, masks, sp, sm, positive_th=0.75, negative_th=0.5)
+                self.last_samples = FU.LAST_NUM_SAMPLES
+                return pos + neg + self.rfn * reg
+            C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
             C_F = FU.get_features_correspondence_matrix(feats, sp)        # bilinear resize folded into the gather
             w = FU.get_pixel_weights(masks, sp)
             loss = LU.pixel_mask_correspondence_loss_soft_hard_positive(C=C, C_F=C_F, positive_th=0.75, weights=w) + \
@@ -619,6 +625,7 @@ def run_ours(args, rank, world, device):
     if args.mlp == "torch-tf32":
         torch.backends.cuda.matmul.allow_tf32 = True
     Workload.full_arena = bool(args.full_arena)
+    Workload.fused_loss = not args.torch_feature_loss
     sampler = ClockSampler(device).start() if rank == 0 else None
     wl = Workload(args.workload, device, rank, mlp_backend="native" if args.mlp == "native" else "torch")
     cfg = wl.cfg
@@ -841,6 +848,9 @@ def main():
                     help="reference arm: precision torch may use for the reference DeformNetwork's matmuls")
     ap.add_argument("--full-arena", action="store_true",
                     help="GAUSSIAN state: also accumulate and all-reduce the (untrained) feature gradient, as round 1 did")
+    ap.add_argument("--torch-feature-loss", action="store_true",
+                    help="FEATURE state: evaluate the contrastive loss with the torch N x N formulation instead of the "
+                         "fused kernels")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--reserve-sms", type=int, default=None,
                     help="SMs the persistent MLP kernels leave to the concurrent NCCL all-reduce (default: 0 at N=1, "

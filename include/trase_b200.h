@@ -276,6 +276,33 @@ TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const float* scalin
                                            float* g_opacity, float* g_fdc, float* g_frest, float* g_feat,
                                            void* stream);
 
+/* FEATURE-state contrastive loss on the sampled pixels without the N x N matrices.
+ * ref: train.py:253-296 in the default 'soft' mode: get_pixel_mask_correspondence_matrix and get_pixel_weights
+ * (utils/feature_utils.py:28-48), C_F = F F^T (:50-55), pixel_mask_correspondence_loss_soft_hard_positive /
+ * _soft_negative (utils/loss_utils.py:304-349).  The reference materialises four N x N tensors (N ~ 5000) and runs
+ * ~40 kernels plus two host synchronisations per loss over them; here the mask relation, the pair weights and the
+ * similarities are recomputed from per-pixel data in three sweeps over the pair space.
+ *   trase_b200_pixel_mask_info: masks [n_masks][HW] uint8 (n_masks <= 256), area[m] = pixels of mask m (int64),
+ *     sampled_mask [n_masks] (0/1), pix [N] = flat indices of the sampled pixels  ->  bits [N][ceil(n_masks/64)]
+ *     (bit m: pixel lies in sampled mask m) and a [N] = mean area of all masks covering the pixel.
+ *   trase_b200_contrastive_soft_forward: f [N][32] L2-normalised sampled features; a / a_minmax ({min a, max a}, device)
+ *     may be NULL (no pair weights); writes result[0..5] = {loss_pos, loss_neg, n_kept_pos, n_kept_neg, selected
+ *     positive pairs, selected negative pairs} and keeps the mined-column flags in `scratch`
+ *     (trase_b200_contrastive_scratch_bytes) for the backward.
+ *   trase_b200_contrastive_soft_backward: df [N][32] = upstream[0] * d loss_pos/df + upstream[1] * d loss_neg/df
+ *     (upstream: two device floats), from the same inputs, scratch and result. */
+TRASE_API size_t trase_b200_contrastive_scratch_bytes(int N);
+TRASE_API int trase_b200_pixel_mask_info(int N, int n_masks, int64_t HW, const unsigned char* masks, const int64_t* area,
+                                         const unsigned char* sampled_mask, const int64_t* pix, uint64_t* bits, float* a,
+                                         void* stream);
+TRASE_API int trase_b200_contrastive_soft_forward(int N, int nwords, const float* f, const uint64_t* bits, const float* a,
+                                                  const float* a_minmax, float pos_th, float neg_th, void* scratch,
+                                                  float* result, void* stream);
+TRASE_API int trase_b200_contrastive_soft_backward(int N, int nwords, const float* f, const uint64_t* bits,
+                                                   const float* a, const float* a_minmax, float pos_th, float neg_th,
+                                                   const void* scratch, const float* result, const float* upstream,
+                                                   float* df, void* stream);
+
 /* kNN-smoothed per-Gaussian features.  ref: GaussianModel.get_smoothed_gaussian_features
  * (scene/gaussian_model.py:79-104), the FEATURE state's default input to render()
  * (train.py:274-275 with smooth_K = 16, gaussian_renderer/__init__.py:116-119):
@@ -474,6 +501,13 @@ TRASE_API int trase_b200_wgrad_bf16(const void* P, int ldp, int I, const void* Q
                                     int ldd, void* stream);
 TRASE_API int trase_b200_f32_to_bf16(int rows, int cols, const float* src, int ld_src, void* dst, int ld_dst,
                                      void* stream);
+/* The two producers of those small operands can write the bf16 copy themselves (no separate conversion pass):
+ * the positional encoding (out16 [M][ld16], ld16 a multiple of 8 and >= the column count, padding zero-filled) and the
+ * packed head gradient (dout16 [M][16]). */
+TRASE_API int trase_b200_deform_embed_bf16(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt,
+                                           float* out, int ld, void* out16, int ld16, void* stream);
+TRASE_API int trase_b200_mlp_pack_dout_bf16(int M, const float* g0, const float* g1, const float* g2, float* dout,
+                                            void* dout16, float* colsum, void* stream);
 /* Debug only (no reference counterpart): device buffer of [grid][8] uint64 stall-cycle counters that the
  * whole-network kernels fill when set (NULL = off); read by tools/check_fused_mlp.py. */
 TRASE_API void trase_b200_mlp_fused_set_prof(unsigned long long* dev_buf);

@@ -95,3 +95,59 @@ def test_feature_state_loss_and_gradient_on_gpu(native_lib, tag):
         assert abs(float(got) - ref) <= 2e-5 * max(1.0, abs(ref))
     gref = g[tag + "_grad"]
     assert np.abs(feat.grad.cpu().numpy() - gref).max() <= 1e-4 * np.abs(gref).max()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", CASES)
+def test_fused_soft_contrastive_losses_on_gpu(native_lib, tag):
+    """The same loss through the fused kernels that never build an N x N tensor (csrc/contrastive.cu): values and the
+    gradient w.r.t. the rendered feature image against the reference's golden vectors, and the per-pixel mask data
+    (membership bits, mean mask area) against the torch formulation."""
+    g = load_golden("contrastive")
+    dev = torch.device("cuda:0")
+    masks, feat, sp, sm = _case(g, tag, dev)
+    feat.requires_grad_(True)
+    reg = LU.feature_norm_reg(feat)
+    pos, neg = FU.soft_contrastive_losses(feat, masks, sp, sm, positive_th=0.75, negative_th=0.5)
+    loss = pos + neg + 1.0 * reg
+    loss.backward()
+    vals = g[tag + "_vals"]
+    for got, ref in zip((pos, neg, reg, loss), vals):
+        assert abs(float(got.detach()) - ref) <= 2e-5 * max(1.0, abs(ref)), (float(got.detach()), ref)
+    gref = g[tag + "_grad"]
+    assert np.abs(feat.grad.cpu().numpy() - gref).max() <= 1e-4 * np.abs(gref).max()
+
+
+@pytest.mark.gpu
+def test_fused_soft_contrastive_matches_torch_formulation_at_training_size(native_lib):
+    """~4000 sampled pixels, 25 masks, unweighted and weighted: fused kernels against the torch restatement (which is
+    pinned to the reference by the golden vectors above).  A column whose only mining pair sits within rounding of a
+    threshold may flip between the two evaluations of C_F; the values must still agree to 1e-4."""
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(11)
+    H, W, Hm, Wm, n_masks = 240, 136, 120, 68, 25
+    masks = torch.zeros(n_masks, Hm, Wm, dtype=torch.uint8)
+    for i in range(n_masks):
+        h, w = int(torch.randint(10, 60, (1,), generator=gen)), int(torch.randint(8, 34, (1,), generator=gen))
+        y, x = int(torch.randint(0, Hm - h, (1,), generator=gen)), int(torch.randint(0, Wm - w, (1,), generator=gen))
+        masks[i, y:y + h, x:x + w] = 1
+    masks = masks.to(dev)
+    base = torch.randn(32, 1, 1, generator=gen)
+    feat0 = (0.6 * torch.randn(32, H, W, generator=gen) + base).to(dev)
+    sp, sm = FU.get_sample_pixel_and_mask(masks, 4000, 20, generator=torch.Generator(device=dev).manual_seed(3))
+    for use_w in (False, True):
+        f1 = feat0.clone().requires_grad_(True)
+        C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
+        C_F = FU.get_features_correspondence_matrix(f1, sp)
+        w = FU.get_pixel_weights(masks, sp) if use_w else None
+        p1 = LU.pixel_mask_correspondence_loss_soft_hard_positive(C=C, C_F=C_F, positive_th=0.75, weights=w)
+        n1 = LU.pixel_mask_correspondence_loss_soft_negative(C=C, C_F=C_F, negative_th=0.5, weights=w)
+        (p1 + 2.0 * n1).backward()
+        f2 = feat0.clone().requires_grad_(True)
+        p2, n2 = FU.soft_contrastive_losses(f2, masks, sp, sm, 0.75, 0.5, use_weights=use_w)
+        (p2 + 2.0 * n2).backward()
+        assert C_F.shape[0] > 2000 and float(n1) != 0.0 and float(p1) != 0.0
+        assert abs(float(p1) - float(p2)) <= 1e-4 * max(1e-3, abs(float(p1))), (float(p1), float(p2))
+        assert abs(float(n1) - float(n2)) <= 1e-4 * max(1e-3, abs(float(n1))), (float(n1), float(n2))
+        gmax = f1.grad.abs().max()
+        assert (f1.grad - f2.grad).abs().max() <= 2e-4 * gmax

@@ -219,8 +219,8 @@ def test_densify_prune_and_opacity_reset_match_the_per_tensor_procedure(native_l
     ref.accum, ref.denom = state.xyz_gradient_accum.clone(), state.denom.clone()
     ref.max_radii2D = state.max_radii2D.clone()
     thr = float((state.xyz_gradient_accum / state.denom.clamp_min(1)).quantile(0.9))     # top 10 % densify
-    extent = 2.0
-    with torch.no_grad():                              # make the split branch and the opacity prune fire too
+    extent = 100.0 * float(torch.exp(pc._scaling.detach()).max(dim=1).values.median())   # percent_dense * extent = the
+    with torch.no_grad():                              # median size: clone and split both fire; and the two prune rules
         big = torch.arange(P0, device=dev) % 7 == 0
         pc._scaling.data[big] += 2.5
         ref.p["_scaling"].data[big] += 2.5

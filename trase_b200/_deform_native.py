@@ -183,13 +183,20 @@ class _DeformMLP(torch.autograd.Function):
             # TF32-rounded weights (forward operand of the layer chain) and their transposes (backward operand);
             # the fused forward packs its own operand, so there the transposes are left to backward()
             Wr, WrT = (None, [None] * nl) if fused else _round_transpose(lib, Ws, sizes, skip, E, True, f32, s)
-            emb = None
+            emb, emb16 = None, None
+            bf16 = fused and keep and BF16_WGRAD and FUSED_BACKWARD and lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
             if fused:
                 # the positional encoding is the longest of the small preparatory kernels: launched first, it
                 # covers the host time needed to launch the others
                 emb = torch.empty((M, E), **f32)
-                _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt, emb.data_ptr(),
-                                                       emb.stride(0), s))
+                if bf16:      # backward reads the embedding only as a weight-gradient operand: a bf16 copy for it
+                    emb16 = torch.empty((M, (E + 7) // 8 * 8), dtype=torch.bfloat16, device=dev)
+                    _lib.check(lib.trase_b200_deform_embed_bf16(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt,
+                                                                emb.data_ptr(), emb.stride(0), emb16.data_ptr(),
+                                                                emb16.stride(0), s))
+                else:
+                    _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt,
+                                                           emb.data_ptr(), emb.stride(0), s))
             hb = torch.empty(16 * W * 2 + 16, **f32)
             wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
             _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
@@ -209,15 +216,13 @@ class _DeformMLP(torch.autograd.Function):
                                                                     out16.data_ptr(), s))
                     return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
                 masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
-                bf16 = BF16_WGRAD and FUSED_BACKWARD and lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
                 acts_all = torch.empty((nl, M, W), dtype=torch.bfloat16 if bf16 else torch.float32, device=dev)
                 fwd = lib.trase_b200_mlp_forward_fused_bf16 if bf16 else lib.trase_b200_mlp_forward_fused
                 with _Span("mlp_fwd"):
                     _lib.check(fwd(M, nl, skip, E, emb.data_ptr(), emb.stride(0), wpack.data_ptr(), ball.data_ptr(),
                                    acts_all.data_ptr(), masks.data_ptr(), out16.data_ptr(), s))
                 acts = list(acts_all.unbind(0))
-                # backward reads the embedding only as a weight-gradient operand: keep the bf16 copy in that case
-                skipbuf = _to_bf16(lib, emb, E, (E + 7) // 8 * 8) if bf16 else emb
+                skipbuf = emb16 if bf16 else emb
             else:
                 masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
                 # skip buffer [M, E + W]: embedding in [:, :E], output of layer `skip` in [:, E:]
@@ -281,11 +286,15 @@ class _DeformMLP(torch.autograd.Function):
             dbh = gbuf[off + W * 16:off + W * 16 + 16]
             dout = torch.empty((M, 16), **f32)
             gs = [None if g is None else g.contiguous() for g in (g_xyz, g_rot, g_scale)]
-            _lib.check(lib.trase_b200_mlp_pack_dout(M, *[None if g is None else g.data_ptr() for g in gs],
-                                                    dout.data_ptr(), dbh.data_ptr(), s))
+            gp = [None if g is None else g.data_ptr() for g in gs]
+            dout16 = torch.empty((M, 16), dtype=torch.bfloat16, device=dev) if bf16 else None
+            if bf16:
+                _lib.check(lib.trase_b200_mlp_pack_dout_bf16(M, *gp, dout.data_ptr(), dout16.data_ptr(), dbh.data_ptr(), s))
+            else:
+                _lib.check(lib.trase_b200_mlp_pack_dout(M, *gp, dout.data_ptr(), dbh.data_ptr(), s))
             # heads: dWh^T = h_last^T dout
             with _Span("mlp_wgrad"):
-                wgrad(lib, acts[-1], _to_bf16(lib, dout, 16, 16) if bf16 else dout, dwhT)
+                wgrad(lib, acts[-1], dout16 if bf16 else dout, dwhT)
             if fused_bwd:
                 # the whole data-gradient chain in one persistent kernel (csrc/mlp_fused.cu): dzs[L] = dZ of
                 # layer nl-1-L, bias gradients straight into their targets

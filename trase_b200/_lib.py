@@ -77,7 +77,9 @@ EXPORTS = [
     "trase_b200_sample_features_backward", "trase_b200_mlp_fused_set_prof",
     "trase_b200_smooth_features_forward", "trase_b200_smooth_features_backward",
     "trase_b200_mlp_forward_fused_bf16", "trase_b200_mlp_backward_fused_bf16", "trase_b200_wgrad_bf16",
-    "trase_b200_f32_to_bf16", "trase_b200_arena_gather_rows",
+    "trase_b200_f32_to_bf16", "trase_b200_arena_gather_rows", "trase_b200_contrastive_scratch_bytes",
+    "trase_b200_pixel_mask_info", "trase_b200_contrastive_soft_forward", "trase_b200_contrastive_soft_backward",
+    "trase_b200_deform_embed_bf16", "trase_b200_mlp_pack_dout_bf16",
 ]
 
 _lib = None
@@ -178,6 +180,21 @@ def load() -> C.CDLL:
     lib.trase_b200_arena_gather_rows.restype = C.c_int
     lib.trase_b200_arena_gather_rows.argtypes = [C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int),
                                                  C.c_int64] + [C.c_void_p] * 9
+    lib.trase_b200_contrastive_scratch_bytes.restype = C.c_size_t
+    lib.trase_b200_contrastive_scratch_bytes.argtypes = [C.c_int]
+    lib.trase_b200_pixel_mask_info.restype = C.c_int
+    lib.trase_b200_pixel_mask_info.argtypes = [C.c_int, C.c_int, C.c_int64] + [C.c_void_p] * 7
+    lib.trase_b200_contrastive_soft_forward.restype = C.c_int
+    lib.trase_b200_contrastive_soft_forward.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_float, C.c_float] + \
+        [C.c_void_p] * 3
+    lib.trase_b200_contrastive_soft_backward.restype = C.c_int
+    lib.trase_b200_contrastive_soft_backward.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_float, C.c_float] + \
+        [C.c_void_p] * 5
+    lib.trase_b200_deform_embed_bf16.restype = C.c_int
+    lib.trase_b200_deform_embed_bf16.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                                 C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+    lib.trase_b200_mlp_pack_dout_bf16.restype = C.c_int
+    lib.trase_b200_mlp_pack_dout_bf16.argtypes = [C.c_int] + [C.c_void_p] * 7
     lib.trase_b200_wgrad_bf16.restype = C.c_int
     lib.trase_b200_wgrad_bf16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                           C.c_void_p, C.c_int, C.c_void_p]

@@ -772,7 +772,8 @@ __device__ __forceinline__ float rna_tf32(float x) {
 constexpr int EMB_MAX_COLS = 128;
 __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* __restrict__ xyz,
                                                            const float* __restrict__ t, int t_stride, int Lx, int Lt,
-                                                           float* __restrict__ out, int ld) {
+                                                           float* __restrict__ out, int ld,
+                                                           __nv_bfloat16* __restrict__ out16, int ld16) {
   __shared__ float s_row[8][EMB_MAX_COLS];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int warps_per_grid = (gridDim.x * blockDim.x) >> 5;
@@ -815,6 +816,10 @@ __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* _
     __syncwarp();
     float* o = out + (size_t)m * ld;
     for (int c = lane; c < ncol; c += 32) o[c] = rna_tf32(row[c]);
+    if (out16) {         // bf16 copy for the weight-gradient products (columns up to ld16 zero-filled)
+      __nv_bfloat16* o16 = out16 + (size_t)m * ld16;
+      for (int c = lane; c < ld16; c += 32) o16[c] = __float2bfloat16_rn(c < ncol ? row[c] : 0.f);
+    }
     __syncwarp();
   }
 }
@@ -823,8 +828,24 @@ __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* _
 }  // namespace tb
 
 // t_stride = 0 broadcasts a single time value to all rows (the usual case: one time stamp per view).
+static int deform_embed_impl(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt, float* out, int ld,
+                             void* out16, int ld16, void* stream);
 extern "C" TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt,
                                                  float* out, int ld, void* stream) {
+  return deform_embed_impl(M, xyz, t, t_stride, Lx, Lt, out, ld, nullptr, 0, stream);
+}
+// same, also writing a bf16 copy out16 [M][ld16] (ld16 >= the column count, a multiple of 8; padding zero-filled):
+// the operand of the bf16 weight-gradient products of the two layers that read the embedding
+extern "C" TRASE_API int trase_b200_deform_embed_bf16(int M, const float* xyz, const float* t, int t_stride, int Lx,
+                                                      int Lt, float* out, int ld, void* out16, int ld16, void* stream) {
+  if (M > 0 && (!out16 || (ld16 & 7) || ld16 < 3 + 6 * Lx + 1 + 2 * Lt || ld16 > tb::mlp::EMB_MAX_COLS)) {
+    tb::set_error("trase_b200_deform_embed_bf16: bad arguments");
+    return 1;
+  }
+  return deform_embed_impl(M, xyz, t, t_stride, Lx, Lt, out, ld, out16, ld16, stream);
+}
+static int deform_embed_impl(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt, float* out, int ld,
+                             void* out16, int ld16, void* stream) {
   using namespace tb;
   if (M <= 0) return 0;
   if (!xyz || !t || !out || Lx < 0 || Lt < 0 || ld < 3 + 6 * Lx + 1 + 2 * Lt ||
@@ -833,8 +854,8 @@ extern "C" TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const 
     return 1;
   }
   const int blocks = (M + 7) / 8 < 148 * 16 ? (M + 7) / 8 : 148 * 16;
-  mlp::deform_embed_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(M, xyz, t, t_stride, Lx, Lt, out,
-                                                                                      ld);
+  mlp::deform_embed_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      M, xyz, t, t_stride, Lx, Lt, out, ld, reinterpret_cast<__nv_bfloat16*>(out16), ld16);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_deform_embed: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);

@@ -3,6 +3,7 @@
 // three upstream gradients into one [M][16] operand (+ their column sums = head bias
 // gradients).  Each replaces a handful of elementwise torch kernels per layer.
 #include "common.cuh"
+#include <cuda_bf16.h>
 
 namespace tb {
 namespace mlp {
@@ -61,7 +62,7 @@ __global__ void __launch_bounds__(256) pack_heads_kernel(const float* __restrict
 // dout[m][16] = rna([g0[m][0..2], g1[m][0..3], g2[m][0..2], 0...]);  colsum[j] += sum_m (unrounded) values
 __global__ void __launch_bounds__(256) pack_dout_kernel(int M, const float* __restrict__ g0, const float* __restrict__ g1,
                                                         const float* __restrict__ g2, float* __restrict__ dout,
-                                                        float* __restrict__ colsum) {
+                                                        __nv_bfloat16* __restrict__ dout16, float* __restrict__ colsum) {
   __shared__ float s_sum[8][16];
   const int lane16 = threadIdx.x & 15;             // column
   const int rsub = threadIdx.x >> 4;               // 16 rows per block iteration
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(256) pack_dout_kernel(int M, const float* __re
     else if (lane16 < 10) v = g2 ? g2[(size_t)m * 3 + (lane16 - 7)] : 0.f;
     acc += v;
     dout[(size_t)m * 16 + lane16] = rna(v);
+    if (dout16) dout16[(size_t)m * 16 + lane16] = __float2bfloat16_rn(v);   // operand of the bf16 head weight gradient
   }
   // rows live in lanes {l, l+16} of each warp and in the 8 warps
   acc += __shfl_xor_sync(0xffffffffu, acc, 16);
@@ -120,13 +122,26 @@ extern "C" TRASE_API int trase_b200_mlp_pack_heads(const float* w0, const float*
   return 0;
 }
 
+static int pack_dout_impl(int M, const float* g0, const float* g1, const float* g2, float* dout, void* dout16,
+                          float* colsum, void* stream);
 extern "C" TRASE_API int trase_b200_mlp_pack_dout(int M, const float* g0, const float* g1, const float* g2, float* dout,
                                                   float* colsum, void* stream) {
+  return pack_dout_impl(M, g0, g1, g2, dout, nullptr, colsum, stream);
+}
+// same, also writing the [M][16] bf16 copy that trase_b200_wgrad_bf16 multiplies with the last activations
+extern "C" TRASE_API int trase_b200_mlp_pack_dout_bf16(int M, const float* g0, const float* g1, const float* g2,
+                                                       float* dout, void* dout16, float* colsum, void* stream) {
+  if (M > 0 && !dout16) { set_error("trase_b200_mlp_pack_dout_bf16: bad arguments"); return 1; }
+  return pack_dout_impl(M, g0, g1, g2, dout, dout16, colsum, stream);
+}
+static int pack_dout_impl(int M, const float* g0, const float* g1, const float* g2, float* dout, void* dout16,
+                          float* colsum, void* stream) {
   if (M <= 0) return 0;
   if (!dout || !colsum) { set_error("trase_b200_mlp_pack_dout: bad arguments"); return 1; }
   int grid = (M + 15) / 16;
   if (grid > 148 * 8) grid = 148 * 8;
-  mlp::pack_dout_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(M, g0, g1, g2, dout, colsum);
+  mlp::pack_dout_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      M, g0, g1, g2, dout, reinterpret_cast<__nv_bfloat16*>(dout16), colsum);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_dout: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);

@@ -123,3 +123,83 @@ def build_feature_smooth_map(xyz, K=16):
     pts = xyz.detach().cpu().double().numpy()
     _, idx = cKDTree(pts).query(pts, k=K)
     return torch.from_numpy(idx.reshape(len(pts), K)).to(device=xyz.device, dtype=torch.int64)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# The whole 'soft' contrastive loss of the FEATURE state on the sampled pixels, without any N x N tensor
+# (csrc/contrastive.cu): mask relation, pair weights and similarities are recomputed from per-pixel data.
+LAST_NUM_SAMPLES = 0
+
+
+class _SoftContrastive(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, f, bits, a, a_minmax, pos_th, neg_th):
+        lib = _lib.load()
+        dev = f.device
+        N, nwords = int(f.shape[0]), int(bits.shape[1])
+        fc = f.detach().contiguous().float()
+        with torch.cuda.device(dev):
+            scratch = torch.empty(max(1, lib.trase_b200_contrastive_scratch_bytes(N)), dtype=torch.uint8, device=dev)
+            result = torch.zeros(8, dtype=torch.float32, device=dev)
+            _lib.check(lib.trase_b200_contrastive_soft_forward(
+                N, nwords, fc.data_ptr(), bits.data_ptr(), None if a is None else a.data_ptr(),
+                None if a is None else a_minmax.data_ptr(), float(pos_th), float(neg_th), scratch.data_ptr(),
+                result.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+        ctx.save_for_backward(fc, bits, a, a_minmax, scratch, result)
+        ctx.th = (float(pos_th), float(neg_th))
+        return result[0:2].clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _lib.load()
+        fc, bits, a, a_minmax, scratch, result = ctx.saved_tensors
+        dev = fc.device
+        N, nwords = int(fc.shape[0]), int(bits.shape[1])
+        with torch.cuda.device(dev):
+            up = g.detach().contiguous().float()
+            df = torch.zeros_like(fc)
+            _lib.check(lib.trase_b200_contrastive_soft_backward(
+                N, nwords, fc.data_ptr(), bits.data_ptr(), None if a is None else a.data_ptr(),
+                None if a is None else a_minmax.data_ptr(), ctx.th[0], ctx.th[1], scratch.data_ptr(), result.data_ptr(),
+                up.data_ptr(), df.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+        return df, None, None, None, None, None
+
+
+def soft_contrastive_losses(rendered_features, sam_masks, sampled_pixel, sampled_mask, positive_th=0.75,
+                            negative_th=0.5, use_weights=True):
+    """(positive loss, negative loss) of train.py:283-292 in the default contrastive_mode 'soft', i.e.
+
+        C   = get_pixel_mask_correspondence_matrix(sam_masks, sampled_pixel, sampled_mask)
+        C_F = get_features_correspondence_matrix(F.interpolate(rendered_features, mask resolution), sampled_pixel)
+        w   = get_pixel_weights(sam_masks, sampled_pixel)
+        pixel_mask_correspondence_loss_soft_hard_positive(C, C_F, positive_th, w),  ..._soft_negative(C, C_F, negative_th, w)
+
+    evaluated by four kernels that never build an N x N tensor.  `rendered_features` is the FULL-resolution [32,H,W]
+    feature image (the bilinear resize is folded into the sampling).  CUDA only; up to 256 masks."""
+    lib = _lib.load()
+    if not rendered_features.is_cuda:
+        raise RuntimeError("trase_b200: soft_contrastive_losses runs on CUDA tensors only")
+    dev = rendered_features.device
+    n_masks, Hm, Wm = int(sam_masks.shape[0]), int(sam_masks.shape[-2]), int(sam_masks.shape[-1])
+    if n_masks > 256:
+        raise RuntimeError("trase_b200: soft_contrastive_losses handles at most 256 masks per view")
+    pix = sampled_pixel.reshape(-1).nonzero().reshape(-1)        # one host sync, like the reference's boolean index
+    f = _SampleFeatures.apply(rendered_features, pix, Hm, Wm, True)           # [N, 32] normalised, differentiable
+    N = int(pix.numel())
+    global LAST_NUM_SAMPLES
+    LAST_NUM_SAMPLES = N                    # for reports (bench.py): how many pixels the last call sampled
+    if N == 0:
+        z = f.sum() * 0.0
+        return z, z
+    with torch.no_grad(), torch.cuda.device(dev):
+        m8 = sam_masks.to(device=dev, dtype=torch.uint8).contiguous()
+        area = m8.sum(dim=(-2, -1), dtype=torch.int64)
+        sm8 = sampled_mask.to(device=dev, dtype=torch.uint8).contiguous()
+        bits = torch.empty((N, (n_masks + 63) // 64), dtype=torch.int64, device=dev)
+        a = torch.empty((N,), dtype=torch.float32, device=dev)
+        _lib.check(lib.trase_b200_pixel_mask_info(N, n_masks, Hm * Wm, m8.data_ptr(), area.data_ptr(), sm8.data_ptr(),
+                                                  pix.data_ptr(), bits.data_ptr(), a.data_ptr(),
+                                                  torch.cuda.current_stream(dev).cuda_stream))
+        a_minmax = torch.stack([a.min(), a.max()]) if use_weights else None
+    out = _SoftContrastive.apply(f, bits, a if use_weights else None, a_minmax, positive_th, negative_th)
+    return out[0], out[1]
