@@ -267,6 +267,8 @@ class Workload:
         self.masks_stage = [torch.empty_like(m, device=self.device) for m in self.masks_host]
         self.num_sampled_pixels, self.num_sampled_masks, self.rfn = 5000, 25, 1.0
         self.sample_gen = torch.Generator(device=self.device).manual_seed(4242 + self.rank)
+        self.sample_stream = torch.cuda.Stream(device=self.device)
+        self.mask_free = {}
         self.last_samples = 0
 
     def _setup_style(self):
@@ -364,20 +366,37 @@ class Workload:
         return float(self.loss_host[0])
 
     # ---- FEATURE state (config 3) ---------------------------------------------
-    def _feature_view_loss(self, view, time_t, masks):
+    def _feature_view_loss(self, view, time_t, masks, masks_host=None):
         """train.py:244-296 for one view; returns the loss tensor."""
         if self.ref is None:
             from trase_b200 import feature_utils as FU, loss_utils as LU
-            sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks,
-                                                  generator=self.sample_gen)
+            # The sampling (train.py:253) does not depend on the render: it runs on a side stream, so the host
+            # synchronisation that brings the sample count back waits for that stream only and the launches of this
+            # view's MLP and render are not held up behind the previous view's backward.
+            main = torch.cuda.current_stream()
+            with torch.cuda.stream(self.sample_stream):
+                if masks_host is not None:                      # e2e: this view's masks come from pinned host memory
+                    ev = self.mask_free.get(masks.data_ptr())   # (the previous step's loss has finished reading them)
+                    if ev is not None:
+                        self.sample_stream.wait_event(ev)
+                    masks.copy_(masks_host, non_blocking=True)
+                sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks,
+                                                      generator=self.sample_gen)
+                pix = FU.sampled_pixel_indices(sp) if self.fused_loss else None
+            main.wait_stream(self.sample_stream)
+            for t_ in (sp, sm, pix):
+                if t_ is not None:
+                    t_.record_stream(main)
             out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16,
                               want_viewspace_grad=False)   # past densify_until_iter nobody reads viewspace_points.grad
             feats = out["render_gaussian_features"]
             reg = LU.feature_norm_reg(feats)
             if self.fused_loss:
                 # mask matrix, pair weights, similarities and both losses without any N x N tensor (csrc/contrastive.cu)
-                pos, neg = FU.soft_contrastive_losses(feats, masks, sp, sm, positive_th=0.75, negative_th=0.5)
+                pos, neg = FU.soft_contrastive_losses(feats, masks, sp, sm, positive_th=0.75, negative_th=0.5, pix=pix)
                 self.last_samples = FU.LAST_NUM_SAMPLES
+                if masks_host is not None:
+                    self.mask_free.setdefault(masks.data_ptr(), torch.cuda.Event()).record(main)
                 return pos + neg + self.rfn * reg
             C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
             C_F = FU.get_features_correspondence_matrix(feats, sp)        # bilinear resize folded into the gather
@@ -389,6 +408,8 @@ class Workload:
             return loss
         ru = self.ref.utils
         FU, LU = ru.feature_utils, ru.loss_utils
+        if masks_host is not None:
+            masks.copy_(masks_host, non_blocking=True)
         sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks)
         C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
         out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16,
@@ -417,8 +438,7 @@ class Workload:
         self.arena.zero_()
         for v in range(self.nviews):
             view, t = self._host_view(v)
-            self.masks_stage[v].copy_(self.masks_host[v], non_blocking=True)
-            loss = self._feature_view_loss(view, t, self.masks_stage[v])
+            loss = self._feature_view_loss(view, t, self.masks_stage[v], self.masks_host[v])
             self.loss_host[v:v + 1].copy_(loss.detach().reshape(1), non_blocking=True)
             if v == self.nviews - 1:
                 self.loss_event.record()

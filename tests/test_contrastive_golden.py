@@ -133,7 +133,7 @@ def test_fused_soft_contrastive_matches_torch_formulation_at_training_size(nativ
         masks[i, y:y + h, x:x + w] = 1
     masks = masks.to(dev)
     base = torch.randn(32, 1, 1, generator=gen)
-    feat0 = (0.6 * torch.randn(32, H, W, generator=gen) + base).to(dev)
+    feat0 = (1.5 * torch.randn(32, H, W, generator=gen) + base).to(dev)   # similarities straddle both thresholds
     sp, sm = FU.get_sample_pixel_and_mask(masks, 4000, 20, generator=torch.Generator(device=dev).manual_seed(3))
     for use_w in (False, True):
         f1 = feat0.clone().requires_grad_(True)

@@ -165,8 +165,17 @@ class _SoftContrastive(torch.autograd.Function):
         return df, None, None, None, None, None
 
 
+def sampled_pixel_indices(sampled_pixel):
+    """Flat indices of the True entries of the [Hm, Wm] sample mask, in row-major order (what boolean indexing
+    yields).  This is the one host synchronisation of the loss front end (the count has to reach the host); it only
+    depends on the sampling, not on the render, so a training loop can take it BEFORE launching the render — or on a
+    side stream — and pass the result to soft_contrastive_losses(..., pix=...), instead of stalling between the
+    forward pass and the loss."""
+    return sampled_pixel.reshape(-1).nonzero().reshape(-1)
+
+
 def soft_contrastive_losses(rendered_features, sam_masks, sampled_pixel, sampled_mask, positive_th=0.75,
-                            negative_th=0.5, use_weights=True):
+                            negative_th=0.5, use_weights=True, pix=None):
     """(positive loss, negative loss) of train.py:283-292 in the default contrastive_mode 'soft', i.e.
 
         C   = get_pixel_mask_correspondence_matrix(sam_masks, sampled_pixel, sampled_mask)
@@ -183,7 +192,8 @@ def soft_contrastive_losses(rendered_features, sam_masks, sampled_pixel, sampled
     n_masks, Hm, Wm = int(sam_masks.shape[0]), int(sam_masks.shape[-2]), int(sam_masks.shape[-1])
     if n_masks > 256:
         raise RuntimeError("trase_b200: soft_contrastive_losses handles at most 256 masks per view")
-    pix = sampled_pixel.reshape(-1).nonzero().reshape(-1)        # one host sync, like the reference's boolean index
+    if pix is None:
+        pix = sampled_pixel_indices(sampled_pixel)                # one host sync, like the reference's boolean index
     f = _SampleFeatures.apply(rendered_features, pix, Hm, Wm, True)           # [N, 32] normalised, differentiable
     N = int(pix.numel())
     global LAST_NUM_SAMPLES
