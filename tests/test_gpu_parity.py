@@ -335,9 +335,9 @@ def test_partial_gradient_variants_equal_the_full_backward(native_lib, ppt):
     assert no_df["objects"] is None and all(df_only[k] is None for k in GRAD_NAMES if k != "objects")
     for k in GRAD_NAMES:
         if k != "objects":
-            assert rel_err(_np(full[k]), _np(no_df[k])) <= 1e-5, k        # same arithmetic, other atomic order
-            assert rel_err(_np(zero_obj[k]), _np(col_only[k])) <= 1e-5, k
-    assert rel_err(_np(full["objects"]), _np(df_only["objects"])) <= 1e-5
+            assert rel_err(_np(full[k]), _np(no_df[k])) <= 1e-4, k        # same arithmetic, other atomic order
+            assert rel_err(_np(zero_obj[k]), _np(col_only[k])) <= 1e-4, k
+    assert rel_err(_np(full["objects"]), _np(df_only["objects"])) <= 1e-4
     assert float(full["objects"].abs().max()) > 0
 
 

@@ -12,8 +12,9 @@
 //                  its minimum over all pairs is exactly 1 (the pair of the largest a with itself) and its maximum
 //                  clamp(top / (a_min a_min), 1), so the min-max normalisation needs only a_min and a_max
 //   C_F[i][j]    = f_i . f_j  (32 channels)
-// so three sweeps over the pair space recompute them on the fly, each block owning 64 pixels and looping over all
-// 64-pixel tiles of partners (one wave of ~80 blocks, no atomics, fixed summation order = deterministic):
+// so three sweeps over the pair space recompute them on the fly.  A block owns 64 pixels and walks 64-pixel tiles of
+// partners (the tiles of one owner are split over a few blocks so that two waves of the SMs are busy); similarities
+// come from channel-major shared-memory tiles with two 16-byte reads per channel for a 4 x 4 patch per thread:
 //   FLAGS: kept_pos[j] = any_i (C_F < pos_th and same mask), kept_neg[j] = any_i (C_F > neg_th and different mask)
 //          — over ALL i, the diagonal included, exactly like torch.any(..., dim=0);
 //   LOSS : pairs i < j of kept columns: sum of -w C_F (same mask) and of w relu(C_F) (different mask), pair counts;
@@ -43,58 +44,67 @@ struct Params {
   float* df;                      // [N][32] (GRAD)
 };
 
+// Pair weight (feature_utils.py:31-37):  (clamp(top / (a_i a_j), 1) - 1) / (hi - 1) * 9 + 1, top = (max a)^2,
+// hi = clamp(top / (min a)^2, 1) (the minimum of the clamped ratio over all pairs is exactly 1: the largest a with
+// itself).  Evaluated as (max(ra_i * ra_j, 1) - 1) * k9 + 1 with ra = max a / a per pixel and k9 = 9 / (hi - 1): no
+// division per pair (differs from the reference's rounding by an ulp or two; all-equal areas give hi = 1, k9 = inf
+// and NaN weights, as in the reference).
 struct WeightCtx {
-  float top, hi;                  // (max a)^2 and the largest clamped ratio
+  float amax, k9;
   bool on;
 };
 __device__ __forceinline__ WeightCtx weight_ctx(const Params& p) {
   WeightCtx w;
   w.on = p.use_weights != 0;
+  w.amax = 1.f;
+  w.k9 = 0.f;
   if (w.on) {
     const float amin = p.a_minmax[0], amax = p.a_minmax[1];
-    w.top = amax * amax;
     float pr = amin * amin;
     if (pr == 0.f) pr = 1e10f;
-    w.hi = fmaxf(w.top / pr, 1.0f);
-  } else {
-    w.top = w.hi = 1.f;
+    const float hi = fmaxf((amax * amax) / pr, 1.0f);
+    w.amax = amax;
+    w.k9 = 9.0f / (hi - 1.0f);
   }
   return w;
 }
-// (clamp(top / (a_i a_j), 1) - 1) / (hi - 1) * 9 + 1     (feature_utils.py:31-37; the minimum over pairs is 1)
-__device__ __forceinline__ float pair_weight(const WeightCtx& w, float ai, float aj) {
+__device__ __forceinline__ float pixel_ratio(const WeightCtx& w, const float* a, int idx, int N) {
+  if (!w.on || idx >= N) return 1.f;
+  const float v = a[idx];
+  return v > 0.f ? w.amax / v : 0.f;          // a == 0: the reference replaces the product by 1e10 -> ratio clamps to 1
+}
+__device__ __forceinline__ float pair_weight(const WeightCtx& w, float rai, float raj) {
   if (!w.on) return 1.f;
-  float pr = ai * aj;
-  if (pr == 0.f) pr = 1e10f;
-  const float r = fmaxf(w.top / pr, 1.0f);
-  return (r - 1.0f) / (w.hi - 1.0f) * 9.0f + 1.0f;
+  return (fmaxf(rai * raj, 1.0f) - 1.0f) * w.k9 + 1.0f;
 }
 
 enum { MODE_FLAGS = 0, MODE_LOSS = 1, MODE_GRAD = 2 };
+constexpr int LD = CT + 4;         // row pitch of the channel-major tiles (float4 reads of 4 consecutive pixels)
 
+// grid = (own 64-pixel blocks, partner splits): block (x, y) pairs its own pixels with partner tiles y, y + S, ...
 template <int MODE>
 __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p) {
-  __shared__ float s_own[CT][CC + 1];
-  __shared__ float s_oth[CT][CC + 1];
+  __shared__ __align__(16) float s_own[CC][LD];      // channel-major: s[k][pixel]
+  __shared__ __align__(16) float s_oth[CC][LD];
   __shared__ unsigned long long s_bown[CT][MAXW], s_both[CT][MAXW];
-  __shared__ float s_aown[CT], s_aoth[CT];
+  __shared__ float s_raown[CT], s_raoth[CT];
   __shared__ unsigned char s_kown[2][CT], s_koth[2][CT];
-  __shared__ float s_G[MODE == MODE_GRAD ? CT : 1][CT + 1];
+  __shared__ __align__(16) float s_Gt[MODE == MODE_GRAD ? CT : 1][LD];   // G transposed: s_Gt[partner][own]
   __shared__ double s_red[4][CT_THREADS / 32];
 
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int own0 = blockIdx.x * CT;
   const WeightCtx wc = weight_ctx(p);
   for (int e = tid; e < CT * CC; e += CT_THREADS) {
-    const int r = e / CC, c = e - r * CC;
-    s_own[r][c] = own0 + r < p.N ? p.f[(size_t)(own0 + r) * CC + c] : 0.f;
+    const int r = e / CC, c = e - r * CC;            // coalesced global read, transposed shared write
+    s_own[c][r] = own0 + r < p.N ? p.f[(size_t)(own0 + r) * CC + c] : 0.f;
   }
   for (int e = tid; e < CT * MAXW; e += CT_THREADS) {
     const int r = e / MAXW, w = e - r * MAXW;
     s_bown[r][w] = (own0 + r < p.N && w < p.nwords) ? p.bits[(size_t)(own0 + r) * p.nwords + w] : 0ull;
   }
   if (tid < CT) {
-    s_aown[tid] = (own0 + tid < p.N && p.use_weights) ? p.a[own0 + tid] : 1.f;
+    s_raown[tid] = pixel_ratio(wc, p.a, own0 + tid, p.N);
     if (MODE != MODE_FLAGS) {
       s_kown[0][tid] = own0 + tid < p.N ? p.kept[own0 + tid] : 0;
       s_kown[1][tid] = own0 + tid < p.N ? p.kept[p.N + own0 + tid] : 0;
@@ -107,34 +117,34 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
     inv_nneg = p.result[5] > 0.f ? p.upstream[1] / p.result[3] : 0.f;
   }
 
-  unsigned flag_pos = 0, flag_neg = 0;                    // FLAGS: per own row (bit r of the thread's 4 rows)
-  double sum_pos = 0, sum_neg = 0, cnt_pos = 0, cnt_neg = 0;
-  const int gr = tid >> 2, gc = (tid & 3) * 8;            // GRAD phase 2: row and first of 8 channels
-  float dacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  unsigned flag_pos = 0, flag_neg = 0;                    // FLAGS: per own row (bit a of the thread's 4 rows)
+  float sum_pos = 0.f, sum_neg = 0.f, cnt_pos = 0.f, cnt_neg = 0.f;   // per thread: at most ~1000 terms each
+  const int rg = (tid >> 4) * 4, cp = (tid & 15) * 2;     // GRAD phase 2: 4 own rows x 2 channels per thread
+  float dacc[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
 
   const int ntiles = (p.N + CT - 1) / CT;
   // LOSS only needs partners i < j: tiles up to the own one
-  const int last_tile = MODE == MODE_LOSS ? blockIdx.x : ntiles - 1;
-  for (int t = 0; t <= last_tile; t++) {
+  const int last_tile = MODE == MODE_LOSS ? (int)blockIdx.x : ntiles - 1;
+  for (int t = blockIdx.y; t <= last_tile; t += gridDim.y) {
     const int oth0 = t * CT;
     __syncthreads();
     for (int e = tid; e < CT * CC; e += CT_THREADS) {
       const int r = e / CC, c = e - r * CC;
-      s_oth[r][c] = oth0 + r < p.N ? p.f[(size_t)(oth0 + r) * CC + c] : 0.f;
+      s_oth[c][r] = oth0 + r < p.N ? p.f[(size_t)(oth0 + r) * CC + c] : 0.f;
     }
     for (int e = tid; e < CT * MAXW; e += CT_THREADS) {
       const int r = e / MAXW, w = e - r * MAXW;
       s_both[r][w] = (oth0 + r < p.N && w < p.nwords) ? p.bits[(size_t)(oth0 + r) * p.nwords + w] : 0ull;
     }
     if (tid < CT) {
-      s_aoth[tid] = (oth0 + tid < p.N && p.use_weights) ? p.a[oth0 + tid] : 1.f;
+      s_raoth[tid] = pixel_ratio(wc, p.a, oth0 + tid, p.N);
       if (MODE == MODE_GRAD) {
         s_koth[0][tid] = oth0 + tid < p.N ? p.kept[oth0 + tid] : 0;
         s_koth[1][tid] = oth0 + tid < p.N ? p.kept[p.N + oth0 + tid] : 0;
       }
     }
     __syncthreads();
-    // 4 x 4 patch of similarities: own rows ty*4.., partner rows tx*4..
+    // 4 x 4 patch of similarities: own pixels ty*4.., partner pixels tx*4..; two 16-byte reads per channel
     float c[4][4];
 #pragma unroll
     for (int a = 0; a < 4; a++)
@@ -142,20 +152,21 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
       for (int b = 0; b < 4; b++) c[a][b] = 0.f;
 #pragma unroll 8
     for (int k = 0; k < CC; k++) {
-      float o[4], q[4];
-#pragma unroll
-      for (int a = 0; a < 4; a++) { o[a] = s_own[ty * 4 + a][k]; q[a] = s_oth[tx * 4 + a][k]; }
+      const float4 o4 = *reinterpret_cast<const float4*>(&s_own[k][ty * 4]);
+      const float4 q4 = *reinterpret_cast<const float4*>(&s_oth[k][tx * 4]);
+      const float o[4] = {o4.x, o4.y, o4.z, o4.w}, q[4] = {q4.x, q4.y, q4.z, q4.w};
 #pragma unroll
       for (int a = 0; a < 4; a++)
 #pragma unroll
         for (int b = 0; b < 4; b++) c[a][b] = fmaf(o[a], q[b], c[a][b]);
     }
 #pragma unroll
-    for (int a = 0; a < 4; a++) {
-      const int ro = ty * 4 + a, own = own0 + ro;
+    for (int b = 0; b < 4; b++) {
+      const int rq = tx * 4 + b, oth = oth0 + rq;
+      float gcol[4];
 #pragma unroll
-      for (int b = 0; b < 4; b++) {
-        const int rq = tx * 4 + b, oth = oth0 + rq;
+      for (int a = 0; a < 4; a++) {
+        const int ro = ty * 4 + a, own = own0 + ro;
         const bool valid = own < p.N && oth < p.N;
         bool same = false;
 #pragma unroll
@@ -167,9 +178,9 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
         } else if (MODE == MODE_LOSS) {
           // own = column j, partner = row i < j
           if (valid && oth < own) {
-            const float w = pair_weight(wc, s_aown[ro], s_aoth[rq]);
-            if (same && s_kown[0][ro]) { sum_pos += (double)(-w * cv); cnt_pos += 1.0; }
-            if (!same && s_kown[1][ro]) { sum_neg += (double)(w * fmaxf(cv, 0.f)); cnt_neg += 1.0; }
+            const float w = pair_weight(wc, s_raown[ro], s_raoth[rq]);
+            if (same && s_kown[0][ro]) { sum_pos -= w * cv; cnt_pos += 1.f; }
+            if (!same && s_kown[1][ro]) { sum_neg += w * fmaxf(cv, 0.f); cnt_neg += 1.f; }
           }
         } else {
           float g = 0.f;
@@ -177,21 +188,27 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
             const bool own_is_col = own > oth;
             const unsigned char kp = own_is_col ? s_kown[0][ro] : s_koth[0][rq];
             const unsigned char kn = own_is_col ? s_kown[1][ro] : s_koth[1][rq];
-            const float w = pair_weight(wc, s_aown[ro], s_aoth[rq]);
+            const float w = pair_weight(wc, s_raown[ro], s_raoth[rq]);
             if (same && kp) g = -w * inv_npos;
             if (!same && kn && cv > 0.f) g = w * inv_nneg;
           }
-          s_G[ro][rq] = g;
+          gcol[a] = g;
         }
       }
+      if (MODE == MODE_GRAD)
+        *reinterpret_cast<float4*>(&s_Gt[rq][ty * 4]) = make_float4(gcol[0], gcol[1], gcol[2], gcol[3]);
     }
     if (MODE == MODE_GRAD) {
       __syncthreads();
+      // d f_own[r][ch] += sum_j G[r][j] f_j[ch]: 4 own rows x 2 channels per thread
 #pragma unroll 4
       for (int j = 0; j < CT; j++) {
-        const float g = s_G[gr][j];
-#pragma unroll
-        for (int q = 0; q < 8; q++) dacc[q] = fmaf(g, s_oth[j][gc + q], dacc[q]);
+        const float4 g4 = *reinterpret_cast<const float4*>(&s_Gt[j][rg]);
+        const float f0 = s_oth[cp][j], f1 = s_oth[cp + 1][j];
+        dacc[0][0] = fmaf(g4.x, f0, dacc[0][0]); dacc[0][1] = fmaf(g4.x, f1, dacc[0][1]);
+        dacc[1][0] = fmaf(g4.y, f0, dacc[1][0]); dacc[1][1] = fmaf(g4.y, f1, dacc[1][1]);
+        dacc[2][0] = fmaf(g4.z, f0, dacc[2][0]); dacc[2][1] = fmaf(g4.z, f1, dacc[2][1]);
+        dacc[3][0] = fmaf(g4.w, f0, dacc[3][0]); dacc[3][1] = fmaf(g4.w, f1, dacc[3][1]);
       }
     }
   }
@@ -207,14 +224,13 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
 #pragma unroll
       for (int a = 0; a < 4; a++) {
         const int own = own0 + ty * 4 + a;
-        if (own < p.N) {
-          p.kept[own] = (flag_pos >> a) & 1u;
-          p.kept[p.N + own] = (flag_neg >> a) & 1u;
-        }
+        // the flag arrays start at zero; blocks of different partner splits only ever write 1
+        if (own < p.N && ((flag_pos >> a) & 1u)) p.kept[own] = 1;
+        if (own < p.N && ((flag_neg >> a) & 1u)) p.kept[p.N + own] = 1;
       }
     }
   } else if (MODE == MODE_LOSS) {
-    double v[4] = {sum_pos, sum_neg, cnt_pos, cnt_neg};
+    double v[4] = {(double)sum_pos, (double)sum_neg, (double)cnt_pos, (double)cnt_neg};
 #pragma unroll
     for (int q = 0; q < 4; q++) {
 #pragma unroll
@@ -225,14 +241,17 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
     if (tid < 4) {
       double tot = 0;
       for (int w = 0; w < CT_THREADS / 32; w++) tot += s_red[tid][w];
-      p.partial[(size_t)blockIdx.x * 4 + tid] = tot;
+      p.partial[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 4 + tid] = tot;
     }
   } else {
-    const int own = own0 + gr;
-    if (own < p.N) {
-      float4* dst = reinterpret_cast<float4*>(p.df + (size_t)own * CC + gc);
-      dst[0] = make_float4(dacc[0], dacc[1], dacc[2], dacc[3]);
-      dst[1] = make_float4(dacc[4], dacc[5], dacc[6], dacc[7]);
+#pragma unroll
+    for (int a = 0; a < 4; a++) {
+      const int own = own0 + rg + a;
+      if (own < p.N) {
+        float* dst = p.df + (size_t)own * CC + cp;
+        if (gridDim.y == 1) { dst[0] = dacc[a][0]; dst[1] = dacc[a][1]; }
+        else { atomicAdd(dst, dacc[a][0]); atomicAdd(dst + 1, dacc[a][1]); }     // df arrives zero-filled
+      }
     }
   }
 }
@@ -297,9 +316,14 @@ __global__ void __launch_bounds__(256) pixel_mask_info_kernel(int N, int n_masks
 
 using namespace tb;
 
+// partner splits per own block: enough blocks for two waves of the 148 SMs
+static int contrastive_splits(int nb) {
+  int s = (2 * 148 + nb - 1) / nb;
+  return s < 1 ? 1 : (s > 8 ? 8 : s);
+}
 extern "C" TRASE_API size_t trase_b200_contrastive_scratch_bytes(int N) {
   const size_t nb = (size_t)((N + contrastive::CT - 1) / contrastive::CT);
-  return align_up(2 * (size_t)(N > 0 ? N : 0), 256) + align_up(nb * 4 * sizeof(double), 256);
+  return align_up(2 * (size_t)(N > 0 ? N : 0), 256) + align_up(nb * 8 * 4 * sizeof(double), 256);
 }
 
 extern "C" TRASE_API int trase_b200_pixel_mask_info(int N, int n_masks, int64_t HW, const unsigned char* masks,
@@ -349,10 +373,13 @@ extern "C" TRASE_API int trase_b200_contrastive_soft_forward(int N, int nwords, 
     return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int nb = (N + contrastive::CT - 1) / contrastive::CT;
-  contrastive::contrastive_kernel<contrastive::MODE_FLAGS><<<nb, contrastive::CT_THREADS, 0, s>>>(p);
-  contrastive::contrastive_kernel<contrastive::MODE_LOSS><<<nb, contrastive::CT_THREADS, 0, s>>>(p);
-  contrastive::contrastive_finish_kernel<<<1, 256, 0, s>>>(p, nb);
-  cudaError_t e = cudaGetLastError();
+  const dim3 grid(nb, contrastive_splits(nb));
+  cudaError_t e = cudaMemsetAsync(p.kept, 0, 2 * (size_t)N, s);           // the mined-column flags are OR-ed into
+  if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  contrastive::contrastive_kernel<contrastive::MODE_FLAGS><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+  contrastive::contrastive_kernel<contrastive::MODE_LOSS><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+  contrastive::contrastive_finish_kernel<<<1, 256, 0, s>>>(p, (int)(grid.x * grid.y));
+  e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(3);
   return 0;
@@ -371,9 +398,13 @@ extern "C" TRASE_API int trase_b200_contrastive_soft_backward(int N, int nwords,
   if (!upstream || !df || ((uintptr_t)df & 15)) { set_error("trase_b200_contrastive_soft_backward: null / unaligned pointer"); return 1; }
   p.upstream = upstream; p.df = df;
   const int nb = (N + contrastive::CT - 1) / contrastive::CT;
-  contrastive::contrastive_kernel<contrastive::MODE_GRAD><<<nb, contrastive::CT_THREADS, 0,
-                                                           reinterpret_cast<cudaStream_t>(stream)>>>(p);
-  cudaError_t e = cudaGetLastError();
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const dim3 grid(nb, contrastive_splits(nb));
+  cudaError_t e = cudaMemsetAsync(df, 0, (size_t)N * contrastive::CC * sizeof(float), s);   // split blocks add into it
+  if (e == cudaSuccess) {
+    contrastive::contrastive_kernel<contrastive::MODE_GRAD><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    e = cudaGetLastError();
+  }
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
   return 0;
