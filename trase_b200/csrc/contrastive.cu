@@ -258,30 +258,34 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
 
 // n_kept = sum_j kept[j] * j (the number of rows i < j of each kept column), loss = sum / n_kept
 __global__ void __launch_bounds__(256) contrastive_finish_kernel(const Params p, int nblocks) {
-  __shared__ double s_n[2][8];
-  double n[2] = {0, 0};
+  __shared__ double s_v[6][8];
+  double v[6] = {0, 0, 0, 0, 0, 0};            // n_pos, n_neg, pos_sum, neg_sum, pos_pairs, neg_pairs
   for (int j = threadIdx.x; j < p.N; j += 256) {
-    if (p.kept[j]) n[0] += (double)j;
-    if (p.kept[p.N + j]) n[1] += (double)j;
+    if (p.kept[j]) v[0] += (double)j;
+    if (p.kept[p.N + j]) v[1] += (double)j;
   }
+  for (int b = threadIdx.x; b < nblocks; b += 256)
 #pragma unroll
-  for (int q = 0; q < 2; q++) {
+    for (int q = 0; q < 4; q++) v[2 + q] += p.partial[(size_t)b * 4 + q];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) n[q] += __shfl_xor_sync(0xffffffffu, n[q], o);
-    if ((threadIdx.x & 31) == 0) s_n[q][threadIdx.x >> 5] = n[q];
+  for (int q = 0; q < 6; q++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+    if ((threadIdx.x & 31) == 0) s_v[q][threadIdx.x >> 5] = v[q];
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    double np = 0, nn = 0, v[4] = {0, 0, 0, 0};
-    for (int w = 0; w < 8; w++) { np += s_n[0][w]; nn += s_n[1][w]; }
-    for (int b = 0; b < nblocks; b++)
-      for (int q = 0; q < 4; q++) v[q] += p.partial[(size_t)b * 4 + q];
-    p.result[0] = v[2] > 0 ? (float)(v[0] / np) : 0.f;
-    p.result[1] = v[3] > 0 ? (float)(v[1] / nn) : 0.f;
-    p.result[2] = (float)np;
-    p.result[3] = (float)nn;
-    p.result[4] = (float)v[2];
-    p.result[5] = (float)v[3];
+    double t[6];
+    for (int q = 0; q < 6; q++) {
+      t[q] = 0;
+      for (int w = 0; w < 8; w++) t[q] += s_v[q][w];
+    }
+    p.result[0] = t[4] > 0 ? (float)(t[2] / t[0]) : 0.f;
+    p.result[1] = t[5] > 0 ? (float)(t[3] / t[1]) : 0.f;
+    p.result[2] = (float)t[0];
+    p.result[3] = (float)t[1];
+    p.result[4] = (float)t[4];
+    p.result[5] = (float)t[5];
   }
 }
 
