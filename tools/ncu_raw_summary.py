@@ -24,7 +24,7 @@ for r in rows[2:]:
     name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "").replace("tb::", "").replace("mlp::", "")
     k = seen.get(name, 0)
     seen[name] = k + 1
-    if not (name.startswith("radix") or (name.startswith("wgrad") and k < 2) or k == 0):
+    if not (name.startswith("radix") or (name.startswith("wgrad") and k < 4) or k == 0):
         continue
     grid = r[idx["Grid Size"]] if "Grid Size" in idx else ""
     block = r[idx["Block Size"]] if "Block Size" in idx else ""
