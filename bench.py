@@ -541,7 +541,11 @@ class _Null:
 
 
 # SMs the persistent MLP kernels leave free when a gradient all-reduce runs under the MLP backward (N > 1)
-RESERVE_SMS_MULTI = 0
+# (N=8 sweep, profiles/r2_l_*: 0 SMs / default NCCL 1493.9 steps/s; 16 SMs / default NCCL 1443.9; 8 SMs with NCCL held
+# to 8 CTAs 1507.7; 16 / 16 1496.4; 0 SMs with 8 CTAs 1404.4: the all-reduce has 1.3 ms of MLP backward to hide under, so
+# a narrow collective on SMs of its own beats a wide one that time-shares the SMs of the persistent kernels)
+RESERVE_SMS_MULTI = 8
+NCCL_CTAS_MULTI = "8"
 MLP_MAC_PER_ROW = 504_320          # 84*256 + 6*256*256 + 340*256 + 256*10
 
 
@@ -888,6 +892,9 @@ def main():
         torch.cuda.set_device(device)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if args.impl == "ours" and WORKLOADS[args.workload]["state"] == "GAUSSIAN":
+            # the state whose all-reduce runs under the MLP backward (the others have nothing to hide it under)
+            os.environ.setdefault("NCCL_MAX_CTAS", NCCL_CTAS_MULTI)   # see RESERVE_SMS_MULTI
         dist.init_process_group("nccl" if have_gpu else "gloo", device_id=device if have_gpu else None)
     try:
         if args.impl == "reference":
@@ -897,13 +904,16 @@ def main():
                 raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
                                  "(use --impl reference for the CPU port)")
             from trase_b200 import _lib
-            reserve = args.reserve_sms if args.reserve_sms is not None else (RESERVE_SMS_MULTI if world > 1 else 0)
+            reserve = args.reserve_sms if args.reserve_sms is not None else (
+                RESERVE_SMS_MULTI if world > 1 and WORKLOADS[args.workload]["state"] == "GAUSSIAN" else 0)
             if args.workload != "inference2m":        # inference has no collective
                 _lib.set_tuning("reserve_sms", reserve)
             line = run_inference(args, rank, world, device) if args.workload == "inference2m" else \
                 run_ours(args, rank, world, device)
             if line is not None and args.workload != "inference2m":
                 line["config"]["reserve_sms"] = reserve
+                if world > 1:
+                    line["config"]["nccl_max_ctas"] = os.environ.get("NCCL_MAX_CTAS")
         if rank == 0 and line is not None:
             print(json.dumps(line), flush=True)
     finally:

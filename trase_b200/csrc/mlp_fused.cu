@@ -39,6 +39,7 @@ using namespace ptx;
 bool make_tmap_2d(CUtensorMap* m, const float* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
                   uint32_t box_cols, CUtensorMapSwizzle swz);
 int num_sms();
+extern int g_reserve_sms;
 
 constexpr int FU_BM = 128;
 constexpr int FU_W = 256;                 // hidden width
@@ -554,7 +555,9 @@ static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMa
     cudaError_t e = ensure_max_dyn_smem(attr_once, mlp_fused_kernel<BWD, A16>, FU_SMEM);
     if (e != cudaSuccess) { set_error("%s: %s", who, cudaGetErrorString(e)); return 2; }
   }
-  const int sms = num_sms() & ~1;          // SMs available to the persistent MLP kernels (see "reserve_sms"), whole pairs
+  // SMs available to the persistent MLP kernels, whole pairs.  "reserve_sms" leaves SMs to a gradient all-reduce that
+  // runs under the MLP BACKWARD (chain + weight gradients); nothing overlaps the forward, which takes them all.
+  const int sms = (BWD ? num_sms() : num_sms() + g_reserve_sms) & ~1;
   const int tiles = (p.M + FU_BM - 1) / FU_BM;
   int grid = tiles < sms ? tiles : sms;
   grid = (grid + FU_CLUSTER - 1) / FU_CLUSTER * FU_CLUSTER;
