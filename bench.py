@@ -650,6 +650,9 @@ def run_ours(args, rank, world, device):
         torch.backends.cuda.matmul.allow_tf32 = True
     Workload.full_arena = bool(args.full_arena)
     Workload.fused_loss = not args.torch_feature_loss
+    for key in ("fwd_ppt", "bwd_ppt"):                      # kernel tuning experiments: TRASE_B200_BWD_PPT=1 ...
+        if os.environ.get("TRASE_B200_" + key.upper()):
+            _lib.set_tuning(key, int(os.environ["TRASE_B200_" + key.upper()]))
     sampler = ClockSampler(device).start() if rank == 0 else None
     wl = Workload(args.workload, device, rank, mlp_backend="native" if args.mlp == "native" else "torch")
     cfg = wl.cfg

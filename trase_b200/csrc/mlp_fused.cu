@@ -50,7 +50,10 @@ constexpr int FU_ECH = 3;                 // up to 96 embedding columns
 // the backward chain gives one stage up for its bias-gradient accumulators
 // A16 (bf16 side output, see below) gives one more stage up: 8 epilogue warps x 2 KB of store staging
 template <bool BWD, bool A16> struct FuCfg { static constexpr int STAGES = (BWD ? 5 : 6) - (A16 ? 1 : 0); };
-constexpr int FU_EPI_WARPS = 8;            // two per TMEM lane quarter, alternating 32-column slabs (12 warps: no gain, the MMA side is the bound)
+#ifndef TB_FU_EPI_WARPS
+#define TB_FU_EPI_WARPS 8
+#endif
+constexpr int FU_EPI_WARPS = TB_FU_EPI_WARPS;            // two per TMEM lane quarter, alternating 32-column slabs (12 warps: no gain, the MMA side is the bound)
 constexpr int FU_THREADS = 128 + 32 * FU_EPI_WARPS;
 constexpr int FU_MAX_LAYERS = 12;
 constexpr int FU_CLUSTER = 2;             // CTA pair: one tcgen05.mma.cta_group::2 spans both         // hidden layers + the head pseudo-layer
