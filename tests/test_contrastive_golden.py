@@ -151,3 +151,41 @@ def test_fused_soft_contrastive_matches_torch_formulation_at_training_size(nativ
         assert abs(float(n1) - float(n2)) <= 1e-4 * max(1e-3, abs(float(n1))), (float(n1), float(n2))
         gmax = f1.grad.abs().max()
         assert (f1.grad - f2.grad).abs().max() <= 2e-4 * gmax
+
+
+@pytest.mark.gpu
+def test_fused_contrastive_many_masks_and_empty_sample(native_lib):
+    """130 masks (three 64-bit membership words per pixel) against the torch formulation, and the degenerate call
+    with no sampled pixel at all (both losses 0, zero gradient, no launch with N = 0)."""
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(21)
+    H, W, Hm, Wm, n_masks = 96, 80, 48, 40, 130
+    masks = torch.zeros(n_masks, Hm, Wm, dtype=torch.uint8)
+    for i in range(n_masks):
+        h, w = int(torch.randint(4, 20, (1,), generator=gen)), int(torch.randint(4, 16, (1,), generator=gen))
+        y, x = int(torch.randint(0, Hm - h, (1,), generator=gen)), int(torch.randint(0, Wm - w, (1,), generator=gen))
+        masks[i, y:y + h, x:x + w] = 1
+    masks = masks.to(dev)
+    feat0 = (1.2 * torch.randn(32, H, W, generator=gen) + torch.randn(32, 1, 1, generator=gen)).to(dev)
+    sp, sm = FU.get_sample_pixel_and_mask(masks, 600, 100, generator=torch.Generator(device=dev).manual_seed(5))
+    assert int(sm.sum()) > 64                              # sampled masks beyond the first membership word
+    f1 = feat0.clone().requires_grad_(True)
+    C = FU.get_pixel_mask_correspondence_matrix(masks, sp, sm)
+    C_F = FU.get_features_correspondence_matrix(f1, sp)
+    w = FU.get_pixel_weights(masks, sp)
+    p1 = LU.pixel_mask_correspondence_loss_soft_hard_positive(C=C, C_F=C_F, positive_th=0.75, weights=w)
+    n1 = LU.pixel_mask_correspondence_loss_soft_negative(C=C, C_F=C_F, negative_th=0.5, weights=w)
+    (p1 + n1).backward()
+    f2 = feat0.clone().requires_grad_(True)
+    p2, n2 = FU.soft_contrastive_losses(f2, masks, sp, sm, 0.75, 0.5)
+    (p2 + n2).backward()
+    assert abs(float(p1) - float(p2)) <= 1e-4 * max(1e-3, abs(float(p1))), (float(p1), float(p2))
+    assert abs(float(n1) - float(n2)) <= 1e-4 * max(1e-3, abs(float(n1))), (float(n1), float(n2))
+    assert (f1.grad - f2.grad).abs().max() <= 2e-4 * f1.grad.abs().max()
+    f3 = feat0.clone().requires_grad_(True)
+    p3, n3 = FU.soft_contrastive_losses(f3, masks, torch.zeros_like(sp), sm, 0.75, 0.5)
+    (p3 + n3).backward()
+    assert float(p3) == 0.0 and float(n3) == 0.0 and not f3.grad.any()
+    with pytest.raises(RuntimeError):
+        FU.soft_contrastive_losses(feat0, torch.zeros(300, Hm, Wm, dtype=torch.uint8, device=dev), sp,
+                                   torch.ones(300, dtype=torch.bool, device=dev))

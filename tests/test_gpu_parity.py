@@ -341,6 +341,40 @@ def test_partial_gradient_variants_equal_the_full_backward(native_lib, ppt):
     assert float(full["objects"].abs().max()) > 0
 
 
+def test_partial_gradients_with_precomputed_colour_and_covariance(native_lib):
+    """The NULL-means-not-wanted convention on the colors_precomp / cov3D_precomp path (no SH block, M = 0; no scale /
+    rotation gradients): the variants against the full backward and the CPU oracle."""
+    from oracle import oracle
+    from trase_b200 import synth, _raster
+    P, W, H = 6000, 88, 72
+    sc = synth.make_scene(P, W, H, 35)
+    up = synth.make_upstream_grads(W, H, 35)
+    g = torch.Generator().manual_seed(2)
+    colors = torch.rand(P, 3, generator=g)
+    f0 = oracle.forward_scene(sc, [0.2] * 3)
+    cov = torch.from_numpy(f0["cov3D"]).float()
+    a = scene_args(sc, 0.2, DEV, colors_precomp=colors, cov3D_precomp=cov)
+    res = cuda_forward(a)
+
+    def bwd(dcol, dobj, **kw):
+        out = _raster.rasterize_backward(a["bg"], a["means3D"], res.radii, a["colors_precomp"], a["scales"],
+                                         a["rotations"], 1.0, a["cov3D_precomp"], a["viewmatrix"], a["projmatrix"],
+                                         a["tanfovx"], a["tanfovy"], dcol, a["sh"], dobj, a["sh_objs"], a["degree"],
+                                         a["campos"], res.geom, res.num_rendered, res.binning, res.img, False,
+                                         capacity=res.capacity, **kw)
+        return dict(zip(GRAD_NAMES, out))
+
+    dc, do = up["dL_dcolor"].to(DEV), up["dL_dobjects"].to(DEV)
+    full = bwd(dc, do)
+    no_df = bwd(dc, do, need_features=False)
+    df_only = bwd(None, do, need_geom=False)
+    assert full["sh"].shape == (P, 0, 3)
+    for k in ("means2D", "colors_precomp", "opacities", "means3D", "cov3D"):
+        assert rel_err(_np(full[k]), _np(no_df[k])) <= 1e-4, k
+        assert df_only[k] is None
+    assert rel_err(_np(full["objects"]), _np(df_only["objects"])) <= 1e-4 and no_df["objects"] is None
+
+
 def test_autograd_skips_what_nobody_needs(native_lib):
     """Through the public API: with only sh_objs requiring grad (FEATURE state) or only the others (GAUSSIAN state,
     frozen features), the gradients that are produced equal those of a run where everything requires grad."""

@@ -277,3 +277,43 @@ def test_densify_prune_and_opacity_reset_match_the_per_tensor_procedure(native_l
                               for k in LRS if k != "_gaussian_features"], lr=0.0, eps=1e-15)
     stock.load_state_dict(model_args[11]["GAUSSIAN"])           # each half is a stock Adam state_dict
     assert len(stock.state) == 6
+
+
+def test_prune_keeps_other_arena_tensors_intact(native_lib):
+    """An arena that also holds the DeformNetwork (as bench.py builds it): resizing the per-Gaussian segments must
+    carry the network's parameters and moments over unchanged and leave every .grad a view of the new arena."""
+    from trase_b200 import densify as D
+    from trase_b200.deform import DeformNetwork
+    from trase_b200.distributed import GradArena
+    from trase_b200.optim import ArenaAdam
+    dev = torch.device("cuda:0")
+    sc, pc, _, _, _ = _build(dev)
+    torch.manual_seed(1)
+    net = DeformNetwork(backend="native").to(dev)
+    params = list(pc.parameters()) + list(net.parameters())
+    arena = GradArena(params, early=list(pc.parameters()))
+    groups = _groups(pc) + [{"params": list(net.parameters()), "lr": 1e-3, "name": "deform"}]
+    opt = ArenaAdam(arena, groups, eps=1e-15)
+    opt.exp_avg.uniform_(-1, 1)
+    opt.exp_avg_sq.uniform_(0, 1)
+    before_net = [p.detach().clone() for p in net.parameters()]
+    seg = {id(p): (off, p.numel()) for p, off in zip(arena.params, arena.offsets)}
+    before_m = [opt.exp_avg[seg[id(p)][0]:seg[id(p)][0] + p.numel()].clone() for p in net.parameters()]
+    xyz_before = pc._xyz.detach().clone()
+    state = D.DensifyState(pc._xyz.shape[0], dev)
+    mask = torch.arange(pc._xyz.shape[0], device=dev) % 3 == 0
+    D.prune_points(pc, opt, state, mask)
+    assert torch.equal(pc._xyz.detach(), xyz_before[~mask])
+    seg = {id(p): (off, p.numel()) for p, off in zip(arena.params, arena.offsets)}
+    for p, b, m in zip(net.parameters(), before_net, before_m):
+        off, n = seg[id(p)]
+        assert torch.equal(p.detach(), b)
+        assert torch.equal(opt.exp_avg[off:off + n], m)
+        assert p.grad.data_ptr() == arena.flat.data_ptr() + 4 * off
+    assert arena.n_early == sum(p.numel() for p in pc.parameters())
+    # the resized model still trains through the native path
+    P = pc._xyz.shape[0]
+    outs = net(pc.get_xyz.detach(), torch.full((P, 1), 0.2, device=dev))
+    sum(o.sum() for o in outs).backward()
+    opt.step()
+    assert torch.isfinite(opt.flat_p).all()
