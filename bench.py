@@ -650,7 +650,7 @@ def run_ours(args, rank, world, device):
         torch.backends.cuda.matmul.allow_tf32 = True
     Workload.full_arena = bool(args.full_arena)
     Workload.fused_loss = not args.torch_feature_loss
-    for key in ("fwd_ppt", "bwd_ppt"):                      # kernel tuning experiments: TRASE_B200_BWD_PPT=1 ...
+    for key in ("fwd_ppt", "bwd_ppt", "fwd_mma"):                      # kernel tuning experiments: TRASE_B200_BWD_PPT=1 ...
         if os.environ.get("TRASE_B200_" + key.upper()):
             _lib.set_tuning(key, int(os.environ["TRASE_B200_" + key.upper()]))
     sampler = ClockSampler(device).start() if rank == 0 else None

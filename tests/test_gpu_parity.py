@@ -64,6 +64,33 @@ def test_golden_backward(native_lib, name, ppt):
         assert rel_err(g["ref_grad_" + k], _np(b[k])) <= 1e-3, k
 
 
+@pytest.mark.parametrize("variant", [3, 4])
+def test_tensor_core_forward_variant_matches_golden(native_lib, variant):
+    """The forward kernel whose per-channel contraction runs on the warp-level tensor cores (csrc/render_mma.cu, off
+    by default because it measured slower): same alpha chain, so contributor counts stay bit-exact, images within
+    1e-4 (3xTF32 split products)."""
+    from trase_b200 import _lib
+    g = load_golden("sh_deg3_bg0")
+    a = golden_inputs_cuda(g, DEV)
+    _lib.set_tuning("fwd_mma", variant)
+    try:
+        res = cuda_forward(a)
+        v = views(res, a)
+        assert np.array_equal(_np(v["n_contrib"]), g["ref_n_contrib"])
+        assert np.array_equal(_np(v["final_T"]), _np(views(cuda_forward_plain(a), a)["final_T"]))
+        assert np.abs(_np(res.color) - g["ref_color"]).max() <= 1e-4
+        assert np.abs(_np(res.objects) - g["ref_objects"]).max() <= 1e-4
+        assert np.abs(_np(res.depth) - g["ref_depth"]).max() <= 1e-4
+    finally:
+        _lib.set_tuning("fwd_mma", 0)
+
+
+def cuda_forward_plain(a):
+    from trase_b200 import _lib
+    _lib.set_tuning("fwd_mma", 0)
+    return cuda_forward(a)
+
+
 # ---------------------------------------------------------------- oracle ----
 @pytest.mark.parametrize("P,W,H,seed,bg,deg", [(20000, 128, 128, 1, 0.0, 3), (5000, 100, 75, 5, 1.0, 2),
                                                (3000, 37, 91, 6, 0.3, 0)])

@@ -20,8 +20,8 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # default -fmad=true, no fast-math: integer parity with the reference depends on it
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 
-SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "render.cu", "no_alloc.cu", "mlp_gemm.cu", "assemble.cu", "mlp_prep.cu", "loss.cu", "mlp_fused.cu", "optim.cu", "contrastive.cu"]
-HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "ptx.cuh"), os.path.join(HERE, "..", "include", "trase_b200.h")]
+SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "render.cu", "render_mma.cu", "no_alloc.cu", "mlp_gemm.cu", "assemble.cu", "mlp_prep.cu", "loss.cu", "mlp_fused.cu", "optim.cu", "contrastive.cu"]
+HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "ptx.cuh"), os.path.join(CSRC, "render_common.cuh"), os.path.join(HERE, "..", "include", "trase_b200.h")]
 
 
 def _stale(out: str, deps: list[str]) -> bool:
