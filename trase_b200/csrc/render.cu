@@ -38,7 +38,8 @@ struct Tuning {
   int bwd_ppt = 2;
   // 3 | 4: forward contraction on the warp-level tensor cores (render_mma.cu) with that many CTAs per SM.  Measured
   // slower than the SIMT kernel at config 2 (1.01 / 1.16 ms against 0.67 ms, profiles/r2_s_*): 3xTF32 on the legacy
-  // mma.sync path (278 TFLOP/s measured) is 93 TFLOP/s effective, below the 149 TFLOP/s of packed fp32 FMAs.  Off.
+  // mma.sync path (278 TFLOP/s measured) is 93 TFLOP/s effective, no better than the 74 TFLOP/s fp32 pipe that the SIMT
+  // kernel drives with packed FFMA2 at half the issue slots: nothing left to pay for staging and splits.  Off.
   int fwd_mma = 0;
 };
 static Tuning g_tuning;

@@ -18,8 +18,9 @@
 // render_fwd_kernel — results identical within the tolerances (all parity tests pass with this kernel selected), but
 // slower.  mma.sync TF32 peaks at 278 TFLOP/s on this GPU (tools/micro/mma_sync_rate.cu, profiles/r2_r_mma_sync_rate.txt);
 // with the 3-way split and half-filled batches at the end of every staged block the kernel issues ~60 M MMAs = 0.12
-// TFLOP per view, 0.44 ms of tensor time alone, and 3xTF32 at 278 TFLOP/s is 93 TFLOP/s effective — below the
-// 149 TFLOP/s of the packed fp32 FMAs (FFMA2) the SIMT kernel uses.  The kernel stays selectable
+// TFLOP per view, 0.44 ms of tensor time alone, and 3xTF32 at 278 TFLOP/s is 93 TFLOP/s effective — no more than the
+// 74 TFLOP/s fp32 pipe that the SIMT kernel drives with packed FFMA2 at half the issue slots, so nothing is left to
+// pay for the staging, the splits and the fragment loads.  The kernel stays selectable
 // (trase_b200_set_tuning("fwd_mma", 3|4)) and tested, off by default.
 #include "common.cuh"
 #include "render_common.cuh"
