@@ -20,7 +20,7 @@ def show(tag):
     for name, sl in (("leader", slice(0, 148, 2)), ("follower", slice(1, 148, 2))):
         b = buf.view(148, 8)[sl].double().mean(0).tolist()
         print(tag, name, "cycles/CTA: total %.0f | MMA thread waits: tmem_empty %.0f a_ready %.0f w_full %.0f store %.0f | "
-              "epilogue warp 4 waits: tmem_full %.0f h_free %.0f" % tuple(b[:7]))
+              "epilogue warp 4 waits: tmem_full %.0f h_free %.0f | MMA issue + commits %.0f" % tuple(b[:8]))
 
 
 MODES = [bool(int(m)) for m in sys.argv[2].split(',')] if len(sys.argv) > 2 else [True, False]

@@ -17,6 +17,7 @@ import bench  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--workload", default="neu3d")
 ap.add_argument("--full-arena", action="store_true")
+ap.add_argument("--timeline", action="store_true", help="also list every kernel of the middle step in launch order with the idle gap before it")
 args = ap.parse_args()
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
@@ -64,5 +65,17 @@ if rank == 0:
         c[1] += 1
     for k, (t, c) in sorted(tot.items(), key=lambda kv: -kv[1][0])[:40]:
         print("%10.1f us  %4d x  %s" % (t, c, k))
+    if args.timeline:
+        n3 = len(ker) // 3
+        mid = ker[n3:2 * n3]
+        print("\n# middle step, in order: start (us), duration, idle gap since the end of everything before it, name")
+        busy_end = ker[n3 - 1][1]
+        idle = 0.0
+        for s, e, n in mid:
+            gap = max(0.0, s - busy_end)
+            idle += gap
+            print("%9.1f %8.1f %6.1f  %s" % (s - mid[0][0], e - s, gap, n.split("(")[0][:90]))
+            busy_end = max(busy_end, e)
+        print("# idle inside the step: %.1f us of %.1f" % (idle, mid[-1][1] - mid[0][0]))
 if world > 1:
     dist.destroy_process_group()
