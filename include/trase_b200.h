@@ -501,6 +501,14 @@ TRASE_API int trase_b200_wgrad_bf16(const void* P, int ldp, int I, const void* Q
                                     int ldd, void* stream);
 TRASE_API int trase_b200_f32_to_bf16(int rows, int cols, const float* src, int ld_src, void* dst, int ld_dst,
                                      void* stream);
+/* All weight-gradient products of one backward pass (ref: the same eleven autograd GEMMs) in ONE launch:
+ * D_j[i][k] += sum_m P_j[m][i] * Q_j[m][k] for j < njobs (<= 12) over the same M rows, per-product arguments as
+ * for trase_b200_wgrad_bf16 (host arrays of njobs entries; the pointers in them are device pointers).  The SMs are
+ * dealt out to the products in proportion to the bytes each streams; each CTA reduces its row slice of one product
+ * in TMEM and adds it to D once. */
+TRASE_API int trase_b200_wgrad_bf16_multi(int njobs, const void* const* P, const int* ldp, const int* I,
+                                          const void* const* Q, const int* ldq, const int* J, int M, float* const* D,
+                                          const int* ldd, void* stream);
 /* The two producers of those small operands can write the bf16 copy themselves (no separate conversion pass):
  * the positional encoding (out16 [M][ld16], ld16 a multiple of 8 and >= the column count, padding zero-filled) and the
  * packed head gradient (dout16 [M][16]). */

@@ -116,6 +116,70 @@ def test_wgrad_bf16(native_lib, M, I, J, ldq):
     assert (D[:, :J].double() - ref).abs().max().item() / scale <= 2e-5
 
 
+@pytest.mark.parametrize("M", [300, 70001])
+def test_wgrad_bf16_multi_equals_one_launch_per_product(native_lib, M):
+    """All products of a backward pass in one launch (CTAs dealt out by bytes streamed) against the exact product of
+    the same bf16 values; the shapes are the DeformNetwork's (heads, embedding, hidden layers, the skip layer's two
+    column blocks of one gradient matrix).  M = 300: fewer row blocks than CTAs, most CTAs of a product get none."""
+    import ctypes
+    g = torch.Generator(device=DEV).manual_seed(M)
+    bf = lambda r, c: torch.randn(r, c, device=DEV, generator=g).to(torch.bfloat16)
+    emb = torch.zeros(M, 96, device=DEV, dtype=torch.bfloat16)
+    emb[:, :84] = bf(M, 84)
+    dW_skip = torch.full((256, 340), 0.25, device=DEV)
+    jobs = [(bf(M, 256), bf(M, 16), torch.full((256, 16), 0.25, device=DEV), 16),      # heads
+            (bf(M, 256), emb, torch.full((256, 84), 0.25, device=DEV), 84),             # layer 0
+            (bf(M, 256), bf(M, 256), torch.full((256, 256), 0.25, device=DEV), 256)]
+    dz_skip = bf(M, 256)
+    jobs += [(dz_skip, emb, dW_skip[:, :84], 84), (dz_skip, bf(M, 256), dW_skip[:, 84:], 256)]
+    jobs += [(bf(M, 256), bf(M, 256), torch.full((256, 256), 0.25, device=DEV), 256) for _ in range(5)]
+    n = len(jobs)
+    vp, ip = ctypes.c_void_p * n, ctypes.c_int * n
+    rc = native_lib.trase_b200_wgrad_bf16_multi(
+        n, vp(*[j[0].data_ptr() for j in jobs]), ip(*[j[0].stride(0) for j in jobs]), ip(*[256] * n),
+        vp(*[j[1].data_ptr() for j in jobs]), ip(*[j[1].stride(0) for j in jobs]), ip(*[j[3] for j in jobs]), M,
+        vp(*[j[2].data_ptr() for j in jobs]), ip(*[j[2].stride(0) for j in jobs]),
+        torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, native_lib.trase_b200_last_error()
+    torch.cuda.synchronize()
+    for P, Q, D, J in jobs:
+        ref = P.double().T @ Q[:, :J].double() + 0.25
+        assert torch.isfinite(D).all()
+        assert (D.double() - ref).abs().max().item() / ref.abs().max().item() <= 2e-5
+    # more products than the launch supports: refused, not truncated
+    big = 13
+    vpb, ipb = ctypes.c_void_p * big, ctypes.c_int * big
+    rc = native_lib.trase_b200_wgrad_bf16_multi(
+        big, vpb(*[jobs[2][0].data_ptr()] * big), ipb(*[256] * big), ipb(*[256] * big),
+        vpb(*[jobs[2][1].data_ptr()] * big), ipb(*[256] * big), ipb(*[256] * big), M,
+        vpb(*[jobs[2][2].data_ptr()] * big), ipb(*[256] * big), torch.cuda.current_stream().cuda_stream)
+    assert rc != 0
+
+
+def test_multi_wgrad_backward_equals_per_layer_launches(native_lib):
+    """The native DeformNetwork backward with all weight-gradient products in one launch against one launch each."""
+    from trase_b200 import _deform_native as dn
+    from trase_b200.deform import DeformNetwork
+    torch.manual_seed(11)
+    M = 50021
+    net = DeformNetwork(backend="native").to(DEV)
+    x = (torch.rand(M, 3, device=DEV) - 0.5) * 4
+    t = torch.full((M, 1), 0.61, device=DEV)
+    go = [torch.randn(M, k, device=DEV) for k in (3, 4, 3)]
+    grads = {}
+    saved = dn.MULTI_WGRAD
+    try:
+        for mode in (False, True):
+            dn.MULTI_WGRAD = mode
+            net.zero_grad()
+            torch.autograd.backward(list(net(x, t)), go)
+            grads[mode] = [p.grad.clone() for p in net.parameters()]
+    finally:
+        dn.MULTI_WGRAD = saved
+    for (name, _), a, b in zip(net.named_parameters(), grads[False], grads[True]):
+        assert ((a - b).norm() / a.norm()).item() <= 1e-5, name
+
+
 def test_bf16_weight_gradient_path_against_fp32_tensors(native_lib):
     """BF16_WGRAD writes the kept activations / layer gradients as bf16 and multiplies them as bf16.  Same outputs
     (the layer chain is untouched), bias gradients identical up to atomics, weight gradients within bf16 rounding of

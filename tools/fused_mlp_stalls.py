@@ -1,5 +1,7 @@
 """Stall-cycle attribution of the two whole-network MLP kernels in TRAINING mode (bf16 side outputs on):
-cycles per CTA the MMA-issuing thread and one epilogue warp spent waiting on each barrier."""
+cycles per CTA the MMA-issuing thread and one epilogue warp spent waiting on each barrier.
+The counters are compiled out of the shipped library (they cost 4-5 % of the kernels); build the instrumented one first:
+    TRASE_B200_EXTRA_NVCC_FLAGS=-DTB_FU_PROF=1 TRASE_B200_LIB_OUT=libtrase_b200_prof.so python -m trase_b200.build"""
 import ctypes, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -11,6 +13,11 @@ M = int(sys.argv[1]) if len(sys.argv) > 1 else 300000
 net = DeformNetwork(backend="native").cuda()
 x = (torch.rand(M, 3, device="cuda") - 0.5) * 3
 t = torch.full((M, 1), 0.37, device="cuda")
+_prof = os.path.join(os.path.dirname(_lib.LIB_PATH), "libtrase_b200_prof.so")
+if os.path.exists(_prof):
+    _lib.LIB_PATH = _prof
+else:
+    print("note: %s not built; the stall counters of the shipped library read 0" % _prof)
 lib = _lib.load()
 lib.trase_b200_mlp_fused_set_prof.argtypes = [ctypes.c_void_p]
 buf = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")

@@ -35,6 +35,8 @@ DIRECT_GRAD_ACCUM = True
 # gradients then carry bf16 rounding noise (8 mantissa bits per factor, averaged over the M rows of the sum;
 # measured against fp32 in tests/test_gpu_mlp.py next to the TF32 yardstick).  False: fp32 tensors, TF32 products.
 BF16_WGRAD = True
+# with bf16 operands: all weight-gradient products of a backward pass in one launch (trase_b200_wgrad_bf16_multi)
+MULTI_WGRAD = True
 
 
 def _direct_ok(p, dev) -> bool:
@@ -121,6 +123,20 @@ def _wgrad16(lib, P16, Q16, D):
     J = D.shape[1]
     _lib.check(lib.trase_b200_wgrad_bf16(P16.data_ptr(), P16.stride(0), I, Q16.data_ptr(), Q16.stride(0), J, M,
                                          D.data_ptr(), D.stride(0), _stream(P16.device)))
+
+
+def _wgrad16_multi(lib, jobs):
+    """All products of `jobs` = [(P16, Q16, D), ...] in one launch (csrc/mlp_gemm.cu wgrad_bf16_multi_kernel)."""
+    n = len(jobs)
+    if n == 0:
+        return
+    M = jobs[0][0].shape[0]
+    vp, ip = ctypes.c_void_p * n, ctypes.c_int * n
+    _lib.check(lib.trase_b200_wgrad_bf16_multi(
+        n, vp(*[P.data_ptr() for P, _, _ in jobs]), ip(*[P.stride(0) for P, _, _ in jobs]),
+        ip(*[P.shape[1] for P, _, _ in jobs]), vp(*[Q.data_ptr() for _, Q, _ in jobs]),
+        ip(*[Q.stride(0) for _, Q, _ in jobs]), ip(*[D.shape[1] for _, _, D in jobs]), M,
+        vp(*[D.data_ptr() for _, _, D in jobs]), ip(*[D.stride(0) for _, _, D in jobs]), _stream(jobs[0][0].device)))
 
 
 def _to_bf16(lib, src, cols, ld_dst):
@@ -259,7 +275,13 @@ class _DeformMLP(torch.autograd.Function):
             # the fused chain packs its operand from the raw weights the fused forward kept
             bf16 = ctx.bf16                 # the forward wrote bf16 activations: the fused chain + bf16 wgrad follow
             fused_bwd = (bf16 or FUSED_BACKWARD) and fused and lib.trase_b200_mlp_fused_pack_bwd_floats(nl) > 0
-            wgrad = _wgrad16 if bf16 else _wgrad
+            # bf16 operands + the fused chain: every product of the pass is queued and runs as ONE launch at the end
+            multi = [] if (bf16 and MULTI_WGRAD and fused_bwd) else None
+            if multi is not None:
+                def wgrad(_lib_, P, Q, D):
+                    multi.append((P, Q, D))
+            else:
+                wgrad = _wgrad16 if bf16 else _wgrad
             raw_w = list(saved[3 + nl:]) if fused else None
             if fused_bwd:
                 WrT = None
@@ -326,6 +348,8 @@ class _DeformMLP(torch.autograd.Function):
                     dz_prev = torch.empty((M, W), **f32)
                     _gemm(lib, dz, WrT[i], dz_prev, mask_in=masks[i - 1], colsum=grads_b[i - 1])
                     dz = dz_prev
+            if multi is not None:
+                _wgrad16_multi(lib, multi)
             span.__exit__()
             dwh = dwhT.t()
             out = [None, None, None, None, None, None]

@@ -76,7 +76,7 @@ EXPORTS = [
     "trase_b200_adam_step", "trase_b200_densification_stats", "trase_b200_sample_features_forward",
     "trase_b200_sample_features_backward", "trase_b200_mlp_fused_set_prof",
     "trase_b200_smooth_features_forward", "trase_b200_smooth_features_backward",
-    "trase_b200_mlp_forward_fused_bf16", "trase_b200_mlp_backward_fused_bf16", "trase_b200_wgrad_bf16",
+    "trase_b200_mlp_forward_fused_bf16", "trase_b200_mlp_backward_fused_bf16", "trase_b200_wgrad_bf16", "trase_b200_wgrad_bf16_multi",
     "trase_b200_f32_to_bf16", "trase_b200_arena_gather_rows", "trase_b200_contrastive_scratch_bytes",
     "trase_b200_pixel_mask_info", "trase_b200_contrastive_soft_forward", "trase_b200_contrastive_soft_backward",
     "trase_b200_deform_embed_bf16", "trase_b200_mlp_pack_dout_bf16",
@@ -195,6 +195,9 @@ def load() -> C.CDLL:
                                                  C.c_int, C.c_void_p, C.c_int, C.c_void_p]
     lib.trase_b200_mlp_pack_dout_bf16.restype = C.c_int
     lib.trase_b200_mlp_pack_dout_bf16.argtypes = [C.c_int] + [C.c_void_p] * 7
+    lib.trase_b200_wgrad_bf16_multi.restype = C.c_int
+    lib.trase_b200_wgrad_bf16_multi.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.trase_b200_wgrad_bf16.restype = C.c_int
     lib.trase_b200_wgrad_bf16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                           C.c_void_p, C.c_int, C.c_void_p]

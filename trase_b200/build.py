@@ -19,6 +19,12 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # default -fmad=true, no fast-math: integer parity with the reference depends on it
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
+# debugging / measurement builds: extra nvcc flags (e.g. -DTB_FU_PROF=1 for tools/fused_mlp_stalls.py) and another output
+# name, so that the shipped library is never overwritten by such a build
+FLAGS += os.environ.get("TRASE_B200_EXTRA_NVCC_FLAGS", "").split()
+if os.environ.get("TRASE_B200_LIB_OUT"):
+    LIB = os.path.join(HERE, os.environ["TRASE_B200_LIB_OUT"])
+    BUILD = os.path.join(HERE, "csrc", "build_" + os.path.splitext(os.environ["TRASE_B200_LIB_OUT"])[0])
 
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "render.cu", "render_mma.cu", "no_alloc.cu", "mlp_gemm.cu", "assemble.cu", "mlp_prep.cu", "loss.cu", "mlp_fused.cu", "optim.cu", "contrastive.cu"]
 HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "ptx.cuh"), os.path.join(CSRC, "render_common.cuh"), os.path.join(HERE, "..", "include", "trase_b200.h")]

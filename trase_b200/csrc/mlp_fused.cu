@@ -49,40 +49,18 @@ constexpr int FU_ECH = 3;                 // up to 96 embedding columns
 // ring stages of 16 KB (this CTA's half of a weight k-block, or a chunk of the first operand);
 // the backward chain gives one stage up for its bias-gradient accumulators
 // A16 (bf16 side output, see below) gives one more stage up: 8 epilogue warps x 2 KB of store staging
-// TB_FU_DIRECT16: the A16 kernels write the bf16 copy with two 32-byte global stores per row and slab straight from the
-// epilogue registers instead of staging it for a TMA store (no staging bytes through the shared-memory port, which
-// bounds these kernels, and the stage is not given up).  TB_FU_PREFETCH: the epilogue warps issue the TMEM load, bias
-// and mask loads of their next slab before they process the current one.
-#ifndef TB_FU_DIRECT16
-#define TB_FU_DIRECT16 0
-#endif
-#ifndef TB_FU_PREFETCH
-#define TB_FU_PREFETCH 0
-#endif
-// TB_FU_HALFSLAB: the two epilogue warps of a lane quarter take the two 16-column halves of the SAME 32-column chunk
-// instead of alternate chunks: chunks are handed to the next layer's MMAs in order, the first one after half the time.
-// TB_FU_PROF: the stall-cycle counters read by tools/fused_mlp_stalls.py.  Off in the shipped library: the clock64()
-// pairs around every wait of the MMA-issuing thread cost 4-5 % of the kernel (profiles/r2_u_mlp_epilogue_variants.txt).
+template <bool BWD, bool A16> struct FuCfg { static constexpr int STAGES = (BWD ? 5 : 6) - (A16 ? 1 : 0); };
+// TB_FU_PROF: the stall-cycle counters read by tools/fused_mlp_stalls.py (build with
+// TRASE_B200_EXTRA_NVCC_FLAGS=-DTB_FU_PROF=1).  Off in the shipped library: the clock64() pairs around every wait of the
+// MMA-issuing thread cost 4-5 % of the kernel (profiles/r2_u_mlp_epilogue_variants.txt).
 #ifndef TB_FU_PROF
 #define TB_FU_PROF 0
 #endif
-#ifndef TB_FU_KFENCE
-#define TB_FU_KFENCE 1
-#endif
-#ifndef TB_FU_HALFSLAB
-#define TB_FU_HALFSLAB 0
-#endif
-template <bool BWD, bool A16> struct FuCfg {
-  static constexpr int STAGES = (BWD ? 5 : 6) - ((A16 && !TB_FU_DIRECT16) ? 1 : 0);
-};
 #ifndef TB_FU_EPI_WARPS
 #define TB_FU_EPI_WARPS 8
 #endif
 constexpr int FU_EPI_WARPS = TB_FU_EPI_WARPS;            // two per TMEM lane quarter, alternating 32-column slabs (12 warps: no gain, the MMA side is the bound)
 constexpr int FU_THREADS = 128 + 32 * FU_EPI_WARPS;
-constexpr int FU_SLAB_SPLIT = TB_FU_HALFSLAB ? 2 : 1;    // epilogue warps that share one 32-column chunk of a lane quarter
-constexpr int FU_SLABW = 32 / FU_SLAB_SPLIT;
-static_assert(!TB_FU_HALFSLAB || (FU_EPI_WARPS == 8 && TB_FU_DIRECT16), "half slabs: 8 epilogue warps, direct bf16 stores");
 constexpr int FU_MAX_LAYERS = 12;
 constexpr int FU_CLUSTER = 2;             // CTA pair: one tcgen05.mma.cta_group::2 spans both         // hidden layers + the head pseudo-layer
 
@@ -100,7 +78,6 @@ struct FusedParams {
   float* out16;                      // [M][16]
   float* acts;                       // [nl][M][256]  (backward: dZ of every layer, in backward order)
   int acts16;                        // A16 kernels: the bf16 tensor map (tmActs) is live
-  __nv_bfloat16* a16;                // the same tensor as a plain pointer (TB_FU_DIRECT16)
   float* colsum[FU_MAX_LAYERS];      // backward: bias gradient [256] of every forward layer (+=)
   unsigned long long* prof;          // optional [grid][8] stall-cycle counters (tools/check_fused_mlp.py)
 };
@@ -121,20 +98,6 @@ __device__ __forceinline__ float fu_transpose_reduce32(float (&v)[32], int lane)
     }
   }
   return v[0];
-}
-// Same for 16 values: every lane l returns the total of v[l & 15].
-__device__ __forceinline__ float fu_transpose_reduce16(float (&v)[16], int lane) {
-#pragma unroll
-  for (int w = 8; w >= 1; w >>= 1) {
-    const bool hi = lane & w;
-#pragma unroll
-    for (int i = 0; i < w; i++) {
-      const float send = hi ? v[i] : v[i + w];
-      const float keep = hi ? v[i + w] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, w);
-    }
-  }
-  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
 __device__ __forceinline__ int fu_h_blocks(int L) { return L == 0 ? 0 : FU_HCH; }
 
@@ -184,7 +147,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
       mbar_init(&full[i], leader ? 2 : 1);
       mbar_init(&empty[i], 1);
     }
-    for (int i = 0; i < FU_HCH; i++) { mbar_init(&a_ready[i], 4 * FU_CLUSTER * FU_SLAB_SPLIT); mbar_init(&a_local[i], 4 * FU_SLAB_SPLIT); }
+    for (int i = 0; i < FU_HCH; i++) { mbar_init(&a_ready[i], 4 * FU_CLUSTER); mbar_init(&a_local[i], 4); }
     for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], FU_EPI_WARPS * FU_CLUSTER); }
     mbar_init(h_free, 1);
     fence_barrier_init();
@@ -237,18 +200,13 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
       constexpr uint32_t idesc_h = make_idesc_tf32(2 * FU_BM, 256, 0, 0);
       constexpr uint32_t idesc_o = make_idesc_tf32(2 * FU_BM, 32, 0, 0);
       uint32_t stage = 0, phase = 0, a_phase = 0, lc = 0;
-      long long w_acc = 0, w_a = 0, w_full = 0, w_st = 0, w_iss = 0, t_all = clock64(), t0;
+      long long w_acc = 0, w_a = 0, w_full = 0, w_st = 0, w_iss = 0, t_all = clock64(), t0 = 0;
 #if TB_FU_PROF
 #define FU_T0() (t0 = clock64())
 #define FU_ADD(x) ((x) += clock64() - t0)
 #else
 #define FU_T0() ((void)0)
 #define FU_ADD(x) ((void)(x), (void)t0)
-#endif
-#if TB_FU_KFENCE
-#define FU_KFENCE() tc_fence_after()
-#else
-#define FU_KFENCE() ((void)0)
 #endif
       for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
         for (int L = 0; L <= p.nl; L++) {
@@ -270,7 +228,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
                 FU_T0();
                 mbar_wait(&full[stage], phase);
                 FU_ADD(w_full);
-                FU_KFENCE();
+                tc_fence_after();
               }
               a_stage = (int)stage;
               a_addr = smem_u32(sW + stage * FU_CHUNK);
@@ -280,7 +238,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
               FU_T0();
               mbar_wait(leader ? &a_ready[j] : &a_local[j], a_phase);
               FU_ADD(w_a);
-              FU_KFENCE();
+              tc_fence_after();
               a_addr = smem_u32(sH + j * FU_CHUNK);
               if (!A16 && p.acts) tma_store_3d(&tmActs, sH + j * FU_CHUNK, j * 32, tile * FU_BM, L - 1);   // h_{L-1}[:, 32j .. 32j+31]
             }
@@ -289,7 +247,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
               FU_T0();
               mbar_wait(&full[stage], phase);
               FU_ADD(w_full);
-              FU_KFENCE();
+              tc_fence_after();
               const uint32_t b_addr = smem_u32(sW + stage * FU_CHUNK);
               FU_T0();
 #pragma unroll
@@ -342,7 +300,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
     const int ew = warp & 3, eh = (warp - 4) >> 2;
     const int r = ew * 32 + lane;                 // row inside the tile
     uint32_t lc = 0;
-    long long e_full = 0, e_free = 0, t0;
+    long long e_full = 0, e_free = 0, t0 = 0;
     for (int it = 0, tile = blockIdx.x; it < iters; it++, tile += gridDim.x) {
       const int grow = tile * FU_BM + r;
       for (int L = 0; L < (BWD ? p.nl : p.nl + 1); L++, lc++) {
@@ -356,38 +314,32 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
         if (BWD || L < p.nl) {
           // forward layer this step belongs to: its bias (forward) or its ReLU mask and bias gradient (backward)
           const int fl = BWD ? p.nl - 1 - L : L;
-          const float4* bias4 = reinterpret_cast<const float4*>(p.bias + fl * FU_W);
+          const float* bias = p.bias + fl * FU_W;
           uint32_t* mask = p.masks + ((size_t)fl * p.M + (grow < p.M ? grow : 0)) * (FU_W / 32);
-          constexpr int SSTEP = TB_FU_HALFSLAB ? 1 : FU_EPI_WARPS / 4;       // chunk stride of one warp
-          constexpr int SW = FU_SLABW, SQ = FU_SLABW / 4;                    // slab width in columns / float4s
-          const int s0 = TB_FU_HALFSLAB ? 0 : eh;                            // first chunk of this warp
-          const int coff = TB_FU_HALFSLAB ? eh * 16 : 0;                     // column offset inside the chunk
-          uint32_t vv[2][SW];
-          float4 bqq[2][SQ];
-          uint32_t kpp[2];
-          // TMEM load of slab s plus what its epilogue needs from global memory (bias row / ReLU mask word)
-          auto fetch = [&](const int s, uint32_t (&v)[SW], float4 (&bq)[SQ], uint32_t& keep) {
-            if constexpr (TB_FU_HALFSLAB) tmem_ld_32x16(t_addr + s * 32 + coff, reinterpret_cast<uint32_t (&)[16]>(v));
-            else tmem_ld_32x32(t_addr + s * 32, reinterpret_cast<uint32_t (&)[32]>(v));
+#pragma unroll 1
+          for (int s = eh; s < FU_HCH; s += FU_EPI_WARPS / 4) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_addr + s * 32, v);
+            float4 bq[8];
+            uint32_t keep = 0;
             if (BWD) {
-              keep = grow < p.M ? (__ldg(mask + s) >> coff) : 0u;
+              keep = grow < p.M ? __ldg(mask + s) : 0u;
             } else {
 #pragma unroll
-              for (int c = 0; c < SQ; c++) bq[c] = __ldg(bias4 + s * 8 + (coff >> 2) + c);
+              for (int c = 0; c < 8; c++) bq[c] = __ldg(reinterpret_cast<const float4*>(bias + s * 32) + c);
             }
-          };
-          auto slab = [&](const int s, uint32_t (&v)[SW], const float4 (&bq)[SQ], const uint32_t keep, const bool first) {
-            if (first) { FU_T0(); mbar_wait(h_free, hfree_parity); FU_ADD(e_free); }
+            tmem_ld_wait();
+            if (s == eh) { FU_T0(); mbar_wait(h_free, hfree_parity); FU_ADD(e_free); }
             uint8_t* dst = sH + s * FU_CHUNK + r * 128;
             uint32_t pos = 0;
             uint8_t* st16 = sStore + (warp - 4) * 2048;
-            if (A16 && !TB_FU_DIRECT16 && p.acts16) {
+            if (A16 && p.acts16) {
               // this warp's previous slab store must have read its staging before it is overwritten
               if (lane == 0) tma_store_wait_read<0>();
               __syncwarp();
             }
 #pragma unroll
-            for (int c = 0; c < SQ; c++) {
+            for (int c = 0; c < 8; c++) {
               const float bb[4] = {bq[c].x, bq[c].y, bq[c].z, bq[c].w};
               float4 o;
               float* of = reinterpret_cast<float*>(&o);
@@ -405,88 +357,44 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
                 if (BWD) v[c * 4 + j] = u;
                 if (A16 && !BWD) v[c * 4 + j] = __float_as_uint(x);      // unrounded value for the bf16 copy
               }
-              *reinterpret_cast<float4*>(dst + (((c + (coff >> 2)) ^ (r & 7)) << 4)) = o;
+              *reinterpret_cast<float4*>(dst + ((c ^ (r & 7)) << 4)) = o;
             }
-            if constexpr (A16 && !TB_FU_DIRECT16) {
-              if (p.acts16) {
-                // 32 values -> 64 bytes of bf16, row `lane` of the warp's staging, 16-byte chunks XOR-swizzled like
-                // CU_TENSOR_MAP_SWIZZLE_64B (chunk ^ bits 7..8 of the address = (row >> 1) & 3): conflict-free STS.128
+            if (A16 && p.acts16) {
+              // 32 values -> 64 bytes of bf16, row `lane` of the warp's staging, 16-byte chunks XOR-swizzled like
+              // CU_TENSOR_MAP_SWIZZLE_64B (chunk ^ bits 7..8 of the address = (row >> 1) & 3): conflict-free STS.128
 #pragma unroll
-                for (int c = 0; c < 4; c++) {
-                  uint4 o16;
-                  uint32_t* ow = reinterpret_cast<uint32_t*>(&o16);
+              for (int c = 0; c < 4; c++) {
+                uint4 o16;
+                uint32_t* ow = reinterpret_cast<uint32_t*>(&o16);
 #pragma unroll
-                  for (int j = 0; j < 4; j++) {
-                    const __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[c * 8 + 2 * j]),
-                                                                    __uint_as_float(v[c * 8 + 2 * j + 1]));
-                    ow[j] = *reinterpret_cast<const uint32_t*>(&h2);
-                  }
-                  *reinterpret_cast<uint4*>(st16 + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4)) = o16;
+                for (int j = 0; j < 4; j++) {
+                  const __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[c * 8 + 2 * j]),
+                                                                  __uint_as_float(v[c * 8 + 2 * j + 1]));
+                  ow[j] = *reinterpret_cast<const uint32_t*>(&h2);
                 }
+                *reinterpret_cast<uint4*>(st16 + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4)) = o16;
               }
             }
-            if (!BWD && p.masks && grow < p.M) {
-              if constexpr (TB_FU_HALFSLAB) reinterpret_cast<uint16_t*>(mask)[2 * s + eh] = (uint16_t)pos;
-              else mask[s] = pos;
-            }
+            if (!BWD && p.masks && grow < p.M) mask[s] = pos;
             fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
             __syncwarp();
             if (lane == 0) {
-              if (A16 && !TB_FU_DIRECT16 && p.acts16) {
+              if (A16 && p.acts16) {
                 tma_store_3d(&tmActs, st16, s * 32, tile * FU_BM + ew * 32, L);     // rows past M are clipped
                 tma_store_commit();
               }
               mbar_arrive(&a_local[s]);
               if (leader) mbar_arrive(&a_ready[s]); else mbar_arrive_cluster(&a_ready[s], 0);
             }
-            if (A16 && TB_FU_DIRECT16 && p.acts16 && grow < p.M) {
-              // the row's values as bf16 in full 32-byte sectors, written after the chunk was handed on
-              uint32_t pk[SW / 2];
-#pragma unroll
-              for (int j = 0; j < SW / 2; j++) {
-                const __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-                pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
-              }
-              __nv_bfloat16* g = p.a16 + ((size_t)L * p.M + grow) * FU_W + s * 32 + coff;
-#pragma unroll
-              for (int h = 0; h < SW / 16; h++)
-                st_global_v8(g + 16 * h, pk[8 * h], pk[8 * h + 1], pk[8 * h + 2], pk[8 * h + 3], pk[8 * h + 4],
-                             pk[8 * h + 5], pk[8 * h + 6], pk[8 * h + 7]);
-            }
             if (BWD) {
               // bias gradient of forward layer fl: column sums of the values just written (rows past M are 0)
-              float cv[SW];
+              float cv[32];
 #pragma unroll
-              for (int i = 0; i < SW; i++) cv[i] = __uint_as_float(v[i]);
-              if constexpr (TB_FU_HALFSLAB) {
-                const float tot = fu_transpose_reduce16(reinterpret_cast<float (&)[16]>(cv), lane);
-                if (lane < 16) atomicAdd(sCol + fl * FU_W + s * 32 + coff + lane, tot);
-              } else {
-                const float tot = fu_transpose_reduce32(reinterpret_cast<float (&)[32]>(cv), lane);
-                atomicAdd(sCol + fl * FU_W + s * 32 + lane, tot);
-              }
-            }
-          };
-#if TB_FU_PREFETCH
-          constexpr int NSLAB = (FU_HCH + SSTEP - 1) / SSTEP;
-          if (s0 < FU_HCH) fetch(s0, vv[0], bqq[0], kpp[0]);
-#pragma unroll
-          for (int i = 0; i < NSLAB; i++) {
-            const int s = s0 + i * SSTEP;
-            if (s < FU_HCH) {
-              tmem_ld_wait();
-              if (i + 1 < NSLAB && s + SSTEP < FU_HCH) fetch(s + SSTEP, vv[(i + 1) & 1], bqq[(i + 1) & 1], kpp[(i + 1) & 1]);
-              slab(s, vv[i & 1], bqq[i & 1], kpp[i & 1], i == 0);
+              for (int i = 0; i < 32; i++) cv[i] = __uint_as_float(v[i]);
+              const float tot = fu_transpose_reduce32(cv, lane);
+              atomicAdd(sCol + fl * FU_W + s * 32 + lane, tot);
             }
           }
-#else
-#pragma unroll 1
-          for (int s = s0; s < FU_HCH; s += SSTEP) {
-            fetch(s, vv[0], bqq[0], kpp[0]);
-            tmem_ld_wait();
-            slab(s, vv[0], bqq[0], kpp[0], s == s0);
-          }
-#endif
         } else if (eh == 0) {
           uint32_t v[16];
           tmem_ld_32x16(t_addr, v);
@@ -508,7 +416,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
         if (lane == 0) { if (leader) mbar_arrive(&tmem_empty[acc]); else mbar_arrive_cluster(&tmem_empty[acc], 0); }
       }
     }
-    if (A16 && !TB_FU_DIRECT16 && lane == 0) tma_store_wait<0>();
+    if (A16 && lane == 0) tma_store_wait<0>();
     if (p.prof && warp == 4 && lane == 0) { p.prof[blockIdx.x * 8 + 5] = e_full; p.prof[blockIdx.x * 8 + 6] = e_free; }
   }
   tc_fence_before();
@@ -714,7 +622,7 @@ static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* e
                                   void* stream) {
   if (M <= 0) return 0;
   if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || !out16 ||
-      (((acts == nullptr) && (acts16 == nullptr)) != (masks == nullptr)) || ((uintptr_t)acts16 & (TB_FU_DIRECT16 ? 31 : 15)) || (ld_emb & 3) ||
+      (((acts == nullptr) && (acts16 == nullptr)) != (masks == nullptr)) || ((uintptr_t)acts16 & 15) || (ld_emb & 3) ||
       ld_emb < E || ((uintptr_t)emb & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)acts & 15) ||
       ((uintptr_t)bias & 15) || ((uintptr_t)out16 & 15)) {
     set_error("trase_b200_mlp_forward_fused: bad arguments (M=%d nl=%d skip=%d E=%d)", M, nl, skip, E);
@@ -725,7 +633,7 @@ static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* e
   int base[mlp::FU_MAX_LAYERS + 2];
   const int total = mlp::fu_layout(nl, skip, E, base);
   for (int L = 0; L <= nl; L++) p.blk_base[L] = base[L];
-  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.acts16 = acts16 ? 1 : 0; p.a16 = reinterpret_cast<__nv_bfloat16*>(acts16);
+  p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.acts16 = acts16 ? 1 : 0;
   for (int i = 0; i < mlp::FU_MAX_LAYERS; i++) p.colsum[i] = nullptr;
   p.prof = mlp::g_fused_prof;
   CUtensorMap tE, tW, tWh, tA;
@@ -799,7 +707,7 @@ static int mlp_backward_fused_impl(int M, int nl, const float* dout, const float
                                    float* dzs, void* dzs16, float* const* colsum, void* stream) {
   if (M <= 0) return 0;
   if (nl < 2 || nl + 1 > mlp::FU_MAX_LAYERS || !dout || !wpack || !masks || !colsum ||
-      ((uintptr_t)dout & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)dzs & 15) || ((uintptr_t)dzs16 & (TB_FU_DIRECT16 ? 31 : 15))) {
+      ((uintptr_t)dout & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)dzs & 15) || ((uintptr_t)dzs16 & 15)) {
     set_error("trase_b200_mlp_backward_fused: bad arguments (M=%d nl=%d)", M, nl);
     return 1;
   }
@@ -807,7 +715,7 @@ static int mlp_backward_fused_impl(int M, int nl, const float* dout, const float
   p.M = M; p.nl = nl; p.skip = -1; p.eb = 1;
   p.blk_base[0] = 0;
   for (int L = 1; L <= nl; L++) p.blk_base[L] = 1 + (L - 1) * mlp::FU_HCH;
-  p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs; p.acts16 = dzs16 ? 1 : 0; p.a16 = reinterpret_cast<__nv_bfloat16*>(dzs16);
+  p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs; p.acts16 = dzs16 ? 1 : 0;
   for (int i = 0; i < nl; i++) {
     if (!colsum[i]) { set_error("trase_b200_mlp_backward_fused: null bias-gradient pointer"); return 1; }
     p.colsum[i] = colsum[i];

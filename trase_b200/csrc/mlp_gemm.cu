@@ -557,8 +557,9 @@ constexpr int WH_STAGES = 3;
 constexpr int WH_BOX_BYTES = WH_ROWS * 128;       // one 64-row x 64-col bf16 box
 constexpr int WH_OP_BYTES = 4 * WH_BOX_BYTES;     // up to 256 columns per operand = 32 KB
 
-__global__ void __launch_bounds__(WG_THREADS, 1)
-wgrad_bf16_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ, const WgradParams p) {
+// One CTA's share of one product: row blocks [blk0, blk1) of 64 rows each, result added to p.D.
+__device__ __forceinline__ void wgrad_bf16_body(const CUtensorMap* tmP, const CUtensorMap* tmQ, const WgradParams& p,
+                                                const int blk0, const int blk1) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
@@ -575,14 +576,10 @@ wgrad_bf16_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
   const int i_boxes = n_halves * 2;                      // 64-column boxes of P
   const int j_boxes = (p.J + 63) / 64;
   const int jpad = ((p.J + 15) / 16) * 16;               // N of the MMA
-  const int nblk = (p.M + WH_ROWS - 1) / WH_ROWS;
-  const int per = (nblk + gridDim.x - 1) / gridDim.x;
-  const int blk0 = blockIdx.x * per;
-  const int blk1 = min(nblk, blk0 + per);
   constexpr uint32_t TMEM_COLS = 512;
 
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmP); prefetch_tmap(&tmQ);
+    prefetch_tmap(tmP); prefetch_tmap(tmQ);
     for (int i = 0; i < WH_STAGES; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(done, 1);
     fence_barrier_init();
@@ -600,9 +597,9 @@ wgrad_bf16_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
         mbar_wait(&empty[stage], phase ^ 1);
         mbar_expect_tx(&full[stage], (i_boxes + j_boxes) * WH_BOX_BYTES);
         for (int c = 0; c < i_boxes; c++)
-          tma_load_2d(sP + stage * WH_OP_BYTES + c * WH_BOX_BYTES, &tmP, &full[stage], c * 64, b * WH_ROWS);
+          tma_load_2d(sP + stage * WH_OP_BYTES + c * WH_BOX_BYTES, tmP, &full[stage], c * 64, b * WH_ROWS);
         for (int c = 0; c < j_boxes; c++)
-          tma_load_2d(sQ + stage * WH_OP_BYTES + c * WH_BOX_BYTES, &tmQ, &full[stage], c * 64, b * WH_ROWS);
+          tma_load_2d(sQ + stage * WH_OP_BYTES + c * WH_BOX_BYTES, tmQ, &full[stage], c * 64, b * WH_ROWS);
         if (++stage == WH_STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -657,6 +654,38 @@ wgrad_bf16_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+wgrad_bf16_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ, const WgradParams p) {
+  const int nblk = (p.M + WH_ROWS - 1) / WH_ROWS;
+  const int per = (nblk + gridDim.x - 1) / gridDim.x;
+  const int blk0 = blockIdx.x * per;
+  wgrad_bf16_body(&tmP, &tmQ, p, blk0, min(nblk, blk0 + per));
+}
+
+// All weight-gradient products of one backward pass in ONE launch: the CTAs are dealt out to the products in
+// proportion to the bytes each has to stream, every CTA reduces its row slice of ONE product in TMEM and adds the
+// I x J result to D once.  Against one launch per product (every one of which ends with all 148 CTAs adding a full
+// I x J tile): a tenth of the reduction traffic, one drain instead of ten, no launch gaps.
+constexpr int WGM_MAX = 12;
+struct WgradMultiParams {
+  CUtensorMap mP[WGM_MAX], mQ[WGM_MAX];
+  float* D[WGM_MAX];
+  int I[WGM_MAX], J[WGM_MAX], ldd[WGM_MAX];
+  int cta_first[WGM_MAX + 1];     // CTAs [cta_first[j], cta_first[j + 1]) work on product j
+  int M, njobs;
+};
+__global__ void __launch_bounds__(WG_THREADS, 1) wgrad_bf16_multi_kernel(const __grid_constant__ WgradMultiParams q) {
+  int job = 0;
+  while (job + 1 < q.njobs && (int)blockIdx.x >= q.cta_first[job + 1]) job++;
+  const int ci = blockIdx.x - q.cta_first[job], nc = q.cta_first[job + 1] - q.cta_first[job];
+  WgradParams p;
+  p.M = q.M; p.I = q.I[job]; p.J = q.J[job]; p.D = q.D[job]; p.ldd = q.ldd[job];
+  const int nblk = (p.M + WH_ROWS - 1) / WH_ROWS;
+  const int per = (nblk + nc - 1) / nc;
+  const int blk0 = ci * per;
+  wgrad_bf16_body(&q.mP[job], &q.mQ[job], p, blk0, min(nblk, blk0 + per));
 }
 
 typedef CUresult (*EncodeTiledFn16)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -728,6 +757,71 @@ extern "C" TRASE_API int trase_b200_wgrad_bf16(const void* P, int ldp, int I, co
   mlp::wgrad_bf16_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
+
+// njobs products D_j[i][k] += sum_m P_j[m][i] * Q_j[m][k] over the same M rows in one launch (arguments per product
+// as for trase_b200_wgrad_bf16; at most 12 products).
+extern "C" TRASE_API int trase_b200_wgrad_bf16_multi(int njobs, const void* const* P, const int* ldp, const int* I,
+                                                     const void* const* Q, const int* ldq, const int* J, int M,
+                                                     float* const* D, const int* ldd, void* stream) {
+  using namespace tb;
+  if (njobs <= 0 || M <= 0) return 0;
+  if (njobs > mlp::WGM_MAX || !P || !ldp || !I || !Q || !ldq || !J || !D || !ldd) {
+    set_error("trase_b200_wgrad_bf16_multi: bad arguments (njobs=%d, at most %d)", njobs, mlp::WGM_MAX);
+    return 1;
+  }
+  mlp::WgradMultiParams q;
+  int cost[mlp::WGM_MAX], total_cost = 0;
+  for (int j = 0; j < njobs; j++) {
+    if (I[j] <= 0 || J[j] <= 0 || I[j] > 256 || J[j] > 256 || (J[j] & 3) || !P[j] || !Q[j] || !D[j] || (ldp[j] & 7) ||
+        (ldq[j] & 7) || (ldd[j] & 3) || ((uintptr_t)P[j] & 15) || ((uintptr_t)Q[j] & 15) || ((uintptr_t)D[j] & 15)) {
+      set_error("trase_b200_wgrad_bf16_multi: product %d: bad shape, pitch or alignment (I=%d J=%d)", j, I[j], J[j]);
+      return 1;
+    }
+    if (!mlp::make_tmap_2d_bf16(&q.mP[j], P[j], M, I[j], ldp[j], mlp::WH_ROWS, 64) ||
+        !mlp::make_tmap_2d_bf16(&q.mQ[j], Q[j], M, J[j], ldq[j], mlp::WH_ROWS, 64)) {
+      set_error("trase_b200_wgrad_bf16_multi: cuTensorMapEncodeTiled failed");
+      return 2;
+    }
+    q.D[j] = D[j]; q.I[j] = I[j]; q.J[j] = J[j]; q.ldd[j] = ldd[j];
+    cost[j] = ((I[j] + 127) / 128) * 2 + (J[j] + 63) / 64;       // 64-column boxes streamed per row block
+    total_cost += cost[j];
+  }
+  q.M = M; q.njobs = njobs;
+  // CTAs per product in proportion to its bytes, at least one each, the grid exactly the SMs available
+  const int sms = mlp::num_sms();
+  if (sms < njobs) { set_error("trase_b200_wgrad_bf16_multi: fewer SMs (%d) than products (%d)", sms, njobs); return 1; }
+  int n[mlp::WGM_MAX], used = 0;
+  for (int j = 0; j < njobs; j++) {
+    n[j] = (int)((long long)sms * cost[j] / total_cost);
+    if (n[j] < 1) n[j] = 1;
+    used += n[j];
+  }
+  while (used != sms) {
+    // hand the spare CTAs to (take the excess from) the product with the most (least) work per CTA
+    int best = -1;
+    for (int j = 0; j < njobs; j++) {
+      if (used > sms && n[j] <= 1) continue;
+      if (best < 0) { best = j; continue; }
+      const long long a = (long long)cost[j] * n[best], b = (long long)cost[best] * n[j];     // cost/n compared
+      if (used < sms ? a > b : a < b) best = j;
+    }
+    n[best] += used < sms ? 1 : -1;
+    used += used < sms ? 1 : -1;
+  }
+  q.cta_first[0] = 0;
+  for (int j = 0; j < njobs; j++) q.cta_first[j + 1] = q.cta_first[j] + n[j];
+  static PerDeviceOnce attr_once;
+  const int smem = 2 * mlp::WH_STAGES * mlp::WH_OP_BYTES + 256 + 1024;
+  {
+    cudaError_t e = ensure_max_dyn_smem(attr_once, mlp::wgrad_bf16_multi_kernel, smem);
+    if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16_multi: %s", cudaGetErrorString(e)); return 2; }
+  }
+  mlp::wgrad_bf16_multi_kernel<<<sms, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(q);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16_multi: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
   return 0;
 }
