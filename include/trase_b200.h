@@ -261,7 +261,8 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
  * shs == NULL (forward) / g_fdc == NULL (backward): the caller's f_dc and f_rest
  * are views of one [P][Mrest+1][3] block already, so the SH copy and its
  * backward split are skipped (the caller passes that block to the rasterizer and
- * slices its gradient).
+ * slices its gradient).  g_feat == NULL (backward): the feature parameter is frozen,
+ * its gradient is not computed.
  * ---------------------------------------------------------------------- */
 TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const float* xyz, const float* d_xyz, const float* scaling,
                                           const float* d_scaling, const float* rotation, const float* d_rotation,
@@ -510,7 +511,8 @@ TRASE_API int trase_b200_wgrad_bf16_multi(int njobs, const void* const* P, const
                                           const void* const* Q, const int* ldq, const int* J, int M, float* const* D,
                                           const int* ldd, void* stream);
 /* The two producers of those small operands can write the bf16 copy themselves (no separate conversion pass):
- * the positional encoding (out16 [M][ld16], ld16 a multiple of 8 and >= the column count, padding zero-filled) and the
+ * the positional encoding (out16 [M][ld16], 16-byte aligned, ld16 a multiple of 8 and >= the column count, padding
+ * zero-filled) and the
  * packed head gradient (dout16 [M][16]). */
 TRASE_API int trase_b200_deform_embed_bf16(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt,
                                            float* out, int ld, void* out16, int ld16, void* stream);

@@ -83,7 +83,8 @@ class _Assemble(torch.autograd.Function):
             outs = [torch.empty((P, 3), **f32), torch.empty((P, 3), **f32), torch.empty((P, 3), **f32),
                     torch.empty((P, 3), **f32), torch.empty((P, 4), **f32), torch.empty((P, 4), **f32),
                     torch.empty((P, 1), **f32), None if alias else torch.empty((P, 1, 3), **f32),
-                    None if alias else torch.empty((P, Mrest, 3), **f32), torch.empty((P, 1, 32), **f32)]
+                    None if alias else torch.empty((P, Mrest, 3), **f32),
+                    torch.empty((P, 1, 32), **f32) if ctx.needs_input_grad[9] else None]     # frozen feature: skipped
             _lib.check(lib.trase_b200_assemble_backward(
                 P, Mrest, scaling.data_ptr(), rotation.data_ptr(), opacity.data_ptr(), feat.data_ptr(),
                 *[None if u is None else u.data_ptr() for u in ups], *[None if o is None else o.data_ptr() for o in outs],

@@ -291,7 +291,7 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
                                                       float* g_fdc, float* g_frest, float* g_feat, void* stream) {
   if (P <= 0) return 0;
   if (!scaling || !rotation || !opacity || !feat || !g_xyz || !g_dxyz || !g_scaling || !g_dscaling || !g_rotation ||
-      !g_drotation || !g_opacity || !g_feat || (g_fdc && Mrest > 0 && !g_frest)) {
+      !g_drotation || !g_opacity || (g_fdc && Mrest > 0 && !g_frest)) {
     set_error("trase_b200_assemble_backward: null pointer");
     return 1;
   }
@@ -302,11 +302,12 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
   const size_t tot = (size_t)P * (Mrest + 1) * 3;
   int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
   if (g_fdc) assemble_sh_bwd_kernel<<<g, 256, 0, s>>>(P, Mrest, g_shs, g_fdc, g_frest);   // NULL: caller slices g_shs itself
-  assemble_feat_bwd_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(
-      P, reinterpret_cast<const float4*>(feat), reinterpret_cast<const float4*>(g_objs),
-      reinterpret_cast<float4*>(g_feat));
+  if (g_feat)      // NULL: the feature parameter is frozen (GAUSSIAN state), nobody wants this gradient
+    assemble_feat_bwd_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(
+        P, reinterpret_cast<const float4*>(feat), reinterpret_cast<const float4*>(g_objs),
+        reinterpret_cast<float4*>(g_feat));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_assemble_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
-  count_launches(g_fdc ? 3 : 2);
+  count_launches(1 + (g_fdc ? 1 : 0) + (g_feat ? 1 : 0));
   return 0;
 }

@@ -333,11 +333,6 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
             uint8_t* dst = sH + s * FU_CHUNK + r * 128;
             uint32_t pos = 0;
             uint8_t* st16 = sStore + (warp - 4) * 2048;
-            if (A16 && p.acts16) {
-              // this warp's previous slab store must have read its staging before it is overwritten
-              if (lane == 0) tma_store_wait_read<0>();
-              __syncwarp();
-            }
 #pragma unroll
             for (int c = 0; c < 8; c++) {
               const float bb[4] = {bq[c].x, bq[c].y, bq[c].z, bq[c].w};
@@ -359,7 +354,19 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
               }
               *reinterpret_cast<float4*>(dst + ((c ^ (r & 7)) << 4)) = o;
             }
+            // the chunk goes to the next layer's MMAs first; what only the backward pass needs (bf16 copy, ReLU mask)
+            // follows, off the critical path of the layer hand-over
+            fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
+            __syncwarp();
+            if (lane == 0) {
+              mbar_arrive(&a_local[s]);
+              if (leader) mbar_arrive(&a_ready[s]); else mbar_arrive_cluster(&a_ready[s], 0);
+            }
+            if (!BWD && p.masks && grow < p.M) mask[s] = pos;
             if (A16 && p.acts16) {
+              // this warp's previous slab store must have read its staging before it is overwritten
+              if (lane == 0) tma_store_wait_read<0>();
+              __syncwarp();
               // 32 values -> 64 bytes of bf16, row `lane` of the warp's staging, 16-byte chunks XOR-swizzled like
               // CU_TENSOR_MAP_SWIZZLE_64B (chunk ^ bits 7..8 of the address = (row >> 1) & 3): conflict-free STS.128
 #pragma unroll
@@ -374,17 +381,12 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
                 }
                 *reinterpret_cast<uint4*>(st16 + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4)) = o16;
               }
-            }
-            if (!BWD && p.masks && grow < p.M) mask[s] = pos;
-            fence_proxy_async_smem();     // generic-proxy writes -> visible to the MMA / TMA (async proxy)
-            __syncwarp();
-            if (lane == 0) {
-              if (A16 && p.acts16) {
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
                 tma_store_3d(&tmActs, st16, s * 32, tile * FU_BM + ew * 32, L);     // rows past M are clipped
                 tma_store_commit();
               }
-              mbar_arrive(&a_local[s]);
-              if (leader) mbar_arrive(&a_ready[s]); else mbar_arrive_cluster(&a_ready[s], 0);
             }
             if (BWD) {
               // bias gradient of forward layer fl: column sums of the values just written (rows past M are 0)

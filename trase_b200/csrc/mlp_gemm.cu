@@ -861,60 +861,81 @@ __device__ __forceinline__ float rna_tf32(float x) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
   return __uint_as_float(u);
 }
-// One warp per row.  Lane (k, comp) evaluates one full-precision sincosf (arguments reach 2^9 * x) and
-// drops sin and cos into the warp's staging row; the row is then written with coalesced stores.
+// One block per 64 rows.  Every thread evaluates full-precision sincosf (arguments reach 2^9 * x) for (row, frequency,
+// component) items of the tile and drops sin and cos into a shared-memory copy of the tile laid out like the output
+// rows; the tile then leaves with 16-byte coalesced stores — fp32 rounded to TF32, and the bf16 copy — when the
+// output rows are contiguous (the native DeformNetwork's buffers), column by column otherwise.
 constexpr int EMB_MAX_COLS = 128;
+constexpr int EMB_ROWS = 64;
 __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* __restrict__ xyz,
                                                            const float* __restrict__ t, int t_stride, int Lx, int Lt,
                                                            float* __restrict__ out, int ld,
                                                            __nv_bfloat16* __restrict__ out16, int ld16) {
-  __shared__ float s_row[8][EMB_MAX_COLS];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int warps_per_grid = (gridDim.x * blockDim.x) >> 5;
+  __shared__ __align__(16) float s_tile[EMB_ROWS * EMB_MAX_COLS];
+  __shared__ float s_x[EMB_ROWS * 3];
   const int nx = 3 + 6 * Lx;           // columns of the xyz part
   const int ncol = nx + 1 + 2 * Lt;
-  float* row = s_row[w];
-  // one time stamp for every row (the usual case: one view = one t): its encoding is evaluated once per warp
-  // instead of once per row (the second sincosf call of a row costs as much as the 30-lane one for xyz)
-  if (t_stride == 0) {
-    const float tv = t[0];
-    if (lane == 0) row[nx] = tv;
-    for (int k = lane; k < Lt; k += 32) {
+  const int m0 = blockIdx.x * EMB_ROWS;
+  const int rows = min(EMB_ROWS, M - m0);
+  for (int i = threadIdx.x; i < rows * 3; i += blockDim.x) s_x[i] = xyz[(size_t)m0 * 3 + i];
+  __syncthreads();
+  // xyz part: item = (row, k, comp)
+  const int per_row = 3 * Lx;
+  for (int e = threadIdx.x; e < rows * per_row; e += blockDim.x) {
+    const int r = e / per_row, j = e - r * per_row;
+    const int k = j / 3, comp = j - 3 * k;
+    float sv, cv;
+    sincosf(s_x[r * 3 + comp] * exp2f((float)k), &sv, &cv);
+    s_tile[r * ncol + 3 + 6 * k + comp] = sv;
+    s_tile[r * ncol + 3 + 6 * k + 3 + comp] = cv;
+  }
+  for (int i = threadIdx.x; i < rows * 3; i += blockDim.x) s_tile[(i / 3) * ncol + (i % 3)] = s_x[i];
+  // time part: item = (row, k), k = -1 is the raw value.  One time stamp for every row (the usual case: one view =
+  // one t) costs Lt + 1 evaluations per row like any other, but reads no per-row input
+  const int per_row_t = Lt + 1;
+  for (int e = threadIdx.x; e < rows * per_row_t; e += blockDim.x) {
+    const int r = e / per_row_t, k = e - r * per_row_t - 1;
+    const float tv = t[(size_t)(m0 + r) * t_stride];
+    if (k < 0) {
+      s_tile[r * ncol + nx] = tv;
+    } else {
       float sv, cv;
       sincosf(tv * exp2f((float)k), &sv, &cv);
-      row[nx + 1 + 2 * k] = sv;
-      row[nx + 2 + 2 * k] = cv;
+      s_tile[r * ncol + nx + 1 + 2 * k] = sv;
+      s_tile[r * ncol + nx + 2 + 2 * k] = cv;
     }
-    __syncwarp();
   }
-  for (int m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < M; m += warps_per_grid) {
-    const float x0 = xyz[3 * m], x1 = xyz[3 * m + 1], x2 = xyz[3 * m + 2];
-    if (lane < 3) row[lane] = lane == 0 ? x0 : (lane == 1 ? x1 : x2);
-    for (int e = lane; e < 3 * Lx; e += 32) {       // (k, comp) pairs of the xyz part
-      const int k = e / 3, comp = e - 3 * k;
-      float sv, cv;
-      sincosf((comp == 0 ? x0 : (comp == 1 ? x1 : x2)) * exp2f((float)k), &sv, &cv);
-      row[3 + 6 * k + comp] = sv;
-      row[3 + 6 * k + 3 + comp] = cv;
+  __syncthreads();
+  float* o = out + (size_t)m0 * ld;
+  if (ld == ncol && (ncol & 3) == 0 && ((uintptr_t)out & 15) == 0) {
+    // the tile is one contiguous piece of the output
+    const float4* src = reinterpret_cast<const float4*>(s_tile);
+    float4* dst = reinterpret_cast<float4*>(o);
+    for (int i = threadIdx.x; i < rows * ncol / 4; i += blockDim.x) {
+      const float4 v = src[i];
+      dst[i] = make_float4(rna_tf32(v.x), rna_tf32(v.y), rna_tf32(v.z), rna_tf32(v.w));
     }
-    if (t_stride != 0) {
-      const float tv = t[(size_t)m * t_stride];
-      if (lane == 3) row[nx] = tv;
-      for (int k = lane; k < Lt; k += 32) {
-        float sv, cv;
-        sincosf(tv * exp2f((float)k), &sv, &cv);
-        row[nx + 1 + 2 * k] = sv;
-        row[nx + 2 + 2 * k] = cv;
+  } else {
+    for (int i = threadIdx.x; i < rows * ncol; i += blockDim.x) {
+      const int r = i / ncol, c = i - r * ncol;
+      o[(size_t)r * ld + c] = rna_tf32(s_tile[i]);
+    }
+  }
+  if (out16) {         // bf16 copy for the weight-gradient products (columns up to ld16 zero-filled), 8 values per store
+    uint4* dst = reinterpret_cast<uint4*>(out16 + (size_t)m0 * ld16);
+    const int per8 = ld16 >> 3;
+    for (int i = threadIdx.x; i < rows * per8; i += blockDim.x) {
+      const int r = i / per8, c0 = (i - r * per8) << 3;
+      uint32_t w[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int c = c0 + 2 * q;
+        const __nv_bfloat162 h2 = __floats2bfloat162_rn(c < ncol ? s_tile[r * ncol + c] : 0.f,
+                                                        c + 1 < ncol ? s_tile[r * ncol + c + 1] : 0.f);
+        w[q] = *reinterpret_cast<const uint32_t*>(&h2);
       }
+      dst[i] = make_uint4(w[0], w[1], w[2], w[3]);
     }
-    __syncwarp();
-    float* o = out + (size_t)m * ld;
-    for (int c = lane; c < ncol; c += 32) o[c] = rna_tf32(row[c]);
-    if (out16) {         // bf16 copy for the weight-gradient products (columns up to ld16 zero-filled)
-      __nv_bfloat16* o16 = out16 + (size_t)m * ld16;
-      for (int c = lane; c < ld16; c += 32) o16[c] = __float2bfloat16_rn(c < ncol ? row[c] : 0.f);
-    }
-    __syncwarp();
   }
 }
 
@@ -928,11 +949,12 @@ extern "C" TRASE_API int trase_b200_deform_embed(int M, const float* xyz, const 
                                                  float* out, int ld, void* stream) {
   return deform_embed_impl(M, xyz, t, t_stride, Lx, Lt, out, ld, nullptr, 0, stream);
 }
-// same, also writing a bf16 copy out16 [M][ld16] (ld16 >= the column count, a multiple of 8; padding zero-filled):
+// same, also writing a bf16 copy out16 [M][ld16] (16-byte aligned, ld16 >= the column count, a multiple of 8; padding
+// zero-filled):
 // the operand of the bf16 weight-gradient products of the two layers that read the embedding
 extern "C" TRASE_API int trase_b200_deform_embed_bf16(int M, const float* xyz, const float* t, int t_stride, int Lx,
                                                       int Lt, float* out, int ld, void* out16, int ld16, void* stream) {
-  if (M > 0 && (!out16 || (ld16 & 7) || ld16 < 3 + 6 * Lx + 1 + 2 * Lt || ld16 > tb::mlp::EMB_MAX_COLS)) {
+  if (M > 0 && (!out16 || ((uintptr_t)out16 & 15) || (ld16 & 7) || ld16 < 3 + 6 * Lx + 1 + 2 * Lt || ld16 > tb::mlp::EMB_MAX_COLS)) {
     tb::set_error("trase_b200_deform_embed_bf16: bad arguments");
     return 1;
   }
@@ -947,7 +969,7 @@ static int deform_embed_impl(int M, const float* xyz, const float* t, int t_stri
     set_error("trase_b200_deform_embed: bad arguments");
     return 1;
   }
-  const int blocks = (M + 7) / 8 < 148 * 16 ? (M + 7) / 8 : 148 * 16;
+  const int blocks = (M + mlp::EMB_ROWS - 1) / mlp::EMB_ROWS;
   mlp::deform_embed_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       M, xyz, t, t_stride, Lx, Lt, out, ld, reinterpret_cast<__nv_bfloat16*>(out16), ld16);
   cudaError_t e = cudaGetLastError();
