@@ -311,9 +311,19 @@ TRASE_API int trase_b200_contrastive_soft_backward(int N, int nwords, const floa
  * knn_idx [P][K] int64 is the caller's neighbour map (the reference gets it from pytorch3d.ops.knn_points and caches
  * it; the search is not part of this library); sel_cols (HOST array of n_sel <= 32 column numbers in [0, K)) are the
  * neighbours that take part in this call — the reference draws int(K*dropout) of them with torch.randperm.
- * feat, out, g_out, g_feat: [P][32] fp32 on the device.  backward overwrites g_feat. */
+ * feat, out, g_out, g_feat: [P][32] fp32 on the device.  backward overwrites g_feat.
+ * unit_scratch (forward, optional [P][32] fp32): with it every row is normalised once and the neighbours' unit rows
+ * are gathered (same values, same order of additions); NULL normalises each neighbour row at every use.
+ * backward_csr: the same gradient as a gather over the REVERSE of the neighbour map, which the caller builds once per
+ * map: rev_ptr [P+1] int32 row starts, rev_ent [P*K] int32, the entries (p << 8 | column) with knn_idx[p][column] == j
+ * listed for every j (any order inside a row).  No atomics and no pre-zeroing; K <= 64, P < 2^23, no column selected
+ * twice. */
 TRASE_API int trase_b200_smooth_features_forward(int P, int K, const int* sel_cols, int n_sel, const float* feat,
-                                                 const long long* knn_idx, float* out, void* stream);
+                                                 const long long* knn_idx, float* out, float* unit_scratch,
+                                                 void* stream);
+TRASE_API int trase_b200_smooth_features_backward_csr(int P, int K, const int* sel_cols, int n_sel, const float* feat,
+                                                      const int* rev_ptr, const int* rev_ent, const float* g_out,
+                                                      float* g_feat, void* stream);
 TRASE_API int trase_b200_smooth_features_backward(int P, int K, const int* sel_cols, int n_sel, const float* feat,
                                                   const long long* knn_idx, const float* g_out, float* g_feat,
                                                   void* stream);

@@ -511,6 +511,48 @@ def test_smoothed_feature_render_matches_torch_glue(native_lib):
     assert pc.get_smoothed_gaussian_features(K=1) is pc._gaussian_features
 
 
+def test_smoothed_feature_backward_gather_equals_scatter(native_lib):
+    """The smoothed-feature backward as a gather over the reverse neighbour map (no atomics) against the atomic scatter
+    over the forward map, and the normalise-once forward against normalising every neighbour at every use."""
+    import ctypes
+    from trase_b200._assemble import build_smooth_reverse, smooth_features
+    P, K = 20011, 16
+    g = torch.Generator().manual_seed(5)
+    knn = torch.randint(0, P, (P, K), generator=g).to(DEV)
+    knn[:, 0] = torch.arange(P, device=DEV)
+    knn[100:200, 3] = 7                                   # one Gaussian named by many others: a long reverse row
+    feat = (torch.randn(P, 1, 32, generator=g) * (torch.rand(P, 1, 1, generator=g) * 3 + 0.1)).to(DEV)
+    feat[17] = 0                                          # clamped branch of F.normalize
+    up = torch.randn(P, 1, 32, generator=g).to(DEV)
+    cols = [3, 0, 9, 12, 5, 1, 7, 15]
+    rev = build_smooth_reverse(knn)
+    ptr, ent = rev
+    assert int(ptr[-1]) == P * K and torch.equal(torch.sort(ent.long() >> 8 << 4 | (ent.long() & 255)).values,
+                                                 torch.arange(P * K, device=DEV))
+    res = []
+    for r in (None, rev):
+        f = feat.clone().requires_grad_(True)
+        out = smooth_features(f, knn, cols, r)
+        out.backward(up)
+        res.append((out.detach(), f.grad.clone()))
+    assert torch.equal(res[0][0], res[1][0])
+    assert rel_err(_np(res[0][1]), _np(res[1][1])) <= 1e-5
+    # forward without the unit-row scratch (normalise at every use): same bits
+    lib = native_lib
+    out2 = torch.empty(P, 32, device=DEV)
+    sel = (ctypes.c_int * len(cols))(*cols)
+    rc = lib.trase_b200_smooth_features_forward(P, K, sel, len(cols), feat.data_ptr(), knn.data_ptr(), out2.data_ptr(),
+                                                None, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, lib.trase_b200_last_error()
+    assert torch.equal(out2.view(P, 1, 32), res[0][0])
+    # a column selected twice is not a gather the reverse map can express: refused
+    sel2 = (ctypes.c_int * 2)(3, 3)
+    gf = torch.empty(P, 32, device=DEV)
+    rc = lib.trase_b200_smooth_features_backward_csr(P, K, sel2, 2, feat.data_ptr(), ptr.data_ptr(), ent.data_ptr(),
+                                                     up.data_ptr(), gf.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    assert rc != 0
+
+
 def test_aliased_sh_parameters_match_separate_storage(native_lib):
     """GaussianParams keeps f_dc / f_rest as adjacent views of one SH block so that render() skips the cat copy
     and the gradient split; a model whose two SH parameters were re-allocated separately (what Module.to or a

@@ -1,8 +1,10 @@
 #!/usr/bin/env bash
 cd "$(dirname "$0")/.."
-timeout 300 python tools/fused_mlp_stalls.py 300000 1 2>&1 | tail -5 | cut -c1-420
-timeout 600 python -m pytest tests/test_gpu_mlp.py -x -q 2>&1 | tail -1
-python bench.py --steps 30 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1])
-print(d['value'], d['ms_per_step'], {k:v['ms'] for k,v in d['stages'].items() if 'mlp' in k})"
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -k "smooth" 2>&1 | tail -3
+python bench.py --workload hypernerf8 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r2_y_hypernerf8.json 2>gpurun_out/r2_y.err || tail -5 gpurun_out/r2_y.err
+python -c "
+import json
+d=json.loads(open('gpurun_out/r2_y_hypernerf8.json').read().strip().splitlines()[-1])
+print(d['value'], d['ms_per_step'], d['e2e']['value'])"
+python tools/profile_step_multi.py --workload hypernerf8 2>&1 | sed -n 3,30p | cut -c1-110

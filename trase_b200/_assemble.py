@@ -101,9 +101,24 @@ def assemble_inputs(xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacit
     return _Assemble.apply(xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat)
 
 
+def build_smooth_reverse(knn_idx):
+    """Reverse of a [P,K] neighbour map for the gather form of the smoothed-feature backward: (rev_ptr [P+1] int32,
+    rev_ent [P*K] int32) with the entries (p << 8 | column) of all (p, column) that name Gaussian j, row by row.
+    Built once per map (a sort of P*K integers); None when the map does not fit the kernel's limits."""
+    P, K = knn_idx.shape
+    if K > 64 or P >= (1 << 23) or P == 0:
+        return None
+    flat = knn_idx.reshape(-1)
+    order = torch.argsort(flat, stable=True)
+    ent = ((torch.div(order, K, rounding_mode="floor") << 8) | (order % K)).to(torch.int32).contiguous()
+    ptr = torch.zeros(P + 1, dtype=torch.int32, device=knn_idx.device)
+    ptr[1:] = torch.cumsum(torch.bincount(flat, minlength=P), 0).to(torch.int32)
+    return ptr, ent
+
+
 class _SmoothFeatures(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, feat, knn_idx, sel_cols):
+    def forward(ctx, feat, knn_idx, sel_cols, rev):
         lib = _lib.load()
         if not feat.is_cuda:
             raise RuntimeError("trase_b200: smoothed features run on CUDA tensors only")
@@ -114,11 +129,15 @@ class _SmoothFeatures(torch.autograd.Function):
         sel = (C.c_int * len(sel_cols))(*[int(c) for c in sel_cols])
         with torch.cuda.device(dev):
             out = torch.empty((P, 1, 32), dtype=torch.float32, device=dev)
+            unit = torch.empty((P, 32), dtype=torch.float32, device=dev)     # every row normalised once, then gathered
             _lib.check(lib.trase_b200_smooth_features_forward(P, K, sel, len(sel_cols), f.data_ptr(), idx.data_ptr(),
-                                                              out.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+                                                              out.data_ptr(), unit.data_ptr(),
+                                                              torch.cuda.current_stream(dev).cuda_stream))
         ctx.save_for_backward(f, idx)
         ctx.sel = sel
         ctx.shape = feat.shape
+        # the gather form of the backward needs the reverse map and distinct columns (the reference's randperm draw)
+        ctx.rev = rev if (rev is not None and len(set(int(c) for c in sel_cols)) == len(sel_cols)) else None
         return out
 
     @staticmethod
@@ -130,13 +149,19 @@ class _SmoothFeatures(torch.autograd.Function):
         with torch.cuda.device(dev):
             g = _c(g_out)
             g_feat = torch.empty((P, 32), dtype=torch.float32, device=dev)
-            _lib.check(lib.trase_b200_smooth_features_backward(P, K, ctx.sel, len(ctx.sel), f.data_ptr(), idx.data_ptr(),
-                                                               g.data_ptr(), g_feat.data_ptr(),
-                                                               torch.cuda.current_stream(dev).cuda_stream))
-        return g_feat.view(ctx.shape), None, None
+            s = torch.cuda.current_stream(dev).cuda_stream
+            if ctx.rev is not None:
+                _lib.check(lib.trase_b200_smooth_features_backward_csr(
+                    P, K, ctx.sel, len(ctx.sel), f.data_ptr(), ctx.rev[0].data_ptr(), ctx.rev[1].data_ptr(),
+                    g.data_ptr(), g_feat.data_ptr(), s))
+            else:
+                _lib.check(lib.trase_b200_smooth_features_backward(P, K, ctx.sel, len(ctx.sel), f.data_ptr(),
+                                                                   idx.data_ptr(), g.data_ptr(), g_feat.data_ptr(), s))
+        return g_feat.view(ctx.shape), None, None, None
 
 
-def smooth_features(feat, knn_idx, sel_cols):
-    """mean over the selected columns of knn_idx of normalize(feat[neighbour]) -> [P,1,32]; one gather kernel per
-    direction (scene/gaussian_model.py:94-103 runs normalize + index + mean + their autograd)."""
-    return _SmoothFeatures.apply(feat, knn_idx, tuple(int(c) for c in sel_cols))
+def smooth_features(feat, knn_idx, sel_cols, rev=None):
+    """mean over the selected columns of knn_idx of normalize(feat[neighbour]) -> [P,1,32] (scene/gaussian_model.py:94-103
+    runs normalize + index + mean + their autograd).  `rev` = build_smooth_reverse(knn_idx) turns the backward from an
+    atomic scatter into a gather."""
+    return _SmoothFeatures.apply(feat, knn_idx, sel_cols, rev)

@@ -76,6 +76,7 @@ EXPORTS = [
     "trase_b200_adam_step", "trase_b200_densification_stats", "trase_b200_sample_features_forward",
     "trase_b200_sample_features_backward", "trase_b200_mlp_fused_set_prof",
     "trase_b200_smooth_features_forward", "trase_b200_smooth_features_backward",
+    "trase_b200_smooth_features_backward_csr",
     "trase_b200_mlp_forward_fused_bf16", "trase_b200_mlp_backward_fused_bf16", "trase_b200_wgrad_bf16", "trase_b200_wgrad_bf16_multi",
     "trase_b200_f32_to_bf16", "trase_b200_arena_gather_rows", "trase_b200_contrastive_scratch_bytes",
     "trase_b200_pixel_mask_info", "trase_b200_contrastive_soft_forward", "trase_b200_contrastive_soft_backward",
@@ -130,7 +131,10 @@ def load() -> C.CDLL:
                                                  C.c_int64, C.c_int, C.c_void_p]
     lib.trase_b200_smooth_features_forward.restype = C.c_int
     lib.trase_b200_smooth_features_forward.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p,
-                                                       C.c_void_p, C.c_void_p, C.c_void_p]
+                                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.trase_b200_smooth_features_backward_csr.restype = C.c_int
+    lib.trase_b200_smooth_features_backward_csr.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p,
+                                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.trase_b200_smooth_features_backward.restype = C.c_int
     lib.trase_b200_smooth_features_backward.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p,
                                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -191,6 +191,84 @@ __global__ void __launch_bounds__(256) smooth_feat_bwd_kernel(int P, int K, Smoo
   }
 }
 
+// The same two passes with each feature row normalised ONCE instead of once per use:
+//   forward : unit[j] = normalize(feat[j]) (smooth_unit_kernel), then out[p] = mean_k unit[idx[p][sel_k]] — the
+//             neighbour loads of a Gaussian are independent of each other (no per-neighbour norm reduction);
+//   backward: the normalisation is linear in its upstream gradient, so the mean's gradient is first summed per
+//             neighbour, G[j] = (1/n) sum over the Gaussians p that list j in a selected column of g_out[p], and the
+//             normalisation backward is applied once per j.  The sum is a GATHER over the reverse of the neighbour map
+//             (rev_ptr [P+1], rev_ent [P*K]: the entries (p << 8 | column) of row j, built once per map by the
+//             caller) — no atomics, no memset, every g_feat row written exactly once.
+__global__ void __launch_bounds__(256) smooth_unit_kernel(int P, const float* __restrict__ feat, float* __restrict__ unit) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= P) return;
+  const float v = feat[(size_t)p * NUM_OBJECTS + lane];
+  float n2 = v * v;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+  unit[(size_t)p * NUM_OBJECTS + lane] = v / fmaxf(sqrtf(n2), 1e-12f);
+}
+__global__ void __launch_bounds__(256) smooth_gather_fwd_kernel(int P, int K, SmoothSel sel,
+                                                                const float* __restrict__ unit,
+                                                                const long long* __restrict__ idx, float* __restrict__ out) {
+  const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= P) return;
+  // lane k fetches the k-th selected neighbour's index; the rows are then read with all loads in flight together
+  const long long mine = lane < sel.n ? __ldg(idx + (size_t)p * K + sel.col[lane]) : 0;
+  float acc = 0.f;
+#pragma unroll 8
+  for (int k = 0; k < sel.n; k++) {
+    const long long j = __shfl_sync(0xffffffffu, mine, k);
+    acc += __ldg(unit + (size_t)j * NUM_OBJECTS + lane);      // same order of additions as the per-use kernel
+  }
+  out[(size_t)p * NUM_OBJECTS + lane] = acc / (float)sel.n;
+}
+__global__ void __launch_bounds__(256) smooth_feat_bwd_csr_kernel(int P, unsigned long long colmask, float inv_n,
+                                                                  const float* __restrict__ feat,
+                                                                  const int* __restrict__ rev_ptr,
+                                                                  const int* __restrict__ rev_ent,
+                                                                  const float* __restrict__ g_out,
+                                                                  float* __restrict__ g_feat) {
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (j >= P) return;
+  const int b = __ldg(rev_ptr + j), e = __ldg(rev_ptr + j + 1);
+  float acc0 = 0.f, acc1 = 0.f;
+  for (int t = b; t < e; t += 32) {
+    const int ent = (t + lane < e) ? __ldg(rev_ent + t + lane) : -1;
+    // entries whose column takes part in this call
+    unsigned live = __ballot_sync(0xffffffffu, ent >= 0 && ((colmask >> (ent & 255)) & 1ull));
+    while (live) {
+      const int q0 = __ffs(live) - 1;
+      live &= live - 1;
+      const int p0 = __shfl_sync(0xffffffffu, ent, q0) >> 8;
+      acc0 += __ldg(g_out + (size_t)p0 * NUM_OBJECTS + lane);
+      if (live) {
+        const int q1 = __ffs(live) - 1;
+        live &= live - 1;
+        const int p1 = __shfl_sync(0xffffffffu, ent, q1) >> 8;
+        acc1 += __ldg(g_out + (size_t)p1 * NUM_OBJECTS + lane);
+      }
+    }
+  }
+  const float g = (acc0 + acc1) * inv_n;
+  const float v = feat[(size_t)j * NUM_OBJECTS + lane];
+  float n2 = v * v;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+  const float n = sqrtf(n2);
+  float gv;
+  if (n > 1e-12f) {
+    const float u = v / n;
+    float ug = u * g;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ug += __shfl_xor_sync(0xffffffffu, ug, o);
+    gv = (g - u * ug) / n;
+  } else {
+    gv = g * 1e12f;                       // clamped branch of F.normalize
+  }
+  g_feat[(size_t)j * NUM_OBJECTS + lane] = gv;
+}
+
 static bool smooth_args_ok(const char* who, int P, int K, const int* sel_cols, int n_sel, const void* a, const void* b,
                            const void* c, SmoothSel& sel) {
   if (!a || !b || !c || !sel_cols || K <= 0 || n_sel <= 0 || n_sel > SMOOTH_MAX_SEL || K > 255) {
@@ -212,15 +290,50 @@ using namespace tb;
 
 extern "C" TRASE_API int trase_b200_smooth_features_forward(int P, int K, const int* sel_cols, int n_sel,
                                                             const float* feat, const long long* knn_idx, float* out,
-                                                            void* stream) {
+                                                            float* unit_scratch, void* stream) {
   clear_error();
   if (P <= 0) return 0;
   SmoothSel sel;
   if (!smooth_args_ok("trase_b200_smooth_features_forward", P, K, sel_cols, n_sel, feat, knn_idx, out, sel)) return 1;
-  smooth_feat_fwd_kernel<<<(int)(((size_t)P * 32 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      P, K, sel, feat, knn_idx, out);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = (int)(((size_t)P * 32 + 255) / 256);
+  if (unit_scratch) {
+    smooth_unit_kernel<<<grid, 256, 0, s>>>(P, feat, unit_scratch);
+    smooth_gather_fwd_kernel<<<grid, 256, 0, s>>>(P, K, sel, unit_scratch, knn_idx, out);
+  } else {
+    smooth_feat_fwd_kernel<<<grid, 256, 0, s>>>(P, K, sel, feat, knn_idx, out);
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_smooth_features_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(unit_scratch ? 2 : 1);
+  return 0;
+}
+
+extern "C" TRASE_API int trase_b200_smooth_features_backward_csr(int P, int K, const int* sel_cols, int n_sel,
+                                                                 const float* feat, const int* rev_ptr,
+                                                                 const int* rev_ent, const float* g_out, float* g_feat,
+                                                                 void* stream) {
+  clear_error();
+  if (P <= 0) return 0;
+  SmoothSel sel;
+  if (!g_out || !rev_ent || K > 64 || P >= (1 << 23) ||
+      !smooth_args_ok("trase_b200_smooth_features_backward_csr", P, K, sel_cols, n_sel, feat, rev_ptr, g_feat, sel)) {
+    if (!g_out || !rev_ent) set_error("trase_b200_smooth_features_backward_csr: null pointer");
+    else if (K > 64 || P >= (1 << 23)) set_error("trase_b200_smooth_features_backward_csr: K <= 64 and P < 2^23 only");
+    return 1;
+  }
+  unsigned long long colmask = 0;
+  for (int i = 0; i < sel.n; i++) {
+    if ((colmask >> sel.col[i]) & 1ull) {
+      set_error("trase_b200_smooth_features_backward_csr: column %d selected twice", (int)sel.col[i]);
+      return 1;
+    }
+    colmask |= 1ull << sel.col[i];
+  }
+  smooth_feat_bwd_csr_kernel<<<(int)(((size_t)P * 32 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, colmask, 1.f / (float)sel.n, feat, rev_ptr, rev_ent, g_out, g_feat);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_smooth_features_backward_csr: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
   return 0;
 }

@@ -95,8 +95,13 @@ class GaussianParams(torch.nn.Module):
             select_point = torch.randperm(K)[:int(K * dropout)] if 0 < dropout < 1 else torch.arange(K)
         cols = [int(c) for c in select_point]
         if self._gaussian_features.is_cuda and FUSED_GLUE:
-            from ._assemble import smooth_features
-            return smooth_features(self._gaussian_features, m, cols)
+            from ._assemble import build_smooth_reverse, smooth_features
+            rev = None
+            if self._gaussian_features.requires_grad and torch.is_grad_enabled():
+                if "rev" not in self.feature_smooth_map:       # once per map: the reverse map of the backward gather
+                    self.feature_smooth_map["rev"] = build_smooth_reverse(m)
+                rev = self.feature_smooth_map["rev"]
+            return smooth_features(self._gaussian_features, m, cols, rev)
         normed = torch.nn.functional.normalize(self._gaussian_features, dim=-1, p=2)
         return normed[m[:, cols], 0, :].mean(dim=1).unsqueeze(1)
 
