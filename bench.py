@@ -366,31 +366,40 @@ class Workload:
         return float(self.loss_host[0])
 
     # ---- FEATURE state (config 3) ---------------------------------------------
-    def _feature_view_loss(self, view, time_t, masks, masks_host=None):
+    def _feature_sample(self, masks, masks_host=None):
+        """train.py:253 for one view: the sampled pixels and masks.  It does not depend on the render, so it runs on a
+        side stream and is issued one view AHEAD (right before the previous view's backward is launched): the host
+        synchronisation inside it — the sample count comes back to size the loss kernels — is then waited out while
+        the GPU still has that view's forward queued, not with the GPU idle."""
+        from trase_b200 import feature_utils as FU
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(self.sample_stream):
+            if masks_host is not None:                      # e2e: this view's masks come from pinned host memory
+                ev = self.mask_free.get(masks.data_ptr())   # (the previous step's loss has finished reading them)
+                if ev is not None:
+                    self.sample_stream.wait_event(ev)
+                masks.copy_(masks_host, non_blocking=True)
+            sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks,
+                                                  generator=self.sample_gen)
+            pix = FU.sampled_pixel_indices(sp) if self.fused_loss else None
+            done = torch.cuda.Event()
+            done.record(self.sample_stream)
+        for t_ in (sp, sm, pix):
+            if t_ is not None:
+                t_.record_stream(main)
+        return sp, sm, pix, done
+
+    def _feature_view_loss(self, view, time_t, masks, masks_host=None, samples=None):
         """train.py:244-296 for one view; returns the loss tensor."""
         if self.ref is None:
             from trase_b200 import feature_utils as FU, loss_utils as LU
-            # The sampling (train.py:253) does not depend on the render: it runs on a side stream, so the host
-            # synchronisation that brings the sample count back waits for that stream only and the launches of this
-            # view's MLP and render are not held up behind the previous view's backward.
             main = torch.cuda.current_stream()
-            with torch.cuda.stream(self.sample_stream):
-                if masks_host is not None:                      # e2e: this view's masks come from pinned host memory
-                    ev = self.mask_free.get(masks.data_ptr())   # (the previous step's loss has finished reading them)
-                    if ev is not None:
-                        self.sample_stream.wait_event(ev)
-                    masks.copy_(masks_host, non_blocking=True)
-                sp, sm = FU.get_sample_pixel_and_mask(masks, self.num_sampled_pixels, self.num_sampled_masks,
-                                                      generator=self.sample_gen)
-                pix = FU.sampled_pixel_indices(sp) if self.fused_loss else None
-            main.wait_stream(self.sample_stream)
-            for t_ in (sp, sm, pix):
-                if t_ is not None:
-                    t_.record_stream(main)
+            sp, sm, pix, done = samples if samples is not None else self._feature_sample(masks, masks_host)
             out = self.render(view, time_t, norm_gaussian_features=True, is_smooth_gaussian_features=True, smooth_K=16,
                               want_viewspace_grad=False)   # past densify_until_iter nobody reads viewspace_points.grad
             feats = out["render_gaussian_features"]
             reg = LU.feature_norm_reg(feats)
+            main.wait_event(done)                          # the samples (and, end to end, the masks) are read from here on
             if self.fused_loss:
                 # mask matrix, pair weights, similarities and both losses without any N x N tensor (csrc/contrastive.cu)
                 pos, neg = FU.soft_contrastive_losses(feats, masks, sp, sm, positive_th=0.75, negative_th=0.5, pix=pix)
@@ -426,9 +435,12 @@ class Workload:
 
     def _feature_resident(self):
         self.arena.zero_()
+        samples = self._feature_sample(self.masks_dev[0])
         for v in range(self.nviews):
-            loss = self._feature_view_loss(self.views[v], self.time_t[v], self.masks_dev[v])
-            if v == self.nviews - 1:
+            loss = self._feature_view_loss(self.views[v], self.time_t[v], self.masks_dev[v], samples=samples)
+            if v + 1 < self.nviews:
+                samples = self._feature_sample(self.masks_dev[v + 1])
+            else:
                 self.grad_arena.arm()
             loss.backward()
         self.grad_arena.all_reduce()
@@ -436,11 +448,14 @@ class Workload:
     def _feature_e2e(self):
         """Per view: H2D of the camera block and of the view's 25 masks (uint8, 268x480), D2H of the loss."""
         self.arena.zero_()
+        samples = self._feature_sample(self.masks_stage[0], self.masks_host[0])
         for v in range(self.nviews):
             view, t = self._host_view(v)
-            loss = self._feature_view_loss(view, t, self.masks_stage[v], self.masks_host[v])
+            loss = self._feature_view_loss(view, t, self.masks_stage[v], self.masks_host[v], samples=samples)
             self.loss_host[v:v + 1].copy_(loss.detach().reshape(1), non_blocking=True)
-            if v == self.nviews - 1:
+            if v + 1 < self.nviews:
+                samples = self._feature_sample(self.masks_stage[v + 1], self.masks_host[v + 1])
+            else:
                 self.loss_event.record()
                 self.grad_arena.arm()
             loss.backward()

@@ -78,15 +78,28 @@ __device__ __forceinline__ float pair_weight(const WeightCtx& w, float rai, floa
   return (fmaxf(rai * raj, 1.0f) - 1.0f) * w.k9 + 1.0f;
 }
 
+// acc = a * b + acc on two packed fp32 lanes (FFMA2); bb holds the second factor of both lanes
+__device__ __forceinline__ void ffma2(float2& acc, const float2 a, const unsigned long long bb) {
+  unsigned long long av, cv;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(av) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(cv) : "f"(acc.x), "f"(acc.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(cv) : "l"(av), "l"(bb));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(acc.x), "=f"(acc.y) : "l"(cv));
+}
+
 enum { MODE_FLAGS = 0, MODE_LOSS = 1, MODE_GRAD = 2 };
 constexpr int LD = CT + 4;         // row pitch of the channel-major tiles (float4 reads of 4 consecutive pixels)
 
 // grid = (own 64-pixel blocks, partner splits): block (x, y) pairs its own pixels with partner tiles y, y + S, ...
-template <int MODE>
+// NW = mask words per pixel the kernel is built for: 1 (up to 64 sampled masks, the usual case: a quarter of the bit
+// logic per pair) or MAXW.
+template <int MODE, int NW>
 __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p) {
-  __shared__ __align__(16) float s_own[CC][LD];      // channel-major: s[k][pixel]
+  // channel-major: s[k][pixel].  The own tile holds every value TWICE, (v, v) side by side: a 16-byte read is then two
+  // own pixels as ready-made packed operands of FFMA2 (two partner pixels per instruction), with no register moves
+  __shared__ __align__(16) float2 s_own[CC][LD];
   __shared__ __align__(16) float s_oth[CC][LD];
-  __shared__ unsigned long long s_bown[CT][MAXW], s_both[CT][MAXW];
+  __shared__ unsigned long long s_bown[CT][NW], s_both[CT][NW];
   __shared__ float s_raown[CT], s_raoth[CT];
   __shared__ unsigned char s_kown[2][CT], s_koth[2][CT];
   __shared__ __align__(16) float s_Gt[MODE == MODE_GRAD ? CT : 1][LD];   // G transposed: s_Gt[partner][own]
@@ -97,10 +110,11 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
   const WeightCtx wc = weight_ctx(p);
   for (int e = tid; e < CT * CC; e += CT_THREADS) {
     const int r = e / CC, c = e - r * CC;            // coalesced global read, transposed shared write
-    s_own[c][r] = own0 + r < p.N ? p.f[(size_t)(own0 + r) * CC + c] : 0.f;
+    const float v = own0 + r < p.N ? p.f[(size_t)(own0 + r) * CC + c] : 0.f;
+    s_own[c][r] = make_float2(v, v);
   }
-  for (int e = tid; e < CT * MAXW; e += CT_THREADS) {
-    const int r = e / MAXW, w = e - r * MAXW;
+  for (int e = tid; e < CT * NW; e += CT_THREADS) {
+    const int r = e / NW, w = e - r * NW;
     s_bown[r][w] = (own0 + r < p.N && w < p.nwords) ? p.bits[(size_t)(own0 + r) * p.nwords + w] : 0ull;
   }
   if (tid < CT) {
@@ -132,8 +146,8 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
       const int r = e / CC, c = e - r * CC;
       s_oth[c][r] = oth0 + r < p.N ? p.f[(size_t)(oth0 + r) * CC + c] : 0.f;
     }
-    for (int e = tid; e < CT * MAXW; e += CT_THREADS) {
-      const int r = e / MAXW, w = e - r * MAXW;
+    for (int e = tid; e < CT * NW; e += CT_THREADS) {
+      const int r = e / NW, w = e - r * NW;
       s_both[r][w] = (oth0 + r < p.N && w < p.nwords) ? p.bits[(size_t)(oth0 + r) * p.nwords + w] : 0ull;
     }
     if (tid < CT) {
@@ -145,20 +159,28 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
     }
     __syncthreads();
     // 4 x 4 patch of similarities: own pixels ty*4.., partner pixels tx*4..; two 16-byte reads per channel
-    float c[4][4];
+    // c2[a][h] = similarities of own pixel a with partner pixels 2h, 2h + 1 (each lane of the packed FMA is the same
+    // fp32 fma, in the same order over k, as the scalar form: identical bits)
+    float2 c2[4][2];
 #pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-      for (int b = 0; b < 4; b++) c[a][b] = 0.f;
+    for (int a = 0; a < 4; a++) c2[a][0] = c2[a][1] = make_float2(0.f, 0.f);
 #pragma unroll 8
     for (int k = 0; k < CC; k++) {
-      const float4 o4 = *reinterpret_cast<const float4*>(&s_own[k][ty * 4]);
+      const ulonglong2 o01 = *reinterpret_cast<const ulonglong2*>(&s_own[k][ty * 4]);
+      const ulonglong2 o23 = *reinterpret_cast<const ulonglong2*>(&s_own[k][ty * 4 + 2]);
       const float4 q4 = *reinterpret_cast<const float4*>(&s_oth[k][tx * 4]);
-      const float o[4] = {o4.x, o4.y, o4.z, o4.w}, q[4] = {q4.x, q4.y, q4.z, q4.w};
+      const unsigned long long oo[4] = {o01.x, o01.y, o23.x, o23.y};
+      const float2 q01 = make_float2(q4.x, q4.y), q23 = make_float2(q4.z, q4.w);
 #pragma unroll
-      for (int a = 0; a < 4; a++)
+      for (int a = 0; a < 4; a++) {
+        ffma2(c2[a][0], q01, oo[a]);
+        ffma2(c2[a][1], q23, oo[a]);
+      }
+    }
+    float c[4][4];
 #pragma unroll
-        for (int b = 0; b < 4; b++) c[a][b] = fmaf(o[a], q[b], c[a][b]);
+    for (int a = 0; a < 4; a++) {
+      c[a][0] = c2[a][0].x; c[a][1] = c2[a][0].y; c[a][2] = c2[a][1].x; c[a][3] = c2[a][1].y;
     }
 #pragma unroll
     for (int b = 0; b < 4; b++) {
@@ -170,7 +192,7 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
         const bool valid = own < p.N && oth < p.N;
         bool same = false;
 #pragma unroll
-        for (int w = 0; w < MAXW; w++) same = same || ((s_bown[ro][w] & s_both[rq][w]) != 0ull);
+        for (int w = 0; w < NW; w++) same = same || ((s_bown[ro][w] & s_both[rq][w]) != 0ull);
         const float cv = c[a][b];
         if (MODE == MODE_FLAGS) {
           if (valid && same && cv < p.pos_th) flag_pos |= 1u << a;
@@ -380,8 +402,13 @@ extern "C" TRASE_API int trase_b200_contrastive_soft_forward(int N, int nwords, 
   const dim3 grid(nb, contrastive_splits(nb));
   cudaError_t e = cudaMemsetAsync(p.kept, 0, 2 * (size_t)N, s);           // the mined-column flags are OR-ed into
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
-  contrastive::contrastive_kernel<contrastive::MODE_FLAGS><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
-  contrastive::contrastive_kernel<contrastive::MODE_LOSS><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+  if (nwords == 1) {
+    contrastive::contrastive_kernel<contrastive::MODE_FLAGS, 1><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    contrastive::contrastive_kernel<contrastive::MODE_LOSS, 1><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+  } else {
+    contrastive::contrastive_kernel<contrastive::MODE_FLAGS, contrastive::MAXW><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    contrastive::contrastive_kernel<contrastive::MODE_LOSS, contrastive::MAXW><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+  }
   contrastive::contrastive_finish_kernel<<<1, 256, 0, s>>>(p, (int)(grid.x * grid.y));
   e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -406,7 +433,8 @@ extern "C" TRASE_API int trase_b200_contrastive_soft_backward(int N, int nwords,
   const dim3 grid(nb, contrastive_splits(nb));
   cudaError_t e = cudaMemsetAsync(df, 0, (size_t)N * contrastive::CC * sizeof(float), s);   // split blocks add into it
   if (e == cudaSuccess) {
-    contrastive::contrastive_kernel<contrastive::MODE_GRAD><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    if (nwords == 1) contrastive::contrastive_kernel<contrastive::MODE_GRAD, 1><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    else contrastive::contrastive_kernel<contrastive::MODE_GRAD, contrastive::MAXW><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
     e = cudaGetLastError();
   }
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }

@@ -351,10 +351,29 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 // FEATURE state (only the feature parameter trains) is GEOM = false: alpha and T are recomputed and dF accumulated,
 // nothing else.  Every variant evaluates alpha and T with the same pinned sequence, so which pairs blend never
 // depends on the variant.
+#ifndef TB_BWD_G_MINB
+#define TB_BWD_G_MINB 3
+#endif
+#ifndef TB_BWD_F_MINB
+#define TB_BWD_F_MINB 3
+#endif
+#ifndef TB_BWD_G_BATCH
+#define TB_BWD_G_BATCH 256
+#endif
+// resident CTAs per SM the register allocation is held to (the kernel is bound by fixed-latency dependencies of the
+// per-pixel chain, so resident warps are what buys throughput)
+constexpr int bwd_min_blocks(int PPT, bool GEOM, bool DF, bool OBJ_UP) {
+  if (PPT != 2) return (GEOM && !OBJ_UP) ? 3 : 2;
+  if (GEOM && !OBJ_UP) return 6;            // colour-only loss: ~80 registers
+  if (GEOM && !DF) return TB_BWD_G_MINB;    // GAUSSIAN state (no feature-row gradient)
+  if (!GEOM) return TB_BWD_F_MINB;          // FEATURE state (feature-row gradient only)
+  return 3;                                 // every gradient: 168 registers (128 would spill)
+}
 template <int PPT, bool GEOM, bool DF, bool OBJ_UP>
-__global__ void __launch_bounds__(256 / PPT, (GEOM && !OBJ_UP) ? (PPT == 2 ? 6 : 3) : (PPT == 2 ? 3 : 2))
+__global__ void __launch_bounds__(256 / PPT, bwd_min_blocks(PPT, GEOM, DF, OBJ_UP))
 render_bwd_kernel(const RenderBwdParams q) {      // the colour-only variant needs ~80 registers: twice the resident warps
   constexpr int NT = 256 / PPT;
+  constexpr int BWD_BATCH = (GEOM && !DF && OBJ_UP && PPT == 2) ? TB_BWD_G_BATCH : tb::BWD_BATCH;
   constexpr bool NEED_FEAT = GEOM && OBJ_UP;        // feature rows are only read for dL/dalpha
   constexpr bool NEED_DLO = DF || NEED_FEAT;        // upstream feature gradient planes
   __shared__ uint32_t s_id[BWD_BATCH];
