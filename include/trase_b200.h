@@ -262,7 +262,8 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
  * are views of one [P][Mrest+1][3] block already, so the SH copy and its
  * backward split are skipped (the caller passes that block to the rasterizer and
  * slices its gradient).  g_feat == NULL (backward): the feature parameter is frozen,
- * its gradient is not computed.
+ * its gradient is not computed; the seven geometry gradients g_xyz .. g_opacity all NULL:
+ * every geometry parameter is frozen (FEATURE state), that kernel is skipped.
  * ---------------------------------------------------------------------- */
 TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const float* xyz, const float* d_xyz, const float* scaling,
                                           const float* d_scaling, const float* rotation, const float* d_rotation,

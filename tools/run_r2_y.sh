@@ -10,3 +10,4 @@ print(d['value'], d['ms_per_step'], d['e2e'])"
 python tools/profile_step_multi.py --workload hypernerf8 --timeline > gpurun_out/r2_z_timeline_hypernerf8.txt 2>&1; tail -1 gpurun_out/r2_z_timeline_hypernerf8.txt
 sed -n 3,16p gpurun_out/r2_z_timeline_hypernerf8.txt | cut -c1-100
 bash tools/run_r2_aa.sh
+python tools/profile_step_multi.py --workload nnfm --timeline > gpurun_out/r2_z_timeline_nnfm.txt 2>&1; tail -1 gpurun_out/r2_z_timeline_nnfm.txt

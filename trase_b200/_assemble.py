@@ -80,11 +80,13 @@ class _Assemble(torch.autograd.Function):
             ups = [None if g is None else _c(g) for g in (g_means3D, g_scales, g_rotations, g_opac, g_shs, g_objs)]
             f32 = dict(dtype=torch.float32, device=dev)
             alias = ctx.sh_aliased
-            outs = [torch.empty((P, 3), **f32), torch.empty((P, 3), **f32), torch.empty((P, 3), **f32),
-                    torch.empty((P, 3), **f32), torch.empty((P, 4), **f32), torch.empty((P, 4), **f32),
-                    torch.empty((P, 1), **f32), None if alias else torch.empty((P, 1, 3), **f32),
+            need = ctx.needs_input_grad
+            geom = any(need[0:7])            # FEATURE state: every geometry parameter and the deformation are frozen
+            mk = (lambda *shape: torch.empty(shape, **f32)) if geom else (lambda *shape: None)
+            outs = [mk(P, 3), mk(P, 3), mk(P, 3), mk(P, 3), mk(P, 4), mk(P, 4), mk(P, 1),
+                    None if alias else torch.empty((P, 1, 3), **f32),
                     None if alias else torch.empty((P, Mrest, 3), **f32),
-                    torch.empty((P, 1, 32), **f32) if ctx.needs_input_grad[9] else None]     # frozen feature: skipped
+                    torch.empty((P, 1, 32), **f32) if need[9] else None]     # frozen feature: skipped
             _lib.check(lib.trase_b200_assemble_backward(
                 P, Mrest, scaling.data_ptr(), rotation.data_ptr(), opacity.data_ptr(), feat.data_ptr(),
                 *[None if u is None else u.data_ptr() for u in ups], *[None if o is None else o.data_ptr() for o in outs],

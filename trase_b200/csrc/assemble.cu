@@ -403,15 +403,18 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
                                                       float* g_rotation, float* g_drotation, float* g_opacity,
                                                       float* g_fdc, float* g_frest, float* g_feat, void* stream) {
   if (P <= 0) return 0;
-  if (!scaling || !rotation || !opacity || !feat || !g_xyz || !g_dxyz || !g_scaling || !g_dscaling || !g_rotation ||
-      !g_drotation || !g_opacity || (g_fdc && Mrest > 0 && !g_frest)) {
+  // the seven geometry gradients come together or not at all (all NULL: every geometry parameter is frozen, FEATURE state)
+  const bool geom = g_xyz || g_dxyz || g_scaling || g_dscaling || g_rotation || g_drotation || g_opacity;
+  if (!scaling || !rotation || !opacity || !feat ||
+      (geom && (!g_xyz || !g_dxyz || !g_scaling || !g_dscaling || !g_rotation || !g_drotation || !g_opacity)) ||
+      (g_fdc && Mrest > 0 && !g_frest)) {
     set_error("trase_b200_assemble_backward: null pointer");
     return 1;
   }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   AssembleBwd a{P, Mrest, scaling, rotation, opacity, feat, g_means3D, g_scales, g_rotations, g_opac, g_shs, g_objs,
                 g_xyz, g_dxyz, g_scaling, g_dscaling, g_rotation, g_drotation, g_opacity, g_fdc, g_frest, g_feat};
-  assemble_bwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+  if (geom) assemble_bwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
   const size_t tot = (size_t)P * (Mrest + 1) * 3;
   int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
   if (g_fdc) assemble_sh_bwd_kernel<<<g, 256, 0, s>>>(P, Mrest, g_shs, g_fdc, g_frest);   // NULL: caller slices g_shs itself
@@ -421,6 +424,6 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
         reinterpret_cast<float4*>(g_feat));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_assemble_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
-  count_launches(1 + (g_fdc ? 1 : 0) + (g_feat ? 1 : 0));
+  count_launches((geom ? 1 : 0) + (g_fdc ? 1 : 0) + (g_feat ? 1 : 0));
   return 0;
 }

@@ -65,8 +65,11 @@ constexpr int FWD_BATCH = 128;
 constexpr int BWD_BATCH = 256;
 constexpr unsigned FULL = 0xffffffffu;
 
+#ifndef TB_FWD_MINB
+#define TB_FWD_MINB 4
+#endif
 template <int PPT>
-__global__ void __launch_bounds__(256 / PPT) render_fwd_kernel(const RenderFwdParams q) {
+__global__ void __launch_bounds__(256 / PPT, PPT == 2 ? TB_FWD_MINB : 2) render_fwd_kernel(const RenderFwdParams q) {
   constexpr int NT = 256 / PPT;
   __shared__ float2 s_xy[FWD_BATCH];
   __shared__ float4 s_co[FWD_BATCH];
@@ -351,11 +354,17 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 // FEATURE state (only the feature parameter trains) is GEOM = false: alpha and T are recomputed and dF accumulated,
 // nothing else.  Every variant evaluates alpha and T with the same pinned sequence, so which pairs blend never
 // depends on the variant.
+// GAUSSIAN-state variant: 128 registers without spills -> 4 CTAs = 16 warps per SM: 1.62 -> 1.43 ms at config 2
+// (5 or 6 CTAs with a smaller staging batch spill and are slower: profiles/r2_aa_bwd_occupancy.txt)
 #ifndef TB_BWD_G_MINB
-#define TB_BWD_G_MINB 3
+#define TB_BWD_G_MINB 4
 #endif
+// FEATURE-state variant: 128 registers without spills as well: 0.44 -> 0.385 ms per 536x960 view
 #ifndef TB_BWD_F_MINB
-#define TB_BWD_F_MINB 3
+#define TB_BWD_F_MINB 4
+#endif
+#ifndef TB_BWD_C_MINB
+#define TB_BWD_C_MINB 6
 #endif
 #ifndef TB_BWD_G_BATCH
 #define TB_BWD_G_BATCH 256
@@ -364,7 +373,7 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 // per-pixel chain, so resident warps are what buys throughput)
 constexpr int bwd_min_blocks(int PPT, bool GEOM, bool DF, bool OBJ_UP) {
   if (PPT != 2) return (GEOM && !OBJ_UP) ? 3 : 2;
-  if (GEOM && !OBJ_UP) return 6;            // colour-only loss: ~80 registers
+  if (GEOM && !OBJ_UP) return TB_BWD_C_MINB;   // colour-only loss: ~80 registers
   if (GEOM && !DF) return TB_BWD_G_MINB;    // GAUSSIAN state (no feature-row gradient)
   if (!GEOM) return TB_BWD_F_MINB;          // FEATURE state (feature-row gradient only)
   return 3;                                 // every gradient: 168 registers (128 would spill)
