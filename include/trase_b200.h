@@ -138,7 +138,8 @@ typedef struct trase_b200_fwd_args {
   void* scratch; size_t scratch_bytes;
   int64_t capacity;             /* instances the binning/scratch buffers hold;    */
                                 /* at least P (the P-sized depth sort borrows them) */
-  int* num_rendered_host;       /* pinned host int or NULL (async D2H of R)       */
+  int* num_rendered_host;       /* pinned host int or NULL: receives R (stored by the scan kernel when the word is
+                                   device-visible, i.e. pinned under unified addressing; else a 4-byte async copy) */
   void* stream;                 /* cudaStream_t                                   */
   void* readback_event;         /* cudaEvent_t or NULL: recorded right after the   */
                                 /* D2H of R is queued, i.e. BEFORE the sort and    */

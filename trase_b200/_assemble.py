@@ -8,7 +8,7 @@ import ctypes as C
 
 import torch
 
-from . import _lib
+from . import _cuda, _lib
 
 
 def _c(t):
@@ -43,7 +43,7 @@ class _Assemble(torch.autograd.Function):
         dev = xyz.device
         P = xyz.shape[0]
         Mrest = f_rest.shape[1]
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             block = sh_block_of(f_dc, f_rest)        # parameters already laid out as the rasterizer's SH input?
             ins = [_c(t) for t in (xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity)] + \
                 ([None, None] if block is not None else [_c(f_dc), _c(f_rest)]) + [_c(feat)]
@@ -57,7 +57,7 @@ class _Assemble(torch.autograd.Function):
             _lib.check(lib.trase_b200_assemble_forward(
                 P, Mrest, *[None if t is None else t.data_ptr() for t in ins], means3D.data_ptr(), scales.data_ptr(),
                 rotations.data_ptr(), opac.data_ptr(), None if block is not None else shs.data_ptr(), sh_objs.data_ptr(),
-                torch.cuda.current_stream(dev).cuda_stream))
+                _cuda.raw_stream(dev)))
         ctx.save_for_backward(ins[2], ins[4], ins[6], ins[9])
         ctx.Mrest = Mrest
         ctx.sh_aliased = block is not None
@@ -76,7 +76,7 @@ class _Assemble(torch.autograd.Function):
         scaling, rotation, opacity, feat = ctx.saved_tensors
         dev = scaling.device
         P, Mrest = scaling.shape[0], ctx.Mrest
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             ups = [None if g is None else _c(g) for g in (g_means3D, g_scales, g_rotations, g_opac, g_shs, g_objs)]
             f32 = dict(dtype=torch.float32, device=dev)
             alias = ctx.sh_aliased
@@ -90,7 +90,7 @@ class _Assemble(torch.autograd.Function):
             _lib.check(lib.trase_b200_assemble_backward(
                 P, Mrest, scaling.data_ptr(), rotation.data_ptr(), opacity.data_ptr(), feat.data_ptr(),
                 *[None if u is None else u.data_ptr() for u in ups], *[None if o is None else o.data_ptr() for o in outs],
-                torch.cuda.current_stream(dev).cuda_stream))
+                _cuda.raw_stream(dev)))
             if alias:
                 # the SH gradient block is already laid out like the parameters: hand out its two slices
                 g = ups[4] if ups[4] is not None else torch.zeros((P, Mrest + 1, 3), **f32)
@@ -129,12 +129,12 @@ class _SmoothFeatures(torch.autograd.Function):
         f = _c(feat).view(P, 32)
         idx = knn_idx.to(device=dev, dtype=torch.int64).contiguous()
         sel = (C.c_int * len(sel_cols))(*[int(c) for c in sel_cols])
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             out = torch.empty((P, 1, 32), dtype=torch.float32, device=dev)
             unit = torch.empty((P, 32), dtype=torch.float32, device=dev)     # every row normalised once, then gathered
             _lib.check(lib.trase_b200_smooth_features_forward(P, K, sel, len(sel_cols), f.data_ptr(), idx.data_ptr(),
                                                               out.data_ptr(), unit.data_ptr(),
-                                                              torch.cuda.current_stream(dev).cuda_stream))
+                                                              _cuda.raw_stream(dev)))
         ctx.save_for_backward(f, idx)
         ctx.sel = sel
         ctx.shape = feat.shape
@@ -148,10 +148,10 @@ class _SmoothFeatures(torch.autograd.Function):
         f, idx = ctx.saved_tensors
         P, K = idx.shape
         dev = f.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             g = _c(g_out)
             g_feat = torch.empty((P, 32), dtype=torch.float32, device=dev)
-            s = torch.cuda.current_stream(dev).cuda_stream
+            s = _cuda.raw_stream(dev)
             if ctx.rev is not None:
                 _lib.check(lib.trase_b200_smooth_features_backward_csr(
                     P, K, ctx.sel, len(ctx.sel), f.data_ptr(), ctx.rev[0].data_ptr(), ctx.rev[1].data_ptr(),

@@ -15,7 +15,7 @@ import ctypes
 
 import torch
 
-from . import _lib
+from . import _cuda, _lib
 
 W = 256
 FUSED_FORWARD = True   # module switch: False runs the layer-by-layer GEMM chain (csrc/mlp_gemm.cu)
@@ -93,7 +93,7 @@ def tf32_round(w: torch.Tensor) -> torch.Tensor:
 
 
 def _stream(dev):
-    return torch.cuda.current_stream(dev).cuda_stream
+    return _cuda.raw_stream(dev)
 
 
 def _gemm(lib, A, B, D, bias=None, relu=False, mask_in=None, mask_out=None, colsum=None, round_tf32=True):
@@ -186,7 +186,7 @@ class _DeformMLP(torch.autograd.Function):
         dev = x.device
         M = x.shape[0]
         E = 3 + 6 * Lx + 1 + 2 * Lt                       # 84
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             s = _stream(dev)
             x = x.detach().contiguous().float()
             t = t.detach().float()
@@ -270,7 +270,7 @@ class _DeformMLP(torch.autograd.Function):
         acts = saved[3:3 + nl]
         dev = skipbuf.device
         f32 = dict(dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             s = _stream(dev)
             # the fused chain packs its operand from the raw weights the fused forward kept
             bf16 = ctx.bf16                 # the forward wrote bf16 activations: the fused chain + bf16 wgrad follow

@@ -15,7 +15,7 @@ from typing import Dict, Optional, Tuple
 
 import torch
 
-from . import _lib
+from . import _cuda, _lib
 
 NUM_CHANNELS = 3
 NUM_OBJECTS = 32
@@ -80,7 +80,7 @@ def rasterize_forward(bg, means3D, colors_precomp, opacities, scales, rotations,
     dev = means3D.device
     P, H, W = int(means3D.shape[0]), int(image_height), int(image_width)
 
-    with torch.cuda.device(dev):
+    with _cuda.on_device(dev):
         means3D = _f32c(means3D, dev)
         bg = _f32c(bg, dev); viewmatrix = _f32c(viewmatrix, dev); projmatrix = _f32c(projmatrix, dev)
         campos = _f32c(campos, dev); opacities = _f32c(opacities, dev)
@@ -193,7 +193,7 @@ def rasterize_backward(bg, means3D, radii, colors_precomp, scales, rotations, sc
         dL_dout_color = torch.zeros((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
     if not need_geom and dL_dout_objects is None:          # feature gradient of a loss that never read the features
         return (None, None, torch.zeros((P, NUM_OBJECTS), dtype=torch.float32, device=dev)) + (None,) * 6
-    with torch.cuda.device(dev):
+    with _cuda.on_device(dev):
         means3D = _f32c(means3D, dev)
         bg = _f32c(bg, dev); viewmatrix = _f32c(viewmatrix, dev); projmatrix = _f32c(projmatrix, dev)
         campos = _f32c(campos, dev)
@@ -242,7 +242,7 @@ def rasterize_backward(bg, means3D, radii, colors_precomp, scales, rotations, sc
             a.dL_dcolors, a.dL_dobjects, a.dL_dmeans3D = _ptr(dL_dcolors), _ptr(dL_dobjects), _ptr(dL_dmeans3D)
             a.dL_dcov3D, a.dL_dsh = _ptr(dL_dcov3D), _ptr(dL_dsh)
             a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
-            a.stream = torch.cuda.current_stream(dev).cuda_stream
+            a.stream = _cuda.raw_stream(dev)
             _lib.check(lib.trase_b200_rasterize_backward(C.byref(a)))
         out = (dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
                dL_drotations)
@@ -257,14 +257,14 @@ def mark_visible(means3D, viewmatrix, projmatrix) -> torch.Tensor:
         raise RuntimeError("trase_b200: mark_visible runs on CUDA tensors only")
     dev = means3D.device
     P = int(means3D.shape[0])
-    with torch.cuda.device(dev):
+    with _cuda.on_device(dev):
         means3D = _f32c(means3D, dev)
         viewmatrix = _f32c(viewmatrix, dev); projmatrix = _f32c(projmatrix, dev)
         present = torch.zeros((P,), dtype=torch.bool, device=dev)
         if P:
             _lib.check(lib.trase_b200_mark_visible(P, means3D.data_ptr(), viewmatrix.data_ptr(),
                                                   projmatrix.data_ptr(), present.data_ptr(),
-                                                  torch.cuda.current_stream(dev).cuda_stream))
+                                                  _cuda.raw_stream(dev)))
         return present
 
 

@@ -195,11 +195,27 @@ static int forward_impl(const trase_b200_fwd_args* a, bool with_preprocess) {
 
   if (with_preprocess) TB_STEP_ST(ST_PREPROCESS_FWD, "preprocess_forward", launch_preprocess_forward(*a, p, stream));
   // depth order of the Gaussians (P-sized sort on the other ping-pong side), block scan, key emission
-  TB_STEP_ST(ST_SCAN_DUP, "scan_and_duplicate", launch_scan_and_duplicate(*a, pd, keys_b, vals_b, stream));
-  if (a->num_rendered_host)
-    TB_STEP("copy num_rendered",
-            cudaMemcpyAsync(a->num_rendered_host, p.counters, sizeof(int), cudaMemcpyDeviceToHost, stream));
-  if (a->readback_event) TB_STEP("record readback event", cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->readback_event), stream));
+  // R reaches the host without a copy-engine operation in the stream when the caller's word is device-visible
+  // (pinned memory under unified addressing): the scan kernel stores it there and the event is recorded behind that
+  // kernel.  Otherwise a 4-byte copy follows the emission as before.
+  int* host_total_dev = nullptr;
+  if (a->num_rendered_host) {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, a->num_rendered_host) == cudaSuccess && attr.type == cudaMemoryTypeHost &&
+        attr.devicePointer)
+      host_total_dev = static_cast<int*>(attr.devicePointer);
+    else
+      cudaGetLastError();      // not a registered pointer: clear the sticky error of the query
+  }
+  TB_STEP_ST(ST_SCAN_DUP, "scan_and_duplicate",
+             launch_scan_and_duplicate(*a, pd, keys_b, vals_b, host_total_dev,
+                                       reinterpret_cast<cudaEvent_t>(a->readback_event), stream));
+  if (!host_total_dev) {
+    if (a->num_rendered_host)
+      TB_STEP("copy num_rendered",
+              cudaMemcpyAsync(a->num_rendered_host, p.counters, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    if (a->readback_event) TB_STEP("record readback event", cudaEventRecord(reinterpret_cast<cudaEvent_t>(a->readback_event), stream));
+  }
   if (a->capacity > 0)
     TB_STEP_ST(ST_SORT, "sort_pairs", launch_sort_pingpong(keys_a, vals_a, keys_b, vals_b, p.counters, a->capacity, 32,
                                                end_bit, p.sort_scratch, p.sort_scratch_bytes, stream));

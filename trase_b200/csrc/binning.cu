@@ -40,7 +40,8 @@ constexpr int SCAN_THREADS = 1024;
 __global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums_kernel(const uint32_t* __restrict__ block_sums,
                                                                        uint32_t* __restrict__ block_offsets, int nblk,
                                                                        uint32_t* __restrict__ counters,
-                                                                       unsigned long long capacity) {
+                                                                       unsigned long long capacity,
+                                                                       int* __restrict__ host_total) {
   __shared__ uint32_t s_warp[SCAN_THREADS / 32];
   __shared__ uint32_t s_carry;
   if (threadIdx.x == 0) s_carry = 0;
@@ -70,6 +71,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums_kernel(const uin
     block_offsets[nblk] = total;
     counters[0] = total;
     counters[1] = ((unsigned long long)total > capacity) ? 1u : 0u;
+    if (host_total) {          // R straight into the caller's pinned host word (zero-copy): no copy-engine operation
+      *host_total = (int)total;  // sits in the stream between the emission and the sort
+      __threadfence_system();
+    }
   }
 }
 
@@ -178,8 +183,11 @@ __global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
 // `p.keys_unsorted / p.vals_unsorted` is where the instances go (the side the R-sized sort starts from);
 // (ok_keys, ok_vals) is the OTHER ping-pong side: the P-sized sort starts and (4 passes) ends there, so the
 // order array is not overwritten while the instances are being written.
+// host_total_dev (optional): device-visible address of the caller's pinned host word for R; readback_event (optional)
+// is recorded right behind the scan that writes it, before the key emission is even launched.
 cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, uint64_t* ok_keys,
-                                      uint32_t* ok_vals, cudaStream_t s) {
+                                      uint32_t* ok_vals, int* host_total_dev, cudaEvent_t readback_event,
+                                      cudaStream_t s) {
   const int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
   gaussian_depth_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, p.depths, p.tiles_touched, ok_keys, ok_vals, p.counters);
   cudaError_t e = cudaGetLastError();
@@ -192,9 +200,13 @@ cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPoi
   const uint32_t* order = ok_vals;
   ordered_block_sums_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, order, p.tiles_touched, p.block_sums);
   scan_block_sums_kernel<<<1, SCAN_THREADS, 0, s>>>(p.block_sums, p.block_offsets, nblk, p.counters,
-                                                   (unsigned long long)a.capacity);
+                                                   (unsigned long long)a.capacity, host_total_dev);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
+  if (host_total_dev && readback_event) {
+    e = cudaEventRecord(readback_event, s);
+    if (e != cudaSuccess) return e;
+  }
   const int grid_x = (a.W + TILE - 1) / TILE, grid_y = (a.H + TILE - 1) / TILE;
   duplicate_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, order, p.means2D, p.depths, p.tiles_touched, p.block_offsets,
                                                    p.point_offsets, p.counters, p.keys_unsorted, p.vals_unsorted,

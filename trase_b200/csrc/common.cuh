@@ -167,7 +167,8 @@ struct FwdPointers {
 
 cudaError_t launch_preprocess_forward(const trase_b200_fwd_args& a, const FwdPointers& p, cudaStream_t s);
 cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPointers& p, uint64_t* ok_keys,
-                                      uint32_t* ok_vals, cudaStream_t s);
+                                      uint32_t* ok_vals, int* host_total_dev, cudaEvent_t readback_event,
+                                      cudaStream_t s);
 cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                               const uint32_t* count_dev, int64_t capacity, int end_bit, void* scratch,
                               size_t scratch_bytes, cudaStream_t s);

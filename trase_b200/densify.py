@@ -18,7 +18,7 @@ from typing import Optional, Tuple
 
 import torch
 
-from . import _lib
+from . import _cuda, _lib
 from .optim import ArenaAdam, add_densification_stats  # noqa: F401  (re-exported: same place as in the reference)
 
 
@@ -73,7 +73,7 @@ def regather(pc, opt: Optional[ArenaAdam], src: torch.Tensor, fresh: torch.Tenso
         for sz in sizes:
             offs.append(n)
             n += sz
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             new_p = torch.empty(n, device=dev)
             new_m = torch.empty(n, device=dev)
             new_v = torch.empty(n, device=dev)
@@ -93,7 +93,7 @@ def regather(pc, opt: Optional[ArenaAdam], src: torch.Tensor, fresh: torch.Tenso
                     ns, (C.c_int64 * ns)(*o_old), (C.c_int64 * ns)(*o_new), (C.c_int * ns)(*width), P_new,
                     src.data_ptr(), fresh.data_ptr(), opt.flat_p.data_ptr(), opt.exp_avg.data_ptr(),
                     opt.exp_avg_sq.data_ptr(), new_p.data_ptr(), new_m.data_ptr(), new_v.data_ptr(),
-                    torch.cuda.current_stream(dev).cuda_stream))
+                    _cuda.raw_stream(dev)))
         ends = []
         for p, on, sz in zip(arena.params, offs, sizes):
             shape = (P_new,) + tuple(p.shape[1:]) if id(p) in mine else tuple(p.shape)

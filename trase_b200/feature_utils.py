@@ -11,7 +11,7 @@ from __future__ import annotations
 
 import torch
 
-from . import _lib
+from . import _cuda, _lib
 
 
 class _SampleFeatures(torch.autograd.Function):
@@ -25,12 +25,12 @@ class _SampleFeatures(torch.autograd.Function):
         C, H, W = f.shape
         N = idx.numel()
         dev = f.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             out = torch.empty((N, C), dtype=torch.float32, device=dev)
             inv = torch.empty((N,), dtype=torch.float32, device=dev)
             _lib.check(lib.trase_b200_sample_features_forward(C, H, W, Hm, Wm, N, f.data_ptr(), idx.data_ptr(),
                                                               int(normalize), out.data_ptr(), inv.data_ptr(),
-                                                              torch.cuda.current_stream(dev).cuda_stream))
+                                                              _cuda.raw_stream(dev)))
         ctx.save_for_backward(idx, out, inv)
         ctx.meta = (C, H, W, Hm, Wm, N, int(normalize))
         return out
@@ -41,12 +41,12 @@ class _SampleFeatures(torch.autograd.Function):
         C, H, W, Hm, Wm, N, normalize = ctx.meta
         lib = _lib.load()
         dev = out.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             d = torch.zeros((C, H, W), dtype=torch.float32, device=dev)
             g = g_out.detach().contiguous().float()
             _lib.check(lib.trase_b200_sample_features_backward(C, H, W, Hm, Wm, N, idx.data_ptr(), normalize,
                                                                out.data_ptr(), inv.data_ptr(), g.data_ptr(), d.data_ptr(),
-                                                               torch.cuda.current_stream(dev).cuda_stream))
+                                                               _cuda.raw_stream(dev)))
         return d, None, None, None, None
 
 
@@ -138,13 +138,13 @@ class _SoftContrastive(torch.autograd.Function):
         dev = f.device
         N, nwords = int(f.shape[0]), int(bits.shape[1])
         fc = f.detach().contiguous().float()
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             scratch = torch.empty(max(1, lib.trase_b200_contrastive_scratch_bytes(N)), dtype=torch.uint8, device=dev)
             result = torch.zeros(8, dtype=torch.float32, device=dev)
             _lib.check(lib.trase_b200_contrastive_soft_forward(
                 N, nwords, fc.data_ptr(), bits.data_ptr(), None if a is None else a.data_ptr(),
                 None if a is None else a_minmax.data_ptr(), float(pos_th), float(neg_th), scratch.data_ptr(),
-                result.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+                result.data_ptr(), _cuda.raw_stream(dev)))
         ctx.save_for_backward(fc, bits, a, a_minmax, scratch, result)
         ctx.th = (float(pos_th), float(neg_th))
         return result[0:2].clone()
@@ -155,13 +155,13 @@ class _SoftContrastive(torch.autograd.Function):
         fc, bits, a, a_minmax, scratch, result = ctx.saved_tensors
         dev = fc.device
         N, nwords = int(fc.shape[0]), int(bits.shape[1])
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             up = g.detach().contiguous().float()
             df = torch.zeros_like(fc)
             _lib.check(lib.trase_b200_contrastive_soft_backward(
                 N, nwords, fc.data_ptr(), bits.data_ptr(), None if a is None else a.data_ptr(),
                 None if a is None else a_minmax.data_ptr(), ctx.th[0], ctx.th[1], scratch.data_ptr(), result.data_ptr(),
-                up.data_ptr(), df.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+                up.data_ptr(), df.data_ptr(), _cuda.raw_stream(dev)))
         return df, None, None, None, None, None
 
 
@@ -201,7 +201,7 @@ def soft_contrastive_losses(rendered_features, sam_masks, sampled_pixel, sampled
     if N == 0:
         z = f.sum() * 0.0
         return z, z
-    with torch.no_grad(), torch.cuda.device(dev):
+    with torch.no_grad(), _cuda.on_device(dev):
         m8 = sam_masks.to(device=dev, dtype=torch.uint8).contiguous()
         area = m8.sum(dim=(-2, -1), dtype=torch.int64)
         sm8 = sampled_mask.to(device=dev, dtype=torch.uint8).contiguous()
@@ -209,7 +209,7 @@ def soft_contrastive_losses(rendered_features, sam_masks, sampled_pixel, sampled
         a = torch.empty((N,), dtype=torch.float32, device=dev)
         _lib.check(lib.trase_b200_pixel_mask_info(N, n_masks, Hm * Wm, m8.data_ptr(), area.data_ptr(), sm8.data_ptr(),
                                                   pix.data_ptr(), bits.data_ptr(), a.data_ptr(),
-                                                  torch.cuda.current_stream(dev).cuda_stream))
+                                                  _cuda.raw_stream(dev)))
         a_minmax = torch.stack([a.min(), a.max()]) if use_weights else None
     out = _SoftContrastive.apply(f, bits, a if use_weights else None, a_minmax, positive_th, negative_th)
     return out[0], out[1]

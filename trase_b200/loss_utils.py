@@ -12,11 +12,11 @@ from __future__ import annotations
 
 import torch
 
-from . import _lib
+from . import _cuda, _lib
 
 
 def _stream(dev):
-    return torch.cuda.current_stream(dev).cuda_stream
+    return _cuda.raw_stream(dev)
 
 
 class _L1SSIM(torch.autograd.Function):
@@ -34,7 +34,7 @@ class _L1SSIM(torch.autograd.Function):
         H, W = x.shape[-2:]
         C = x.numel() // (H * W)
         dev = x.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             need_maps = w_ssim != 0.0 and ctx.needs_input_grad[0]
             maps = torch.empty((3, C, H, W), dtype=torch.float32, device=dev) if need_maps else None
             scratch = torch.empty(lib.trase_b200_loss_scratch_bytes(C, H, W) // 4, dtype=torch.float32, device=dev)
@@ -52,7 +52,7 @@ class _L1SSIM(torch.autograd.Function):
         C, H, W, w_l1, w_ssim, shape = ctx.meta
         lib = _lib.load()
         dev = x.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             d_img = torch.empty_like(x)
             go = g_out3.detach().contiguous().float()
             _lib.check(lib.trase_b200_l1_ssim_backward(C, H, W, x.data_ptr(), y.data_ptr(),
@@ -92,7 +92,7 @@ class _FeatureNormReg(torch.autograd.Function):
         f = feat.detach().contiguous().float()
         C, N = f.shape[0], f.shape[1] * f.shape[2]
         dev = f.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             norm = torch.empty(N, dtype=torch.float32, device=dev)
             scratch = torch.empty(lib.trase_b200_feature_norm_scratch_bytes(N) // 4, dtype=torch.float32, device=dev)
             out2 = torch.empty(2, dtype=torch.float32, device=dev)
@@ -107,7 +107,7 @@ class _FeatureNormReg(torch.autograd.Function):
         f, norm, out2 = ctx.saved_tensors
         lib = _lib.load()
         dev = f.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             d = torch.empty_like(f)
             go = g_out2.detach().contiguous().float()
             _lib.check(lib.trase_b200_feature_norm_reg_backward(f.shape[0], norm.numel(), f.data_ptr(), norm.data_ptr(),

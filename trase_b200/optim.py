@@ -17,7 +17,7 @@ from typing import Dict, List, Sequence
 
 import torch
 
-from . import _lib
+from . import _cuda, _lib
 from .distributed import GradArena
 
 
@@ -74,11 +74,11 @@ class ArenaAdam:
                 step_size[i] = float(self.param_groups[gi]["lr"]) / (1.0 - b1 ** t)
                 bc2[i] = math.sqrt(1.0 - b2 ** t)
         dev = self.flat_p.device
-        with torch.cuda.device(dev):
+        with _cuda.on_device(dev):
             _lib.check(lib.trase_b200_adam_step(self.flat_p.numel(), self.flat_p.data_ptr(), self.arena.flat.data_ptr(),
                                                 self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), nseg, ends,
                                                 step_size, bc2, b1, b2, self.eps,
-                                                torch.cuda.current_stream(dev).cuda_stream))
+                                                _cuda.raw_stream(dev)))
 
 
 def add_densification_stats(xyz_gradient_accum: torch.Tensor, denom: torch.Tensor, viewspace_point_tensor: torch.Tensor,
@@ -97,6 +97,6 @@ def add_densification_stats(xyz_gradient_accum: torch.Tensor, denom: torch.Tenso
     if not (xyz_gradient_accum.is_contiguous() and denom.is_contiguous() and xyz_gradient_accum.numel() == P
             and denom.numel() == P and g.shape[1] >= 2 and g.shape[1] == 3 and f.numel() == P):
         raise RuntimeError("trase_b200: add_densification_stats expects [P,3] gradients, [P] filter, [P,1] accumulators")
-    with torch.cuda.device(g.device):
+    with _cuda.on_device(g.device):
         _lib.check(lib.trase_b200_densification_stats(P, g.data_ptr(), f.data_ptr(), xyz_gradient_accum.data_ptr(),
-                                                      denom.data_ptr(), torch.cuda.current_stream(g.device).cuda_stream))
+                                                      denom.data_ptr(), _cuda.raw_stream(g.device)))
