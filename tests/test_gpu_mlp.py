@@ -180,6 +180,51 @@ def test_multi_wgrad_backward_equals_per_layer_launches(native_lib):
         assert ((a - b).norm() / a.norm()).item() <= 1e-5, name
 
 
+def test_inference_pack_cache_follows_the_weights(native_lib):
+    """Inference calls (torch.no_grad) reuse the packed operands while the parameters are unchanged.  The cache must
+    miss after an in-place update, after load_state_dict, and for a NEW network whose parameters land on the addresses
+    of a deleted one."""
+    from trase_b200 import _deform_native as dn
+    from trase_b200.deform import DeformNetwork
+    torch.manual_seed(5)
+    M = 4099
+    x = (torch.rand(M, 3, device=DEV) - 0.5) * 4
+    t = torch.full((M, 1), 0.42, device=DEV)
+
+    def check(nat):
+        ref = DeformNetwork(backend="torch").to(DEV)
+        ref.load_state_dict(nat.state_dict())
+        with torch.no_grad():
+            a, b = nat(x, t), ref(x, t)
+        for u, v in zip(a, b):
+            assert (u - v).abs().max().item() <= 2e-3 * max(1.0, v.abs().max().item())
+        return a
+
+    dn._PACK_CACHE.clear()
+    nat = DeformNetwork(backend="native").to(DEV)
+    first = check(nat)
+    assert len(dn._PACK_CACHE) == 1
+    n0 = native_lib.trase_b200_launch_count()
+    again = check(nat)                                   # same weights: cache hit, no packing launches
+    n1 = native_lib.trase_b200_launch_count()
+    assert all(torch.equal(u, v) for u, v in zip(first, again))
+    assert n1 - n0 == 2, n1 - n0                         # embedding + the whole-network kernel only
+    with torch.no_grad():                                # in-place update: version counters move
+        nat.linear[3].weight.mul_(1.5)
+        nat.gaussian_warp.bias.add_(0.25)
+    changed = check(nat)
+    assert not torch.equal(first[0], changed[0])
+    other = DeformNetwork(backend="native").to(DEV)
+    nat.load_state_dict(other.state_dict())
+    check(nat)
+    # a new network on recycled memory
+    for _ in range(3):
+        del nat
+        torch.manual_seed(100 + _)
+        nat = DeformNetwork(backend="native").to(DEV)
+        check(nat)
+
+
 def test_bf16_weight_gradient_path_against_fp32_tensors(native_lib):
     """BF16_WGRAD writes the kept activations / layer gradients as bf16 and multiplies them as bf16.  Same outputs
     (the layer chain is untouched), bias gradients identical up to atomics, weight gradients within bf16 rounding of

@@ -12,6 +12,7 @@ detaches xyz).
 from __future__ import annotations
 
 import ctypes
+import weakref
 
 import torch
 
@@ -176,6 +177,10 @@ def _round_transpose(lib, Ws, sizes, skip, E, want_rounded, f32, s):
     return Wr, WrT
 
 
+# packed forward operands of frozen networks: (stream, shape, (data_ptr, version) of every parameter) -> tensors
+_PACK_CACHE: dict = {}
+
+
 class _DeformMLP(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, t, Lx, Lt, skip, keep, *params):
@@ -213,17 +218,40 @@ class _DeformMLP(torch.autograd.Function):
                 else:
                     _lib.check(lib.trase_b200_deform_embed(M, x.data_ptr(), t_c.data_ptr(), t_stride, Lx, Lt,
                                                            emb.data_ptr(), emb.stride(0), s))
-            hb = torch.empty(16 * W * 2 + 16, **f32)
-            wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
-            _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
-                                                     wh.data_ptr(), whT.data_ptr(), bh.data_ptr(), s))
+            # An inference call (torch.no_grad: FEATURE state, style transfer, rendering) on weights that have not
+            # changed since the last one reuses the packed operands instead of re-packing them per view.  Training
+            # calls always pack: their weights change every step.
+            pack_key = None
+            cached = None
+            if fused and not keep and all(isinstance(p, torch.nn.Parameter) for p in params):
+                # keyed on the parameter OBJECTS (checked through weak references: an address or id recycled by a new
+                # network never matches), their storage and their version counters (any in-place update bumps them)
+                pack_key = (s, nl, skip, E) + tuple((id(p), p.data_ptr(), p._version) for p in params)
+                cached = _PACK_CACHE.get(pack_key)
+                if cached is not None and not all(r() is p for r, p in zip(cached[0], params)):
+                    cached = None
+                if cached is not None:
+                    cached = cached[1:]
             out16 = torch.empty((M, 16), **f32)
+            if cached is not None:
+                hb, wpack, ball = cached
+                wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
+            else:
+                hb = torch.empty(16 * W * 2 + 16, **f32)
+                wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
+                _lib.check(lib.trase_b200_mlp_pack_heads(*[p.detach().contiguous().data_ptr() for p in heads], W,
+                                                         wh.data_ptr(), whT.data_ptr(), bh.data_ptr(), s))
             if fused:
                 # one persistent kernel carries each 128-row tile through all layers (csrc/mlp_fused.cu)
-                wpack = torch.empty(lib.trase_b200_mlp_fused_pack_floats(nl, skip, E), **f32)
-                wptrs = (ctypes.c_void_p * nl)(*[w.detach().contiguous().data_ptr() for w in Ws])
-                _lib.check(lib.trase_b200_mlp_pack_fused(nl, skip, E, wptrs, wh.data_ptr(), wpack.data_ptr(), s))
-                ball = torch.cat([b.detach().reshape(-1) for b in bs] + [bh])
+                if cached is None:
+                    wpack = torch.empty(lib.trase_b200_mlp_fused_pack_floats(nl, skip, E), **f32)
+                    wptrs = (ctypes.c_void_p * nl)(*[w.detach().contiguous().data_ptr() for w in Ws])
+                    _lib.check(lib.trase_b200_mlp_pack_fused(nl, skip, E, wptrs, wh.data_ptr(), wpack.data_ptr(), s))
+                    ball = torch.cat([b.detach().reshape(-1) for b in bs] + [bh])
+                    if pack_key is not None:
+                        if len(_PACK_CACHE) >= 4:
+                            _PACK_CACHE.clear()
+                        _PACK_CACHE[pack_key] = (tuple(weakref.ref(p) for p in params), hb, wpack, ball)
                 if not keep:
                     # inference (torch.no_grad / frozen network): no activations or masks leave the chip
                     with _Span("mlp_fwd"):
