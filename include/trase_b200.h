@@ -525,7 +525,10 @@ TRASE_API int trase_b200_wgrad_bf16_multi(int njobs, const void* const* P, const
 /* The two producers of those small operands can write the bf16 copy themselves (no separate conversion pass):
  * the positional encoding (out16 [M][ld16], 16-byte aligned, ld16 a multiple of 8 and >= the column count, padding
  * zero-filled) and the
- * packed head gradient (dout16 [M][16]). */
+ * packed head gradient, as two bf16 terms per value: dout16 [M][32] = [hi(16) | lo(16)], hi = bf16(v),
+ * lo = bf16(v - hi).  The head weight gradient is then the product with all 32 columns, D [256][32], and
+ * dWh^T = D[:, :16] + D[:, 16:] (the upstream gradient comes out of atomics; one 8-bit rounding of it would turn
+ * last-bit run-to-run differences into 0.4 % steps). */
 TRASE_API int trase_b200_deform_embed_bf16(int M, const float* xyz, const float* t, int t_stride, int Lx, int Lt,
                                            float* out, int ld, void* out16, int ld16, void* stream);
 TRASE_API int trase_b200_mlp_pack_dout_bf16(int M, const float* g0, const float* g1, const float* g2, float* dout,

@@ -337,14 +337,19 @@ class _DeformMLP(torch.autograd.Function):
             dout = torch.empty((M, 16), **f32)
             gs = [None if g is None else g.contiguous() for g in (g_xyz, g_rot, g_scale)]
             gp = [None if g is None else g.data_ptr() for g in gs]
-            dout16 = torch.empty((M, 16), dtype=torch.bfloat16, device=dev) if bf16 else None
+            # bf16 path: the head gradient travels as bf16 hi + lo parts ([M][32]) and its product lands in d32
+            dout16 = torch.empty((M, 32), dtype=torch.bfloat16, device=dev) if bf16 else None
+            d32 = torch.zeros((W, 32), **f32) if bf16 else None
             if bf16:
                 _lib.check(lib.trase_b200_mlp_pack_dout_bf16(M, *gp, dout.data_ptr(), dout16.data_ptr(), dbh.data_ptr(), s))
             else:
                 _lib.check(lib.trase_b200_mlp_pack_dout(M, *gp, dout.data_ptr(), dbh.data_ptr(), s))
             # heads: dWh^T = h_last^T dout
             with _Span("mlp_wgrad"):
-                wgrad(lib, acts[-1], dout16 if bf16 else dout, dwhT)
+                if bf16:
+                    wgrad(lib, acts[-1], dout16, d32)
+                else:
+                    wgrad(lib, acts[-1], dout, dwhT)
             if fused_bwd:
                 # the whole data-gradient chain in one persistent kernel (csrc/mlp_fused.cu): dzs[L] = dZ of
                 # layer nl-1-L, bias gradients straight into their targets
@@ -379,6 +384,8 @@ class _DeformMLP(torch.autograd.Function):
             if multi is not None:
                 _wgrad16_multi(lib, multi)
             span.__exit__()
+            if bf16:
+                torch.add(d32[:, :16], d32[:, 16:], out=dwhT)       # hi-part and lo-part products of the head gradient
             dwh = dwhT.t()
             out = [None, None, None, None, None, None]
             for i in range(nl):

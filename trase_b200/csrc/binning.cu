@@ -374,8 +374,12 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
 // over up to 32 sectors per request (the tile-bit passes of depth-ordered instances are fully scattered).
 // Same ranks, same stable order as radix_downsweep_kernel.  Dynamic shared memory: keys (aliasing the
 // per-warp counters once every thread holds its local position), values, three digit tables.
+// 3 CTAs per SM (80 registers, 24 bytes of spill) instead of the 2 that 116 registers allow: tile passes 0.142 -> 0.132 ms
+#ifndef TB_SORT_MINB
+#define TB_SORT_MINB 3
+#endif
 template <int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_staged_kernel(
+__global__ void __launch_bounds__(SORT_THREADS, TB_SORT_MINB) radix_downsweep_staged_kernel(
     const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, uint64_t* __restrict__ keys_out,
     uint32_t* __restrict__ vals_out, const uint32_t* __restrict__ count_dev, unsigned long long capacity, int shift,
     const uint32_t* __restrict__ hist, int nblk_stride) {

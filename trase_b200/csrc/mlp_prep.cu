@@ -59,7 +59,8 @@ __global__ void __launch_bounds__(256) pack_heads_kernel(const float* __restrict
   if (e < 16) bh[e] = e < 3 ? b0[e] : (e < 7 ? b1[e - 3] : (e < 10 ? b2[e - 7] : 0.f));
 }
 
-// dout[m][16] = rna([g0[m][0..2], g1[m][0..3], g2[m][0..2], 0...]);  colsum[j] += sum_m (unrounded) values
+// dout[m][16] = rna([g0[m][0..2], g1[m][0..3], g2[m][0..2], 0...]);  colsum[j] += sum_m (unrounded) values;
+// dout16[m][32] (optional) = the same 16 values as bf16 hi and lo parts
 __global__ void __launch_bounds__(256) pack_dout_kernel(int M, const float* __restrict__ g0, const float* __restrict__ g1,
                                                         const float* __restrict__ g2, float* __restrict__ dout,
                                                         __nv_bfloat16* __restrict__ dout16, float* __restrict__ colsum) {
@@ -74,7 +75,14 @@ __global__ void __launch_bounds__(256) pack_dout_kernel(int M, const float* __re
     else if (lane16 < 10) v = g2 ? g2[(size_t)m * 3 + (lane16 - 7)] : 0.f;
     acc += v;
     dout[(size_t)m * 16 + lane16] = rna(v);
-    if (dout16) dout16[(size_t)m * 16 + lane16] = __float2bfloat16_rn(v);   // operand of the bf16 head weight gradient
+    if (dout16) {
+      // operand of the bf16 head weight gradient, as TWO bf16 terms [hi(16) | lo(16)] per row: this factor comes out of
+      // the rasterizer's atomics (last-bit differences from run to run), and a single 8-bit rounding of it turns such a
+      // difference into a 0.4 % step of an element — visible in the head gradients' cancelling sums
+      const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+      dout16[(size_t)m * 32 + lane16] = hi;
+      dout16[(size_t)m * 32 + 16 + lane16] = __float2bfloat16_rn(v - __bfloat162float(hi));
+    }
   }
   // rows live in lanes {l, l+16} of each warp and in the 8 warps
   acc += __shfl_xor_sync(0xffffffffu, acc, 16);
