@@ -470,7 +470,10 @@ TRASE_API int trase_b200_feature_norm_reg_backward(int C, int64_t N, const float
  *     nl*256 hidden biases then 16 head biases; writes acts [nl][M][256]
  *     (TF32-rounded post-ReLU activations), masks [nl][M][8] (bit = output > 0)
  *     and out16 [M][16] (heads: 3 warp, 4 rotation, 3 scaling, 6 zero).  acts and masks
- *     both NULL = inference: nothing is kept for a backward pass.
+ *     both NULL = inference: nothing is kept for a backward pass.  d_xyz [M][3],
+ *     d_rot [M][4] (16-byte aligned), d_scale [M][3]: optional, all three or none; with
+ *     them the heads are written as those three contiguous tensors (what the caller hands
+ *     to the rasterizer glue) instead of the packed rows, and out16 may be NULL.
  * Restrictions: width 256, 2 <= nl <= 11, E <= 96 and a multiple of 4,
  * skip < nl - 1 (or -1 for none).
  * ---------------------------------------------------------------------- */
@@ -479,7 +482,7 @@ TRASE_API int trase_b200_mlp_pack_fused(int nl, int skip, int E, const float* co
                                         float* wpack, void* stream);
 TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const float* emb, int ld_emb,
                                            const float* wpack, const float* bias, float* acts, uint32_t* masks,
-                                           float* out16, void* stream);
+                                           float* out16, float* d_xyz, float* d_rot, float* d_scale, void* stream);
 /* The matching data-gradient chain of autograd's backward through the same layers,
  *   dZ_{l-1} = (dZ_l W_l[:, hidden columns]) * relu'(h_{l-1}),  db_l = column sums of dZ_l,
  * again one persistent kernel: the gradient tile stays on chip between layers and is
@@ -506,7 +509,8 @@ TRASE_API int trase_b200_mlp_backward_fused(int M, int nl, const float* dout, co
  * >= cols zero-filled. */
 TRASE_API int trase_b200_mlp_forward_fused_bf16(int M, int nl, int skip, int E, const float* emb, int ld_emb,
                                                 const float* wpack, const float* bias, void* acts16,
-                                                uint32_t* masks, float* out16, void* stream);
+                                                uint32_t* masks, float* out16, float* d_xyz, float* d_rot,
+                                                float* d_scale, void* stream);
 TRASE_API int trase_b200_mlp_backward_fused_bf16(int M, int nl, const float* dout, const float* wpack,
                                                  const uint32_t* masks, void* dzs16, float* const* colsum,
                                                  void* stream);

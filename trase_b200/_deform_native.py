@@ -232,7 +232,11 @@ class _DeformMLP(torch.autograd.Function):
                     cached = None
                 if cached is not None:
                     cached = cached[1:]
-            out16 = torch.empty((M, 16), **f32)
+            # fused path: the kernel writes the three heads as the contiguous tensors handed on; the layer-by-layer
+            # path produces the packed [M][16] rows and slices them
+            out16 = None if fused else torch.empty((M, 16), **f32)
+            heads_out = (torch.empty((M, 3), **f32), torch.empty((M, 4), **f32), torch.empty((M, 3), **f32)) \
+                if fused else None
             if cached is not None:
                 hb, wpack, ball = cached
                 wh, whT, bh = hb[:16 * W].view(16, W), hb[16 * W:32 * W].view(W, 16), hb[32 * W:]
@@ -257,14 +261,14 @@ class _DeformMLP(torch.autograd.Function):
                     with _Span("mlp_fwd"):
                         _lib.check(lib.trase_b200_mlp_forward_fused(M, nl, skip, E, emb.data_ptr(), emb.stride(0),
                                                                     wpack.data_ptr(), ball.data_ptr(), None, None,
-                                                                    out16.data_ptr(), s))
-                    return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
+                                                                    None, *[h.data_ptr() for h in heads_out], s))
+                    return heads_out
                 masks = torch.empty((nl, M, W // 32), dtype=torch.int32, device=dev)
                 acts_all = torch.empty((nl, M, W), dtype=torch.bfloat16 if bf16 else torch.float32, device=dev)
                 fwd = lib.trase_b200_mlp_forward_fused_bf16 if bf16 else lib.trase_b200_mlp_forward_fused
                 with _Span("mlp_fwd"):
                     _lib.check(fwd(M, nl, skip, E, emb.data_ptr(), emb.stride(0), wpack.data_ptr(), ball.data_ptr(),
-                                   acts_all.data_ptr(), masks.data_ptr(), out16.data_ptr(), s))
+                                   acts_all.data_ptr(), masks.data_ptr(), None, *[h.data_ptr() for h in heads_out], s))
                 acts = list(acts_all.unbind(0))
                 skipbuf = emb16 if bf16 else emb
             else:
@@ -287,6 +291,8 @@ class _DeformMLP(torch.autograd.Function):
         # the parameter objects themselves: backward looks their .grad up (DIRECT_GRAD_ACCUM)
         hp = list(params[:2 * nl])
         ctx.hidden_params = hp if all(isinstance(p, torch.nn.Parameter) for p in hp) else None
+        if heads_out is not None:
+            return heads_out
         return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
 
     @staticmethod

@@ -177,7 +177,7 @@ def load() -> C.CDLL:
     lib.trase_b200_mlp_pack_fused_bwd.restype = C.c_int
     lib.trase_b200_mlp_pack_fused_bwd.argtypes = [C.c_int] * 3 + [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]
     lib.trase_b200_mlp_forward_fused_bf16.restype = C.c_int
-    lib.trase_b200_mlp_forward_fused_bf16.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 6
+    lib.trase_b200_mlp_forward_fused_bf16.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 9
     lib.trase_b200_mlp_backward_fused_bf16.restype = C.c_int
     lib.trase_b200_mlp_backward_fused_bf16.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.POINTER(C.c_void_p),
                                                                                              C.c_void_p]
@@ -220,7 +220,7 @@ def load() -> C.CDLL:
     lib.trase_b200_densification_stats.restype = C.c_int
     lib.trase_b200_densification_stats.argtypes = [C.c_int] + [C.c_void_p] * 5
     lib.trase_b200_mlp_forward_fused.restype = C.c_int
-    lib.trase_b200_mlp_forward_fused.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 6
+    lib.trase_b200_mlp_forward_fused.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int] + [C.c_void_p] * 9
     lib.trase_b200_l1_ssim_backward.restype = C.c_int
     lib.trase_b200_l1_ssim_backward.argtypes = [C.c_int] * 3 + [C.c_void_p] * 3 + [C.c_float] * 2 + [C.c_void_p] * 3
     lib.trase_b200_launch_count.restype = C.c_ulonglong

@@ -75,7 +75,8 @@ struct FusedParams {
   int blk_base[FU_MAX_LAYERS + 1];   // first packed k-block of each layer (layer nl = heads)
   const float* bias;                 // [nl][256], then the 16 head biases
   uint32_t* masks;                   // [nl][M][8]  ReLU bit masks
-  float* out16;                      // [M][16]
+  float* out16;                      // [M][16] (or NULL when the three heads go to o3)
+  float* o3[3];                      // optional separate head outputs: d_xyz [M][3], d_rotation [M][4], d_scaling [M][3]
   float* acts;                       // [nl][M][256]  (backward: dZ of every layer, in backward order)
   int acts16;                        // A16 kernels: the bf16 tensor map (tmActs) is live
   float* colsum[FU_MAX_LAYERS];      // backward: bias gradient [256] of every forward layer (+=)
@@ -406,11 +407,23 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constan
           for (int c = 0; c < 4; c++) bq[c] = __ldg(reinterpret_cast<const float4*>(bias) + c);
           tmem_ld_wait();
           if (grow < p.M) {
-            float4* o = reinterpret_cast<float4*>(p.out16 + (size_t)grow * 16);
+            float4 o[4];
 #pragma unroll
             for (int c = 0; c < 4; c++)
               o[c] = make_float4(__uint_as_float(v[c * 4]) + bq[c].x, __uint_as_float(v[c * 4 + 1]) + bq[c].y,
                                  __uint_as_float(v[c * 4 + 2]) + bq[c].z, __uint_as_float(v[c * 4 + 3]) + bq[c].w);
+            if (p.o3[0]) {
+              // the three heads as the contiguous tensors the caller hands on (columns 0-2, 3-6, 7-9 of the packed row)
+              float* x = p.o3[0] + (size_t)grow * 3;
+              x[0] = o[0].x; x[1] = o[0].y; x[2] = o[0].z;
+              *reinterpret_cast<float4*>(p.o3[1] + (size_t)grow * 4) = make_float4(o[0].w, o[1].x, o[1].y, o[1].z);
+              float* sc = p.o3[2] + (size_t)grow * 3;
+              sc[0] = o[1].w; sc[1] = o[2].x; sc[2] = o[2].y;
+            } else {
+              float4* dst = reinterpret_cast<float4*>(p.out16 + (size_t)grow * 16);
+#pragma unroll
+              for (int c = 0; c < 4; c++) dst[c] = o[c];
+            }
           }
         }
         tc_fence_before();
@@ -605,25 +618,36 @@ static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMa
 // acts == masks == NULL: inference, nothing is kept for a backward pass (no activation traffic to HBM at all).
 static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* emb, int ld_emb, const float* wpack,
                                   const float* bias, float* acts, void* acts16, uint32_t* masks, float* out16,
-                                  void* stream);
+                                  float* d_xyz, float* d_rot, float* d_scale, void* stream);
+// d_xyz [M][3], d_rot [M][4] (16-byte aligned), d_scale [M][3]: optional (all three or none); with them the three heads
+// are written as those contiguous tensors and out16 may be NULL.
 extern "C" TRASE_API int trase_b200_mlp_forward_fused(int M, int nl, int skip, int E, const float* emb, int ld_emb,
                                                       const float* wpack, const float* bias, float* acts,
-                                                      uint32_t* masks, float* out16, void* stream) {
-  return mlp_forward_fused_impl(M, nl, skip, E, emb, ld_emb, wpack, bias, acts, nullptr, masks, out16, stream);
+                                                      uint32_t* masks, float* out16, float* d_xyz, float* d_rot,
+                                                      float* d_scale, void* stream) {
+  return mlp_forward_fused_impl(M, nl, skip, E, emb, ld_emb, wpack, bias, acts, nullptr, masks, out16, d_xyz, d_rot,
+                                d_scale, stream);
 }
 // Same network, but the activations kept for the backward pass are written as BF16 (acts16: [nl][M][256] bf16,
 // 16-byte aligned): their only reader is the weight-gradient product (trase_b200_wgrad_bf16).
 extern "C" TRASE_API int trase_b200_mlp_forward_fused_bf16(int M, int nl, int skip, int E, const float* emb,
                                                            int ld_emb, const float* wpack, const float* bias,
-                                                           void* acts16, uint32_t* masks, float* out16, void* stream) {
+                                                           void* acts16, uint32_t* masks, float* out16, float* d_xyz,
+                                                           float* d_rot, float* d_scale, void* stream) {
   if (!acts16 || !masks) { set_error("trase_b200_mlp_forward_fused_bf16: acts16 and masks are required"); return 1; }
-  return mlp_forward_fused_impl(M, nl, skip, E, emb, ld_emb, wpack, bias, nullptr, acts16, masks, out16, stream);
+  return mlp_forward_fused_impl(M, nl, skip, E, emb, ld_emb, wpack, bias, nullptr, acts16, masks, out16, d_xyz, d_rot,
+                                d_scale, stream);
 }
 static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* emb, int ld_emb, const float* wpack,
                                   const float* bias, float* acts, void* acts16, uint32_t* masks, float* out16,
-                                  void* stream) {
+                                  float* d_xyz, float* d_rot, float* d_scale, void* stream) {
   if (M <= 0) return 0;
-  if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || !out16 ||
+  const bool split = d_xyz || d_rot || d_scale;
+  if (split && (!d_xyz || !d_rot || !d_scale || ((uintptr_t)d_rot & 15))) {
+    set_error("trase_b200_mlp_forward_fused: d_xyz / d_rot / d_scale come together, d_rot 16-byte aligned");
+    return 1;
+  }
+  if (!mlp::fu_shape_ok(nl, skip, E) || !emb || !wpack || !bias || (!out16 && !split) ||
       (((acts == nullptr) && (acts16 == nullptr)) != (masks == nullptr)) || ((uintptr_t)acts16 & 15) || (ld_emb & 3) ||
       ld_emb < E || ((uintptr_t)emb & 15) || ((uintptr_t)wpack & 15) || ((uintptr_t)acts & 15) ||
       ((uintptr_t)bias & 15) || ((uintptr_t)out16 & 15)) {
@@ -636,6 +660,7 @@ static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* e
   const int total = mlp::fu_layout(nl, skip, E, base);
   for (int L = 0; L <= nl; L++) p.blk_base[L] = base[L];
   p.bias = bias; p.masks = masks; p.out16 = out16; p.acts = acts; p.acts16 = acts16 ? 1 : 0;
+  p.o3[0] = d_xyz; p.o3[1] = d_rot; p.o3[2] = d_scale;
   for (int i = 0; i < mlp::FU_MAX_LAYERS; i++) p.colsum[i] = nullptr;
   p.prof = mlp::g_fused_prof;
   CUtensorMap tE, tW, tWh, tA;
@@ -643,7 +668,7 @@ static int mlp_forward_fused_impl(int M, int nl, int skip, int E, const float* e
       !mlp::make_tmap_2d(&tW, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 128, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !mlp::make_tmap_2d(&tWh, wpack, (uint64_t)total * mlp::FU_W, 32, 32, 16, 32, CU_TENSOR_MAP_SWIZZLE_128B) ||
       !(acts16 ? mlp::make_tmap_acts16(&tA, acts16, M, nl)
-               : mlp::make_tmap_acts(&tA, acts ? acts : out16, M, acts ? nl : 1))) {   // inference: map unused, must still be valid
+               : mlp::make_tmap_acts(&tA, acts ? acts : const_cast<float*>(emb), M, acts ? nl : 1))) {   // inference: map unused, must still be valid
     set_error("trase_b200_mlp_forward_fused: cuTensorMapEncodeTiled failed");
     return 2;
   }
@@ -718,6 +743,7 @@ static int mlp_backward_fused_impl(int M, int nl, const float* dout, const float
   p.blk_base[0] = 0;
   for (int L = 1; L <= nl; L++) p.blk_base[L] = 1 + (L - 1) * mlp::FU_HCH;
   p.bias = nullptr; p.masks = const_cast<uint32_t*>(masks); p.out16 = nullptr; p.acts = dzs; p.acts16 = dzs16 ? 1 : 0;
+  p.o3[0] = p.o3[1] = p.o3[2] = nullptr;
   for (int i = 0; i < nl; i++) {
     if (!colsum[i]) { set_error("trase_b200_mlp_backward_fused: null bias-gradient pointer"); return 1; }
     p.colsum[i] = colsum[i];

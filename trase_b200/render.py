@@ -133,11 +133,9 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
         raise NotImplementedError("6-DoF deformation and the *_python pipeline switches are outside the "
                                   "accelerated path")
     if want_viewspace_grad:
-        screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True) + 0
-        try:
-            screenspace_points.retain_grad()
-        except Exception:
-            pass
+        # a LEAF that requires grad: its .grad is kept like the reference's `zeros(..., requires_grad=True) + 0` followed
+        # by retain_grad() (gaussian_renderer/__init__.py:40-44), without the extra add kernel
+        screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True)
     else:
         screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype)
     raster_settings = GaussianRasterizationSettings(
