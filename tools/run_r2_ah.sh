@@ -1,0 +1,18 @@
+#!/usr/bin/env bash
+# programmatic dependent launch on every kernel of the library (-DTB_PDL=1 variant) against the plain launches
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+cp trase_b200/libtrase_b200.so /tmp/lib_base.so
+cp trase_b200/libtrase_b200_vPDL.so trase_b200/libtrase_b200.so
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -2 | tee -a gpurun_out/r2_ah_pdl.txt
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
+for w in neu3d hypernerf8 nnfm; do
+ for v in base PDL; do
+  [ $v = base ] && cp /tmp/lib_base.so trase_b200/libtrase_b200.so || cp trase_b200/libtrase_b200_v$v.so trase_b200/libtrase_b200.so
+  python bench.py --workload $w --steps $([ $w = hypernerf8 ] && echo 10 || echo 30) --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1])
+print('$v $w', d['value'], d['ms_per_step'], 'e2e', d['e2e']['value'], {k:v['ms'] for k,v in d['stages'].items()})" | tee -a gpurun_out/r2_ah_pdl.txt
+ done
+done
+cp /tmp/lib_base.so trase_b200/libtrase_b200.so

@@ -20,6 +20,7 @@ struct AssembleFwd {
 };
 
 __global__ void __launch_bounds__(256) assemble_fwd_kernel(const AssembleFwd a) {
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < a.P) {
 #pragma unroll
@@ -39,6 +40,7 @@ __global__ void __launch_bounds__(256) assemble_fwd_kernel(const AssembleFwd a) 
 // SH rows: out[i][0] = f_dc[i][0], out[i][1..] = f_rest[i][..]; flat float copy, coalesced
 __global__ void __launch_bounds__(256) assemble_sh_kernel(int P, int Mrest, const float* __restrict__ f_dc,
                                                           const float* __restrict__ f_rest, float* __restrict__ shs) {
+  pdl_wait();
   const int M3 = (Mrest + 1) * 3;
   const size_t total = (size_t)P * M3;
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
@@ -51,6 +53,7 @@ __global__ void __launch_bounds__(256) assemble_sh_kernel(int P, int Mrest, cons
 // feature rows: 8 lanes per Gaussian, float4 each; norm by shuffle over the 8 lanes
 __global__ void __launch_bounds__(256) assemble_feat_kernel(int P, const float4* __restrict__ feat,
                                                             float4* __restrict__ out) {
+  pdl_wait();
   const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = e < (size_t)P * 8;
   float4 f = valid ? feat[e] : make_float4(0, 0, 0, 0);
@@ -70,6 +73,7 @@ struct AssembleBwd {
 };
 
 __global__ void __launch_bounds__(256) assemble_bwd_kernel(const AssembleBwd a) {
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < a.P) {
 #pragma unroll
@@ -103,6 +107,7 @@ __global__ void __launch_bounds__(256) assemble_bwd_kernel(const AssembleBwd a) 
 
 __global__ void __launch_bounds__(256) assemble_sh_bwd_kernel(int P, int Mrest, const float* __restrict__ g_shs,
                                                               float* __restrict__ g_fdc, float* __restrict__ g_frest) {
+  pdl_wait();
   const int M3 = (Mrest + 1) * 3;
   const size_t total = (size_t)P * M3;
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
@@ -118,6 +123,7 @@ __global__ void __launch_bounds__(256) assemble_sh_bwd_kernel(int P, int Mrest, 
 __global__ void __launch_bounds__(256) assemble_feat_bwd_kernel(int P, const float4* __restrict__ feat,
                                                                 const float4* __restrict__ g_objs,
                                                                 float4* __restrict__ g_feat) {
+  pdl_wait();
   const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = e < (size_t)P * 8;
   const float4 f = valid ? feat[e] : make_float4(0, 0, 0, 0);
@@ -148,6 +154,7 @@ struct SmoothSel { int n; unsigned char col[SMOOTH_MAX_SEL]; };
 __global__ void __launch_bounds__(256) smooth_feat_fwd_kernel(int P, int K, SmoothSel sel,
                                                               const float* __restrict__ feat,
                                                               const long long* __restrict__ idx, float* __restrict__ out) {
+  pdl_wait();
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= P) return;
   float acc = 0.f;
@@ -167,6 +174,7 @@ __global__ void __launch_bounds__(256) smooth_feat_bwd_kernel(int P, int K, Smoo
                                                               const float* __restrict__ feat,
                                                               const long long* __restrict__ idx,
                                                               const float* __restrict__ g_out, float* __restrict__ g_feat) {
+  pdl_wait();
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= P) return;
   const float g = g_out[(size_t)p * NUM_OBJECTS + lane] / (float)sel.n;
@@ -200,6 +208,7 @@ __global__ void __launch_bounds__(256) smooth_feat_bwd_kernel(int P, int K, Smoo
 //             (rev_ptr [P+1], rev_ent [P*K]: the entries (p << 8 | column) of row j, built once per map by the
 //             caller) — no atomics, no memset, every g_feat row written exactly once.
 __global__ void __launch_bounds__(256) smooth_unit_kernel(int P, const float* __restrict__ feat, float* __restrict__ unit) {
+  pdl_wait();
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= P) return;
   const float v = feat[(size_t)p * NUM_OBJECTS + lane];
@@ -211,6 +220,7 @@ __global__ void __launch_bounds__(256) smooth_unit_kernel(int P, const float* __
 __global__ void __launch_bounds__(256) smooth_gather_fwd_kernel(int P, int K, SmoothSel sel,
                                                                 const float* __restrict__ unit,
                                                                 const long long* __restrict__ idx, float* __restrict__ out) {
+  pdl_wait();
   const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= P) return;
   // lane k fetches the k-th selected neighbour's index; the rows are then read with all loads in flight together
@@ -229,6 +239,7 @@ __global__ void __launch_bounds__(256) smooth_feat_bwd_csr_kernel(int P, unsigne
                                                                   const int* __restrict__ rev_ent,
                                                                   const float* __restrict__ g_out,
                                                                   float* __restrict__ g_feat) {
+  pdl_wait();
   const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (j >= P) return;
   const int b = __ldg(rev_ptr + j), e = __ldg(rev_ptr + j + 1);
@@ -298,10 +309,10 @@ extern "C" TRASE_API int trase_b200_smooth_features_forward(int P, int K, const 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int grid = (int)(((size_t)P * 32 + 255) / 256);
   if (unit_scratch) {
-    smooth_unit_kernel<<<grid, 256, 0, s>>>(P, feat, unit_scratch);
-    smooth_gather_fwd_kernel<<<grid, 256, 0, s>>>(P, K, sel, unit_scratch, knn_idx, out);
+    launch_k(smooth_unit_kernel, grid, 256, 0, s, P, feat, unit_scratch);
+    launch_k(smooth_gather_fwd_kernel, grid, 256, 0, s, P, K, sel, unit_scratch, knn_idx, out);
   } else {
-    smooth_feat_fwd_kernel<<<grid, 256, 0, s>>>(P, K, sel, feat, knn_idx, out);
+    launch_k(smooth_feat_fwd_kernel, grid, 256, 0, s, P, K, sel, feat, knn_idx, out);
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_smooth_features_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -330,7 +341,7 @@ extern "C" TRASE_API int trase_b200_smooth_features_backward_csr(int P, int K, c
     }
     colmask |= 1ull << sel.col[i];
   }
-  smooth_feat_bwd_csr_kernel<<<(int)(((size_t)P * 32 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(smooth_feat_bwd_csr_kernel, (int)(((size_t)P * 32 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       P, colmask, 1.f / (float)sel.n, feat, rev_ptr, rev_ent, g_out, g_feat);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_smooth_features_backward_csr: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -351,7 +362,7 @@ extern "C" TRASE_API int trase_b200_smooth_features_backward(int P, int K, const
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   cudaError_t e = cudaMemsetAsync(g_feat, 0, (size_t)P * NUM_OBJECTS * 4, s);      // accumulated into below
   if (e == cudaSuccess) {
-    smooth_feat_bwd_kernel<<<(int)(((size_t)P * 32 + 255) / 256), 256, 0, s>>>(P, K, sel, feat, knn_idx, g_out, g_feat);
+    launch_k(smooth_feat_bwd_kernel, (int)(((size_t)P * 32 + 255) / 256), 256, 0, s, P, K, sel, feat, knn_idx, g_out, g_feat);
     e = cudaGetLastError();
   }
   if (e != cudaSuccess) { set_error("trase_b200_smooth_features_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -382,12 +393,12 @@ extern "C" TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const flo
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   AssembleFwd a{P, Mrest, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat,
                 means3D, scales, rotations, opac_out, shs, sh_objs};
-  assemble_fwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+  launch_k(assemble_fwd_kernel, (P + 255) / 256, 256, 0, s, a);
   const size_t tot = (size_t)P * (Mrest + 1) * 3;
   int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
-  if (shs) assemble_sh_kernel<<<g, 256, 0, s>>>(P, Mrest, f_dc, f_rest, shs);
+  if (shs) launch_k(assemble_sh_kernel, g, 256, 0, s, P, Mrest, f_dc, f_rest, shs);
   const int n_launched_f = shs ? 3 : 2;
-  assemble_feat_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(P, reinterpret_cast<const float4*>(feat),
+  launch_k(assemble_feat_kernel, (int)(((size_t)P * 8 + 255) / 256), 256, 0, s, P, reinterpret_cast<const float4*>(feat),
                                                                        reinterpret_cast<float4*>(sh_objs));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_assemble_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -414,12 +425,12 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   AssembleBwd a{P, Mrest, scaling, rotation, opacity, feat, g_means3D, g_scales, g_rotations, g_opac, g_shs, g_objs,
                 g_xyz, g_dxyz, g_scaling, g_dscaling, g_rotation, g_drotation, g_opacity, g_fdc, g_frest, g_feat};
-  if (geom) assemble_bwd_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+  if (geom) launch_k(assemble_bwd_kernel, (P + 255) / 256, 256, 0, s, a);
   const size_t tot = (size_t)P * (Mrest + 1) * 3;
   int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
-  if (g_fdc) assemble_sh_bwd_kernel<<<g, 256, 0, s>>>(P, Mrest, g_shs, g_fdc, g_frest);   // NULL: caller slices g_shs itself
+  if (g_fdc) launch_k(assemble_sh_bwd_kernel, g, 256, 0, s, P, Mrest, g_shs, g_fdc, g_frest);   // NULL: caller slices g_shs itself
   if (g_feat)      // NULL: the feature parameter is frozen (GAUSSIAN state), nobody wants this gradient
-    assemble_feat_bwd_kernel<<<(int)(((size_t)P * 8 + 255) / 256), 256, 0, s>>>(
+    launch_k(assemble_feat_bwd_kernel, (int)(((size_t)P * 8 + 255) / 256), 256, 0, s, 
         P, reinterpret_cast<const float4*>(feat), reinterpret_cast<const float4*>(g_objs),
         reinterpret_cast<float4*>(g_feat));
   cudaError_t e = cudaGetLastError();

@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums_kernel(const uin
                                                                        uint32_t* __restrict__ counters,
                                                                        unsigned long long capacity,
                                                                        int* __restrict__ host_total) {
+  pdl_wait();
   __shared__ uint32_t s_warp[SCAN_THREADS / 32];
   __shared__ uint32_t s_carry;
   if (threadIdx.x == 0) s_carry = 0;
@@ -86,6 +87,7 @@ __global__ void __launch_bounds__(PRE_BLOCK) gaussian_depth_keys_kernel(int P, c
                                                                          uint64_t* __restrict__ keys,
                                                                          uint32_t* __restrict__ vals,
                                                                          uint32_t* __restrict__ counters) {
+  pdl_wait();
   const int i = blockIdx.x * PRE_BLOCK + threadIdx.x;
   if (i < P) {
     keys[i] = tiles_touched[i] ? (uint64_t)__float_as_uint(depths[i]) : 0xffffffffull;
@@ -98,6 +100,7 @@ __global__ void __launch_bounds__(PRE_BLOCK) gaussian_depth_keys_kernel(int P, c
 __global__ void __launch_bounds__(PRE_BLOCK) ordered_block_sums_kernel(int P, const uint32_t* __restrict__ order,
                                                                         const uint32_t* __restrict__ tiles_touched,
                                                                         uint32_t* __restrict__ block_sums) {
+  pdl_wait();
   __shared__ uint32_t s_warp[PRE_BLOCK / 32];
   const int pos = blockIdx.x * PRE_BLOCK + threadIdx.x;
   uint32_t v = (pos < P) ? tiles_touched[order[pos]] : 0u;
@@ -121,6 +124,7 @@ __global__ void __launch_bounds__(PRE_BLOCK) duplicate_keys_kernel(
     const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ block_offsets,
     uint32_t* __restrict__ point_offsets, const uint32_t* __restrict__ counters, uint64_t* __restrict__ keys,
     uint32_t* __restrict__ vals, const int* __restrict__ radii, int grid_x, int grid_y) {
+  pdl_wait();
   __shared__ uint32_t s_warp[PRE_BLOCK / 32];
   const int pos = blockIdx.x * PRE_BLOCK + threadIdx.x;
   const int idx = (pos < P) ? (int)order[pos] : P;
@@ -189,7 +193,7 @@ cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPoi
                                       uint32_t* ok_vals, int* host_total_dev, cudaEvent_t readback_event,
                                       cudaStream_t s) {
   const int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
-  gaussian_depth_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, p.depths, p.tiles_touched, ok_keys, ok_vals, p.counters);
+  launch_k(gaussian_depth_keys_kernel, nblk, PRE_BLOCK, 0, s, a.P, p.depths, p.tiles_touched, ok_keys, ok_vals, p.counters);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   e = launch_sort_pingpong(ok_keys, ok_vals, p.keys_unsorted, p.vals_unsorted, p.counters + 2, a.P, 0, 32,
@@ -198,8 +202,8 @@ cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPoi
   static_assert(((32 + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS) % 2 == 0,
                 "the depth sort must take an even number of passes so that it ends on the side it started from");
   const uint32_t* order = ok_vals;
-  ordered_block_sums_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, order, p.tiles_touched, p.block_sums);
-  scan_block_sums_kernel<<<1, SCAN_THREADS, 0, s>>>(p.block_sums, p.block_offsets, nblk, p.counters,
+  launch_k(ordered_block_sums_kernel, nblk, PRE_BLOCK, 0, s, a.P, order, p.tiles_touched, p.block_sums);
+  launch_k(scan_block_sums_kernel, 1, SCAN_THREADS, 0, s, p.block_sums, p.block_offsets, nblk, p.counters,
                                                    (unsigned long long)a.capacity, host_total_dev);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
@@ -208,7 +212,7 @@ cudaError_t launch_scan_and_duplicate(const trase_b200_fwd_args& a, const FwdPoi
     if (e != cudaSuccess) return e;
   }
   const int grid_x = (a.W + TILE - 1) / TILE, grid_y = (a.H + TILE - 1) / TILE;
-  duplicate_keys_kernel<<<nblk, PRE_BLOCK, 0, s>>>(a.P, order, p.means2D, p.depths, p.tiles_touched, p.block_offsets,
+  launch_k(duplicate_keys_kernel, nblk, PRE_BLOCK, 0, s, a.P, order, p.means2D, p.depths, p.tiles_touched, p.block_offsets,
                                                    p.point_offsets, p.counters, p.keys_unsorted, p.vals_unsorted,
                                                    a.radii, grid_x, grid_y);
   count_launches(4);      // depth keys, ordered block sums, block-sum scan, key emission (the sort counts its own)
@@ -235,6 +239,7 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_upsweep_kernel(const uint6
                                                                      unsigned long long capacity, int shift,
                                                                      uint32_t* __restrict__ hist, int nblk_stride,
                                                                      uint32_t* __restrict__ digit_total) {
+  pdl_wait();
   const uint32_t R = sort_count(count_dev, capacity);
   const uint32_t block_start = blockIdx.x * (SORT_THREADS * ITEMS);
   if (block_start >= R) return;
@@ -263,6 +268,7 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scan_kernel(uint32_t* __re
                                                                   const uint32_t* __restrict__ digit_total,
                                                                   const uint32_t* __restrict__ count_dev,
                                                                   unsigned long long capacity, int tile_keys) {
+  pdl_wait();
   const uint32_t R = sort_count(count_dev, capacity);
   const int nblk = (int)((R + tile_keys - 1) / tile_keys);
   const int d = blockIdx.x;
@@ -313,6 +319,7 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_downsweep_kernel(
     const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, uint64_t* __restrict__ keys_out,
     uint32_t* __restrict__ vals_out, const uint32_t* __restrict__ count_dev, unsigned long long capacity, int shift,
     const uint32_t* __restrict__ hist, int nblk_stride) {
+  pdl_wait();
   const uint32_t R = sort_count(count_dev, capacity);
   const uint32_t block_start = blockIdx.x * (SORT_THREADS * ITEMS);
   if (block_start >= R) return;
@@ -383,6 +390,7 @@ __global__ void __launch_bounds__(SORT_THREADS, TB_SORT_MINB) radix_downsweep_st
     const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, uint64_t* __restrict__ keys_out,
     uint32_t* __restrict__ vals_out, const uint32_t* __restrict__ count_dev, unsigned long long capacity, int shift,
     const uint32_t* __restrict__ hist, int nblk_stride) {
+  pdl_wait();
   const uint32_t R = sort_count(count_dev, capacity);
   constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
   const uint32_t block_start = blockIdx.x * TILE_KEYS;
@@ -499,6 +507,7 @@ constexpr int SORT_STAGED_SMEM = SORT_TILE * 12 + 2 * SORT_RADIX * 4;
 __global__ void copy_pairs_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                   uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                   const uint32_t* __restrict__ count_dev, unsigned long long capacity) {
+  pdl_wait();
   const uint32_t R = sort_count(count_dev, capacity);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < R; i += gridDim.x * blockDim.x) {
     keys_out[i] = keys_in[i];
@@ -538,21 +547,21 @@ cudaError_t launch_sort_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* k
     const int shift = begin_bit + pass * SORT_RADIX_BITS;
     uint32_t* tot = digit_total + pass * SORT_RADIX;
     if (sort_is_small(capacity)) {
-      radix_upsweep_kernel<SORT_ITEMS_SMALL><<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
-      radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap, SORT_TILE_SMALL);
-      radix_downsweep_kernel<SORT_ITEMS_SMALL><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift,
+      launch_k(radix_upsweep_kernel<SORT_ITEMS_SMALL>, nblk, SORT_THREADS, 0, s, kin, count_dev, cap, shift, hist, nblk, tot);
+      launch_k(radix_scan_kernel, SORT_RADIX, SORT_THREADS, 0, s, hist, nblk, tot, count_dev, cap, SORT_TILE_SMALL);
+      launch_k(radix_downsweep_kernel<SORT_ITEMS_SMALL>, nblk, SORT_THREADS, 0, s, kin, vin, kout, vout, count_dev, cap, shift,
                                                                             hist, nblk);
     } else {
-      radix_upsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, count_dev, cap, shift, hist, nblk, tot);
-      radix_scan_kernel<<<SORT_RADIX, SORT_THREADS, 0, s>>>(hist, nblk, tot, count_dev, cap, SORT_TILE);
+      launch_k(radix_upsweep_kernel<SORT_ITEMS>, nblk, SORT_THREADS, 0, s, kin, count_dev, cap, shift, hist, nblk, tot);
+      launch_k(radix_scan_kernel, SORT_RADIX, SORT_THREADS, 0, s, hist, nblk, tot, count_dev, cap, SORT_TILE);
       if (g_sort_staged) {
         static PerDeviceOnce attr_once;
         e = ensure_max_dyn_smem(attr_once, radix_downsweep_staged_kernel<SORT_ITEMS>, SORT_STAGED_SMEM);
         if (e != cudaSuccess) return e;
-        radix_downsweep_staged_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, SORT_STAGED_SMEM, s>>>(
+        launch_k(radix_downsweep_staged_kernel<SORT_ITEMS>, nblk, SORT_THREADS, SORT_STAGED_SMEM, s, 
             kin, vin, kout, vout, count_dev, cap, shift, hist, nblk);
       } else {
-        radix_downsweep_kernel<SORT_ITEMS><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, count_dev, cap, shift, hist,
+        launch_k(radix_downsweep_kernel<SORT_ITEMS>, nblk, SORT_THREADS, 0, s, kin, vin, kout, vout, count_dev, cap, shift, hist,
                                                                         nblk);
       }
     }
@@ -575,7 +584,7 @@ cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* ke
   if ((sort_num_passes(0, end_bit) & 1) == 0) {  // result sits in the input buffers
     int g = (int)((capacity + 1023) / 1024);
     if (g < 1) g = 1;
-    copy_pairs_kernel<<<g, SORT_THREADS, 0, s>>>(keys_in, vals_in, keys_out, vals_out, count_dev,
+    launch_k(copy_pairs_kernel, g, SORT_THREADS, 0, s, keys_in, vals_in, keys_out, vals_out, count_dev,
                                                  (unsigned long long)capacity);
     e = cudaGetLastError();
   }
@@ -586,6 +595,7 @@ cudaError_t launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* ke
 // Tile ranges: ranges[t] = [first, last) positions of tile t in the sorted list.
 __global__ void identify_ranges_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ counters,
                                        unsigned long long capacity, uint2* __restrict__ ranges) {
+  pdl_wait();
   if (counters[1]) return;  // overflow: leave every range empty
   const uint32_t L = sort_count(counters, capacity);
   for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < L; idx += gridDim.x * blockDim.x) {
@@ -610,7 +620,7 @@ cudaError_t launch_identify_ranges(const trase_b200_fwd_args& a, const FwdPointe
   if (a.capacity <= 0) return cudaSuccess;
   long long g = (a.capacity + 255) / 256;
   if (g > 148 * 16) g = 148 * 16;
-  identify_ranges_kernel<<<(int)g, 256, 0, s>>>(p.point_list_keys, p.counters, (unsigned long long)a.capacity,
+  launch_k(identify_ranges_kernel, (int)g, 256, 0, s, p.point_list_keys, p.counters, (unsigned long long)a.capacity,
                                                 p.ranges);
   return cudaGetLastError();
 }

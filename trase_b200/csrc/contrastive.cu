@@ -95,6 +95,7 @@ constexpr int LD = CT + 4;         // row pitch of the channel-major tiles (floa
 // logic per pair) or MAXW.
 template <int MODE, int NW>
 __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p) {
+  pdl_wait();
   // channel-major: s[k][pixel].  The own tile holds every value TWICE, (v, v) side by side: a 16-byte read is then two
   // own pixels as ready-made packed operands of FFMA2 (two partner pixels per instruction), with no register moves
   __shared__ __align__(16) float2 s_own[CC][LD];
@@ -280,6 +281,7 @@ __global__ void __launch_bounds__(CT_THREADS) contrastive_kernel(const Params p)
 
 // n_kept = sum_j kept[j] * j (the number of rows i < j of each kept column), loss = sum / n_kept
 __global__ void __launch_bounds__(256) contrastive_finish_kernel(const Params p, int nblocks) {
+  pdl_wait();
   __shared__ double s_v[6][8];
   double v[6] = {0, 0, 0, 0, 0, 0};            // n_pos, n_neg, pos_sum, neg_sum, pos_pairs, neg_pairs
   for (int j = threadIdx.x; j < p.N; j += 256) {
@@ -320,6 +322,7 @@ __global__ void __launch_bounds__(256) pixel_mask_info_kernel(int N, int n_masks
                                                               const long long* __restrict__ pix,
                                                               unsigned long long* __restrict__ bits,
                                                               float* __restrict__ a) {
+  pdl_wait();
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   const long long px = pix[n];
@@ -362,7 +365,7 @@ extern "C" TRASE_API int trase_b200_pixel_mask_info(int N, int n_masks, int64_t 
     return 1;
   }
   const int nwords = (n_masks + 63) / 64;
-  contrastive::pixel_mask_info_kernel<<<(N + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(contrastive::pixel_mask_info_kernel, (N + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       N, n_masks, (long long)HW, nwords, masks, reinterpret_cast<const long long*>(area), sampled_mask,
       reinterpret_cast<const long long*>(pix), reinterpret_cast<unsigned long long*>(bits), a);
   cudaError_t e = cudaGetLastError();
@@ -403,13 +406,13 @@ extern "C" TRASE_API int trase_b200_contrastive_soft_forward(int N, int nwords, 
   cudaError_t e = cudaMemsetAsync(p.kept, 0, 2 * (size_t)N, s);           // the mined-column flags are OR-ed into
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   if (nwords == 1) {
-    contrastive::contrastive_kernel<contrastive::MODE_FLAGS, 1><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
-    contrastive::contrastive_kernel<contrastive::MODE_LOSS, 1><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    launch_k(contrastive::contrastive_kernel<contrastive::MODE_FLAGS, 1>, grid, contrastive::CT_THREADS, 0, s, p);
+    launch_k(contrastive::contrastive_kernel<contrastive::MODE_LOSS, 1>, grid, contrastive::CT_THREADS, 0, s, p);
   } else {
-    contrastive::contrastive_kernel<contrastive::MODE_FLAGS, contrastive::MAXW><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
-    contrastive::contrastive_kernel<contrastive::MODE_LOSS, contrastive::MAXW><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    launch_k(contrastive::contrastive_kernel<contrastive::MODE_FLAGS, contrastive::MAXW>, grid, contrastive::CT_THREADS, 0, s, p);
+    launch_k(contrastive::contrastive_kernel<contrastive::MODE_LOSS, contrastive::MAXW>, grid, contrastive::CT_THREADS, 0, s, p);
   }
-  contrastive::contrastive_finish_kernel<<<1, 256, 0, s>>>(p, (int)(grid.x * grid.y));
+  launch_k(contrastive::contrastive_finish_kernel, 1, 256, 0, s, p, (int)(grid.x * grid.y));
   e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(3);
@@ -433,8 +436,8 @@ extern "C" TRASE_API int trase_b200_contrastive_soft_backward(int N, int nwords,
   const dim3 grid(nb, contrastive_splits(nb));
   cudaError_t e = cudaMemsetAsync(df, 0, (size_t)N * contrastive::CC * sizeof(float), s);   // split blocks add into it
   if (e == cudaSuccess) {
-    if (nwords == 1) contrastive::contrastive_kernel<contrastive::MODE_GRAD, 1><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
-    else contrastive::contrastive_kernel<contrastive::MODE_GRAD, contrastive::MAXW><<<grid, contrastive::CT_THREADS, 0, s>>>(p);
+    if (nwords == 1) launch_k(contrastive::contrastive_kernel<contrastive::MODE_GRAD, 1>, grid, contrastive::CT_THREADS, 0, s, p);
+    else launch_k(contrastive::contrastive_kernel<contrastive::MODE_GRAD, contrastive::MAXW>, grid, contrastive::CT_THREADS, 0, s, p);
     e = cudaGetLastError();
   }
   if (e != cudaSuccess) { set_error("trase_b200_contrastive_soft_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }

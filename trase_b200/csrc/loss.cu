@@ -57,6 +57,7 @@ __device__ __forceinline__ float block_sum(float v, float* s_red) {
 __global__ void __launch_bounds__(LOSS_THREADS)
 l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, const LossWindow win,
                    int do_ssim, float* __restrict__ maps, float* __restrict__ partials) {
+  pdl_wait();
   __shared__ float sx[LHY][LHX + 1], sy[LHY][LHX + 1];
   __shared__ __align__(16) float sh[5][LHY][LTX];
   __shared__ float s_red[LOSS_THREADS / 32];
@@ -160,6 +161,7 @@ l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
 __global__ void __launch_bounds__(LOSS_THREADS)
 l1_ssim_finalize_kernel(int nblocks, const float* __restrict__ partials, double inv_n, float w_l1, float w_ssim,
                         float bias, float* __restrict__ out) {
+  pdl_wait();
   __shared__ double s0[LOSS_THREADS], s1[LOSS_THREADS];
   double a = 0.0, b = 0.0;
   for (int i = threadIdx.x; i < nblocks; i += LOSS_THREADS) {
@@ -188,6 +190,7 @@ __global__ void __launch_bounds__(LOSS_THREADS)
 l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt,
                    const float* __restrict__ maps, const LossWindow win, float w_l1, float w_ssim, float inv_n,
                    const float* __restrict__ grad_out3, float* __restrict__ d_img) {
+  pdl_wait();
   __shared__ float sm[3][LHY][LHX + 1];
   __shared__ __align__(16) float sh[3][LHY][LTX];
   const int tx0 = blockIdx.x * LTX, ty0 = blockIdx.y * LTY;
@@ -268,6 +271,7 @@ constexpr int FN_MAX_BLOCKS = 148 * 8;
 __global__ void __launch_bounds__(LOSS_THREADS)
 feat_norm_fwd_kernel(int C, long long N, const float* __restrict__ feat, float* __restrict__ norm,
                      float* __restrict__ partials) {
+  pdl_wait();
   __shared__ float s_red[LOSS_THREADS / 32];
   float acc = 0.f;
   for (long long p = (long long)blockIdx.x * LOSS_THREADS + threadIdx.x; p < N; p += (long long)gridDim.x * LOSS_THREADS) {
@@ -286,6 +290,7 @@ feat_norm_fwd_kernel(int C, long long N, const float* __restrict__ feat, float* 
 
 __global__ void __launch_bounds__(LOSS_THREADS)
 feat_norm_finalize_kernel(int nblocks, const float* __restrict__ partials, double inv_n, float* __restrict__ out2) {
+  pdl_wait();
   __shared__ double s0[LOSS_THREADS];
   double a = 0.0;
   for (int i = threadIdx.x; i < nblocks; i += LOSS_THREADS) a += (double)partials[i];
@@ -307,6 +312,7 @@ __global__ void __launch_bounds__(LOSS_THREADS)
 feat_norm_bwd_kernel(int C, long long N, const float* __restrict__ feat, const float* __restrict__ norm,
                      const float* __restrict__ out2, const float* __restrict__ grad_out2, float inv_n,
                      float* __restrict__ d_feat) {
+  pdl_wait();
   const float g_mean = grad_out2 ? grad_out2[0] : 0.f, g_reg = grad_out2 ? grad_out2[1] : 1.f;
   const float k = (g_mean + g_reg * 2.f * (out2[0] - 1.f)) * inv_n;
   for (long long p = (long long)blockIdx.x * LOSS_THREADS + threadIdx.x; p < N; p += (long long)gridDim.x * LOSS_THREADS) {
@@ -343,8 +349,8 @@ extern "C" TRASE_API int trase_b200_l1_ssim_forward(int C, int H, int W, const f
   static const LossWindow win = make_window();
   const dim3 grid((W + LTX - 1) / LTX, (H + LTY - 1) / LTY, C);
   const int nblocks = (int)(grid.x * grid.y * grid.z);
-  l1_ssim_fwd_kernel<<<grid, LOSS_THREADS, 0, s>>>(H, W, img, gt, win, w_ssim != 0.f ? 1 : 0, maps, scratch);
-  l1_ssim_finalize_kernel<<<1, LOSS_THREADS, 0, s>>>(nblocks, scratch, 1.0 / ((double)C * H * W), w_l1, w_ssim, bias,
+  launch_k(l1_ssim_fwd_kernel, grid, LOSS_THREADS, 0, s, H, W, img, gt, win, w_ssim != 0.f ? 1 : 0, maps, scratch);
+  launch_k(l1_ssim_finalize_kernel, 1, LOSS_THREADS, 0, s, nblocks, scratch, 1.0 / ((double)C * H * W), w_l1, w_ssim, bias,
                                                      out3);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_l1_ssim_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -360,7 +366,7 @@ extern "C" TRASE_API int trase_b200_l1_ssim_backward(int C, int H, int W, const 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   static const LossWindow win = make_window();
   const dim3 grid((W + LTX - 1) / LTX, (H + LTY - 1) / LTY, C);
-  l1_ssim_bwd_kernel<<<grid, LOSS_THREADS, 0, s>>>(H, W, img, gt, maps, win, w_l1, w_ssim,
+  launch_k(l1_ssim_bwd_kernel, grid, LOSS_THREADS, 0, s, H, W, img, gt, maps, win, w_l1, w_ssim,
                                                    (float)(1.0 / ((double)C * H * W)), grad_out3, d_img);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_l1_ssim_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -378,8 +384,8 @@ extern "C" TRASE_API int trase_b200_feature_norm_reg_forward(int C, int64_t N, c
   if (!feat || !norm || !scratch || !out2) { set_error("trase_b200_feature_norm_reg_forward: null pointer"); return 1; }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int nb = feat_norm_blocks(N);
-  feat_norm_fwd_kernel<<<nb, LOSS_THREADS, 0, s>>>(C, N, feat, norm, scratch);
-  feat_norm_finalize_kernel<<<1, LOSS_THREADS, 0, s>>>(nb, scratch, 1.0 / (double)N, out2);
+  launch_k(feat_norm_fwd_kernel, nb, LOSS_THREADS, 0, s, C, N, feat, norm, scratch);
+  launch_k(feat_norm_finalize_kernel, 1, LOSS_THREADS, 0, s, nb, scratch, 1.0 / (double)N, out2);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_feature_norm_reg_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(2);
@@ -392,7 +398,7 @@ extern "C" TRASE_API int trase_b200_feature_norm_reg_backward(int C, int64_t N, 
   if (C <= 0 || N <= 0) { set_error("trase_b200_feature_norm_reg_backward: empty feature image"); return 1; }
   if (!feat || !norm || !out2 || !d_feat) { set_error("trase_b200_feature_norm_reg_backward: null pointer"); return 1; }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  feat_norm_bwd_kernel<<<feat_norm_blocks(N), LOSS_THREADS, 0, s>>>(C, N, feat, norm, out2, grad_out2,
+  launch_k(feat_norm_bwd_kernel, feat_norm_blocks(N), LOSS_THREADS, 0, s, C, N, feat, norm, out2, grad_out2,
                                                                     (float)(1.0 / (double)N), d_feat);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_feature_norm_reg_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -424,6 +430,7 @@ __global__ void __launch_bounds__(256) sample_features_fwd_kernel(int C, int H, 
                                                                   const float* __restrict__ feat,
                                                                   const long long* __restrict__ idx, int normalize,
                                                                   float* __restrict__ out, float* __restrict__ inv_norm) {
+  pdl_wait();
   const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (n >= N) return;
   const long long p = idx[n];
@@ -465,6 +472,7 @@ __global__ void __launch_bounds__(256) sample_features_bwd_kernel(int C, int H, 
                                                                   const float* __restrict__ inv_norm,
                                                                   const float* __restrict__ g_out,
                                                                   float* __restrict__ d_feat) {
+  pdl_wait();
   const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (n >= N) return;
   const long long p = idx[n];
@@ -514,7 +522,7 @@ extern "C" TRASE_API int trase_b200_sample_features_forward(int C, int H, int W,
     set_error("trase_b200_sample_features_forward: bad arguments (C=%d, at most %d channels)", C, SF_MAX_C);
     return 1;
   }
-  sample_features_fwd_kernel<<<(N + 7) / 8, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(sample_features_fwd_kernel, (N + 7) / 8, 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       C, H, W, Hm, Wm, N, feat, reinterpret_cast<const long long*>(idx), normalize, out, inv_norm);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_sample_features_forward: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -532,7 +540,7 @@ extern "C" TRASE_API int trase_b200_sample_features_backward(int C, int H, int W
     set_error("trase_b200_sample_features_backward: bad arguments");
     return 1;
   }
-  sample_features_bwd_kernel<<<(N + 7) / 8, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(sample_features_bwd_kernel, (N + 7) / 8, 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       C, H, W, Hm, Wm, N, reinterpret_cast<const long long*>(idx), normalize, out, inv_norm, g_out, d_feat);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_sample_features_backward: CUDA error: %s", cudaGetErrorString(e)); return 2; }

@@ -118,6 +118,7 @@ __global__ void __launch_bounds__(FU_THREADS, 1)
 mlp_fused_kernel(const __grid_constant__ CUtensorMap tmEmb, const __grid_constant__ CUtensorMap tmW,
                          const __grid_constant__ CUtensorMap tmWh, const __grid_constant__ CUtensorMap tmActs,
                          const FusedParams p) {
+  pdl_wait();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if (threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) __trap();
@@ -455,6 +456,7 @@ struct PackTable {
 };
 
 __global__ void __launch_bounds__(256) mlp_pack_fused_kernel(const PackTable t, float* __restrict__ out) {
+  pdl_wait();
   const int blk = blockIdx.x;
   int si = 0;
   while (si + 1 < t.nseg && blk >= t.seg[si + 1].blk0) si++;
@@ -569,7 +571,7 @@ extern "C" TRASE_API int trase_b200_mlp_pack_fused(int nl, int skip, int E, cons
       t.seg[t.nseg++] = {src, rows, mlp::FU_W, 0, mlp::FU_W, base[L], mlp::FU_HCH, 0, 0};
     }
   }
-  mlp::mlp_pack_fused_kernel<<<total, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(t, wpack);
+  launch_k(mlp::mlp_pack_fused_kernel, total, 256, 0, reinterpret_cast<cudaStream_t>(stream), t, wpack);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_fused: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
@@ -598,13 +600,18 @@ static int launch_fused(const char* who, const CUtensorMap& tE, const CUtensorMa
   cfg.blockDim = dim3(FU_THREADS);
   cfg.dynamicSmemBytes = FU_SMEM;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = FU_CLUSTER;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+#if TB_PDL
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.numAttrs = 2;
+#endif
   cudaError_t le = cudaLaunchKernelEx(&cfg, mlp_fused_kernel<BWD, A16>, tE, tW, tWh, tA, p);
   if (le != cudaSuccess) { set_error("%s: launch failed: %s", who, cudaGetErrorString(le)); return 2; }
   count_launches(1);
@@ -705,7 +712,7 @@ extern "C" TRASE_API int trase_b200_mlp_pack_fused_bwd(int nl, int skip, int E, 
     t.seg[t.nseg++] = {src, mlp::FU_W, off + mlp::FU_W, 0, mlp::FU_W, 1 + (L - 1) * mlp::FU_HCH, mlp::FU_HCH, 1, off};
   }
   const int total = 1 + mlp::FU_HCH * (nl - 1);
-  mlp::mlp_pack_fused_kernel<<<total, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(t, wpack);
+  launch_k(mlp::mlp_pack_fused_kernel, total, 256, 0, reinterpret_cast<cudaStream_t>(stream), t, wpack);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_fused_bwd: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);

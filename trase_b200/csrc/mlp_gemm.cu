@@ -63,6 +63,7 @@ template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tn_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmEpilogue ep) {
+  pdl_wait();
   using L = GemmSmem<BN>;
   // 1024-byte alignment (128-byte swizzle atoms) comes from the declaration: aligning the pointer
   // by integer arithmetic would hide the shared address space from the compiler and turn every
@@ -327,7 +328,7 @@ static cudaError_t launch_gemm_tn(const CUtensorMap& tA, const CUtensorMap& tB, 
   }
   const int tiles = (ep.M + BM - 1) / BM;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tn_tf32_kernel<BN><<<grid, GEMM_THREADS, smem, s>>>(tA, tB, ep);
+  launch_k(gemm_tn_tf32_kernel<BN>, grid, GEMM_THREADS, smem, s, tA, tB, ep);
   return cudaGetLastError();
 }
 
@@ -395,6 +396,7 @@ constexpr int WG_THREADS = 256;
 __global__ void __launch_bounds__(WG_THREADS, 1)
 wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ,
                   const WgradParams p) {
+  pdl_wait();
   // 1024-byte alignment (128-byte swizzle atoms) comes from the declaration: aligning the pointer
   // by integer arithmetic would hide the shared address space from the compiler and turn every
   // LDS/STS of the epilogue into a generic LD/ST.
@@ -534,7 +536,7 @@ extern "C" TRASE_API int trase_b200_wgrad_tf32(const float* P, int ldp, int I, c
   wp.M = M; wp.I = I; wp.J = J; wp.D = D; wp.ldd = ldd;
   const int nblk = (M + mlp::WG_ROWS - 1) / mlp::WG_ROWS;
   const int grid = nblk < mlp::num_sms() ? nblk : mlp::num_sms();
-  mlp::wgrad_tf32_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
+  launch_k(mlp::wgrad_tf32_kernel, grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream), tP, tQ, wp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_wgrad_tf32: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
@@ -658,6 +660,7 @@ __device__ __forceinline__ void wgrad_bf16_body(const CUtensorMap* tmP, const CU
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
 wgrad_bf16_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ, const WgradParams p) {
+  pdl_wait();
   const int nblk = (p.M + WH_ROWS - 1) / WH_ROWS;
   const int per = (nblk + gridDim.x - 1) / gridDim.x;
   const int blk0 = blockIdx.x * per;
@@ -677,6 +680,7 @@ struct WgradMultiParams {
   int M, njobs;
 };
 __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_bf16_multi_kernel(const __grid_constant__ WgradMultiParams q) {
+  pdl_wait();
   int job = 0;
   while (job + 1 < q.njobs && (int)blockIdx.x >= q.cta_first[job + 1]) job++;
   const int ci = blockIdx.x - q.cta_first[job], nc = q.cta_first[job + 1] - q.cta_first[job];
@@ -714,6 +718,7 @@ static bool make_tmap_2d_bf16(CUtensorMap* m, const void* base, uint64_t rows, u
 // dst[r][c] = bf16(src[r][c]) for c < cols; columns [cols, ld_dst) of dst are zero-filled
 __global__ void __launch_bounds__(256) f32_to_bf16_kernel(int rows, int cols, const float* __restrict__ src, int ld_src,
                                                           __nv_bfloat16* __restrict__ dst, int ld_dst) {
+  pdl_wait();
   const size_t total = (size_t)rows * ld_dst;
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
     const size_t r = e / ld_dst;
@@ -754,7 +759,7 @@ extern "C" TRASE_API int trase_b200_wgrad_bf16(const void* P, int ldp, int I, co
   wp.M = M; wp.I = I; wp.J = J; wp.D = D; wp.ldd = ldd;
   const int nblk = (M + mlp::WH_ROWS - 1) / mlp::WH_ROWS;
   const int grid = nblk < mlp::num_sms() ? nblk : mlp::num_sms();
-  mlp::wgrad_bf16_kernel<<<grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tP, tQ, wp);
+  launch_k(mlp::wgrad_bf16_kernel, grid, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream), tP, tQ, wp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
@@ -819,7 +824,7 @@ extern "C" TRASE_API int trase_b200_wgrad_bf16_multi(int njobs, const void* cons
     cudaError_t e = ensure_max_dyn_smem(attr_once, mlp::wgrad_bf16_multi_kernel, smem);
     if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16_multi: %s", cudaGetErrorString(e)); return 2; }
   }
-  mlp::wgrad_bf16_multi_kernel<<<sms, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream)>>>(q);
+  launch_k(mlp::wgrad_bf16_multi_kernel, sms, mlp::WG_THREADS, smem, reinterpret_cast<cudaStream_t>(stream), q);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_wgrad_bf16_multi: CUDA error: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
@@ -839,7 +844,7 @@ extern "C" TRASE_API int trase_b200_f32_to_bf16(int rows, int cols, const float*
   }
   const size_t total = (size_t)rows * ld_dst;
   const int grid = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-  mlp::f32_to_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(mlp::f32_to_bf16_kernel, grid, 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       rows, cols, src, ld_src, reinterpret_cast<__nv_bfloat16*>(dst), ld_dst);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_f32_to_bf16: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -871,6 +876,7 @@ __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* _
                                                            const float* __restrict__ t, int t_stride, int Lx, int Lt,
                                                            float* __restrict__ out, int ld,
                                                            __nv_bfloat16* __restrict__ out16, int ld16) {
+  pdl_wait();
   __shared__ __align__(16) float s_tile[EMB_ROWS * EMB_MAX_COLS];
   __shared__ float s_x[EMB_ROWS * 3];
   const int nx = 3 + 6 * Lx;           // columns of the xyz part
@@ -970,7 +976,7 @@ static int deform_embed_impl(int M, const float* xyz, const float* t, int t_stri
     return 1;
   }
   const int blocks = (M + mlp::EMB_ROWS - 1) / mlp::EMB_ROWS;
-  mlp::deform_embed_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(mlp::deform_embed_kernel, blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       M, xyz, t, t_stride, Lx, Lt, out, ld, reinterpret_cast<__nv_bfloat16*>(out16), ld16);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_deform_embed: CUDA error: %s", cudaGetErrorString(e)); return 2; }

@@ -18,6 +18,7 @@ __device__ __forceinline__ float rna(float x) {
 __global__ void __launch_bounds__(256) round_transpose_kernel(const float* __restrict__ W, int rows, int cols, int col0,
                                                               int ncols, float* __restrict__ Wr,
                                                               float* __restrict__ WrT) {
+  pdl_wait();
   __shared__ float tile[32][33];
   const int bx = blockIdx.x * 32, by = blockIdx.y * 32;   // bx: column block, by: row block
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5; // 32 x 8
@@ -45,6 +46,7 @@ __global__ void __launch_bounds__(256) pack_heads_kernel(const float* __restrict
                                                          const float* __restrict__ w2, const float* __restrict__ b2,
                                                          int K, float* __restrict__ wh, float* __restrict__ whT,
                                                          float* __restrict__ bh) {
+  pdl_wait();
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e < 16 * K) {
     const int r = e / K, c = e - r * K;
@@ -64,6 +66,7 @@ __global__ void __launch_bounds__(256) pack_heads_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) pack_dout_kernel(int M, const float* __restrict__ g0, const float* __restrict__ g1,
                                                         const float* __restrict__ g2, float* __restrict__ dout,
                                                         __nv_bfloat16* __restrict__ dout16, float* __restrict__ colsum) {
+  pdl_wait();
   __shared__ float s_sum[8][16];
   const int lane16 = threadIdx.x & 15;             // column
   const int rsub = threadIdx.x >> 4;               // 16 rows per block iteration
@@ -108,7 +111,7 @@ extern "C" TRASE_API int trase_b200_mlp_round_transpose(const float* W, int rows
     return 1;
   }
   dim3 grid((cols + 31) / 32, (rows + 31) / 32);
-  mlp::round_transpose_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(W, rows, cols, col0, ncols, Wr, WrT);
+  launch_k(mlp::round_transpose_kernel, grid, 256, 0, reinterpret_cast<cudaStream_t>(stream), W, rows, cols, col0, ncols, Wr, WrT);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_round_transpose: %s", cudaGetErrorString(e)); return 2; }
   count_launches(1);
@@ -122,7 +125,7 @@ extern "C" TRASE_API int trase_b200_mlp_pack_heads(const float* w0, const float*
     set_error("trase_b200_mlp_pack_heads: bad arguments");
     return 1;
   }
-  mlp::pack_heads_kernel<<<(16 * K + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(w0, b0, w1, b1, w2, b2, K,
+  launch_k(mlp::pack_heads_kernel, (16 * K + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream), w0, b0, w1, b1, w2, b2, K,
                                                                                                wh, whT, bh);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_heads: %s", cudaGetErrorString(e)); return 2; }
@@ -148,7 +151,7 @@ static int pack_dout_impl(int M, const float* g0, const float* g1, const float* 
   if (!dout || !colsum) { set_error("trase_b200_mlp_pack_dout: bad arguments"); return 1; }
   int grid = (M + 15) / 16;
   if (grid > 148 * 8) grid = 148 * 8;
-  mlp::pack_dout_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(mlp::pack_dout_kernel, grid, 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       M, g0, g1, g2, dout, reinterpret_cast<__nv_bfloat16*>(dout16), colsum);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_mlp_pack_dout: %s", cudaGetErrorString(e)); return 2; }

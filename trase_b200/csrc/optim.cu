@@ -24,6 +24,7 @@ struct AdamTable {
 __global__ void __launch_bounds__(256) adam_step_kernel(long long n, float* __restrict__ p, const float* __restrict__ g,
                                                         float* __restrict__ m, float* __restrict__ v,
                                                         const AdamTable t, float beta1, float beta2, float eps) {
+  pdl_wait();
   const float w1 = 1.f - beta1, w2 = 1.f - beta2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     int lo = 0, hi = t.nseg - 1;            // first segment whose end is > i
@@ -46,6 +47,7 @@ __global__ void __launch_bounds__(256) adam_step_kernel(long long n, float* __re
 __global__ void __launch_bounds__(256) densification_stats_kernel(int P, const float* __restrict__ grad3,
                                                                   const bool* __restrict__ filter,
                                                                   float* __restrict__ accum, float* __restrict__ denom) {
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < P && filter[i]) {
     const float x = grad3[3 * i], y = grad3[3 * i + 1];
@@ -71,6 +73,7 @@ __global__ void __launch_bounds__(256) arena_gather_rows_kernel(const GatherTabl
                                                                 const float* __restrict__ old_m,
                                                                 const float* __restrict__ old_v, float* __restrict__ new_p,
                                                                 float* __restrict__ new_m, float* __restrict__ new_v) {
+  pdl_wait();
   const int sgi = blockIdx.y;
   const int w = t.width[sgi];
   const long long total = P_new * w;
@@ -113,7 +116,7 @@ extern "C" TRASE_API int trase_b200_arena_gather_rows(int nseg, const int64_t* o
   }
   long long blocks = (P_new * wmax + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  arena_gather_rows_kernel<<<dim3((unsigned)blocks, (unsigned)nseg), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(arena_gather_rows_kernel, dim3((unsigned)blocks, (unsigned)nseg), 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       t, P_new, reinterpret_cast<const long long*>(src_rows), fresh, old_p, old_m, old_v, new_p, new_m, new_v);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_arena_gather_rows: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -144,7 +147,7 @@ extern "C" TRASE_API int trase_b200_adam_step(int64_t n, float* params, const fl
   if (prev != n) { set_error("trase_b200_adam_step: segments must cover the buffer"); return 1; }
   long long blocks = (n + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  adam_step_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(n, params, grads, exp_avg, exp_avg_sq,
+  launch_k(adam_step_kernel, (int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream), n, params, grads, exp_avg, exp_avg_sq,
                                                                                   t, beta1, beta2, eps);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_adam_step: CUDA error: %s", cudaGetErrorString(e)); return 2; }
@@ -156,7 +159,7 @@ extern "C" TRASE_API int trase_b200_densification_stats(int P, const float* view
                                                         float* grad_accum, float* denom, void* stream) {
   if (P <= 0) return 0;
   if (!viewspace_grad || !filter || !grad_accum || !denom) { set_error("trase_b200_densification_stats: null pointer"); return 1; }
-  densification_stats_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  launch_k(densification_stats_kernel, (P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream), 
       P, viewspace_grad, reinterpret_cast<const bool*>(filter), grad_accum, denom);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("trase_b200_densification_stats: CUDA error: %s", cudaGetErrorString(e)); return 2; }

@@ -254,6 +254,7 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(const float3& mean, float foc
 }
 
 __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreFwdParams q) {
+  pdl_wait();
   __shared__ float s_mean[PRE_BLOCK * 3];
   __shared__ float s_scale[PRE_BLOCK * 3];
   __shared__ uint32_t s_warp_sum[PRE_BLOCK / 32];
@@ -366,7 +367,7 @@ cudaError_t launch_preprocess_forward(const trase_b200_fwd_args& a, const FwdPoi
   q.conic_opacity = p.conic_opacity; q.clamped = p.clamped; q.tiles_touched = p.tiles_touched;
   q.block_sums = p.block_sums;
   int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
-  preprocess_fwd_kernel<<<nblk, PRE_BLOCK, 0, s>>>(q);
+  launch_k(preprocess_fwd_kernel, nblk, PRE_BLOCK, 0, s, q);
   return cudaGetLastError();
 }
 
@@ -374,6 +375,7 @@ cudaError_t launch_preprocess_forward(const trase_b200_fwd_args& a, const FwdPoi
 // Frustum test (rasterizer_impl.cu:57-69)
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
                                     uint8_t* __restrict__ present) {
+  pdl_wait();
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;
   float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
@@ -381,7 +383,7 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
   present[idx] = (pv.z <= 0.2f) ? 0 : 1;
 }
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
-  mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+  launch_k(mark_visible_kernel, (P + 255) / 256, 256, 0, s, P, means3D, view, present);
   return cudaGetLastError();
 }
 
@@ -507,6 +509,7 @@ __device__ __forceinline__ void scale_rotation_backward(const float3 scale, floa
 }
 
 __global__ void __launch_bounds__(PRE_BLOCK) preprocess_bwd_kernel(const PreBwdParams q) {
+  pdl_wait();
   const int idx = blockIdx.x * PRE_BLOCK + threadIdx.x;
   // dL/dSH of a Gaussian is (basis value i) x (dL/dRGB): 16 + 3 numbers.  They are staged per warp and written
   // by the whole warp as one contiguous block (a thread writing its own 192 bytes with 4-byte stores at a
@@ -669,7 +672,7 @@ cudaError_t launch_preprocess_backward(const trase_b200_bwd_args& a, const FwdPo
   q.dL_dmeans3D = a.dL_dmeans3D; q.dL_dcov3D = a.dL_dcov3D; q.dL_dsh = a.dL_dsh;
   q.dL_dscale = a.dL_dscales; q.dL_drot = a.dL_drotations;
   int nblk = (a.P + PRE_BLOCK - 1) / PRE_BLOCK;
-  preprocess_bwd_kernel<<<nblk, PRE_BLOCK, 0, s>>>(q);
+  launch_k(preprocess_bwd_kernel, nblk, PRE_BLOCK, 0, s, q);
   return cudaGetLastError();
 }
 

@@ -70,6 +70,7 @@ constexpr unsigned FULL = 0xffffffffu;
 #endif
 template <int PPT>
 __global__ void __launch_bounds__(256 / PPT, PPT == 2 ? TB_FWD_MINB : 2) render_fwd_kernel(const RenderFwdParams q) {
+  pdl_wait();
   constexpr int NT = 256 / PPT;
   __shared__ float2 s_xy[FWD_BATCH];
   __shared__ float4 s_co[FWD_BATCH];
@@ -250,9 +251,9 @@ cudaError_t launch_render_forward(const trase_b200_fwd_args& a, const FwdPointer
   dim3 grid((a.W + TILE - 1) / TILE, (a.H + TILE - 1) / TILE, 1);
   if (g_tuning.fwd_mma) return launch_render_forward_mma(q, grid, g_tuning.fwd_mma, s);
   if (g_tuning.fwd_ppt == 1)
-    render_fwd_kernel<1><<<grid, 256, 0, s>>>(q);
+    launch_k(render_fwd_kernel<1>, grid, 256, 0, s, q);
   else
-    render_fwd_kernel<2><<<grid, 128, 0, s>>>(q);
+    launch_k(render_fwd_kernel<2>, grid, 128, 0, s, q);
   return cudaGetLastError();
 }
 
@@ -380,7 +381,8 @@ constexpr int bwd_min_blocks(int PPT, bool GEOM, bool DF, bool OBJ_UP) {
 }
 template <int PPT, bool GEOM, bool DF, bool OBJ_UP>
 __global__ void __launch_bounds__(256 / PPT, bwd_min_blocks(PPT, GEOM, DF, OBJ_UP))
-render_bwd_kernel(const RenderBwdParams q) {      // the colour-only variant needs ~80 registers: twice the resident warps
+render_bwd_kernel(const RenderBwdParams q) {
+  pdl_wait();      // the colour-only variant needs ~80 registers: twice the resident warps
   constexpr int NT = 256 / PPT;
   constexpr int BWD_BATCH = (GEOM && !DF && OBJ_UP && PPT == 2) ? TB_BWD_G_BATCH : tb::BWD_BATCH;
   constexpr bool NEED_FEAT = GEOM && OBJ_UP;        // feature rows are only read for dL/dalpha
@@ -622,8 +624,8 @@ cudaError_t launch_render_backward(const trase_b200_bwd_args& a, const FwdPointe
   const bool one = g_tuning.bwd_ppt == 1;
 #define TB_BWD(G_, D_, O_)                                                    \
   do {                                                                        \
-    if (one) render_bwd_kernel<1, G_, D_, O_><<<grid, 256, 0, s>>>(q);        \
-    else render_bwd_kernel<2, G_, D_, O_><<<grid, 128, 0, s>>>(q);            \
+    if (one) launch_k(render_bwd_kernel<1, G_, D_, O_>, grid, 256, 0, s, q);        \
+    else launch_k(render_bwd_kernel<2, G_, D_, O_>, grid, 128, 0, s, q);            \
   } while (0)
   if (!geom) TB_BWD(false, true, true);
   else if (df && obj_up) TB_BWD(true, true, true);
