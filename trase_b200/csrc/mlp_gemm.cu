@@ -866,9 +866,8 @@ __device__ __forceinline__ float rna_tf32(float x) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
   return __uint_as_float(u);
 }
-// One block per 64 rows.  Every thread evaluates full-precision sincosf (arguments reach 2^9 * x) for (row, frequency,
-// component) items of the tile and drops sin and cos into a shared-memory copy of the tile laid out like the output
-// rows; the tile then leaves with 16-byte coalesced stores — fp32 rounded to TF32, and the bf16 copy — when the
+// One block per 64 rows.  The sines and cosines of the tile (see the two loops below for how few transcendental
+// evaluations that takes) go into a shared-memory copy of the tile laid out like the output rows; the tile then leaves with 16-byte coalesced stores — fp32 rounded to TF32, and the bf16 copy — when the
 // output rows are contiguous (the native DeformNetwork's buffers), column by column otherwise.
 constexpr int EMB_MAX_COLS = 128;
 constexpr int EMB_ROWS = 64;
@@ -879,36 +878,63 @@ __global__ void __launch_bounds__(256) deform_embed_kernel(int M, const float* _
   pdl_wait();
   __shared__ __align__(16) float s_tile[EMB_ROWS * EMB_MAX_COLS];
   __shared__ float s_x[EMB_ROWS * 3];
+  __shared__ float s_t[EMB_MAX_COLS];
   const int nx = 3 + 6 * Lx;           // columns of the xyz part
   const int ncol = nx + 1 + 2 * Lt;
   const int m0 = blockIdx.x * EMB_ROWS;
   const int rows = min(EMB_ROWS, M - m0);
   for (int i = threadIdx.x; i < rows * 3; i += blockDim.x) s_x[i] = xyz[(size_t)m0 * 3 + i];
   __syncthreads();
-  // xyz part: item = (row, k, comp)
-  const int per_row = 3 * Lx;
-  for (int e = threadIdx.x; e < rows * per_row; e += blockDim.x) {
-    const int r = e / per_row, j = e - r * per_row;
-    const int k = j / 3, comp = j - 3 * k;
-    float sv, cv;
-    sincosf(s_x[r * 3 + comp] * exp2f((float)k), &sv, &cv);
-    s_tile[r * ncol + 3 + 6 * k + comp] = sv;
-    s_tile[r * ncol + 3 + 6 * k + 3 + comp] = cv;
+  // xyz part: item = (row, comp).  sin / cos of 2^k x for k = 0 .. Lx-1 by the double-angle recurrence in fp64 from one
+  // fp64 sincos of x (2^k x is exact, so these ARE the reference's arguments; the recurrence doubles a 1e-16 error per
+  // step, far below the fp32 rounding of the result): one transcendental evaluation per (row, component) instead of Lx
+  for (int e = threadIdx.x; e < rows * 3; e += blockDim.x) {
+    const int r = e / 3, comp = e - 3 * r;
+    double sv, cv;
+    sincos((double)s_x[e], &sv, &cv);
+    float* dst = s_tile + r * ncol + 3 + comp;
+    for (int k = 0; k < Lx; k++) {
+      dst[6 * k] = (float)sv;
+      dst[6 * k + 3] = (float)cv;
+      const double s2 = 2.0 * sv * cv;
+      cv = (cv - sv) * (cv + sv);
+      sv = s2;
+    }
   }
   for (int i = threadIdx.x; i < rows * 3; i += blockDim.x) s_tile[(i / 3) * ncol + (i % 3)] = s_x[i];
-  // time part: item = (row, k), k = -1 is the raw value.  One time stamp for every row (the usual case: one view =
-  // one t) costs Lt + 1 evaluations per row like any other, but reads no per-row input
-  const int per_row_t = Lt + 1;
-  for (int e = threadIdx.x; e < rows * per_row_t; e += blockDim.x) {
-    const int r = e / per_row_t, k = e - r * per_row_t - 1;
-    const float tv = t[(size_t)(m0 + r) * t_stride];
-    if (k < 0) {
-      s_tile[r * ncol + nx] = tv;
-    } else {
-      float sv, cv;
-      sincosf(tv * exp2f((float)k), &sv, &cv);
-      s_tile[r * ncol + nx + 1 + 2 * k] = sv;
-      s_tile[r * ncol + nx + 2 + 2 * k] = cv;
+  // time part: one time stamp for every row (the usual case: one view = one t) is evaluated once per block and copied
+  // into the rows; per-row time stamps cost Lt + 1 evaluations per row
+  if (t_stride == 0) {
+    for (int k = threadIdx.x; k <= Lt; k += blockDim.x) {
+      const float tv = t[0];
+      if (k == 0) {
+        s_t[0] = tv;
+      } else {
+        float sv, cv;
+        sincosf(tv * exp2f((float)(k - 1)), &sv, &cv);
+        s_t[2 * k - 1] = sv;
+        s_t[2 * k] = cv;
+      }
+    }
+    __syncthreads();
+    const int nt = 2 * Lt + 1;
+    for (int e = threadIdx.x; e < rows * nt; e += blockDim.x) {
+      const int r = e / nt, c = e - r * nt;
+      s_tile[r * ncol + nx + c] = s_t[c];
+    }
+  } else {
+    const int per_row_t = Lt + 1;
+    for (int e = threadIdx.x; e < rows * per_row_t; e += blockDim.x) {
+      const int r = e / per_row_t, k = e - r * per_row_t - 1;
+      const float tv = t[(size_t)(m0 + r) * t_stride];
+      if (k < 0) {
+        s_tile[r * ncol + nx] = tv;
+      } else {
+        float sv, cv;
+        sincosf(tv * exp2f((float)k), &sv, &cv);
+        s_tile[r * ncol + nx + 1 + 2 * k] = sv;
+        s_tile[r * ncol + nx + 2 + 2 * k] = cv;
+      }
     }
   }
   __syncthreads();
