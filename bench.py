@@ -371,6 +371,8 @@ class Workload:
         side stream and is issued one view AHEAD (right before the previous view's backward is launched): the host
         synchronisation inside it — the sample count comes back to size the loss kernels — is then waited out while
         the GPU still has that view's forward queued, not with the GPU idle."""
+        if self.ref is not None:
+            return None                                     # the reference arm samples inline, as train.py does
         from trase_b200 import feature_utils as FU
         main = torch.cuda.current_stream()
         with torch.cuda.stream(self.sample_stream):
