@@ -537,6 +537,13 @@ TRASE_API int trase_b200_deform_embed_bf16(int M, const float* xyz, const float*
                                            float* out, int ld, void* out16, int ld16, void* stream);
 TRASE_API int trase_b200_mlp_pack_dout_bf16(int M, const float* g0, const float* g1, const float* g2, float* dout,
                                             void* dout16, float* colsum, void* stream);
+/* Head gradients straight into the parameters' gradient buffers (ref: autograd's accumulation of the three heads'
+ * weight and bias gradients, utils/time_utils.py:119-129): dwhT [K][ld] is the head weight gradient transposed (ld = 16,
+ * halves = 1; or ld = 32, halves = 2 for the bf16 path's hi and lo products), dbh [16] the bias gradient; the three
+ * heads' [rows][K] weight gradients and bias gradients are ACCUMULATED into.  One launch. */
+TRASE_API int trase_b200_mlp_heads_grad_accumulate(const float* dwhT, int ld, int halves, const float* dbh, float* gw0,
+                                                   float* gb0, float* gw1, float* gb1, float* gw2, float* gb2, int K,
+                                                   void* stream);
 /* Debug only (no reference counterpart): device buffer of [grid][8] uint64 stall-cycle counters that the
  * whole-network kernels fill when set (NULL = off); read by tools/check_fused_mlp.py. */
 TRASE_API void trase_b200_mlp_fused_set_prof(unsigned long long* dev_buf);

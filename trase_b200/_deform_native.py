@@ -40,11 +40,11 @@ BF16_WGRAD = True
 MULTI_WGRAD = True
 
 
-def _direct_ok(p, dev) -> bool:
+def _direct_ok(p, dev, align=16) -> bool:
     g = p.grad
     return (getattr(p, "_trase_arena_grad_ptr", None) is not None and g is not None and
             g.data_ptr() == p._trase_arena_grad_ptr and g.is_contiguous() and g.dtype == torch.float32 and
-            g.device == dev and g.data_ptr() % 16 == 0 and g.shape == p.shape and
+            g.device == dev and g.data_ptr() % align == 0 and g.shape == p.shape and
             not getattr(p, "_post_accumulate_grad_hooks", None) and not getattr(p, "_backward_hooks", None))
 
 
@@ -291,6 +291,8 @@ class _DeformMLP(torch.autograd.Function):
         # the parameter objects themselves: backward looks their .grad up (DIRECT_GRAD_ACCUM)
         hp = list(params[:2 * nl])
         ctx.hidden_params = hp if all(isinstance(p, torch.nn.Parameter) for p in hp) else None
+        hd = list(params[2 * nl:])
+        ctx.head_params = hd if all(isinstance(p, torch.nn.Parameter) for p in hd) else None
         if heads_out is not None:
             return heads_out
         return out16[:, 0:3].contiguous(), out16[:, 3:7].contiguous(), out16[:, 7:10].contiguous()
@@ -390,13 +392,22 @@ class _DeformMLP(torch.autograd.Function):
             if multi is not None:
                 _wgrad16_multi(lib, multi)
             span.__exit__()
-            if bf16:
-                torch.add(d32[:, :16], d32[:, 16:], out=dwhT)       # hi-part and lo-part products of the head gradient
-            dwh = dwhT.t()
             out = [None, None, None, None, None, None]
             for i in range(nl):
                 out += [None, None] if direct else [grads_w[i], grads_b[i]]
-            out += [dwh[0:3], dbh[0:3], dwh[3:7], dbh[3:7], dwh[7:10], dbh[7:10]]
+            heads = ctx.head_params
+            if DIRECT_GRAD_ACCUM and heads is not None and all(_direct_ok(p, dev, align=4) for p in heads):
+                # the six head gradients straight into their arena slots: one launch instead of the hi + lo add and
+                # six accumulations by autograd
+                src, ld, halves = (d32, 32, 2) if bf16 else (dwhT, 16, 1)
+                _lib.check(lib.trase_b200_mlp_heads_grad_accumulate(
+                    src.data_ptr(), ld, halves, dbh.data_ptr(), *[p.grad.data_ptr() for p in heads], W, s))
+                out += [None] * 6
+            else:
+                if bf16:
+                    torch.add(d32[:, :16], d32[:, 16:], out=dwhT)   # hi-part and lo-part products of the head gradient
+                dwh = dwhT.t()
+                out += [dwh[0:3], dbh[0:3], dwh[3:7], dbh[3:7], dwh[7:10], dbh[7:10]]
         return tuple(out)
 
 

@@ -68,7 +68,7 @@ EXPORTS = [
     "trase_b200_sort_scratch_bytes", "trase_b200_sort_pairs", "trase_b200_higher_msb",
     "trase_b200_set_tuning", "trase_b200_rasterize_backward_stages", "trase_b200_profile_enable",
     "trase_b200_profile_read", "trase_b200_sort_pairs_static", "trase_b200_gemm_tf32", "trase_b200_wgrad_tf32", "trase_b200_deform_embed", "trase_b200_assemble_forward", "trase_b200_assemble_backward", "trase_b200_mlp_round_transpose", "trase_b200_mlp_pack_heads",
-    "trase_b200_mlp_pack_dout", "trase_b200_launch_count", "trase_b200_loss_scratch_bytes",
+    "trase_b200_mlp_pack_dout", "trase_b200_mlp_heads_grad_accumulate", "trase_b200_launch_count", "trase_b200_loss_scratch_bytes",
     "trase_b200_l1_ssim_forward", "trase_b200_l1_ssim_backward", "trase_b200_feature_norm_scratch_bytes",
     "trase_b200_feature_norm_reg_forward", "trase_b200_feature_norm_reg_backward",
     "trase_b200_mlp_fused_pack_floats", "trase_b200_mlp_pack_fused", "trase_b200_mlp_forward_fused",
@@ -199,6 +199,9 @@ def load() -> C.CDLL:
                                                  C.c_int, C.c_void_p, C.c_int, C.c_void_p]
     lib.trase_b200_mlp_pack_dout_bf16.restype = C.c_int
     lib.trase_b200_mlp_pack_dout_bf16.argtypes = [C.c_int] + [C.c_void_p] * 7
+    lib.trase_b200_mlp_heads_grad_accumulate.restype = C.c_int
+    lib.trase_b200_mlp_heads_grad_accumulate.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7 + [C.c_int,
+                                                                                                         C.c_void_p]
     lib.trase_b200_wgrad_bf16_multi.restype = C.c_int
     lib.trase_b200_wgrad_bf16_multi.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                                 C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -99,10 +99,47 @@ __global__ void __launch_bounds__(256) pack_dout_kernel(int M, const float* __re
   }
 }
 
+// Head gradients straight into the parameters' gradient buffers: gw_h[j][i] += sum over the `halves` 16-column blocks
+// of dwhT[i][16 b + col0_h + j], gb_h[j] += dbh[col0_h + j] for the three heads (3 / 4 / 3 rows, columns 0 / 3 / 7 of
+// the packed head matrix).  One launch instead of the hi + lo add and six gradient accumulations.
+__global__ void __launch_bounds__(256) heads_grad_accum_kernel(const float* __restrict__ dwhT, int ld, int halves,
+                                                               const float* __restrict__ dbh, float* gw0, float* gb0,
+                                                               float* gw1, float* gb1, float* gw2, float* gb2, int K) {
+  pdl_wait();
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < 10 * K; e += gridDim.x * blockDim.x) {
+    const int j = e / K, i = e - j * K;                 // row j of the packed head matrix, input feature i
+    float v = 0.f;
+    for (int b = 0; b < halves; b++) v += dwhT[(size_t)i * ld + 16 * b + j];
+    float* dst = j < 3 ? gw0 + (size_t)j * K : (j < 7 ? gw1 + (size_t)(j - 3) * K : gw2 + (size_t)(j - 7) * K);
+    dst[i] += v;
+    if (i == 0) {
+      float* bd = j < 3 ? gb0 + j : (j < 7 ? gb1 + (j - 3) : gb2 + (j - 7));
+      *bd += dbh[j];
+    }
+  }
+}
+
 }  // namespace mlp
 }  // namespace tb
 
 using namespace tb;
+
+// dwhT: [K][ld] (ld = 16, halves = 1: fp32 path; ld = 32, halves = 2: the bf16 path's hi and lo products), dbh: [16]
+// head bias gradient; gw*/gb*: the three heads' weight [rows][K] and bias gradients, ACCUMULATED into.
+extern "C" TRASE_API int trase_b200_mlp_heads_grad_accumulate(const float* dwhT, int ld, int halves, const float* dbh,
+                                                              float* gw0, float* gb0, float* gw1, float* gb1,
+                                                              float* gw2, float* gb2, int K, void* stream) {
+  if (!dwhT || !dbh || !gw0 || !gb0 || !gw1 || !gb1 || !gw2 || !gb2 || K <= 0 || halves < 1 || ld < 16 * halves) {
+    set_error("trase_b200_mlp_heads_grad_accumulate: bad arguments");
+    return 1;
+  }
+  launch_k(mlp::heads_grad_accum_kernel, (10 * K + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream), dwhT, ld,
+           halves, dbh, gw0, gb0, gw1, gb1, gw2, gb2, K);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("trase_b200_mlp_heads_grad_accumulate: %s", cudaGetErrorString(e)); return 2; }
+  count_launches(1);
+  return 0;
+}
 
 extern "C" TRASE_API int trase_b200_mlp_round_transpose(const float* W, int rows, int cols, int col0, int ncols,
                                                         float* Wr, float* WrT, void* stream) {
@@ -139,7 +176,8 @@ extern "C" TRASE_API int trase_b200_mlp_pack_dout(int M, const float* g0, const 
                                                   float* colsum, void* stream) {
   return pack_dout_impl(M, g0, g1, g2, dout, nullptr, colsum, stream);
 }
-// same, also writing the [M][16] bf16 copy that trase_b200_wgrad_bf16 multiplies with the last activations
+// same, also writing the [M][32] bf16 copy (hi | lo parts) that the bf16 head weight gradient multiplies with the last
+// activations
 extern "C" TRASE_API int trase_b200_mlp_pack_dout_bf16(int M, const float* g0, const float* g1, const float* g2,
                                                        float* dout, void* dout16, float* colsum, void* stream) {
   if (M > 0 && !dout16) { set_error("trase_b200_mlp_pack_dout_bf16: bad arguments"); return 1; }
