@@ -265,6 +265,10 @@ TRASE_API int trase_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64
  * slices its gradient).  g_feat == NULL (backward): the feature parameter is frozen,
  * its gradient is not computed; the seven geometry gradients g_xyz .. g_opacity all NULL:
  * every geometry parameter is frozen (FEATURE state), that kernel is skipped.
+ * accumulate_mask (backward): bit 0 xyz, 1 scaling, 2 rotation, 3 opacity, 4 SH (g_fdc and
+ * g_frest) — that PARAMETER gradient is added to what the buffer holds instead of
+ * overwriting it (the caller points it at the parameter's own gradient storage); the
+ * gradients of the deformation inputs (g_dxyz, g_dscaling, g_drotation) are always written.
  * ---------------------------------------------------------------------- */
 TRASE_API int trase_b200_assemble_forward(int P, int Mrest, const float* xyz, const float* d_xyz, const float* scaling,
                                           const float* d_scaling, const float* rotation, const float* d_rotation,
@@ -277,7 +281,7 @@ TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const float* scalin
                                            const float* g_shs, const float* g_objs, float* g_xyz, float* g_dxyz,
                                            float* g_scaling, float* g_dscaling, float* g_rotation, float* g_drotation,
                                            float* g_opacity, float* g_fdc, float* g_frest, float* g_feat,
-                                           void* stream);
+                                           int accumulate_mask, void* stream);
 
 /* FEATURE-state contrastive loss on the sampled pixels without the N x N matrices.
  * ref: train.py:253-296 in the default 'soft' mode: get_pixel_mask_correspondence_matrix and get_pixel_weights

@@ -317,3 +317,46 @@ def test_prune_keeps_other_arena_tensors_intact(native_lib):
     sum(o.sum() for o in outs).backward()
     opt.step()
     assert torch.isfinite(opt.flat_p).all()
+
+
+@pytest.mark.gpu
+def test_direct_gaussian_gradient_accumulation_matches_autograd(native_lib):
+    """With the Gaussian parameters' `.grad` in a GradArena, the activation-glue backward adds their gradients straight
+    into the arena slots (xyz, scaling, rotation, opacity, and the SH block split into f_dc / f_rest); autograd still
+    fires the parameters' post-accumulate hooks (the arena's overlap trigger is one).  Same arena contents as
+    autograd's own accumulation, also on top of existing contents and over two views; same hook count either way."""
+    from trase_b200 import _assemble, synth
+    from trase_b200 import render as R
+    from trase_b200.distributed import GradArena
+    dev = torch.device("cuda:0")
+    P, W, H = 20000, 160, 128
+    sc = synth.make_scene(P, W, H, 7)
+    view = R.make_view(sc["cam"], dev)
+    ups = [synth.make_upstream_grads(W, H, 7 + v) for v in range(2)]
+    res, seen = {}, {}
+    saved = _assemble.DIRECT_GRAD_ACCUM
+    try:
+        for direct in (False, True):
+            _assemble.DIRECT_GRAD_ACCUM = direct
+            pc = R.GaussianParams.from_activated(sc, dev)
+            pc._gaussian_features.requires_grad_(False)                    # GAUSSIAN state
+            params = [p for p in pc.parameters() if p.requires_grad]
+            arena = GradArena(params, early=params)
+            calls = []
+            for p in params:                        # a second post-accumulate hook per parameter: must fire either way
+                p.register_post_accumulate_grad_hook(lambda q: calls.append(float(q.grad.abs().sum()) > 0))
+            arena.flat.fill_(0.125)
+            for v in range(2):
+                d = [torch.full((P, k), 1e-3 * (v + 1), device=dev, requires_grad=True) for k in (3, 4, 3)]
+                out = R.render(view, pc, R.PIPE_DEFAULT, torch.zeros(3, device=dev), d[0], d[1], d[2])
+                torch.autograd.backward([out["render"], out["render_gaussian_features"]],
+                                        [ups[v]["dL_dcolor"].to(dev), ups[v]["dL_dobjects"].to(dev)])
+            torch.cuda.synchronize()
+            res[direct] = arena.flat.clone()
+            seen[direct] = len(calls)
+    finally:
+        _assemble.DIRECT_GRAD_ACCUM = saved
+    scale = (res[False] - 0.125).abs().max()
+    assert scale > 0
+    assert (res[False] - res[True]).abs().max() <= 1e-4 * scale + 1e-7      # atomics: the two runs differ in last bits
+    assert seen[True] == seen[False] == 2 * 6            # six parameters, two views: the hooks fire on both paths

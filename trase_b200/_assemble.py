@@ -36,6 +36,28 @@ def sh_block_of(f_dc, f_rest):
     return torch.as_strided(f_dc.detach(), (P, Mrest + 1, 3), (row, 3, 1))
 
 
+# Parameters whose `.grad` is a slot of a GradArena (trase_b200/distributed.py marks them) get their gradient ADDED
+# straight into that slot by the backward kernels instead of being returned to autograd (which would launch one
+# accumulation kernel per parameter, two of them on strided SH slices).  Autograd still runs the parameter's
+# AccumulateGrad node with an undefined gradient, and post-accumulate hooks (the arena's own among them) still fire
+# there — after the kernels that did the adding were queued — so they see the accumulated `.grad` as before.
+# Opt-in through the arena; parameters with tensor (pre-accumulation) hooks, or models driven through
+# torch.autograd.grad, take the ordinary path.
+DIRECT_GRAD_ACCUM = True
+
+
+def _arena_slot(p, dev, align):
+    """The gradient tensor to add into, or None when the parameter is not an arena parameter in good standing."""
+    if not (DIRECT_GRAD_ACCUM and isinstance(p, torch.nn.Parameter)):
+        return None
+    g = p.grad
+    if (getattr(p, "_trase_arena_grad_ptr", None) is None or g is None or g.data_ptr() != p._trase_arena_grad_ptr or
+            not g.is_contiguous() or g.dtype != torch.float32 or g.device != dev or g.data_ptr() % align or
+            g.shape != p.shape or getattr(p, "_backward_hooks", None)):
+        return None
+    return g
+
+
 class _Assemble(torch.autograd.Function):
     @staticmethod
     def forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, f_dc, f_rest, feat):
@@ -59,6 +81,7 @@ class _Assemble(torch.autograd.Function):
                 rotations.data_ptr(), opac.data_ptr(), None if block is not None else shs.data_ptr(), sh_objs.data_ptr(),
                 _cuda.raw_stream(dev)))
         ctx.save_for_backward(ins[2], ins[4], ins[6], ins[9])
+        ctx.leaves = (xyz, scaling, rotation, opacity, f_dc, f_rest)      # the objects themselves: backward looks at .grad
         ctx.Mrest = Mrest
         ctx.sh_aliased = block is not None
         # an output whose sources are all frozen is not differentiable: the rasterizer then knows (needs_input_grad)
@@ -87,14 +110,35 @@ class _Assemble(torch.autograd.Function):
                     None if alias else torch.empty((P, 1, 3), **f32),
                     None if alias else torch.empty((P, Mrest, 3), **f32),
                     torch.empty((P, 1, 32), **f32) if need[9] else None]     # frozen feature: skipped
+            # arena parameters: the kernels add into the parameter's own gradient slot (accumulate_mask)
+            xyz_p, scaling_p, rotation_p, opacity_p, fdc_p, frest_p = ctx.leaves
+            acc, direct = 0, []
+            if geom:
+                for bit, idx, leaf, align in ((1, 0, xyz_p, 4), (2, 2, scaling_p, 4), (4, 4, rotation_p, 16),
+                                              (8, 6, opacity_p, 4)):
+                    slot = _arena_slot(leaf, dev, align) if need[idx] else None
+                    if slot is not None:
+                        acc |= bit
+                        outs[idx] = slot
+                        direct.append((idx, leaf))
+            sh_slots = None
+            if need[7] and need[8] and ups[4] is not None and Mrest > 0:
+                a, b = _arena_slot(fdc_p, dev, 4), _arena_slot(frest_p, dev, 4)
+                if a is not None and b is not None:
+                    sh_slots = (a, b)
+                    acc |= 16
+                    outs[7], outs[8] = a, b
+                    direct += [(7, fdc_p), (8, frest_p)]
             _lib.check(lib.trase_b200_assemble_backward(
                 P, Mrest, scaling.data_ptr(), rotation.data_ptr(), opacity.data_ptr(), feat.data_ptr(),
                 *[None if u is None else u.data_ptr() for u in ups], *[None if o is None else o.data_ptr() for o in outs],
-                _cuda.raw_stream(dev)))
-            if alias:
+                acc, _cuda.raw_stream(dev)))
+            if alias and sh_slots is None:
                 # the SH gradient block is already laid out like the parameters: hand out its two slices
                 g = ups[4] if ups[4] is not None else torch.zeros((P, Mrest + 1, 3), **f32)
                 outs[7], outs[8] = g[:, :1], g[:, 1:]
+            for idx, leaf in direct:
+                outs[idx] = None                       # nothing left for autograd to add (its hooks still fire)
         return tuple(outs)
 
 

@@ -150,7 +150,7 @@ def load() -> C.CDLL:
     lib.trase_b200_assemble_forward.restype = C.c_int
     lib.trase_b200_assemble_forward.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 17
     lib.trase_b200_assemble_backward.restype = C.c_int
-    lib.trase_b200_assemble_backward.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 21
+    lib.trase_b200_assemble_backward.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 20 + [C.c_int, C.c_void_p]
     lib.trase_b200_mlp_round_transpose.restype = C.c_int
     lib.trase_b200_mlp_round_transpose.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                                    C.c_void_p]

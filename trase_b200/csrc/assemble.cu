@@ -70,6 +70,7 @@ struct AssembleBwd {
   const float *scaling, *rotation, *opacity, *feat;                          // raw parameters
   const float *g_means3D, *g_scales, *g_rotations, *g_opac, *g_shs, *g_objs; // upstream gradients (may be null)
   float *g_xyz, *g_dxyz, *g_scaling, *g_dscaling, *g_rotation, *g_drotation, *g_opacity, *g_fdc, *g_frest, *g_feat;
+  int acc;   // bit 0 xyz, 1 scaling, 2 rotation, 3 opacity, 4 SH: that PARAMETER gradient is added to, not overwritten
 };
 
 __global__ void __launch_bounds__(256) assemble_bwd_kernel(const AssembleBwd a) {
@@ -79,10 +80,11 @@ __global__ void __launch_bounds__(256) assemble_bwd_kernel(const AssembleBwd a) 
 #pragma unroll
     for (int c = 0; c < 3; c++) {
       const float gm = a.g_means3D ? a.g_means3D[3 * i + c] : 0.f;
-      a.g_xyz[3 * i + c] = gm;
+      a.g_xyz[3 * i + c] = (a.acc & 1) ? a.g_xyz[3 * i + c] + gm : gm;
       a.g_dxyz[3 * i + c] = gm;
       const float gs = a.g_scales ? a.g_scales[3 * i + c] : 0.f;
-      a.g_scaling[3 * i + c] = gs * expf(a.scaling[3 * i + c]);
+      const float gsc = gs * expf(a.scaling[3 * i + c]);
+      a.g_scaling[3 * i + c] = (a.acc & 2) ? a.g_scaling[3 * i + c] + gsc : gsc;
       a.g_dscaling[3 * i + c] = gs;
     }
     const float4 q = reinterpret_cast<const float4*>(a.rotation)[i];
@@ -98,24 +100,46 @@ __global__ void __launch_bounds__(256) assemble_bwd_kernel(const AssembleBwd a) 
     } else {
       gq = make_float4(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f, g.w * 1e12f);   // clamped branch of F.normalize
     }
+    if (a.acc & 4) {
+      const float4 o = reinterpret_cast<float4*>(a.g_rotation)[i];
+      gq = make_float4(o.x + gq.x, o.y + gq.y, o.z + gq.z, o.w + gq.w);
+    }
     reinterpret_cast<float4*>(a.g_rotation)[i] = gq;
     reinterpret_cast<float4*>(a.g_drotation)[i] = g;
     const float sgm = 1.f / (1.f + expf(-a.opacity[i]));
-    a.g_opacity[i] = (a.g_opac ? a.g_opac[i] : 0.f) * sgm * (1.f - sgm);
+    const float gop = (a.g_opac ? a.g_opac[i] : 0.f) * sgm * (1.f - sgm);
+    a.g_opacity[i] = (a.acc & 8) ? a.g_opacity[i] + gop : gop;
   }
 }
 
+// block (64, 4): x = coefficient*3 + channel of one Gaussian's SH row (at most 48 used), y = one of 4 rows per trip
 __global__ void __launch_bounds__(256) assemble_sh_bwd_kernel(int P, int Mrest, const float* __restrict__ g_shs,
-                                                              float* __restrict__ g_fdc, float* __restrict__ g_frest) {
+                                                              float* __restrict__ g_fdc, float* __restrict__ g_frest,
+                                                              int accumulate) {
   pdl_wait();
-  const int M3 = (Mrest + 1) * 3;
-  const size_t total = (size_t)P * M3;
-  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-    const size_t i = e / M3;
-    const int c = (int)(e - i * M3);
-    const float v = g_shs ? g_shs[e] : 0.f;
-    if (c < 3) g_fdc[i * 3 + c] = v;
-    else g_frest[i * (size_t)(Mrest * 3) + (c - 3)] = v;
+  const int M3 = (Mrest + 1) * 3, R3 = Mrest * 3;
+  const int c = threadIdx.x;
+  if (c >= M3) return;
+  // eight rows per thread in flight: the loop is a chain of dependent load / load / store otherwise
+  constexpr int U = 8;
+  const int step = gridDim.x * 4;
+  for (int i0 = blockIdx.x * 4 + threadIdx.y; i0 < P; i0 += step * U) {
+    float v[U], o[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int i = i0 + u * step;
+      v[u] = (g_shs && i < P) ? g_shs[(size_t)i * M3 + c] : 0.f;
+      o[u] = 0.f;
+      if (accumulate && i < P) o[u] = c < 3 ? g_fdc[(size_t)i * 3 + c] : g_frest[(size_t)i * R3 + (c - 3)];
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int i = i0 + u * step;
+      if (i < P) {
+        float* dst = c < 3 ? g_fdc + (size_t)i * 3 + c : g_frest + (size_t)i * R3 + (c - 3);
+        *dst = o[u] + v[u];
+      }
+    }
   }
 }
 
@@ -412,7 +436,8 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
                                                       const float* g_opac, const float* g_shs, const float* g_objs,
                                                       float* g_xyz, float* g_dxyz, float* g_scaling, float* g_dscaling,
                                                       float* g_rotation, float* g_drotation, float* g_opacity,
-                                                      float* g_fdc, float* g_frest, float* g_feat, void* stream) {
+                                                      float* g_fdc, float* g_frest, float* g_feat, int accumulate_mask,
+                                                      void* stream) {
   if (P <= 0) return 0;
   // the seven geometry gradients come together or not at all (all NULL: every geometry parameter is frozen, FEATURE state)
   const bool geom = g_xyz || g_dxyz || g_scaling || g_dscaling || g_rotation || g_drotation || g_opacity;
@@ -424,11 +449,14 @@ extern "C" TRASE_API int trase_b200_assemble_backward(int P, int Mrest, const fl
   }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   AssembleBwd a{P, Mrest, scaling, rotation, opacity, feat, g_means3D, g_scales, g_rotations, g_opac, g_shs, g_objs,
-                g_xyz, g_dxyz, g_scaling, g_dscaling, g_rotation, g_drotation, g_opacity, g_fdc, g_frest, g_feat};
+                g_xyz, g_dxyz, g_scaling, g_dscaling, g_rotation, g_drotation, g_opacity, g_fdc, g_frest, g_feat,
+                accumulate_mask};
   if (geom) launch_k(assemble_bwd_kernel, (P + 255) / 256, 256, 0, s, a);
-  const size_t tot = (size_t)P * (Mrest + 1) * 3;
-  int g = (int)((tot + 255) / 256 < 148 * 32 ? (tot + 255) / 256 : 148 * 32);
-  if (g_fdc) launch_k(assemble_sh_bwd_kernel, g, 256, 0, s, P, Mrest, g_shs, g_fdc, g_frest);   // NULL: caller slices g_shs itself
+  if (g_fdc) {
+    if ((Mrest + 1) * 3 > 64) { set_error("trase_b200_assemble_backward: at most 21 SH coefficients"); return 1; }
+    const int gb = (P + 3) / 4 < 148 * 16 ? (P + 3) / 4 : 148 * 16;
+    launch_k(assemble_sh_bwd_kernel, gb, dim3(64, 4), 0, s, P, Mrest, g_shs, g_fdc, g_frest, (accumulate_mask >> 4) & 1);
+  }   // NULL: caller slices g_shs itself
   if (g_feat)      // NULL: the feature parameter is frozen (GAUSSIAN state), nobody wants this gradient
     launch_k(assemble_feat_bwd_kernel, (int)(((size_t)P * 8 + 255) / 256), 256, 0, s, 
         P, reinterpret_cast<const float4*>(feat), reinterpret_cast<const float4*>(g_objs),

@@ -28,9 +28,10 @@ class GradArena:
     """Flat gradient buffer shared by a list of parameters.
 
     Every `.grad` becomes a view into `flat`.  Parameters of an arena are marked so that the native DeformNetwork
-    backward may add weight/bias gradients straight into their slots instead of returning them to autograd; drive
-    such a network with `.backward()` (not torch.autograd.grad), and do not hang gradient hooks on those parameters
-    if the direct path is wanted (parameters with hooks are handled the ordinary way)."""
+    backward and the fused parameter-activation backward (`_assemble.py`) may add gradients straight into their slots
+    instead of returning them to autograd; drive such models with `.backward()` (not torch.autograd.grad), and do not
+    hang tensor (pre-accumulation) gradient hooks on those parameters if the direct path is wanted (such parameters
+    are handled the ordinary way; post-accumulate hooks are fine)."""
 
     def __init__(self, params: Iterable[torch.nn.Parameter], early: Iterable[torch.nn.Parameter] = ()):
         params = [p for p in params if p.requires_grad]
@@ -57,6 +58,8 @@ class GradArena:
             # backward, trase_b200/_deform_native.py DIRECT_GRAD_ACCUM): records WHICH buffer was agreed on
             p._trase_arena_grad_ptr = p.grad.data_ptr()
         for p in first:
+            # fires when autograd reaches the parameter's AccumulateGrad node — also when a kernel has already added
+            # the gradient into the slot and handed autograd None (trase_b200/_assemble.py)
             p.register_post_accumulate_grad_hook(self._early_hook)
 
     def zero(self) -> None:
