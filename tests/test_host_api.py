@@ -79,3 +79,54 @@ def test_synthetic_camera_matches_reference_conventions():
         2 * torch.atan(torch.tensor(cam["tanfovy"])).item()).T)
     assert cam["projmatrix"][2, 3] == 1.0 and abs(cam["projmatrix"][0, 0].item() - 2.2) < 1e-5
     assert torch.equal(cam["campos"], torch.zeros(3))
+
+
+def test_smooth_reverse_map_lists_every_entry_once():
+    """build_smooth_reverse (the gather form of the smoothed-feature backward): row j of the reverse map holds exactly
+    the (p, column) pairs with knn_idx[p][column] == j, encoded (p << 8 | column); every entry appears once."""
+    import torch
+    from trase_b200._assemble import build_smooth_reverse
+    g = torch.Generator().manual_seed(3)
+    P, K = 257, 16
+    knn = torch.randint(0, P, (P, K), generator=g)
+    knn[:, 0] = torch.arange(P)
+    knn[10:40, 5] = 3                                     # a long reverse row
+    ptr, ent = build_smooth_reverse(knn)
+    assert ptr.dtype == torch.int32 and ent.dtype == torch.int32
+    assert int(ptr[0]) == 0 and int(ptr[-1]) == P * K and bool((ptr[1:] >= ptr[:-1]).all())
+    seen = set()
+    for j in range(P):
+        for e in ent[int(ptr[j]):int(ptr[j + 1])].tolist():
+            p, c = e >> 8, e & 255
+            assert int(knn[p, c]) == j
+            seen.add((p, c))
+    assert len(seen) == P * K
+    assert build_smooth_reverse(torch.zeros((4, 65), dtype=torch.int64)) is None      # more columns than the kernel takes
+
+
+def test_arena_slot_only_for_arena_parameters_in_good_standing():
+    """_assemble._arena_slot: the direct-accumulation target exists only for a Parameter whose .grad is the arena's
+    own slot; a replaced .grad, a tensor hook, a misaligned slot or the switch turned off all fall back to autograd."""
+    import torch
+    from trase_b200 import _assemble
+    from trase_b200.distributed import GradArena
+    a, b = torch.nn.Parameter(torch.zeros(5, 3)), torch.nn.Parameter(torch.zeros(5, 4))
+    loose = torch.nn.Parameter(torch.zeros(5, 3))
+    loose.grad = torch.zeros(5, 3)
+    arena = GradArena([a, b], early=[a, b])
+    dev = a.device
+    assert _assemble._arena_slot(a, dev, 4) is a.grad and _assemble._arena_slot(b, dev, 4) is b.grad
+    assert _assemble._arena_slot(loose, dev, 4) is None                     # not an arena parameter
+    assert _assemble._arena_slot(torch.zeros(5, 3), dev, 4) is None         # not a Parameter at all
+    assert _assemble._arena_slot(b, dev, 1 << 20) is None                   # alignment the kernel would need
+    saved = _assemble.DIRECT_GRAD_ACCUM
+    try:
+        _assemble.DIRECT_GRAD_ACCUM = False
+        assert _assemble._arena_slot(a, dev, 4) is None
+    finally:
+        _assemble.DIRECT_GRAD_ACCUM = saved
+    a.register_hook(lambda g: g * 2)                                         # a tensor hook must see the gradient
+    assert _assemble._arena_slot(a, dev, 4) is None
+    b.grad = torch.zeros(5, 4)                                              # .grad replaced: no longer the arena's slot
+    assert _assemble._arena_slot(b, dev, 4) is None
+    assert arena.flat.numel() == 35
